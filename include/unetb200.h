@@ -1,0 +1,118 @@
+/* libunetb200 -- C ABI of the B200 (sm_100a) UNet training hot path.
+ *
+ * The reference (dmsuehir/unet_distributed) has no FFI of its own: its hot path is the TensorFlow-1.4 graph that
+ * model.py:36-130 builds and test_dist.py:396-398 runs. Each entry point below replaces the TF op(s) one reference
+ * line lowers to; the citation names that line. Host code (Python, ctypes) owns every buffer; this library never
+ * allocates or frees caller memory.
+ *
+ * Conventions
+ *   - all pointers are DEVICE pointers unless the name ends in _host; activations are NHWC bf16 (16-byte aligned),
+ *     master weights / gradients / optimizer state are fp32 in the TensorFlow variable layouts
+ *     (Conv2D kernel [kh][kw][Cin][Cout]; Conv2DTranspose kernel [kh][kw][Cout][Cin]);
+ *   - `stream` is a cudaStream_t passed as void*; every call is asynchronous on it and never synchronises;
+ *   - return value 0 = OK, negative = error (unetb200_last_error_string() gives the text for the calling thread);
+ *   - `ws` arguments are caller-provided scratch of at least the matching *_ws_bytes() size.
+ */
+#ifndef UNETB200_H_
+#define UNETB200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+int unetb200_version(void);
+const char* unetb200_last_error_string(void);
+
+/* ---- weight packing: fp32 TF-layout master -> bf16 GEMM operand (run after every optimizer update) ------------- */
+/* Conv2D kernel (model.py:47-49, he_uniform HWIO) -> [Cout][9][Cin] for the forward implicit GEMM. */
+int unetb200_pack_conv3x3_fwd(const float* w_hwio, void* w_packed, int Cin, int Cout, void* stream);
+/* Same kernel, tap-flipped and transposed -> [Cin][9][Cout] for Conv2DBackpropInput. */
+int unetb200_pack_conv3x3_dgrad(const float* w_hwio, void* w_packed, int Cin, int Cout, void* stream);
+/* Conv2DTranspose kernel (model.py:79-80, [2][2][Cout][Cin]) -> [4*Cout][Cin] (a cast). */
+int unetb200_pack_tconv2x2_fwd(const float* w, void* w_packed, int Cin, int Cout, void* stream);
+/* -> [Cin][4][Cout] for the transposed conv's input gradient. */
+int unetb200_pack_tconv2x2_dgrad(const float* w, void* w_packed, int Cin, int Cout, void* stream);
+
+/* ---- Conv2D 3x3 'same' + bias + ReLU: model.py:51-117 (18 call sites) ------------------------------------------ */
+/* Forward. Two sources implement concatenate([x0, x1], -1) (model.py:76-80,...) without materialising it; pass
+ * x1=NULL,C1=0 for a single input. Dropout (model.py:60,66; keep<1) is applied after ReLU with scale 1/keep;
+ * element i of the output keeps iff the Philox stream (seed, stream_id) says so -- see unetb200_dropout_mask. */
+int unetb200_conv3x3_fwd(const void* x0, int C0, const void* x1, int C1, const void* w_packed, const float* bias,
+                         void* y, int N, int H, int W, int Cout, int relu, float drop_keep, uint64_t drop_seed,
+                         uint32_t drop_stream, void* stream);
+/* Conv2DBackpropInput fused with the producer's ReluGrad: dx_k = dgrad(dz)[source k] * (mask_k > 0 ? scale : 0).
+ * mask_k is the producer's forward output (NULL = no activation to undo); scale = 1/keep undoes dropout. */
+int unetb200_conv3x3_dgrad(const void* dz, int Cout, const void* w_packed_d, void* dx0, int C0, const void* mask0,
+                           void* dx1, int C1, const void* mask1, float scale, int N, int H, int W, void* stream);
+/* Conv2DBackpropFilter: dw fp32 [3][3][C0+C1][Cout]. */
+size_t unetb200_conv3x3_wgrad_ws_bytes(int N, int H, int W, int Cin_total, int Cout);
+int unetb200_conv3x3_wgrad(const void* dz, int Cout, const void* x0, int C0, const void* x1, int C1, float* dw,
+                           void* ws, size_t ws_bytes, int N, int H, int W, void* stream);
+/* First layer (model.py:51, conv1a): fp32 NHWC network input with Cin in 1..8, fp32 HWIO weights, bf16 output. */
+int unetb200_conv_first_fwd(const float* x, const float* w_hwio, const float* bias, void* y, int N, int H, int W,
+                            int Cin, int Cout, void* stream);
+size_t unetb200_conv_first_wgrad_ws_bytes(int Cin, int Cout);
+int unetb200_conv_first_wgrad(const float* x, const void* dz, float* dw, float* db, void* ws, int N, int H, int W,
+                              int Cin, int Cout, void* stream);
+/* BiasAddGrad: db[c] = sum over N*H*W of dz[., c]. */
+size_t unetb200_bias_grad_ws_bytes(int C);
+int unetb200_bias_grad(const void* dz, float* db, void* ws, long long pixels, int C, void* stream);
+
+/* ---- MaxPooling2D 2x2: model.py:53,57,63,69 -------------------------------------------------------------------- */
+int unetb200_maxpool2x2_fwd(const void* x, void* y, int N, int H, int W, int C, void* stream);
+/* MaxPoolGrad + ReluGrad of the pooled conv + the skip-connection gradient:
+ * dz = (skip_grad or 0) + route_to_first_max(dpool) * (x > 0). skip_grad may be NULL or alias dz. */
+int unetb200_maxpool2x2_bwd(const void* x, const void* dpool, const void* skip_grad, void* dz, int N, int H, int W,
+                            int C, void* stream);
+
+/* ---- decoder up path ------------------------------------------------------------------------------------------- */
+/* Conv2DTranspose 2x2 stride 2 (model.py:79-80,90-91,101-102,112-113); (N,H,W) is the INPUT grid. */
+int unetb200_tconv2x2_fwd(const void* x, int Cin, const void* w_packed, const float* bias, void* y, int Cout, int N,
+                          int H, int W, void* stream);
+int unetb200_tconv2x2_dgrad(const void* dy, int Cout, const void* w_packed_d, void* dx, int Cin, const void* mask,
+                            float scale, int N, int H, int W, void* stream);
+size_t unetb200_tconv2x2_wgrad_ws_bytes(int N, int H, int W, int Cin, int Cout);
+int unetb200_tconv2x2_wgrad(const void* dy, int Cout, const void* x, int Cin, float* dw, void* ws, size_t ws_bytes,
+                            int N, int H, int W, void* stream);
+/* UpSampling2D 2x2 nearest (model.py:76,87,98,109; --use_upsampling); (N,H,W) is the INPUT grid. */
+int unetb200_upsample2x2_fwd(const void* x, void* y, int N, int H, int W, int C, void* stream);
+int unetb200_upsample2x2_bwd(const void* dy, const void* x, void* dx, int N, int H, int W, int C, int relu_mask,
+                             void* stream);
+
+/* ---- head: Conv2D 1x1 + sigmoid (model.py:119-120) fused with dice_coef / dice_coef_loss (model.py:4-21) ------- */
+size_t unetb200_head_ws_bytes(long long pixels, int C, int n_cl);
+/* p = sigmoid(x.w + b) (fp32 [pixels][n_cl]); sums[3] = {sum y*p, sum y, sum p} over the whole batch tensor. */
+int unetb200_head_fwd(const void* x, const float* w, const float* b, const float* y_true, float* p, float* sums,
+                      void* ws, long long pixels, int C, int n_cl, void* stream);
+/* out4 = {dice_coef_loss, dice_coef, sensitivity, specificity} (model.py:13-21, 4-10, 133-137, 139-143). */
+int unetb200_dice_finalize(const float* sums, float smooth, float* out4, void* stream);
+/* Gradient of dice_coef_loss through the sigmoid and the 1x1 conv, times grad_scale; dx is masked by x > 0. */
+int unetb200_head_bwd(const void* x, const float* w, const float* y_true, const float* p, const float* sums,
+                      float smooth, float grad_scale, void* dx, float* dw, float* db, void* ws, long long pixels,
+                      int C, int n_cl, void* stream);
+
+/* ---- optimizer: tf.train.AdamOptimizer + exponential_decay (test_dist.py:228-248) ------------------------------ */
+/* step is a device int64 holding global_step (updates applied so far); the LR uses its value before the increment.
+ * grad_scale multiplies g first (1/replicas: SyncReplicasOptimizer averages, test_dist.py:251-258). */
+int unetb200_adam_step(float* theta, float* m, float* v, const float* g, long long n, const long long* step, float lr0,
+                       int const_lr, float lr_fraction, float decay_steps, float beta1, float beta2, float eps,
+                       float grad_scale, void* stream);
+/* GradientDescentOptimizer (commented alternative at test_dist.py:239-244). */
+int unetb200_sgd_step(float* theta, const float* g, long long n, const long long* step, float lr0, int const_lr,
+                      float lr_fraction, float decay_steps, float grad_scale, void* stream);
+int unetb200_step_increment(long long* step, void* stream);
+
+/* ---- utilities --------------------------------------------------------------------------------------------------- */
+/* keep[i] in {0,1}: the exact dropout decisions the conv epilogue makes for output element i (n multiple of 8). */
+int unetb200_dropout_mask(unsigned char* keep, long long n, float keep_prob, uint64_t seed, uint32_t stream_id,
+                          void* stream);
+int unetb200_cast_f32_to_bf16(const float* x, void* y, long long n, void* stream);
+int unetb200_cast_bf16_to_f32(const void* x, float* y, long long n, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* UNETB200_H_ */

@@ -1,0 +1,46 @@
+// Host-side shared declarations for libunetb200: error reporting, tensor-map construction, device info.
+#pragma once
+#include <cstdint>
+#include <cstdio>
+#include <cuda.h>
+#include <cuda_runtime.h>
+
+namespace ub {
+
+// Error codes returned across the C ABI (0 = OK, negative = failure; text via unetb200_last_error_string()).
+enum : int {
+  UB_OK = 0,
+  UB_ERR_INVALID = -1,    // bad argument / unsupported shape
+  UB_ERR_CUDA = -2,       // CUDA runtime or driver error
+  UB_ERR_WORKSPACE = -3,  // workspace too small
+  UB_ERR_UNSUPPORTED = -4
+};
+
+void set_error(const char* fmt, ...);
+const char* last_error();
+
+#define UB_CHECK_CUDA(expr)                                                                        \
+  do {                                                                                             \
+    cudaError_t _e = (expr);                                                                       \
+    if (_e != cudaSuccess) {                                                                       \
+      ::ub::set_error("%s:%d: %s -> %s", __FILE__, __LINE__, #expr, cudaGetErrorString(_e));       \
+      return ::ub::UB_ERR_CUDA;                                                                    \
+    }                                                                                              \
+  } while (0)
+
+#define UB_REQUIRE(cond, ...)                 \
+  do {                                        \
+    if (!(cond)) {                            \
+      ::ub::set_error(__VA_ARGS__);           \
+      return ::ub::UB_ERR_INVALID;            \
+    }                                         \
+  } while (0)
+
+// Encode a tiled bf16 tensor map. dims/box are innermost-first; strides_bytes has rank-1 entries (dims 1..rank-1).
+// swizzle_bytes: 128, 64, 32 or 0. Out-of-bounds elements read as zero.
+int make_tmap_bf16(CUtensorMap* out, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
+                   const uint32_t* box, int swizzle_bytes);
+
+int device_sm_count();
+
+}  // namespace ub

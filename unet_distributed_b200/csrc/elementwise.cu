@@ -1,0 +1,749 @@
+#include "elementwise.cuh"
+
+#include "common.h"
+#include "igemm.cuh"
+#include "ptx.cuh"
+
+namespace ub {
+
+namespace {
+
+constexpr int kRedBlocks = 296;  // 2 x 148 SMs: fixed so per-block partial layouts are shape independent
+constexpr int kThreads = 256;
+
+__device__ __forceinline__ void unpack8(const uint4& v, float (&f)[8]) {
+  f[0] = bf16_lo(v.x); f[1] = bf16_hi(v.x); f[2] = bf16_lo(v.y); f[3] = bf16_hi(v.y);
+  f[4] = bf16_lo(v.z); f[5] = bf16_hi(v.z); f[6] = bf16_lo(v.w); f[7] = bf16_hi(v.w);
+}
+__device__ __forceinline__ uint4 pack8(const float (&f)[8]) {
+  uint4 o;
+  o.x = pack_bf16x2(f[0], f[1]); o.y = pack_bf16x2(f[2], f[3]);
+  o.z = pack_bf16x2(f[4], f[5]); o.w = pack_bf16x2(f[6], f[7]);
+  return o;
+}
+
+inline unsigned grid_for(long long items, int threads) {
+  long long b = (items + threads - 1) / threads;
+  if (b < 1) b = 1;
+  return static_cast<unsigned>(b);
+}
+
+// ------------------------------------------------------------------------------------------ conv1a forward
+__global__ void conv_first_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w,
+                                      const float* __restrict__ bias, uint4* __restrict__ y, int N, int H, int W,
+                                      int Cin, int Cout) {
+  extern __shared__ float sw[];  // [9*Cin*Cout] weights then [Cout] bias
+  const int nw = 9 * Cin * Cout;
+  for (int i = threadIdx.x; i < nw; i += blockDim.x) sw[i] = w[i];
+  for (int i = threadIdx.x; i < Cout; i += blockDim.x) sw[nw + i] = bias ? bias[i] : 0.0f;
+  __syncthreads();
+  const int groups = Cout / 8;
+  const long long total = static_cast<long long>(N) * H * W * groups;
+  const long long idx = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (idx >= total) return;
+  const int g = static_cast<int>(idx % groups);
+  long long pix = idx / groups;
+  const int wq = static_cast<int>(pix % W);
+  const int hq = static_cast<int>((pix / W) % H);
+  const long long n = pix / (static_cast<long long>(W) * H);
+  float acc[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) acc[j] = sw[nw + g * 8 + j];
+  for (int r = 0; r < 3; ++r) {
+    const int hh = hq + r - 1;
+    if (hh < 0 || hh >= H) continue;
+    for (int s = 0; s < 3; ++s) {
+      const int ww = wq + s - 1;
+      if (ww < 0 || ww >= W) continue;
+      const float* xp = x + ((n * H + hh) * W + ww) * Cin;
+      const float* wp = sw + ((r * 3 + s) * Cin) * Cout + g * 8;
+      for (int ci = 0; ci < Cin; ++ci) {
+        const float xv = __ldg(xp + ci);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[j] = fmaf(xv, wp[ci * Cout + j], acc[j]);
+      }
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < 8; ++j) acc[j] = fmaxf(acc[j], 0.0f);
+  y[idx] = pack8(acc);
+}
+
+// ------------------------------------------------------------------------------------------ conv1a wgrad (+ bias grad)
+// Each thread owns one 8-channel group of dz and walks pixels with a stride; partial sums go block -> ws -> final.
+__global__ void conv_first_wgrad_kernel(const float* __restrict__ x, const uint4* __restrict__ dz,
+                                        float* __restrict__ ws, int N, int H, int W, int Cin, int Cout) {
+  extern __shared__ float red[];  // [9*Cin*Cout + Cout]
+  const int nout = 9 * Cin * Cout + Cout;
+  for (int i = threadIdx.x; i < nout; i += blockDim.x) red[i] = 0.0f;
+  __syncthreads();
+  const int groups = Cout / 8;
+  const int g = threadIdx.x % groups;
+  const long long total = static_cast<long long>(N) * H * W * groups;
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  for (int ci = 0; ci < Cin; ++ci) {
+    float acc[9][8];
+    float accb[8];
+#pragma unroll
+    for (int t = 0; t < 9; ++t)
+#pragma unroll
+      for (int j = 0; j < 8; ++j) acc[t][j] = 0.0f;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) accb[j] = 0.0f;
+    for (long long idx = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; idx < total; idx += stride) {
+      long long pix = idx / groups;
+      const int wq = static_cast<int>(pix % W);
+      const int hq = static_cast<int>((pix / W) % H);
+      const long long n = pix / (static_cast<long long>(W) * H);
+      float d[8];
+      unpack8(__ldg(dz + idx), d);
+      if (ci == 0) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) accb[j] += d[j];
+      }
+#pragma unroll
+      for (int r = 0; r < 3; ++r) {
+        const int hh = hq + r - 1;
+#pragma unroll
+        for (int s = 0; s < 3; ++s) {
+          const int ww = wq + s - 1;
+          float xv = 0.0f;
+          if (hh >= 0 && hh < H && ww >= 0 && ww < W) xv = __ldg(x + ((n * H + hh) * W + ww) * Cin + ci);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) acc[r * 3 + s][j] = fmaf(xv, d[j], acc[r * 3 + s][j]);
+        }
+      }
+    }
+    // lanes with the same channel group: xor-shuffle over offsets >= groups
+#pragma unroll
+    for (int t = 0; t < 9; ++t) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        float v = acc[t][j];
+        for (int o = 16; o >= groups; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+        if ((threadIdx.x & 31) < groups) atomicAdd(&red[(t * Cin + ci) * Cout + g * 8 + j], v);
+      }
+    }
+    if (ci == 0) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        float v = accb[j];
+        for (int o = 16; o >= groups; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+        if ((threadIdx.x & 31) < groups) atomicAdd(&red[9 * Cin * Cout + g * 8 + j], v);
+      }
+    }
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < nout; i += blockDim.x) ws[static_cast<long long>(blockIdx.x) * nout + i] = red[i];
+}
+
+// out[i] = sum_b ws[b*n + i], fixed order; first n_a outputs to out_a, the rest to out_b.
+__global__ void block_partials_reduce_kernel(const float* __restrict__ ws, int nblocks, int n, float* __restrict__ out_a,
+                                             int n_a, float* __restrict__ out_b) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  float acc = 0.0f;
+  for (int b = 0; b < nblocks; ++b) acc += ws[static_cast<long long>(b) * n + i];
+  if (i < n_a) out_a[i] = acc;
+  else if (out_b) out_b[i - n_a] = acc;
+}
+
+// ------------------------------------------------------------------------------------------ pooling
+__global__ void maxpool_fwd_kernel(const uint4* __restrict__ x, uint4* __restrict__ y, int N, int H, int W, int C) {
+  const int groups = C / 8;
+  const int Ho = H / 2, Wo = W / 2;
+  const long long total = static_cast<long long>(N) * Ho * Wo * groups;
+  const long long idx = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (idx >= total) return;
+  const int g = static_cast<int>(idx % groups);
+  long long t = idx / groups;
+  const int wo = static_cast<int>(t % Wo);
+  t /= Wo;
+  const int ho = static_cast<int>(t % Ho);
+  const long long n = t / Ho;
+  const long long base = ((n * H + 2 * ho) * W + 2 * wo) * groups + g;
+  const uint4 a = __ldg(x + base), b = __ldg(x + base + groups);
+  const uint4 c = __ldg(x + base + static_cast<long long>(W) * groups), d = __ldg(x + base + static_cast<long long>(W) * groups + groups);
+  float fa[8], fb[8], fc[8], fd[8], o[8];
+  unpack8(a, fa); unpack8(b, fb); unpack8(c, fc); unpack8(d, fd);
+#pragma unroll
+  for (int j = 0; j < 8; ++j) o[j] = fmaxf(fmaxf(fa[j], fb[j]), fmaxf(fc[j], fd[j]));
+  y[idx] = pack8(o);
+}
+
+__global__ void maxpool_bwd_kernel(const uint4* __restrict__ x, const uint4* __restrict__ dp,
+                                   const uint4* skip, uint4* dz, int N, int H, int W, int C) {
+  const int groups = C / 8;
+  const int Ho = H / 2, Wo = W / 2;
+  const long long total = static_cast<long long>(N) * Ho * Wo * groups;
+  const long long idx = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (idx >= total) return;
+  const int g = static_cast<int>(idx % groups);
+  long long t = idx / groups;
+  const int wo = static_cast<int>(t % Wo);
+  t /= Wo;
+  const int ho = static_cast<int>(t % Ho);
+  const long long n = t / Ho;
+  const long long base = ((n * H + 2 * ho) * W + 2 * wo) * groups + g;
+  const long long off[4] = {base, base + groups, base + static_cast<long long>(W) * groups,
+                            base + static_cast<long long>(W) * groups + groups};
+  float xv[4][8], gv[4][8], d[8];
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    unpack8(__ldg(x + off[k]), xv[k]);
+    if (skip) {
+      unpack8(skip[off[k]], gv[k]);
+    } else {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) gv[k][j] = 0.0f;
+    }
+  }
+  unpack8(__ldg(dp + idx), d);
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    int arg = 0;
+    float m = xv[0][j];
+#pragma unroll
+    for (int k = 1; k < 4; ++k) {
+      if (xv[k][j] > m) { m = xv[k][j]; arg = k; }
+    }
+    // ReLU of the producer: the pooled tensor is a ReLU output, so a zero maximum carries no gradient.
+    if (m > 0.0f) {
+#pragma unroll
+      for (int k = 0; k < 4; ++k) gv[k][j] += (k == arg) ? d[j] : 0.0f;
+    }
+  }
+#pragma unroll
+  for (int k = 0; k < 4; ++k) dz[off[k]] = pack8(gv[k]);
+}
+
+// ------------------------------------------------------------------------------------------ nearest 2x upsampling
+__global__ void upsample_fwd_kernel(const uint4* __restrict__ x, uint4* __restrict__ y, int N, int H, int W, int C) {
+  const int groups = C / 8;
+  const long long total = static_cast<long long>(N) * (2 * H) * (2 * W) * groups;
+  const long long idx = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (idx >= total) return;
+  const int g = static_cast<int>(idx % groups);
+  long long t = idx / groups;
+  const int wo = static_cast<int>(t % (2 * W));
+  t /= (2 * W);
+  const int ho = static_cast<int>(t % (2 * H));
+  const long long n = t / (2 * H);
+  y[idx] = __ldg(x + ((n * H + ho / 2) * W + wo / 2) * groups + g);
+}
+
+__global__ void upsample_bwd_kernel(const uint4* __restrict__ dy, const uint4* __restrict__ x, uint4* __restrict__ dx,
+                                    int N, int H, int W, int C, int relu_mask) {
+  const int groups = C / 8;
+  const long long total = static_cast<long long>(N) * H * W * groups;
+  const long long idx = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (idx >= total) return;
+  const int g = static_cast<int>(idx % groups);
+  long long t = idx / groups;
+  const int w = static_cast<int>(t % W);
+  t /= W;
+  const int h = static_cast<int>(t % H);
+  const long long n = t / H;
+  const long long base = ((n * 2 * H + 2 * h) * (2 * W) + 2 * w) * groups + g;
+  float a[8], b[8], c[8], d[8], o[8];
+  unpack8(__ldg(dy + base), a);
+  unpack8(__ldg(dy + base + groups), b);
+  unpack8(__ldg(dy + base + static_cast<long long>(2 * W) * groups), c);
+  unpack8(__ldg(dy + base + static_cast<long long>(2 * W) * groups + groups), d);
+#pragma unroll
+  for (int j = 0; j < 8; ++j) o[j] = (a[j] + b[j]) + (c[j] + d[j]);
+  if (relu_mask) {
+    float xv[8];
+    unpack8(__ldg(x + idx), xv);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) o[j] = xv[j] > 0.0f ? o[j] : 0.0f;
+  }
+  dx[idx] = pack8(o);
+}
+
+// ------------------------------------------------------------------------------------------ head: 1x1 conv + sigmoid + dice sums
+constexpr int kMaxCl = 4;
+
+__global__ void head_fwd_kernel(const uint4* __restrict__ x, const float* __restrict__ w, const float* __restrict__ b,
+                                const float* __restrict__ y_true, float* __restrict__ p_out, float* __restrict__ ws,
+                                long long P, int C, int n_cl) {
+  extern __shared__ float sh[];  // [C*n_cl] weights, [n_cl] bias, then 3 floats per warp
+  const int subs = C / 8;
+  for (int i = threadIdx.x; i < C * n_cl; i += blockDim.x) sh[i] = w[i];
+  for (int i = threadIdx.x; i < n_cl; i += blockDim.x) sh[C * n_cl + i] = b ? b[i] : 0.0f;
+  __syncthreads();
+  const int sub = threadIdx.x % subs;
+  const long long total = P * subs;
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  float sI = 0.0f, sY = 0.0f, sP = 0.0f;
+  // every lane of a pixel group must stay in the loop for the shuffles: iterate on a uniform bound
+  const long long iters = (total + stride - 1) / stride;
+  long long idx = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  for (long long itn = 0; itn < iters; ++itn, idx += stride) {
+    const bool live = idx < total;
+    float acc[kMaxCl] = {0.0f, 0.0f, 0.0f, 0.0f};
+    if (live) {
+      float f[8];
+      unpack8(__ldg(x + idx), f);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        for (int k = 0; k < n_cl; ++k) acc[k] = fmaf(f[j], sh[(sub * 8 + j) * n_cl + k], acc[k]);
+      }
+    }
+    for (int k = 0; k < n_cl; ++k) {
+      for (int o = subs >> 1; o > 0; o >>= 1) acc[k] += __shfl_xor_sync(0xffffffffu, acc[k], o);
+    }
+    if (live && sub == 0) {
+      const long long pix = idx / subs;
+      for (int k = 0; k < n_cl; ++k) {
+        const float z = acc[k] + sh[C * n_cl + k];
+        const float p = 1.0f / (1.0f + expf(-z));
+        const float yt = __ldg(y_true + pix * n_cl + k);
+        p_out[pix * n_cl + k] = p;
+        sI = fmaf(yt, p, sI);
+        sY += yt;
+        sP += p;
+      }
+    }
+  }
+  sI = warp_sum(sI); sY = warp_sum(sY); sP = warp_sum(sP);
+  float* wred = sh + C * n_cl + n_cl;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (lane == 0) { wred[warp * 3 + 0] = sI; wred[warp * 3 + 1] = sY; wred[warp * 3 + 2] = sP; }
+  __syncthreads();
+  if (threadIdx.x < 3) {
+    float a = 0.0f;
+    for (int wv = 0; wv < static_cast<int>(blockDim.x >> 5); ++wv) a += wred[wv * 3 + threadIdx.x];
+    ws[blockIdx.x * 3 + threadIdx.x] = a;
+  }
+}
+
+__global__ void dice_finalize_kernel(const float* __restrict__ sums, float smooth, float* __restrict__ out4) {
+  const float I = sums[0], Sy = sums[1], Sp = sums[2];
+  out4[0] = -logf(2.0f * I + smooth) + logf(Sy + Sp + smooth);
+  out4[1] = (2.0f * I + smooth) / (Sy + Sp + smooth);
+  out4[2] = (I + smooth) / (Sy + smooth);
+  out4[3] = (I + smooth) / (Sp + smooth);
+}
+
+__global__ void head_bwd_kernel(const uint4* __restrict__ x, const float* __restrict__ w,
+                                const float* __restrict__ y_true, const float* __restrict__ p,
+                                const float* __restrict__ sums, float smooth, float grad_scale, uint4* __restrict__ dx,
+                                float* __restrict__ ws, long long P, int C, int n_cl) {
+  extern __shared__ float sh[];  // [C*n_cl] weights, then [C*n_cl + n_cl] block accumulators
+  const int subs = C / 8;
+  float* red = sh + C * n_cl;
+  for (int i = threadIdx.x; i < C * n_cl; i += blockDim.x) sh[i] = w[i];
+  for (int i = threadIdx.x; i < C * n_cl + n_cl; i += blockDim.x) red[i] = 0.0f;
+  __syncthreads();
+  const float I = sums[0], Sy = sums[1], Sp = sums[2];
+  const float ca = -2.0f / (2.0f * I + smooth);
+  const float cb = 1.0f / (Sy + Sp + smooth);
+  const int sub = threadIdx.x % subs;
+  const long long total = P * subs;
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  float adw[8][kMaxCl];
+  float adb[kMaxCl];
+#pragma unroll
+  for (int j = 0; j < 8; ++j)
+#pragma unroll
+    for (int k = 0; k < kMaxCl; ++k) adw[j][k] = 0.0f;
+#pragma unroll
+  for (int k = 0; k < kMaxCl; ++k) adb[k] = 0.0f;
+  for (long long idx = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; idx < total; idx += stride) {
+    const long long pix = idx / subs;
+    float f[8], o[8];
+    unpack8(__ldg(x + idx), f);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) o[j] = 0.0f;
+#pragma unroll
+    for (int k = 0; k < kMaxCl; ++k) {
+      if (k < n_cl) {
+        const float pv = __ldg(p + pix * n_cl + k);
+        const float yt = __ldg(y_true + pix * n_cl + k);
+        const float dl = (ca * yt + cb) * pv * (1.0f - pv) * grad_scale;
+        if (sub == 0) adb[k] += dl;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          adw[j][k] = fmaf(f[j], dl, adw[j][k]);
+          o[j] = fmaf(dl, sh[(sub * 8 + j) * n_cl + k], o[j]);
+        }
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) o[j] = f[j] > 0.0f ? o[j] : 0.0f;
+    dx[idx] = pack8(o);
+  }
+  // reduce over lanes sharing `sub`, then one shared-memory atomic per warp and value
+  const int lane = threadIdx.x & 31;
+#pragma unroll
+  for (int k = 0; k < kMaxCl; ++k) {
+    if (k < n_cl) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        float v = adw[j][k];
+        for (int o2 = 16; o2 >= subs; o2 >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o2);
+        if (lane < subs) atomicAdd(&red[(sub * 8 + j) * n_cl + k], v);
+      }
+      float vb = adb[k];
+      vb = warp_sum(vb);
+      if (lane == 0) atomicAdd(&red[C * n_cl + k], vb);
+    }
+  }
+  __syncthreads();
+  const int nout = C * n_cl + n_cl;
+  for (int i = threadIdx.x; i < nout; i += blockDim.x) ws[static_cast<long long>(blockIdx.x) * nout + i] = red[i];
+}
+
+// ------------------------------------------------------------------------------------------ bias gradient (column sums)
+__global__ void colsum_kernel(const uint4* __restrict__ dz, float* __restrict__ ws, long long P, int C) {
+  extern __shared__ float red[];  // [C]
+  for (int i = threadIdx.x; i < C; i += blockDim.x) red[i] = 0.0f;
+  __syncthreads();
+  const int groups = C / 8;
+  const int g = threadIdx.x % groups;
+  const long long total = P * groups;
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+  for (long long idx = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; idx < total; idx += stride) {
+    float f[8];
+    unpack8(__ldg(dz + idx), f);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[j] += f[j];
+  }
+  const int lane = threadIdx.x & 31;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    float v = acc[j];
+    for (int o = 16; o >= groups; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    if (groups >= 32 || lane < groups) atomicAdd(&red[g * 8 + j], v);
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < C; i += blockDim.x) ws[static_cast<long long>(blockIdx.x) * C + i] = red[i];
+}
+
+// ------------------------------------------------------------------------------------------ weight packing
+__global__ void pack_conv_fwd_kernel(const float* __restrict__ w, __nv_bfloat16* __restrict__ out, int taps, int Cin,
+                                     int Cout) {
+  const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  const long long n = static_cast<long long>(taps) * Cin * Cout;
+  if (i >= n) return;
+  const int ci = static_cast<int>(i % Cin);
+  const int tap = static_cast<int>((i / Cin) % taps);
+  const int co = static_cast<int>(i / (static_cast<long long>(Cin) * taps));
+  out[i] = __float2bfloat16(w[(static_cast<long long>(tap) * Cin + ci) * Cout + co]);
+}
+__global__ void pack_conv_dgrad_kernel(const float* __restrict__ w, __nv_bfloat16* __restrict__ out, int taps, int Cin,
+                                       int Cout) {
+  const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  const long long n = static_cast<long long>(taps) * Cin * Cout;
+  if (i >= n) return;
+  const int co = static_cast<int>(i % Cout);
+  const int tap = static_cast<int>((i / Cout) % taps);
+  const int ci = static_cast<int>(i / (static_cast<long long>(Cout) * taps));
+  out[i] = __float2bfloat16(w[(static_cast<long long>(taps - 1 - tap) * Cin + ci) * Cout + co]);
+}
+__global__ void pack_tconv_dgrad_kernel(const float* __restrict__ w, __nv_bfloat16* __restrict__ out, int Cin, int Cout) {
+  const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  const long long n = 4ll * Cin * Cout;
+  if (i >= n) return;
+  const int o = static_cast<int>(i % Cout);
+  const int ab = static_cast<int>((i / Cout) % 4);
+  const int c = static_cast<int>(i / (4ll * Cout));
+  out[i] = __float2bfloat16(w[(static_cast<long long>(ab) * Cout + o) * Cin + c]);
+}
+__global__ void cast_f32_bf16_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ y, long long n) {
+  const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i < n) y[i] = __float2bfloat16(x[i]);
+}
+__global__ void cast_bf16_f32_kernel(const __nv_bfloat16* __restrict__ x, float* __restrict__ y, long long n) {
+  const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i < n) y[i] = __bfloat162float(x[i]);
+}
+
+// ------------------------------------------------------------------------------------------ optimizers
+__device__ __forceinline__ float schedule_lr(long long step, float lr0, int const_lr, float lr_fraction,
+                                             float decay_steps) {
+  if (const_lr) return lr0;
+  return static_cast<float>(static_cast<double>(lr0) *
+                            pow(static_cast<double>(lr_fraction), static_cast<double>(step) / decay_steps));
+}
+
+__global__ void adam_kernel(float* __restrict__ theta, float* __restrict__ m, float* __restrict__ v,
+                            const float* __restrict__ g, long long n, const long long* __restrict__ step_ptr, float lr0,
+                            int const_lr, float lr_fraction, float decay_steps, float beta1, float beta2, float eps,
+                            float grad_scale) {
+  __shared__ float s_lrt;
+  if (threadIdx.x == 0) {
+    const long long step = *step_ptr;
+    const double t = static_cast<double>(step + 1);
+    const double lr = schedule_lr(step, lr0, const_lr, lr_fraction, decay_steps);
+    s_lrt = static_cast<float>(lr * sqrt(1.0 - pow(static_cast<double>(beta2), t)) /
+                               (1.0 - pow(static_cast<double>(beta1), t)));
+  }
+  __syncthreads();
+  const float lrt = s_lrt;
+  const float omb1 = 1.0f - beta1, omb2 = 1.0f - beta2;
+  const long long n4 = n / 4;
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < n4; i += stride) {
+    float4 gt = reinterpret_cast<const float4*>(g)[i];
+    float4 mt = reinterpret_cast<float4*>(m)[i];
+    float4 vt = reinterpret_cast<float4*>(v)[i];
+    float4 th = reinterpret_cast<float4*>(theta)[i];
+    float* gp = &gt.x; float* mp = &mt.x; float* vp = &vt.x; float* tp = &th.x;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const float gk = gp[k] * grad_scale;
+      mp[k] = beta1 * mp[k] + omb1 * gk;
+      vp[k] = beta2 * vp[k] + omb2 * gk * gk;
+      tp[k] = tp[k] - lrt * mp[k] / (sqrtf(vp[k]) + eps);
+    }
+    reinterpret_cast<float4*>(m)[i] = mt;
+    reinterpret_cast<float4*>(v)[i] = vt;
+    reinterpret_cast<float4*>(theta)[i] = th;
+  }
+  if (blockIdx.x == 0) {
+    for (long long i = n4 * 4 + threadIdx.x; i < n; i += blockDim.x) {
+      const float gk = g[i] * grad_scale;
+      const float mk = beta1 * m[i] + omb1 * gk;
+      const float vk = beta2 * v[i] + omb2 * gk * gk;
+      m[i] = mk;
+      v[i] = vk;
+      theta[i] = theta[i] - lrt * mk / (sqrtf(vk) + eps);
+    }
+  }
+}
+
+__global__ void sgd_kernel(float* __restrict__ theta, const float* __restrict__ g, long long n,
+                           const long long* __restrict__ step_ptr, float lr0, int const_lr, float lr_fraction,
+                           float decay_steps, float grad_scale) {
+  __shared__ float s_lr;
+  if (threadIdx.x == 0) s_lr = schedule_lr(*step_ptr, lr0, const_lr, lr_fraction, decay_steps);
+  __syncthreads();
+  const float lr = s_lr * grad_scale;
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += stride) {
+    theta[i] = theta[i] - lr * g[i];
+  }
+}
+
+__global__ void step_increment_kernel(long long* step_ptr) { *step_ptr += 1; }
+
+__global__ void dropout_mask_kernel(unsigned char* __restrict__ keep, long long ngroups, float keep_prob,
+                                    unsigned long long seed, unsigned int stream_id) {
+  const long long g = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (g >= ngroups) return;
+  const uint32_t bits = dropout_keep_bits8(seed, stream_id, static_cast<unsigned long long>(g), keep_prob);
+#pragma unroll
+  for (int i = 0; i < 8; ++i) keep[g * 8 + i] = (bits >> i) & 1u;
+}
+
+int check_groups(int C, const char* what) {
+  const int groups = C / 8;
+  if (C % 8 != 0 || groups < 1 || groups > 256 || (groups & (groups - 1)) != 0) {
+    set_error("%s: channel count %d must be 8 * power of two (<= 2048)", what, C);
+    return UB_ERR_INVALID;
+  }
+  return UB_OK;
+}
+
+}  // namespace
+
+// ============================================================================================ host launchers
+int conv_first_fwd(const float* x, const float* w, const float* bias, void* y, int N, int H, int W, int Cin, int Cout,
+                   cudaStream_t s) {
+  UB_REQUIRE(Cin >= 1 && Cin <= 8, "conv_first_fwd: Cin %d outside 1..8", Cin);
+  UB_REQUIRE(Cout % 8 == 0 && Cout <= 64, "conv_first_fwd: Cout %d unsupported", Cout);
+  const long long total = static_cast<long long>(N) * H * W * (Cout / 8);
+  const size_t smem = (9 * Cin * Cout + Cout) * sizeof(float);
+  conv_first_fwd_kernel<<<grid_for(total, kThreads), kThreads, smem, s>>>(x, w, bias, reinterpret_cast<uint4*>(y), N, H,
+                                                                          W, Cin, Cout);
+  UB_CHECK_CUDA(cudaGetLastError());
+  return UB_OK;
+}
+
+long long conv_first_wgrad_ws_floats(int Cin, int Cout) {
+  return static_cast<long long>(kRedBlocks) * (9 * Cin * Cout + Cout);
+}
+
+int conv_first_wgrad(const float* x, const void* dz, float* dw, float* db, float* ws, int N, int H, int W, int Cin,
+                     int Cout, cudaStream_t s) {
+  UB_REQUIRE(Cin >= 1 && Cin <= 8, "conv_first_wgrad: Cin %d outside 1..8", Cin);
+  const int groups = Cout / 8;
+  UB_REQUIRE(Cout % 8 == 0 && groups >= 1 && groups <= 8 && (groups & (groups - 1)) == 0,
+             "conv_first_wgrad: Cout %d unsupported", Cout);
+  const int nout = 9 * Cin * Cout + Cout;
+  conv_first_wgrad_kernel<<<kRedBlocks, kThreads, nout * sizeof(float), s>>>(x, reinterpret_cast<const uint4*>(dz), ws,
+                                                                             N, H, W, Cin, Cout);
+  UB_CHECK_CUDA(cudaGetLastError());
+  block_partials_reduce_kernel<<<grid_for(nout, 128), 128, 0, s>>>(ws, kRedBlocks, nout, dw, 9 * Cin * Cout, db);
+  UB_CHECK_CUDA(cudaGetLastError());
+  return UB_OK;
+}
+
+int maxpool2x2_fwd(const void* x, void* y, int N, int H, int W, int C, cudaStream_t s) {
+  UB_REQUIRE(C % 8 == 0 && H % 2 == 0 && W % 2 == 0, "maxpool2x2_fwd: shape %dx%dx%d unsupported", H, W, C);
+  const long long total = static_cast<long long>(N) * (H / 2) * (W / 2) * (C / 8);
+  maxpool_fwd_kernel<<<grid_for(total, kThreads), kThreads, 0, s>>>(reinterpret_cast<const uint4*>(x),
+                                                                    reinterpret_cast<uint4*>(y), N, H, W, C);
+  UB_CHECK_CUDA(cudaGetLastError());
+  return UB_OK;
+}
+
+int maxpool2x2_bwd(const void* x, const void* dpool, const void* skip_grad, void* dz_full, int N, int H, int W, int C,
+                   cudaStream_t s) {
+  UB_REQUIRE(C % 8 == 0 && H % 2 == 0 && W % 2 == 0, "maxpool2x2_bwd: shape %dx%dx%d unsupported", H, W, C);
+  const long long total = static_cast<long long>(N) * (H / 2) * (W / 2) * (C / 8);
+  maxpool_bwd_kernel<<<grid_for(total, kThreads), kThreads, 0, s>>>(
+      reinterpret_cast<const uint4*>(x), reinterpret_cast<const uint4*>(dpool),
+      reinterpret_cast<const uint4*>(skip_grad), reinterpret_cast<uint4*>(dz_full), N, H, W, C);
+  UB_CHECK_CUDA(cudaGetLastError());
+  return UB_OK;
+}
+
+int upsample2x2_fwd(const void* x, void* y, int N, int H, int W, int C, cudaStream_t s) {
+  UB_REQUIRE(C % 8 == 0, "upsample2x2_fwd: C %d", C);
+  const long long total = static_cast<long long>(N) * (2 * H) * (2 * W) * (C / 8);
+  upsample_fwd_kernel<<<grid_for(total, kThreads), kThreads, 0, s>>>(reinterpret_cast<const uint4*>(x),
+                                                                     reinterpret_cast<uint4*>(y), N, H, W, C);
+  UB_CHECK_CUDA(cudaGetLastError());
+  return UB_OK;
+}
+
+int upsample2x2_bwd(const void* dy, const void* x, void* dx, int N, int H, int W, int C, int relu_mask, cudaStream_t s) {
+  UB_REQUIRE(C % 8 == 0, "upsample2x2_bwd: C %d", C);
+  const long long total = static_cast<long long>(N) * H * W * (C / 8);
+  upsample_bwd_kernel<<<grid_for(total, kThreads), kThreads, 0, s>>>(
+      reinterpret_cast<const uint4*>(dy), reinterpret_cast<const uint4*>(x), reinterpret_cast<uint4*>(dx), N, H, W, C,
+      relu_mask);
+  UB_CHECK_CUDA(cudaGetLastError());
+  return UB_OK;
+}
+
+long long head_ws_floats(long long, int C, int n_cl) {
+  const long long fwd = 3ll * kRedBlocks;
+  const long long bwd = static_cast<long long>(kRedBlocks) * (C * n_cl + n_cl);
+  return fwd > bwd ? fwd : bwd;
+}
+
+int head_fwd(const void* x, const float* w, const float* b, const float* y_true, float* p_out, float* sums, float* ws,
+             long long P, int C, int n_cl, cudaStream_t s) {
+  UB_REQUIRE(n_cl >= 1 && n_cl <= kMaxCl, "head_fwd: n_cl_out %d outside 1..%d", n_cl, kMaxCl);
+  const int subs = C / 8;
+  UB_REQUIRE(C % 8 == 0 && subs >= 1 && subs <= 32 && (subs & (subs - 1)) == 0, "head_fwd: C %d unsupported", C);
+  const size_t smem = (C * n_cl + n_cl + 3 * (kThreads / 32)) * sizeof(float);
+  head_fwd_kernel<<<kRedBlocks, kThreads, smem, s>>>(reinterpret_cast<const uint4*>(x), w, b, y_true, p_out, ws, P, C,
+                                                     n_cl);
+  UB_CHECK_CUDA(cudaGetLastError());
+  block_partials_reduce_kernel<<<1, 32, 0, s>>>(ws, kRedBlocks, 3, sums, 3, nullptr);
+  UB_CHECK_CUDA(cudaGetLastError());
+  return UB_OK;
+}
+
+int dice_finalize(const float* sums, float smooth, float* out4, cudaStream_t s) {
+  dice_finalize_kernel<<<1, 1, 0, s>>>(sums, smooth, out4);
+  UB_CHECK_CUDA(cudaGetLastError());
+  return UB_OK;
+}
+
+int head_bwd(const void* x, const float* w, const float* y_true, const float* p, const float* sums, float smooth,
+             float grad_scale, void* dx, float* dw, float* db, float* ws, long long P, int C, int n_cl, cudaStream_t s) {
+  UB_REQUIRE(n_cl >= 1 && n_cl <= kMaxCl, "head_bwd: n_cl_out %d outside 1..%d", n_cl, kMaxCl);
+  const int subs = C / 8;
+  UB_REQUIRE(C % 8 == 0 && subs >= 1 && subs <= 32 && (subs & (subs - 1)) == 0, "head_bwd: C %d unsupported", C);
+  const int nout = C * n_cl + n_cl;
+  const size_t smem = (C * n_cl + nout) * sizeof(float);
+  head_bwd_kernel<<<kRedBlocks, kThreads, smem, s>>>(reinterpret_cast<const uint4*>(x), w, y_true, p, sums, smooth,
+                                                     grad_scale, reinterpret_cast<uint4*>(dx), ws, P, C, n_cl);
+  UB_CHECK_CUDA(cudaGetLastError());
+  block_partials_reduce_kernel<<<grid_for(nout, 128), 128, 0, s>>>(ws, kRedBlocks, nout, dw, C * n_cl, db);
+  UB_CHECK_CUDA(cudaGetLastError());
+  return UB_OK;
+}
+
+long long colsum_ws_floats(int C) { return static_cast<long long>(kRedBlocks) * C; }
+
+int colsum_bf16(const void* dz, float* db, float* ws, long long P, int C, cudaStream_t s) {
+  int rc = check_groups(C, "colsum_bf16");
+  if (rc) return rc;
+  colsum_kernel<<<kRedBlocks, kThreads, C * sizeof(float), s>>>(reinterpret_cast<const uint4*>(dz), ws, P, C);
+  UB_CHECK_CUDA(cudaGetLastError());
+  block_partials_reduce_kernel<<<grid_for(C, 128), 128, 0, s>>>(ws, kRedBlocks, C, db, C, nullptr);
+  UB_CHECK_CUDA(cudaGetLastError());
+  return UB_OK;
+}
+
+int pack_conv_fwd(const float* w, void* out, int taps, int Cin, int Cout, cudaStream_t s) {
+  const long long n = static_cast<long long>(taps) * Cin * Cout;
+  pack_conv_fwd_kernel<<<grid_for(n, kThreads), kThreads, 0, s>>>(w, reinterpret_cast<__nv_bfloat16*>(out), taps, Cin,
+                                                                  Cout);
+  UB_CHECK_CUDA(cudaGetLastError());
+  return UB_OK;
+}
+int pack_conv_dgrad(const float* w, void* out, int taps, int Cin, int Cout, cudaStream_t s) {
+  const long long n = static_cast<long long>(taps) * Cin * Cout;
+  pack_conv_dgrad_kernel<<<grid_for(n, kThreads), kThreads, 0, s>>>(w, reinterpret_cast<__nv_bfloat16*>(out), taps, Cin,
+                                                                    Cout);
+  UB_CHECK_CUDA(cudaGetLastError());
+  return UB_OK;
+}
+int pack_tconv_fwd(const float* w, void* out, int Cin, int Cout, cudaStream_t s) {
+  return cast_f32_to_bf16(w, out, 4ll * Cin * Cout, s);
+}
+int pack_tconv_dgrad(const float* w, void* out, int Cin, int Cout, cudaStream_t s) {
+  const long long n = 4ll * Cin * Cout;
+  pack_tconv_dgrad_kernel<<<grid_for(n, kThreads), kThreads, 0, s>>>(w, reinterpret_cast<__nv_bfloat16*>(out), Cin,
+                                                                     Cout);
+  UB_CHECK_CUDA(cudaGetLastError());
+  return UB_OK;
+}
+
+int adam_step(float* theta, float* m, float* v, const float* g, long long n, const long long* step_ptr, float lr0,
+              int const_lr, float lr_fraction, float decay_steps, float beta1, float beta2, float eps, float grad_scale,
+              cudaStream_t s) {
+  UB_REQUIRE((reinterpret_cast<uintptr_t>(theta) | reinterpret_cast<uintptr_t>(m) | reinterpret_cast<uintptr_t>(v) |
+              reinterpret_cast<uintptr_t>(g)) % 16 == 0,
+             "adam_step: buffers must be 16-byte aligned");
+  const int blocks = 4 * device_sm_count();
+  adam_kernel<<<blocks, kThreads, 0, s>>>(theta, m, v, g, n, step_ptr, lr0, const_lr, lr_fraction, decay_steps, beta1,
+                                          beta2, eps, grad_scale);
+  UB_CHECK_CUDA(cudaGetLastError());
+  return UB_OK;
+}
+
+int sgd_step(float* theta, const float* g, long long n, const long long* step_ptr, float lr0, int const_lr,
+             float lr_fraction, float decay_steps, float grad_scale, cudaStream_t s) {
+  const int blocks = 4 * device_sm_count();
+  sgd_kernel<<<blocks, kThreads, 0, s>>>(theta, g, n, step_ptr, lr0, const_lr, lr_fraction, decay_steps, grad_scale);
+  UB_CHECK_CUDA(cudaGetLastError());
+  return UB_OK;
+}
+
+int step_increment(long long* step_ptr, cudaStream_t s) {
+  step_increment_kernel<<<1, 1, 0, s>>>(step_ptr);
+  UB_CHECK_CUDA(cudaGetLastError());
+  return UB_OK;
+}
+
+int dropout_mask(unsigned char* keep, long long n, float keep_prob, unsigned long long seed, unsigned int stream_id,
+                 cudaStream_t s) {
+  UB_REQUIRE(n % 8 == 0, "dropout_mask: n %lld must be a multiple of 8", n);
+  const long long ng = n / 8;
+  dropout_mask_kernel<<<grid_for(ng, kThreads), kThreads, 0, s>>>(keep, ng, keep_prob, seed, stream_id);
+  UB_CHECK_CUDA(cudaGetLastError());
+  return UB_OK;
+}
+
+int cast_f32_to_bf16(const float* x, void* y, long long n, cudaStream_t s) {
+  cast_f32_bf16_kernel<<<grid_for(n, kThreads), kThreads, 0, s>>>(x, reinterpret_cast<__nv_bfloat16*>(y), n);
+  UB_CHECK_CUDA(cudaGetLastError());
+  return UB_OK;
+}
+int cast_bf16_to_f32(const void* x, float* y, long long n, cudaStream_t s) {
+  cast_bf16_f32_kernel<<<grid_for(n, kThreads), kThreads, 0, s>>>(reinterpret_cast<const __nv_bfloat16*>(x), y, n);
+  UB_CHECK_CUDA(cudaGetLastError());
+  return UB_OK;
+}
+
+}  // namespace ub

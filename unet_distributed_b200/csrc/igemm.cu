@@ -1,0 +1,280 @@
+#include "igemm.cuh"
+
+#include "common.h"
+#include "ptx.cuh"
+
+namespace ub {
+
+namespace {
+
+constexpr int kThreads = 192;  // warp0: TMA producer, warp1: MMA issuer + TMEM owner, warps 2..5: epilogue
+constexpr int kMaxStages = 8;
+
+struct __align__(8) IgemmBarriers {
+  uint64_t full[kMaxStages];
+  uint64_t empty[kMaxStages];
+  uint64_t tmem_full[2];
+  uint64_t tmem_empty[2];
+  uint32_t tmem_base;
+};
+
+__device__ __forceinline__ void decode_tile(const IgemmParams& p, int tile, int& n0, int& h0, int& w0, int& nt) {
+  nt = tile % p.n_tiles;
+  int mt = tile / p.n_tiles;
+  int tw_i = mt % p.tiles_w;
+  mt /= p.tiles_w;
+  int th_i = mt % p.tiles_h;
+  int tn_i = mt / p.tiles_h;
+  n0 = tn_i * p.TN;
+  h0 = th_i * p.TH;
+  w0 = tw_i * p.TW;
+}
+
+__global__ void __launch_bounds__(kThreads, 1)
+igemm_kernel(const __grid_constant__ IgemmParams p, const __grid_constant__ CUtensorMap tmA0,
+             const __grid_constant__ CUtensorMap tmA1, const __grid_constant__ CUtensorMap tmB) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t raw_addr = smem_u32(smem_raw);
+  uint8_t* smem = smem_raw + ((1024u - (raw_addr & 1023u)) & 1023u);
+
+  const int a_bytes = 128 * p.kc * 2;
+  const int b_bytes = p.block_n * p.kc * 2;
+  const int stage_bytes = a_bytes + b_bytes;
+  IgemmBarriers* bars = reinterpret_cast<IgemmBarriers*>(smem + p.stages * stage_bytes);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int num_tiles = p.tiles_n * p.tiles_h * p.tiles_w * p.n_tiles;
+  const int kb_per_tap = p.src_kblocks[0] + (p.num_src > 1 ? p.src_kblocks[1] : 0);
+  const int num_kb = p.taps_r * p.taps_s * kb_per_tap;
+  const uint32_t tmem_cols = (2 * p.block_n) < 32 ? 32u : static_cast<uint32_t>(2 * p.block_n);
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < p.stages; ++s) {
+      mbar_init(&bars->full[s], 1);
+      mbar_init(&bars->empty[s], 1);
+    }
+    for (int a = 0; a < 2; ++a) {
+      mbar_init(&bars->tmem_full[a], 1);
+      mbar_init(&bars->tmem_empty[a], 4);
+    }
+    mbar_fence_init();
+    tma_prefetch_desc(&tmA0);
+    if (p.num_src > 1) tma_prefetch_desc(&tmA1);
+    tma_prefetch_desc(&tmB);
+  }
+  if (warp == 1) {
+    tmem_alloc(&bars->tmem_base, tmem_cols);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = bars->tmem_base;
+
+  if (warp == 0) {
+    // ------------------------------------------------------------ TMA producer (one thread)
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        int n0, h0, w0, nt;
+        decode_tile(p, tile, n0, h0, w0, nt);
+        for (int tap = 0; tap < p.taps_r * p.taps_s; ++tap) {
+          const int tr = tap / p.taps_s, ts = tap % p.taps_s;
+          for (int src = 0; src < p.num_src; ++src) {
+            const CUtensorMap* tmA = src == 0 ? &tmA0 : &tmA1;
+            for (int cb = 0; cb < p.src_kblocks[src]; ++cb) {
+              mbar_wait(&bars->empty[stage], phase ^ 1u);
+              uint8_t* sa = smem + stage * stage_bytes;
+              uint8_t* sb = sa + a_bytes;
+              mbar_arrive_expect_tx(&bars->full[stage], static_cast<uint32_t>(stage_bytes));
+              if (p.a_mode == IG_A_SHIFT4D) {
+                tma_load_4d(sa, tmA, &bars->full[stage], cb * p.kc, w0 + ts - p.pad, h0 + tr - p.pad, n0);
+              } else {
+                tma_load_5d(sa, tmA, &bars->full[stage], cb * p.kc, ts, w0, tr, n0 * p.H + h0);
+              }
+              tma_load_3d(sb, &tmB, &bars->full[stage], p.src_ci_off[src] + cb * p.kc, tap, nt * p.block_n);
+              if (++stage == p.stages) { stage = 0; phase ^= 1u; }
+            }
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ------------------------------------------------------------ MMA issuer (one thread)
+    if (lane == 0) {
+      const uint32_t idesc = umma_idesc_bf16(128, static_cast<uint32_t>(p.block_n), 0, 0);
+      const uint32_t sw = p.kc == 64 ? UMMA_SW_128B : UMMA_SW_64B;
+      const uint32_t sbo = static_cast<uint32_t>(8 * p.kc * 2);  // 8 rows of kc bf16
+      const int ksteps = p.kc / 16;
+      int stage = 0;
+      uint32_t phase = 0;
+      int it = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
+        const int acc = it & 1;
+        mbar_wait(&bars->tmem_empty[acc], (((it >> 1) & 1) ^ 1u));
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + static_cast<uint32_t>(acc * p.block_n);
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait(&bars->full[stage], phase);
+          tc_fence_after();
+          const uint32_t sa = smem_u32(smem + stage * stage_bytes);
+          const uint32_t sb = sa + static_cast<uint32_t>(a_bytes);
+          const uint64_t adesc = umma_smem_desc(sa, 0, sbo, sw);
+          const uint64_t bdesc = umma_smem_desc(sb, 0, sbo, sw);
+          for (int k = 0; k < ksteps; ++k) {
+            umma_f16(d_tmem, adesc + static_cast<uint64_t>(2 * k), bdesc + static_cast<uint64_t>(2 * k), idesc,
+                     (kb | k) ? 1u : 0u);
+          }
+          umma_commit(&bars->empty[stage]);
+          if (++stage == p.stages) { stage = 0; phase ^= 1u; }
+        }
+        umma_commit(&bars->tmem_full[acc]);
+      }
+    }
+  } else {
+    // ------------------------------------------------------------ epilogue (4 warps, one TMEM lane quarter each)
+    const int quarter = warp & 3;
+    const int m = quarter * 32 + lane;
+    const int tw = m % p.TW;
+    const int th = (m / p.TW) % p.TH;
+    const int tn = m / (p.TW * p.TH);
+    const IgemmEpilogue& e = p.epi;
+    int it = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
+      const int acc = it & 1;
+      int n0, h0, w0, nt;
+      decode_tile(p, tile, n0, h0, w0, nt);
+      const int n = n0 + tn, h = h0 + th, w = w0 + tw;
+      const bool valid = (n < p.N) && (h < p.H) && (w < p.W);
+      const int col0 = nt * p.block_n;  // first GEMM column of this tile
+
+      // Destination slot, pixel index and channel origin.
+      int slot = 0, ch0 = col0;
+      size_t pix;
+      if (e.d2s_cout > 0) {
+        const int ab = col0 / e.d2s_cout;
+        ch0 = col0 % e.d2s_cout;
+        pix = (static_cast<size_t>(n) * (2 * p.H) + (2 * h + (ab >> 1))) * (2 * p.W) + (2 * w + (ab & 1));
+      } else {
+        if (col0 >= e.split_col) { slot = 1; ch0 = col0 - e.split_col; }
+        pix = (static_cast<size_t>(n) * p.H + h) * p.W + w;
+      }
+      __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(e.dst[slot]) + pix * e.dst_C[slot] + e.dst_coff[slot] + ch0;
+      const __nv_bfloat16* aux = nullptr;
+      if (e.aux[slot]) {
+        aux = reinterpret_cast<const __nv_bfloat16*>(e.aux[slot]) + pix * e.aux_C[slot] + e.aux_coff[slot] + ch0;
+      }
+      const size_t drop_elem0 = pix * e.dst_C[slot] + e.dst_coff[slot] + ch0;
+      const int bias0 = (e.d2s_cout > 0) ? ch0 : col0;
+
+      mbar_wait(&bars->tmem_full[acc], (it >> 1) & 1);
+      tc_fence_after();
+      const uint32_t t_row = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) +
+                             static_cast<uint32_t>(acc * p.block_n);
+      for (int c = 0; c < p.block_n; c += 16) {
+        uint32_t r[16];
+        tmem_ld_32x32b_x16(t_row + static_cast<uint32_t>(c), r);
+        tmem_ld_wait();
+        if (valid) {
+          float v[16];
+#pragma unroll
+          for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
+          if (e.bias) {
+            const float4* bp = reinterpret_cast<const float4*>(e.bias + bias0 + c);
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+              const float4 bq = __ldg(bp + q);
+              v[4 * q + 0] += bq.x; v[4 * q + 1] += bq.y; v[4 * q + 2] += bq.z; v[4 * q + 3] += bq.w;
+            }
+          }
+          if (e.relu) {
+#pragma unroll
+            for (int i = 0; i < 16; ++i) v[i] = fmaxf(v[i], 0.0f);
+          }
+          if (e.drop_keep < 1.0f) {
+            const float inv = 1.0f / e.drop_keep;
+#pragma unroll
+            for (int g = 0; g < 2; ++g) {
+              const uint32_t bits = dropout_keep_bits8(e.drop_seed, e.drop_stream, (drop_elem0 + c) / 8 + g, e.drop_keep);
+#pragma unroll
+              for (int i = 0; i < 8; ++i) v[8 * g + i] = ((bits >> i) & 1u) ? v[8 * g + i] * inv : 0.0f;
+            }
+          }
+          if (aux) {
+            const uint4* ap = reinterpret_cast<const uint4*>(aux + c);
+#pragma unroll
+            for (int g = 0; g < 2; ++g) {
+              const uint4 a = __ldg(ap + g);
+              const uint32_t aw[4] = {a.x, a.y, a.z, a.w};
+#pragma unroll
+              for (int i = 0; i < 4; ++i) {
+                v[8 * g + 2 * i] = bf16_lo(aw[i]) > 0.0f ? v[8 * g + 2 * i] * e.mask_scale : 0.0f;
+                v[8 * g + 2 * i + 1] = bf16_hi(aw[i]) > 0.0f ? v[8 * g + 2 * i + 1] * e.mask_scale : 0.0f;
+              }
+            }
+          }
+          uint4* dp = reinterpret_cast<uint4*>(dst + c);
+#pragma unroll
+          for (int g = 0; g < 2; ++g) {
+            uint4 o;
+            o.x = pack_bf16x2(v[8 * g + 0], v[8 * g + 1]);
+            o.y = pack_bf16x2(v[8 * g + 2], v[8 * g + 3]);
+            o.z = pack_bf16x2(v[8 * g + 4], v[8 * g + 5]);
+            o.w = pack_bf16x2(v[8 * g + 6], v[8 * g + 7]);
+            dp[g] = o;
+          }
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&bars->tmem_empty[acc]);
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, tmem_cols);
+  }
+}
+
+}  // namespace
+
+int igemm_launch(const IgemmParams& p, const CUtensorMap& a0, const CUtensorMap& a1, const CUtensorMap& b,
+                 cudaStream_t stream) {
+  UB_REQUIRE(p.TN * p.TH * p.TW == 128, "igemm: tile box %dx%dx%d is not 128 pixels", p.TN, p.TH, p.TW);
+  UB_REQUIRE(p.block_n == 32 || p.block_n == 64 || p.block_n == 128 || p.block_n == 256,
+             "igemm: block_n %d unsupported", p.block_n);
+  UB_REQUIRE(p.kc == 32 || p.kc == 64, "igemm: kc %d unsupported", p.kc);
+  UB_REQUIRE(p.stages >= 2 && p.stages <= kMaxStages, "igemm: stages %d out of range", p.stages);
+  const int stage_bytes = 128 * p.kc * 2 + p.block_n * p.kc * 2;
+  const size_t smem = static_cast<size_t>(p.stages) * stage_bytes + sizeof(IgemmBarriers) + 1024;
+  UB_REQUIRE(smem <= 227 * 1024, "igemm: %zu bytes of shared memory requested", smem);
+  static bool attr_set[64] = {false};
+  int dev = 0;
+  UB_CHECK_CUDA(cudaGetDevice(&dev));
+  if (dev >= 0 && dev < 64 && !attr_set[dev]) {
+    UB_CHECK_CUDA(cudaFuncSetAttribute(igemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    attr_set[dev] = true;
+  }
+  const int num_tiles = p.tiles_n * p.tiles_h * p.tiles_w * p.n_tiles;
+  UB_REQUIRE(num_tiles > 0, "igemm: empty problem");
+  int grid = device_sm_count();
+  if (grid > num_tiles) grid = num_tiles;
+  igemm_kernel<<<grid, kThreads, smem, stream>>>(p, a0, a1, b);
+  UB_CHECK_CUDA(cudaGetLastError());
+  return UB_OK;
+}
+
+int igemm_pick_stages(int block_n, int kc) {
+  const int stage_bytes = 128 * kc * 2 + block_n * kc * 2;
+  int s = (200 * 1024) / stage_bytes;
+  if (s > kMaxStages) s = kMaxStages;
+  if (s < 2) s = 2;
+  return s;
+}
+
+}  // namespace ub

@@ -1,0 +1,370 @@
+#include "ops.cuh"
+
+#include <climits>
+#include <cstring>
+
+#include "common.h"
+#include "igemm.cuh"
+#include "wgrad.cuh"
+
+namespace ub {
+
+int igemm_pick_stages(int block_n, int kc);
+
+namespace {
+
+struct Box {
+  int TN, TH, TW;
+};
+
+// 128-pixel output tile (igemm) or 64-pixel reduction block (wgrad) for an NHWC grid.
+Box pick_box(int pixels, int W) {
+  Box b;
+  b.TW = W >= 16 ? 16 : 8;
+  b.TH = pixels == 128 ? 8 : (b.TW == 16 ? 4 : 8);
+  b.TN = pixels / (b.TW * b.TH);
+  return b;
+}
+
+int cdiv(int a, int b) { return (a + b - 1) / b; }
+
+int pick_kc(int C0, int C1) {
+  if (C0 % 64 == 0 && (C1 == 0 || C1 % 64 == 0)) return 64;
+  if (C0 % 32 == 0 && (C1 == 0 || C1 % 32 == 0)) return 32;
+  return 0;
+}
+
+int nhwc_map(CUtensorMap* m, const void* p, int N, int H, int W, int C, int box_c, Box b) {
+  const uint64_t dims[4] = {static_cast<uint64_t>(C), static_cast<uint64_t>(W), static_cast<uint64_t>(H),
+                            static_cast<uint64_t>(N)};
+  const uint64_t str[3] = {static_cast<uint64_t>(C) * 2, static_cast<uint64_t>(W) * C * 2,
+                           static_cast<uint64_t>(H) * W * C * 2};
+  const uint32_t box[4] = {static_cast<uint32_t>(box_c), static_cast<uint32_t>(b.TW), static_cast<uint32_t>(b.TH),
+                           static_cast<uint32_t>(b.TN)};
+  return make_tmap_bf16(m, p, 4, dims, str, box, box_c * 2);
+}
+
+// 5-D view of the fine tensor y[N, 2H, 2W, C] as (c, b, j, a, n*H+i) with y[n, 2i+a, 2j+b, c]; (H, W) = coarse grid.
+int fine_view_map(CUtensorMap* m, const void* p, int N, int H, int W, int C, int box_c, Box b) {
+  const uint64_t dims[5] = {static_cast<uint64_t>(C), 2, static_cast<uint64_t>(W), 2,
+                            static_cast<uint64_t>(N) * H};
+  const uint64_t str[4] = {static_cast<uint64_t>(C) * 2, static_cast<uint64_t>(2) * C * 2,
+                           static_cast<uint64_t>(2) * W * C * 2, static_cast<uint64_t>(4) * W * C * 2};
+  const uint32_t box[5] = {static_cast<uint32_t>(box_c), 1, static_cast<uint32_t>(b.TW), 1,
+                           static_cast<uint32_t>(b.TN * b.TH)};
+  return make_tmap_bf16(m, p, 5, dims, str, box, box_c * 2);
+}
+
+// Packed weights [ncols][taps][ktot] bf16.
+int weight_map(CUtensorMap* m, const void* p, int ncols, int taps, int ktot, int kc, int block_n) {
+  const uint64_t dims[3] = {static_cast<uint64_t>(ktot), static_cast<uint64_t>(taps), static_cast<uint64_t>(ncols)};
+  const uint64_t str[2] = {static_cast<uint64_t>(ktot) * 2, static_cast<uint64_t>(taps) * ktot * 2};
+  const uint32_t box[3] = {static_cast<uint32_t>(kc), 1, static_cast<uint32_t>(block_n)};
+  return make_tmap_bf16(m, p, 3, dims, str, box, kc * 2);
+}
+
+void fill_grid(IgemmParams& p, int N, int H, int W, Box b) {
+  p.N = N; p.H = H; p.W = W;
+  p.TN = b.TN; p.TH = b.TH; p.TW = b.TW;
+  p.tiles_n = cdiv(N, b.TN);
+  p.tiles_h = cdiv(H, b.TH);
+  p.tiles_w = cdiv(W, b.TW);
+}
+
+int pick_block_n(int ncols_per_dest) {
+  if (ncols_per_dest % 256 == 0) return 256;
+  if (ncols_per_dest % 128 == 0) return 128;
+  if (ncols_per_dest % 64 == 0) return 64;
+  if (ncols_per_dest % 32 == 0) return 32;
+  return 0;
+}
+
+}  // namespace
+
+// ------------------------------------------------------------------------------------------------ conv3x3 forward
+int conv3x3_fwd(ConvSrc x0, ConvSrc x1, const void* w_packed, const float* bias, void* y, int N, int H, int W, int Cout,
+                int relu, DropoutCfg drop, cudaStream_t s) {
+  const int C1 = x1.ptr ? x1.C : 0;
+  const int kc = pick_kc(x0.C, C1);
+  UB_REQUIRE(kc != 0, "conv3x3_fwd: input channels %d/%d must be multiples of 32", x0.C, C1);
+  const int block_n = pick_block_n(Cout);
+  UB_REQUIRE(block_n != 0, "conv3x3_fwd: Cout %d must be a multiple of 32", Cout);
+  IgemmParams p;
+  std::memset(&p, 0, sizeof(p));
+  const Box b = pick_box(128, W);
+  fill_grid(p, N, H, W, b);
+  p.n_tiles = Cout / block_n;
+  p.block_n = block_n;
+  p.a_mode = IG_A_SHIFT4D;
+  p.taps_r = 3; p.taps_s = 3; p.pad = 1;
+  p.num_src = C1 ? 2 : 1;
+  p.src_kblocks[0] = x0.C / kc;
+  p.src_kblocks[1] = C1 / kc;
+  p.src_ci_off[0] = 0;
+  p.src_ci_off[1] = x0.C;
+  p.kc = kc;
+  p.stages = igemm_pick_stages(block_n, kc);
+  p.epi.dst[0] = y; p.epi.dst_C[0] = Cout; p.epi.dst_coff[0] = 0;
+  p.epi.split_col = INT_MAX;
+  p.epi.bias = bias;
+  p.epi.relu = relu;
+  p.epi.mask_scale = 1.0f;
+  p.epi.drop_keep = drop.keep;
+  p.epi.drop_seed = drop.seed;
+  p.epi.drop_stream = drop.stream;
+  CUtensorMap a0, a1, bm;
+  int rc = nhwc_map(&a0, x0.ptr, N, H, W, x0.C, kc, b);
+  if (rc) return rc;
+  a1 = a0;
+  if (C1) {
+    rc = nhwc_map(&a1, x1.ptr, N, H, W, C1, kc, b);
+    if (rc) return rc;
+  }
+  rc = weight_map(&bm, w_packed, Cout, 9, x0.C + C1, kc, block_n);
+  if (rc) return rc;
+  return igemm_launch(p, a0, a1, bm, s);
+}
+
+// ------------------------------------------------------------------------------------------------ conv3x3 dgrad
+int conv3x3_dgrad(const void* dz, int Cout, const void* w_packed_d, DgradDst d0, DgradDst d1, int N, int H, int W,
+                  cudaStream_t s) {
+  const int C1 = d1.ptr ? d1.C : 0;
+  const int kc = pick_kc(Cout, 0);
+  UB_REQUIRE(kc != 0, "conv3x3_dgrad: Cout %d must be a multiple of 32", Cout);
+  int block_n = pick_block_n(d0.C);
+  if (C1) {
+    const int b1 = pick_block_n(C1);
+    block_n = b1 < block_n ? b1 : block_n;
+  }
+  UB_REQUIRE(block_n != 0, "conv3x3_dgrad: destination channels %d/%d must be multiples of 32", d0.C, C1);
+  IgemmParams p;
+  std::memset(&p, 0, sizeof(p));
+  const Box b = pick_box(128, W);
+  fill_grid(p, N, H, W, b);
+  p.n_tiles = (d0.C + C1) / block_n;
+  p.block_n = block_n;
+  p.a_mode = IG_A_SHIFT4D;
+  p.taps_r = 3; p.taps_s = 3; p.pad = 1;
+  p.num_src = 1;
+  p.src_kblocks[0] = Cout / kc;
+  p.kc = kc;
+  p.stages = igemm_pick_stages(block_n, kc);
+  p.epi.dst[0] = d0.ptr; p.epi.dst_C[0] = d0.C; p.epi.aux[0] = d0.mask; p.epi.aux_C[0] = d0.C;
+  p.epi.dst[1] = d1.ptr; p.epi.dst_C[1] = C1; p.epi.aux[1] = d1.mask; p.epi.aux_C[1] = C1;
+  p.epi.split_col = C1 ? d0.C : INT_MAX;
+  p.epi.mask_scale = d0.scale;
+  UB_REQUIRE(!C1 || !d0.mask || !d1.mask || d0.scale == d1.scale,
+             "conv3x3_dgrad: both destinations must share the mask scale");
+  if (!d0.mask && d1.mask) p.epi.mask_scale = d1.scale;
+  p.epi.drop_keep = 1.0f;
+  CUtensorMap a0, bm;
+  int rc = nhwc_map(&a0, dz, N, H, W, Cout, kc, b);
+  if (rc) return rc;
+  rc = weight_map(&bm, w_packed_d, d0.C + C1, 9, Cout, kc, block_n);
+  if (rc) return rc;
+  return igemm_launch(p, a0, a0, bm, s);
+}
+
+// ------------------------------------------------------------------------------------------------ wgrad helpers
+namespace {
+
+struct WgradPlan {
+  WgradParams p;
+  long long nweights;
+};
+
+int plan_wgrad(WgradPlan& wp, int N, int H, int W, int taps_r, int taps_s, int pad, int z_C, int C0, int C1) {
+  WgradParams& p = wp.p;
+  std::memset(&p, 0, sizeof(p));
+  const Box b = pick_box(64, W);
+  p.N = N; p.H = H; p.W = W;
+  p.TN = b.TN; p.TH = b.TH; p.TW = b.TW;
+  p.blocks_n = cdiv(N, b.TN);
+  p.blocks_h = cdiv(H, b.TH);
+  p.blocks_w = cdiv(W, b.TW);
+  p.taps_r = taps_r; p.taps_s = taps_s; p.pad = pad;
+  UB_REQUIRE(z_C % 32 == 0, "wgrad: gradient channels %d must be a multiple of 32", z_C);
+  p.z_C = z_C;
+  p.z_atom = (z_C % 64 == 0) ? 64 : 32;
+  p.m_tiles = cdiv(z_C, 128);
+  p.num_src = C1 ? 2 : 1;
+  const int Cs[2] = {C0, C1};
+  int off = 0;
+  int total_nt = 0;
+  for (int s = 0; s < p.num_src; ++s) {
+    UB_REQUIRE(Cs[s] % 32 == 0, "wgrad: input channels %d must be a multiple of 32", Cs[s]);
+    p.x_C[s] = Cs[s];
+    p.x_atom[s] = (Cs[s] % 64 == 0) ? 64 : 32;
+    p.x_block_n[s] = Cs[s] >= 128 ? 128 : Cs[s];
+    UB_REQUIRE(Cs[s] % p.x_block_n[s] == 0, "wgrad: input channels %d not tileable", Cs[s]);
+    p.x_ntiles[s] = Cs[s] / p.x_block_n[s];
+    p.x_col_off[s] = off;
+    off += Cs[s];
+    total_nt += p.x_ntiles[s];
+  }
+  const int total_pb = p.blocks_n * p.blocks_h * p.blocks_w;
+  const int base = taps_r * taps_s * p.m_tiles * total_nt;
+  int splits = cdiv(2 * device_sm_count(), base);
+  const int max_splits = total_pb / 8 > 1 ? total_pb / 8 : 1;
+  if (splits > max_splits) splits = max_splits;
+  if (splits < 1) splits = 1;
+  const int per = cdiv(total_pb, splits);
+  p.splits = cdiv(total_pb, per);
+  p.stages = 6;
+  wp.nweights = static_cast<long long>(taps_r) * taps_s * (C0 + C1) * z_C;
+  return UB_OK;
+}
+
+}  // namespace
+
+size_t conv3x3_wgrad_ws_bytes(int N, int H, int W, int Cin_total, int Cout) {
+  WgradPlan wp;
+  // the split count does not depend on how Cin is divided between sources beyond the tile count; use the
+  // single-source plan as an upper bound (two sources never have fewer tiles, hence never more splits).
+  if (plan_wgrad(wp, N, H, W, 3, 3, 1, Cout, Cin_total, 0) != UB_OK) return 0;
+  return static_cast<size_t>(wp.p.splits) * wp.nweights * sizeof(float);
+}
+
+int conv3x3_wgrad(const void* dz, int Cout, ConvSrc x0, ConvSrc x1, float* dw, void* ws, size_t ws_bytes, int N, int H,
+                  int W, cudaStream_t s) {
+  const int C1 = x1.ptr ? x1.C : 0;
+  WgradPlan wp;
+  int rc = plan_wgrad(wp, N, H, W, 3, 3, 1, Cout, x0.C, C1);
+  if (rc) return rc;
+  WgradParams& p = wp.p;
+  p.z_mode = 0;
+  p.x_shift = 1;
+  const long long cin = x0.C + C1;
+  p.out_tap_stride = cin * Cout;
+  p.out_n_stride = Cout;
+  p.out_m_stride = 1;
+  p.out_split_stride = wp.nweights;
+  if (p.splits > 1) {
+    UB_REQUIRE(ws != nullptr && ws_bytes >= static_cast<size_t>(p.splits) * wp.nweights * sizeof(float),
+               "conv3x3_wgrad: workspace of %zu bytes needed, %zu given",
+               static_cast<size_t>(p.splits) * wp.nweights * sizeof(float), ws_bytes);
+    p.out = reinterpret_cast<float*>(ws);
+  } else {
+    p.out = dw;
+  }
+  const Box b = {p.TN, p.TH, p.TW};
+  CUtensorMap zm, xm0, xm1;
+  rc = nhwc_map(&zm, dz, N, H, W, Cout, p.z_atom, b);
+  if (rc) return rc;
+  rc = nhwc_map(&xm0, x0.ptr, N, H, W, x0.C, p.x_atom[0], b);
+  if (rc) return rc;
+  xm1 = xm0;
+  if (C1) {
+    rc = nhwc_map(&xm1, x1.ptr, N, H, W, C1, p.x_atom[1], b);
+    if (rc) return rc;
+  }
+  rc = wgrad_launch(p, zm, xm0, xm1, s);
+  if (rc) return rc;
+  if (p.splits > 1) return splitk_reduce_launch(p.out, wp.nweights, p.splits, dw, wp.nweights, s);
+  return UB_OK;
+}
+
+// ------------------------------------------------------------------------------------------------ transposed conv
+int tconv2x2_fwd(const void* x, int Cin, const void* w_packed, const float* bias, void* y, int Cout, int N, int H, int W,
+                 cudaStream_t s) {
+  const int kc = pick_kc(Cin, 0);
+  UB_REQUIRE(kc != 0, "tconv2x2_fwd: Cin %d must be a multiple of 32", Cin);
+  const int block_n = pick_block_n(Cout);
+  UB_REQUIRE(block_n != 0, "tconv2x2_fwd: Cout %d must be a multiple of 32", Cout);
+  IgemmParams p;
+  std::memset(&p, 0, sizeof(p));
+  const Box b = pick_box(128, W);
+  fill_grid(p, N, H, W, b);
+  p.n_tiles = 4 * Cout / block_n;
+  p.block_n = block_n;
+  p.a_mode = IG_A_SHIFT4D;
+  p.taps_r = 1; p.taps_s = 1; p.pad = 0;
+  p.num_src = 1;
+  p.src_kblocks[0] = Cin / kc;
+  p.kc = kc;
+  p.stages = igemm_pick_stages(block_n, kc);
+  p.epi.dst[0] = y; p.epi.dst_C[0] = Cout;
+  p.epi.split_col = INT_MAX;
+  p.epi.bias = bias;
+  p.epi.mask_scale = 1.0f;
+  p.epi.d2s_cout = Cout;
+  p.epi.drop_keep = 1.0f;
+  CUtensorMap a0, bm;
+  int rc = nhwc_map(&a0, x, N, H, W, Cin, kc, b);
+  if (rc) return rc;
+  rc = weight_map(&bm, w_packed, 4 * Cout, 1, Cin, kc, block_n);
+  if (rc) return rc;
+  return igemm_launch(p, a0, a0, bm, s);
+}
+
+int tconv2x2_dgrad(const void* dy, int Cout, const void* w_packed_d, void* dx, int Cin, const void* mask, float scale,
+                   int N, int H, int W, cudaStream_t s) {
+  const int kc = pick_kc(Cout, 0);
+  UB_REQUIRE(kc != 0, "tconv2x2_dgrad: Cout %d must be a multiple of 32", Cout);
+  const int block_n = pick_block_n(Cin);
+  UB_REQUIRE(block_n != 0, "tconv2x2_dgrad: Cin %d must be a multiple of 32", Cin);
+  IgemmParams p;
+  std::memset(&p, 0, sizeof(p));
+  const Box b = pick_box(128, W);
+  UB_REQUIRE(b.TN == 1 || b.TH == H, "tconv2x2_dgrad: %dx%d grid needs an image-aligned tile", H, W);
+  fill_grid(p, N, H, W, b);
+  p.n_tiles = Cin / block_n;
+  p.block_n = block_n;
+  p.a_mode = IG_A_TCONV5D;
+  p.taps_r = 2; p.taps_s = 2; p.pad = 0;
+  p.num_src = 1;
+  p.src_kblocks[0] = Cout / kc;
+  p.kc = kc;
+  p.stages = igemm_pick_stages(block_n, kc);
+  p.epi.dst[0] = dx; p.epi.dst_C[0] = Cin; p.epi.aux[0] = mask; p.epi.aux_C[0] = Cin;
+  p.epi.split_col = INT_MAX;
+  p.epi.mask_scale = scale;
+  p.epi.drop_keep = 1.0f;
+  CUtensorMap a0, bm;
+  int rc = fine_view_map(&a0, dy, N, H, W, Cout, kc, b);
+  if (rc) return rc;
+  rc = weight_map(&bm, w_packed_d, Cin, 4, Cout, kc, block_n);
+  if (rc) return rc;
+  return igemm_launch(p, a0, a0, bm, s);
+}
+
+size_t tconv2x2_wgrad_ws_bytes(int N, int H, int W, int Cin, int Cout) {
+  WgradPlan wp;
+  if (plan_wgrad(wp, N, H, W, 2, 2, 0, Cout, Cin, 0) != UB_OK) return 0;
+  return static_cast<size_t>(wp.p.splits) * wp.nweights * sizeof(float);
+}
+
+int tconv2x2_wgrad(const void* dy, int Cout, const void* x, int Cin, float* dw, void* ws, size_t ws_bytes, int N, int H,
+                   int W, cudaStream_t s) {
+  WgradPlan wp;
+  int rc = plan_wgrad(wp, N, H, W, 2, 2, 0, Cout, Cin, 0);
+  if (rc) return rc;
+  WgradParams& p = wp.p;
+  UB_REQUIRE(p.TN == 1 || p.TH == H, "tconv2x2_wgrad: %dx%d grid needs an image-aligned block", H, W);
+  p.z_mode = 1;
+  p.x_shift = 0;
+  p.out_tap_stride = static_cast<long long>(Cout) * Cin;
+  p.out_m_stride = Cin;
+  p.out_n_stride = 1;
+  p.out_split_stride = wp.nweights;
+  if (p.splits > 1) {
+    UB_REQUIRE(ws != nullptr && ws_bytes >= static_cast<size_t>(p.splits) * wp.nweights * sizeof(float),
+               "tconv2x2_wgrad: workspace of %zu bytes needed, %zu given",
+               static_cast<size_t>(p.splits) * wp.nweights * sizeof(float), ws_bytes);
+    p.out = reinterpret_cast<float*>(ws);
+  } else {
+    p.out = dw;
+  }
+  const Box b = {p.TN, p.TH, p.TW};
+  CUtensorMap zm, xm;
+  rc = fine_view_map(&zm, dy, N, H, W, Cout, p.z_atom, b);
+  if (rc) return rc;
+  rc = nhwc_map(&xm, x, N, H, W, Cin, p.x_atom[0], b);
+  if (rc) return rc;
+  rc = wgrad_launch(p, zm, xm, xm, s);
+  if (rc) return rc;
+  if (p.splits > 1) return splitk_reduce_launch(p.out, wp.nweights, p.splits, dw, wp.nweights, s);
+  return UB_OK;
+}
+
+}  // namespace ub

@@ -1,0 +1,52 @@
+// Layer-level operations built on the igemm / wgrad tile engines: shape -> tile choice -> tensor maps -> launch.
+#pragma once
+#include <cstddef>
+#include <cstdint>
+#include <cuda_runtime.h>
+
+namespace ub {
+
+struct ConvSrc {
+  const void* ptr;  // NHWC bf16
+  int C;
+};
+
+struct DropoutCfg {
+  float keep;  // 1.0 = off
+  unsigned long long seed;
+  unsigned int stream;
+};
+
+// y = relu?(conv3x3_same([x0, x1]) + bias) (* dropout); w_packed = bf16 [Cout][9][C0+C1].
+int conv3x3_fwd(ConvSrc x0, ConvSrc x1, const void* w_packed, const float* bias, void* y, int N, int H, int W, int Cout,
+                int relu, DropoutCfg drop, cudaStream_t s);
+
+// dx_k = conv3x3_same(dz, flipped weights)[channels of source k] * (mask_k > 0 ? scale_k : 0)   (mask optional)
+// w_packed_d = bf16 [C0+C1][9][Cout] (tap-flipped).
+struct DgradDst {
+  void* ptr;         // NHWC bf16, C channels
+  int C;
+  const void* mask;  // same shape as ptr, or null
+  float scale;
+};
+int conv3x3_dgrad(const void* dz, int Cout, const void* w_packed_d, DgradDst d0, DgradDst d1, int N, int H, int W,
+                  cudaStream_t s);
+
+// dw (fp32 [3][3][C0+C1][Cout]) = correlation of [x0,x1] with dz over all pixels. ws: conv3x3_wgrad_ws_bytes().
+size_t conv3x3_wgrad_ws_bytes(int N, int H, int W, int Cin_total, int Cout);
+int conv3x3_wgrad(const void* dz, int Cout, ConvSrc x0, ConvSrc x1, float* dw, void* ws, size_t ws_bytes, int N, int H,
+                  int W, cudaStream_t s);
+
+// Conv2DTranspose 2x2 stride 2: y[n,2i+a,2j+b,o] = sum_c x[n,i,j,c] w[a,b,o,c] + bias[o].
+// w_packed = bf16 [4*Cout][Cin] (cast of the TF layout); (N,H,W) is the input grid.
+int tconv2x2_fwd(const void* x, int Cin, const void* w_packed, const float* bias, void* y, int Cout, int N, int H, int W,
+                 cudaStream_t s);
+// dx[n,i,j,c] = sum_{a,b,o} dy[n,2i+a,2j+b,o] w[a,b,o,c], masked by (mask>0). w_packed_d = bf16 [Cin][4][Cout].
+int tconv2x2_dgrad(const void* dy, int Cout, const void* w_packed_d, void* dx, int Cin, const void* mask, float scale,
+                   int N, int H, int W, cudaStream_t s);
+// dw fp32 [2][2][Cout][Cin].
+size_t tconv2x2_wgrad_ws_bytes(int N, int H, int W, int Cin, int Cout);
+int tconv2x2_wgrad(const void* dy, int Cout, const void* x, int Cin, float* dw, void* ws, size_t ws_bytes, int N, int H,
+                   int W, cudaStream_t s);
+
+}  // namespace ub

@@ -1,0 +1,239 @@
+#include "wgrad.cuh"
+
+#include "common.h"
+#include "ptx.cuh"
+
+namespace ub {
+
+namespace {
+
+constexpr int kThreads = 192;
+constexpr int kMaxStages = 6;
+constexpr int kKP = 64;                    // pixels per K block
+constexpr int kOperandBytes = 16 * 1024;   // smem reserved per operand per stage (128 channels x 64 pixels bf16)
+constexpr int kStageBytes = 2 * kOperandBytes;
+
+struct __align__(8) WgradBarriers {
+  uint64_t full[kMaxStages];
+  uint64_t empty[kMaxStages];
+  uint64_t tmem_full;
+  uint32_t tmem_base;
+};
+
+__global__ void __launch_bounds__(kThreads, 1)
+wgrad_kernel(const __grid_constant__ WgradParams p, const __grid_constant__ CUtensorMap tmZ,
+             const __grid_constant__ CUtensorMap tmX0, const __grid_constant__ CUtensorMap tmX1) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t raw_addr = smem_u32(smem_raw);
+  uint8_t* smem = smem_raw + ((1024u - (raw_addr & 1023u)) & 1023u);
+  WgradBarriers* bars = reinterpret_cast<WgradBarriers*>(smem + p.stages * kStageBytes);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  // ---- which output tile / pixel range does this CTA own?
+  const int total_nt = p.x_ntiles[0] + (p.num_src > 1 ? p.x_ntiles[1] : 0);
+  int bid = blockIdx.x;
+  int ntg = bid % total_nt;
+  bid /= total_nt;
+  const int mt = bid % p.m_tiles;
+  bid /= p.m_tiles;
+  const int ntaps = p.taps_r * p.taps_s;
+  const int tap = bid % ntaps;
+  const int split = bid / ntaps;
+  const int src = (ntg >= p.x_ntiles[0]) ? 1 : 0;
+  const int nt = src ? ntg - p.x_ntiles[0] : ntg;
+  const int block_n = p.x_block_n[src];
+  const int x_atom = p.x_atom[src];
+  const int tr = tap / p.taps_s, ts = tap % p.taps_s;
+  const int m0 = mt * 128;
+  const int c0 = nt * block_n;
+
+  const int total_pb = p.blocks_n * p.blocks_h * p.blocks_w;
+  const int per_split = (total_pb + p.splits - 1) / p.splits;
+  const int pb_begin = split * per_split;
+  const int pb_end = (pb_begin + per_split < total_pb) ? pb_begin + per_split : total_pb;
+  const int nkb = pb_end > pb_begin ? pb_end - pb_begin : 0;
+
+  int m_atoms = (p.z_C - m0 + p.z_atom - 1) / p.z_atom;
+  if (m_atoms > 128 / p.z_atom) m_atoms = 128 / p.z_atom;
+  const int n_atoms = block_n / x_atom;
+  const uint32_t z_atom_bytes = static_cast<uint32_t>(kKP * p.z_atom * 2);
+  const uint32_t x_atom_bytes = static_cast<uint32_t>(kKP * x_atom * 2);
+  const uint32_t tmem_cols = block_n < 32 ? 32u : static_cast<uint32_t>(block_n);
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < p.stages; ++s) {
+      mbar_init(&bars->full[s], 1);
+      mbar_init(&bars->empty[s], 1);
+    }
+    mbar_init(&bars->tmem_full, 1);
+    mbar_fence_init();
+    tma_prefetch_desc(&tmZ);
+    tma_prefetch_desc(src ? &tmX1 : &tmX0);
+  }
+  if (warp == 1) {
+    tmem_alloc(&bars->tmem_base, tmem_cols);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = bars->tmem_base;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      const CUtensorMap* tmX = src ? &tmX1 : &tmX0;
+      int stage = 0;
+      uint32_t phase = 0;
+      const uint32_t tx = m_atoms * z_atom_bytes + n_atoms * x_atom_bytes;
+      for (int pb = pb_begin; pb < pb_end; ++pb) {
+        int t = pb;
+        const int bw = t % p.blocks_w;
+        t /= p.blocks_w;
+        const int bh = t % p.blocks_h;
+        const int bn = t / p.blocks_h;
+        const int n0 = bn * p.TN, h0 = bh * p.TH, w0 = bw * p.TW;
+        mbar_wait(&bars->empty[stage], phase ^ 1u);
+        uint8_t* sa = smem + stage * kStageBytes;
+        uint8_t* sb = sa + kOperandBytes;
+        mbar_arrive_expect_tx(&bars->full[stage], tx);
+        for (int a = 0; a < m_atoms; ++a) {
+          if (p.z_mode == 0) {
+            tma_load_4d(sa + a * z_atom_bytes, &tmZ, &bars->full[stage], m0 + a * p.z_atom, w0, h0, n0);
+          } else {
+            tma_load_5d(sa + a * z_atom_bytes, &tmZ, &bars->full[stage], m0 + a * p.z_atom, ts, w0, tr,
+                        n0 * p.H + h0);
+          }
+        }
+        const int dw = p.x_shift ? ts - p.pad : 0;
+        const int dh = p.x_shift ? tr - p.pad : 0;
+        for (int a = 0; a < n_atoms; ++a) {
+          tma_load_4d(sb + a * x_atom_bytes, tmX, &bars->full[stage], c0 + a * x_atom, w0 + dw, h0 + dh, n0);
+        }
+        if (++stage == p.stages) { stage = 0; phase ^= 1u; }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0 && nkb > 0) {
+      const uint32_t idesc = umma_idesc_bf16(128, static_cast<uint32_t>(block_n), 1, 1);
+      const uint32_t z_sw = p.z_atom == 64 ? UMMA_SW_128B : UMMA_SW_64B;
+      const uint32_t x_sw = x_atom == 64 ? UMMA_SW_128B : UMMA_SW_64B;
+      const uint32_t z_sbo = static_cast<uint32_t>(8 * p.z_atom * 2);
+      const uint32_t x_sbo = static_cast<uint32_t>(8 * x_atom * 2);
+      const uint32_t z_kstep = static_cast<uint32_t>(16 * p.z_atom * 2) >> 4;  // 16 pixels, in 16-byte units
+      const uint32_t x_kstep = static_cast<uint32_t>(16 * x_atom * 2) >> 4;
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int kb = 0; kb < nkb; ++kb) {
+        mbar_wait(&bars->full[stage], phase);
+        tc_fence_after();
+        const uint32_t sa = smem_u32(smem + stage * kStageBytes);
+        const uint32_t sb = sa + kOperandBytes;
+        const uint64_t adesc = umma_smem_desc(sa, z_atom_bytes, z_sbo, z_sw);
+        const uint64_t bdesc = umma_smem_desc(sb, x_atom_bytes, x_sbo, x_sw);
+#pragma unroll
+        for (int k = 0; k < kKP / 16; ++k) {
+          umma_f16(tmem_base, adesc + static_cast<uint64_t>(k * z_kstep), bdesc + static_cast<uint64_t>(k * x_kstep),
+                   idesc, (kb | k) ? 1u : 0u);
+        }
+        umma_commit(&bars->empty[stage]);
+        if (++stage == p.stages) { stage = 0; phase ^= 1u; }
+      }
+      umma_commit(&bars->tmem_full);
+    }
+  } else {
+    const int quarter = warp & 3;
+    const int row = quarter * 32 + lane;
+    const int co = m0 + row;
+    const bool valid = co < p.z_C;
+    float* out = p.out + split * p.out_split_stride + tap * p.out_tap_stride + co * p.out_m_stride +
+                 static_cast<long long>(p.x_col_off[src] + c0) * p.out_n_stride;
+    if (nkb > 0) {
+      mbar_wait(&bars->tmem_full, 0);
+      tc_fence_after();
+    }
+    const uint32_t t_row = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16);
+    for (int c = 0; c < block_n; c += 16) {
+      uint32_t r[16];
+      if (nkb > 0) {
+        tmem_ld_32x32b_x16(t_row + static_cast<uint32_t>(c), r);
+        tmem_ld_wait();
+      } else {
+#pragma unroll
+        for (int i = 0; i < 16; ++i) r[i] = 0u;
+      }
+      if (valid) {
+        if (p.out_n_stride == 1) {
+          float4* o4 = reinterpret_cast<float4*>(out + c);
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            o4[q] = make_float4(__uint_as_float(r[4 * q]), __uint_as_float(r[4 * q + 1]),
+                                __uint_as_float(r[4 * q + 2]), __uint_as_float(r[4 * q + 3]));
+          }
+        } else {
+#pragma unroll
+          for (int i = 0; i < 16; ++i) out[static_cast<long long>(c + i) * p.out_n_stride] = __uint_as_float(r[i]);
+        }
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, tmem_cols);
+  }
+}
+
+__global__ void splitk_reduce_kernel(const float* __restrict__ ws, long long split_stride, int splits,
+                                     float* __restrict__ out, long long n) {
+  const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  float acc = 0.0f;
+  for (int s = 0; s < splits; ++s) acc += ws[s * split_stride + i];
+  out[i] = acc;
+}
+
+}  // namespace
+
+int wgrad_launch(const WgradParams& p, const CUtensorMap& z, const CUtensorMap& x0, const CUtensorMap& x1,
+                 cudaStream_t stream) {
+  UB_REQUIRE(p.TN * p.TH * p.TW == kKP, "wgrad: pixel box %dx%dx%d is not %d pixels", p.TN, p.TH, p.TW, kKP);
+  UB_REQUIRE(p.stages >= 2 && p.stages <= kMaxStages, "wgrad: stages %d out of range", p.stages);
+  UB_REQUIRE(p.z_atom == 64 || p.z_atom == 32, "wgrad: z_atom %d", p.z_atom);
+  for (int s = 0; s < p.num_src; ++s) {
+    UB_REQUIRE(p.x_atom[s] == 64 || p.x_atom[s] == 32, "wgrad: x_atom %d", p.x_atom[s]);
+    UB_REQUIRE(p.x_block_n[s] >= 32 && p.x_block_n[s] <= 128 && p.x_block_n[s] % 16 == 0, "wgrad: block_n %d",
+               p.x_block_n[s]);
+  }
+  const int total_pb = p.blocks_n * p.blocks_h * p.blocks_w;
+  UB_REQUIRE(p.splits >= 1 && p.splits <= total_pb, "wgrad: splits %d vs %d pixel blocks", p.splits, total_pb);
+  const size_t smem = static_cast<size_t>(p.stages) * kStageBytes + sizeof(WgradBarriers) + 1024;
+  static bool attr_set[64] = {false};
+  int dev = 0;
+  UB_CHECK_CUDA(cudaGetDevice(&dev));
+  if (dev >= 0 && dev < 64 && !attr_set[dev]) {
+    UB_CHECK_CUDA(cudaFuncSetAttribute(wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    attr_set[dev] = true;
+  }
+  const int total_nt = p.x_ntiles[0] + (p.num_src > 1 ? p.x_ntiles[1] : 0);
+  const long long grid = static_cast<long long>(p.splits) * p.taps_r * p.taps_s * p.m_tiles * total_nt;
+  UB_REQUIRE(grid > 0 && grid < (1ll << 30), "wgrad: grid %lld", grid);
+  wgrad_kernel<<<static_cast<unsigned>(grid), kThreads, smem, stream>>>(p, z, x0, x1);
+  UB_CHECK_CUDA(cudaGetLastError());
+  return UB_OK;
+}
+
+int splitk_reduce_launch(const float* ws, long long split_stride, int splits, float* out, long long n,
+                         cudaStream_t stream) {
+  if (n <= 0) return UB_OK;
+  const int threads = 256;
+  const long long blocks = (n + threads - 1) / threads;
+  splitk_reduce_kernel<<<static_cast<unsigned>(blocks), threads, 0, stream>>>(ws, split_stride, splits, out, n);
+  UB_CHECK_CUDA(cudaGetLastError());
+  return UB_OK;
+}
+
+}  // namespace ub

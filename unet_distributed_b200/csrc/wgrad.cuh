@@ -1,0 +1,43 @@
+// Weight-gradient tile engine: dW[tap][ci][co] = sum over pixels  dZ[pixel][co] * X[pixel + tap][ci].
+//
+// The reduction (GEMM K) dimension is the pixel dimension, which is the *slow* dimension of both NHWC operands, so
+// both are fed to tcgen05.mma as MN-major tiles: a TMA box of KP pixels x 64 (or 32) channels lands in shared memory
+// exactly in the canonical MN-major swizzled layout. The tap shift of X is a TMA coordinate shift with zero fill.
+// One CTA owns one (tap, 128 output channels, <=128 input channels, pixel range) and accumulates in TMEM; pixel
+// ranges (split-K) go to separate slices of the output that a second kernel sums in a fixed order (deterministic).
+#pragma once
+#include <cstdint>
+#include <cuda.h>
+
+namespace ub {
+
+struct WgradParams {
+  int N, H, W;              // pixel grid walked by the reduction (conv: activation grid; tconv: the coarse grid)
+  int TN, TH, TW;           // pixel box per K block, TN*TH*TW == 64
+  int blocks_n, blocks_h, blocks_w;
+  int splits;               // pixel-range splits; blocks_per_split = ceil(total/splits)
+  int taps_r, taps_s, pad;
+  int z_mode;               // 0: dZ is a plain 4-D map (c,w,h,n); 1: 5-D tconv view (o,b,j,a,n*h), tap = (a,b)
+  int x_shift;              // 1: X box is shifted by the tap (conv); 0: not shifted (tconv)
+  int z_C;                  // channels of dZ (GEMM M extent)
+  int z_atom;               // 64 (SWIZZLE_128B) or 32 (SWIZZLE_64B)
+  int m_tiles;              // ceil(z_C / 128)
+  int num_src;              // X sources (concat inputs)
+  int x_C[2];               // channels per source
+  int x_atom[2];            // 64 or 32
+  int x_block_n[2];         // GEMM N per tile for that source: min(x_C, 128)
+  int x_ntiles[2];
+  int x_col_off[2];         // column offset of the source in the output (channel offset in the concat)
+  int stages;
+  float* out;
+  long long out_split_stride, out_tap_stride, out_m_stride, out_n_stride;
+};
+
+int wgrad_launch(const WgradParams& p, const CUtensorMap& z, const CUtensorMap& x0, const CUtensorMap& x1,
+                 cudaStream_t stream);
+
+// out[i] = sum_s ws[s*stride + i] (fixed order), i < n.
+int splitk_reduce_launch(const float* ws, long long split_stride, int splits, float* out, long long n,
+                         cudaStream_t stream);
+
+}  // namespace ub
