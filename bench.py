@@ -1,0 +1,325 @@
+#!/usr/bin/env python
+"""Benchmark of the UNet training hot path (BASELINE.json metric: train images/sec, 128x128 slices, bs128 per GPU).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--decoder upsampling|tconv] [--impl reference]
+
+One "step" = one optimizer step over one synthetic batch: forward, fused dice loss, backward, gradient all-reduce
+(N > 1), TF-style Adam, weight re-pack.  N > 1 is launched by torchrun (one rank per GPU, weak scaling: bs128 per GPU).
+Prints ONE JSON line on rank 0.  `--impl reference` times the CPU restatement of the reference (oracle/) on the host
+cores instead -- the reference itself (TensorFlow 1.4, Python 2.7) cannot be installed here."""
+from __future__ import annotations
+
+import argparse
+import ctypes
+import json
+import os
+import statistics
+import subprocess
+import sys
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+# algorithmic training GFLOP per image: fwd + dgrad + wgrad of every conv / tconv / 1x1
+TRAIN_GFLOP_PER_IMG = {("tconv", 128, 1): 18.0408, ("upsampling", 128, 1): 15.4235,
+                       ("tconv", 240, 4): 63.6236, ("upsampling", 240, 4): 54.4223}
+FALLBACK_PEAKS = {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0}
+
+
+def parse_args():
+    p = argparse.ArgumentParser()
+    p.add_argument("--gpus", type=int, default=1)
+    p.add_argument("--steps", type=int, default=30)
+    p.add_argument("--warmup", type=int, default=5)
+    p.add_argument("--impl", type=str, default="b200", choices=["b200", "reference"])
+    p.add_argument("--decoder", type=str, default="upsampling", choices=["upsampling", "tconv"],
+                   help="configs[1] of BASELINE.json (--use_upsampling) is the default single-GPU workload")
+    p.add_argument("--batch", type=int, default=128, help="per-GPU batch")
+    p.add_argument("--size", type=int, default=128)
+    p.add_argument("--channels", type=int, default=1)
+    p.add_argument("--no-graph", action="store_true", help="do not replay the step from a CUDA graph (1 GPU)")
+    p.add_argument("--no-cpu-baseline", action="store_true")
+    p.add_argument("--const_learningrate", type=int, default=1)
+    p.add_argument("--decay_steps", type=int, default=100)
+    p.add_argument("--lr_fraction", type=float, default=0.2)
+    return p.parse_args()
+
+
+def load_peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as f:
+            d = json.load(f)
+        d["_source"] = "measured (MEASURED_PEAKS.json)"
+        return d
+    d = dict(FALLBACK_PEAKS)
+    d["_source"] = "fallback (B200_PROFILING.md)"
+    return d
+
+
+class ClockSampler:
+    """nvidia-smi clocks and throttle reasons sampled every 200 ms during the timed region."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index=0):
+        self.proc, self.path = None, f"/tmp/unetb200_clocks_{os.getpid()}.csv"
+        self.gpu = gpu_index
+
+    def start(self):
+        try:
+            self.f = open(self.path, "w")
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "200", "-i", str(self.gpu)], stdout=self.f,
+                                         stderr=subprocess.DEVNULL)
+        except Exception:
+            self.proc = None
+
+    def stop(self):
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        if self.proc is None:
+            return out
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        self.f.close()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        try:
+            for line in open(self.path):
+                parts = [x.strip() for x in line.split(",")]
+                if len(parts) < 8:
+                    continue
+                try:
+                    sm.append(float(parts[1]))
+                    mx.append(float(parts[2]))
+                except ValueError:
+                    continue
+                for nm, v in zip(names, parts[4:8]):
+                    if v.lower().startswith("active"):
+                        reasons.add(nm)
+            os.remove(self.path)
+        except Exception:
+            pass
+        if sm:
+            out.update(sm_mhz=statistics.median(sm), sm_max_mhz=max(mx), reasons=sorted(reasons), samples=len(sm))
+        return out
+
+
+# ---------------------------------------------------------------------------------------------------- CPU arms
+def cpu_train_images_per_sec(decoder, size, channels, images_per_step, steps, warmup, threads):
+    """The oracle's training step (fwd + dice loss + bwd + TF-Adam, fp32, dropout on) on the host cores."""
+    import numpy as np
+    import torch
+    from oracle import unet_oracle as O
+    from unet_distributed_b200.synthetic import make_slices
+    torch.set_num_threads(threads)
+    ups = decoder == "upsampling"
+    w = O.init_weights(1234, ups, channels)
+    m, v = O.zeros_like_weights(w), O.zeros_like_weights(w)
+    imgs, msks = make_slices(images_per_step, size, size, channels)
+    t_total, step = 0.0, 0
+    for it in range(warmup + steps):
+        t0 = time.perf_counter()
+        res = O.loss_and_grads(w, imgs, msks, ups, None, 0.2, torch.float32)
+        O.adam_update(w, m, v, res["grads"], step)
+        step += 1
+        dt = time.perf_counter() - t0
+        if it >= warmup:
+            t_total += dt
+    return images_per_step * steps / t_total, t_total / steps * 1e3
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    cores = os.cpu_count() or 1
+    sample = 16
+    value, ms = cpu_train_images_per_sec(args.decoder, args.size, args.channels, sample, args.steps, args.warmup, cores)
+    line = {
+        "impl": "reference", "metric": "train images/sec", "value": value, "unit": "images/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": f"UNet {args.size}x{args.size}x{args.channels} {args.decoder} decoder, train step "
+                               f"(fwd+dice+bwd+Adam), bs{args.batch} per GPU in the GPU arm",
+                   "decoder": args.decoder, "image": [args.size, args.size, args.channels]},
+        "cpu_baseline": {"value": value, "unit": "images/s", "cores": cores, "kind": "port",
+                         "sample": f"{sample} images per step (of the bs{args.batch} workload), torch-CPU fp32 "
+                                   "restatement of the reference (oracle/unet_oracle.py); TF 1.4 is not installable"},
+        "e2e": {"value": value, "unit": "images/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(line), flush=True)
+    return 0
+
+
+# ---------------------------------------------------------------------------------------------------- GPU arm
+def run_b200(args):
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    from unet_distributed_b200 import _lib, parallel
+    from unet_distributed_b200.synthetic import make_slices
+    from unet_distributed_b200.trainer import Trainer
+
+    world, rank, local = parallel.init_from_env("nccl")
+    if world == 1:
+        torch.cuda.set_device(0)
+    dev = torch.device("cuda", torch.cuda.current_device())
+    N, S, C = args.batch, args.size, args.channels
+    ups = args.decoder == "upsampling"
+    tr = Trainer(N, S, S, C, 1, ups, dropout=0.2, learning_rate=0.0005,
+                 const_learningrate=bool(args.const_learningrate), lr_fraction=args.lr_fraction,
+                 decay_steps=args.decay_steps, use_cuda_graph=(world == 1 and not args.no_graph))
+    # synthetic batches: a few distinct ones per rank, rotated (inputs are far smaller than the per-step working set)
+    nb = 4
+    base_imgs, base_msks = make_slices(min(N, 64), S, S, C, seed=816 + rank)
+    reps = -(-N // base_imgs.shape[0])
+    h_batches = []
+    for b in range(nb):
+        im = np.roll(np.tile(base_imgs, (reps, 1, 1, 1))[:N], b, axis=0).copy()
+        mk = np.roll(np.tile(base_msks, (reps, 1, 1, 1))[:N], b, axis=0).copy()
+        h_batches.append((torch.from_numpy(im).pin_memory(), torch.from_numpy(mk).pin_memory()))
+    d_batches = [(a.to(dev), b.to(dev)) for a, b in h_batches]
+    L = _lib.lib()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- device-resident timing
+    for i in range(args.warmup):
+        tr.train_step(*d_batches[i % nb])
+    barrier()
+    sampler = ClockSampler(torch.cuda.current_device())
+    if rank == 0:
+        sampler.start()
+    launches0 = L.unetb200_launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(args.steps):
+        tr.train_step(*d_batches[i % nb])
+    e1.record()
+    barrier()
+    launches = L.unetb200_launch_count() - launches0
+    if tr.use_cuda_graph:   # replays bypass the library's counter: kernels per captured step x steps
+        launches = tr.graph_launches_per_step * args.steps
+    ms_total = torch.tensor([e0.elapsed_time(e1)], device=dev)
+    if world > 1:
+        dist.all_reduce(ms_total, op=dist.ReduceOp.MAX)
+    ms_step = float(ms_total.item()) / args.steps
+    clocks = sampler.stop() if rank == 0 else None
+    metrics_last = tr.plan.metrics.cpu().numpy()
+
+    # ---- end-to-end timing through the host-facing call (pinned host -> device copy and loss read-back per step)
+    for i in range(max(3, args.warmup // 2)):
+        tr.train_step_pinned(*h_batches[i % nb])
+    barrier()
+    e2, e3 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e2.record()
+    for i in range(args.steps):
+        tr.train_step_pinned(*h_batches[i % nb])
+    e3.record()
+    barrier()
+    ms_e2e = torch.tensor([e2.elapsed_time(e3)], device=dev)
+    if world > 1:
+        dist.all_reduce(ms_e2e, op=dist.ReduceOp.MAX)
+    ms_e2e_step = float(ms_e2e.item()) / args.steps
+
+    # ---- per-kernel-class timing for the roofline (events around every tile-engine launch; graph replay off)
+    roof = None
+    if rank == 0:
+        tr_prof = tr
+        if tr.use_cuda_graph:
+            tr.use_cuda_graph = False
+        for i in range(2):
+            tr_prof.train_step(*d_batches[i % nb])
+        torch.cuda.synchronize()
+        L.unetb200_profile_enable(1)
+        psteps = 3
+        for i in range(psteps):
+            tr_prof.train_step(*d_batches[i % nb])
+        ms = (ctypes.c_double * 3)()
+        fl = (ctypes.c_double * 3)()
+        by = (ctypes.c_double * 3)()
+        ln = (ctypes.c_longlong * 3)()
+        _lib.check(L.unetb200_profile_collect(ms, fl, by, ln), "profile_collect")
+        L.unetb200_profile_enable(0)
+        roof = {"igemm": (ms[0], fl[0], by[0], ln[0]), "wgrad": (ms[1], fl[1], by[1], ln[1]), "steps": psteps}
+    barrier()
+
+    if rank == 0:
+        peaks = load_peaks()
+        gb = N * world
+        value = gb / (ms_step * 1e-3)
+        e2e_value = gb / (ms_e2e_step * 1e-3)
+        key = (args.decoder, S, C)
+        gflop_img = TRAIN_GFLOP_PER_IMG.get(key)
+        ig_ms, ig_fl, ig_by, ig_n = roof["igemm"]
+        wg_ms, wg_fl, wg_by, wg_n = roof["wgrad"]
+        peak_tf = float(peaks.get("bf16_tflops_sustained", FALLBACK_PEAKS["bf16_tflops_sustained"]))
+        achieved = ig_fl / (ig_ms * 1e-3) / 1e12 if ig_ms > 0 else 0.0
+        traffic = None
+        tpath = os.path.join(ROOT, "profiles", "traffic.json")
+        if os.path.exists(tpath):
+            try:
+                traffic = json.load(open(tpath)).get("igemm_dram_bytes_per_launch")
+            except Exception:
+                traffic = None
+        line = {
+            "metric": "train images/sec", "value": value, "unit": "images/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+            "config": {
+                "workload": f"UNet {S}x{S}x{C} {args.decoder} decoder (BASELINE configs[{1 if ups else 0}] shape), "
+                            f"bs{N} per GPU, Adam, dropout 0.2, train step fwd+dice+bwd+allreduce+Adam",
+                "decoder": args.decoder, "per_gpu_batch": N, "global_batch": gb, "image": [S, S, C],
+                "parallelism": f"dp{world}", "cuda_graph": bool(world == 1 and not args.no_graph),
+                "l2": "no explicit flush: one step touches >2.5 GB of activations and gradients (L2 is 126 MB); "
+                      "input batches rotate",
+                "const_learningrate": bool(args.const_learningrate)},
+            "clocks": clocks,
+            "e2e": {"value": e2e_value, "unit": "images/s", "ms_per_step": ms_e2e_step,
+                    "h2d_bytes_per_step": tr.h2d_bytes_per_step(), "d2h_bytes_per_step": tr.d2h_bytes_per_step()},
+            "gpu_launches": int(launches),
+            "roofline": {
+                "kernel": "igemm_kernel (3x3 conv / transposed conv forward + dgrad, tcgen05 implicit GEMM)",
+                "bound": "tensor", "achieved": achieved, "peak": peak_tf, "unit": "TFLOP/s",
+                "frac": achieved / peak_tf if peak_tf else None, "traffic": traffic,
+                "peak_source": "bf16_tflops_sustained, " + peaks["_source"],
+                "launches_per_step": ig_n / roof["steps"], "ms_per_step": ig_ms / roof["steps"],
+                "wgrad": {"achieved": (wg_fl / (wg_ms * 1e-3) / 1e12 if wg_ms > 0 else 0.0), "unit": "TFLOP/s",
+                          "launches_per_step": wg_n / roof["steps"], "ms_per_step": wg_ms / roof["steps"]},
+                "whole_step": ({"achieved": value * gflop_img / 1e3 / world, "unit": "TFLOP/s per GPU",
+                                "frac": value * gflop_img / 1e3 / world / peak_tf} if gflop_img else None)},
+            "loss": float(metrics_last[0]), "dice": float(metrics_last[1]),
+        }
+        if world == 1 and not args.no_cpu_baseline:
+            cores = os.cpu_count() or 1
+            cpu_v, cpu_ms = cpu_train_images_per_sec(args.decoder, S, C, 32, 3, 1, cores)
+            line["cpu_baseline"] = {
+                "value": cpu_v, "unit": "images/s", "cores": cores, "kind": "port",
+                "sample": "3 timed steps of 32 images (of the bs128 workload) after 1 warm-up, torch-CPU fp32 "
+                          "restatement of the reference's train step (oracle/unet_oracle.py)"}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    return 0
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        return run_reference(args)
+    return run_b200(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -89,7 +89,15 @@ int unetb200_head_fwd(const void* x, const float* w, const float* b, const float
                       void* ws, long long pixels, int C, int n_cl, void* stream);
 /* out4 = {dice_coef_loss, dice_coef, sensitivity, specificity} (model.py:13-21, 4-10, 133-137, 139-143). */
 int unetb200_dice_finalize(const float* sums, float smooth, float* out4, void* stream);
-/* Gradient of dice_coef_loss through the sigmoid and the 1x1 conv, times grad_scale; dx is masked by x > 0. */
+/* Stand-alone forms of the same reductions on arbitrary fp32 tensors of n elements, for the eager call pattern
+ * `dice_coef_loss(msks, preds)` of test_dist.py:211-215. which: 0 loss, 1 dice, 2 sensitivity, 3 specificity;
+ * dp = (*upstream or 1) * d(metric)/d(y_pred). */
+size_t unetb200_dice_sums_ws_bytes(void);
+int unetb200_dice_sums(const float* y_true, const float* y_pred, long long n, float* sums, void* ws, void* stream);
+int unetb200_dice_grad(const float* y_true, const float* sums, float smooth, int which, const float* upstream,
+                       float* dp, long long n, void* stream);
+/* Gradient of dice_coef_loss through the sigmoid and the 1x1 conv, times grad_scale; dx is masked by x > 0.
+ * With sums == NULL, y_true is taken to be an explicit dL/dp instead of the labels (generic autograd). */
 int unetb200_head_bwd(const void* x, const float* w, const float* y_true, const float* p, const float* sums,
                       float smooth, float grad_scale, void* dx, float* dw, float* db, void* ws, long long pixels,
                       int C, int n_cl, void* stream);
@@ -109,8 +117,45 @@ int unetb200_step_increment(long long* step, void* stream);
 /* keep[i] in {0,1}: the exact dropout decisions the conv epilogue makes for output element i (n multiple of 8). */
 int unetb200_dropout_mask(unsigned char* keep, long long n, float keep_prob, uint64_t seed, uint32_t stream_id,
                           void* stream);
+/* Measurement hooks (no reference counterpart; bench.py uses them). launch_count: kernels this library has launched
+ * in this process. With profiling enabled every tile-engine launch is bracketed by CUDA events on its stream;
+ * profile_collect synchronises and returns, per kind {0 igemm (conv/tconv fwd+dgrad), 1 wgrad, 2 other}, the summed
+ * milliseconds, algorithmic FLOPs, minimum HBM bytes and launch count (arrays of 3), then clears the records. */
+long long unetb200_launch_count(void);
+int unetb200_profile_enable(int on);
+int unetb200_profile_collect(double* ms, double* flops, double* bytes, long long* launches);
 int unetb200_cast_f32_to_bf16(const float* x, void* y, long long n, void* stream);
 int unetb200_cast_bf16_to_f32(const void* x, float* y, long long n, void* stream);
+
+/* ---- whole-network plan: the graph define_model builds (model.py:36-130) as one launch sequence ---------------- */
+/* The plan allocates nothing on the device: query unetb200_plan_arena_bytes(), allocate, then bind the arena and the
+ * flat fp32 parameter / gradient buffers. Variables sit in the flat buffers in TF creation order with TF names
+ * ("conv1a/kernel", "transConv6/bias", "Mask/kernel", ...) and TF layouts; each starts on a 4-float boundary. */
+typedef struct unetb200_plan unetb200_plan;
+int unetb200_plan_create(unetb200_plan** out, int N, int H, int W, int in_channels, int n_cl_out, int use_upsampling,
+                         float dropout);
+void unetb200_plan_destroy(unetb200_plan* plan);
+long long unetb200_plan_num_params(const unetb200_plan* plan); /* floats in the flat buffers, padding included */
+int unetb200_plan_num_variables(const unetb200_plan* plan);
+int unetb200_plan_variable(const unetb200_plan* plan, int i, char* name, int name_cap, long long* offset, int* rank,
+                           int* shape4);
+size_t unetb200_plan_arena_bytes(const unetb200_plan* plan);
+int unetb200_plan_bind(unetb200_plan* plan, void* arena, float* params, float* grads);
+/* Arena offset and shape of an activation ("a1".."a9", "c1".."c9", "p1".."p4", "u6".."u9"), its gradient ("g"+name),
+ * "preds" (fp32) or "metrics" (fp32 {loss, dice, sensitivity, specificity}). */
+int unetb200_plan_tensor(const unetb200_plan* plan, const char* name, long long* offset, int* n, int* h, int* w,
+                         int* c, int* elem_bytes);
+int unetb200_plan_pack_weights(unetb200_plan* plan, void* stream);
+/* Forward (model.py:45-120) and, when msks != NULL, the dice metrics. imgs fp32 [N,H,W,Cin], msks fp32 [N,H,W,n_cl].
+ * Dropout stream seed = seed + *seed_add (seed_add: optional device int64, e.g. the global step). */
+int unetb200_plan_forward(unetb200_plan* plan, const float* imgs, const float* msks, uint64_t seed,
+                          const long long* seed_add, void* stream);
+/* Backward in three segments (0: head + decoder, 1: conv5a/b, 2: encoder); gradients land in the bound flat buffer,
+ * multiplied by grad_scale. The loss is dice_coef_loss(msks, preds) of the last forward, unless dpreds (fp32
+ * [N,H,W,n_cl], an explicit dL/dpreds) is given. unetb200_plan_bucket gives the flat range complete after a segment. */
+int unetb200_plan_backward(unetb200_plan* plan, const float* imgs, const float* msks, const float* dpreds,
+                           float grad_scale, int segment, void* stream);
+int unetb200_plan_bucket(const unetb200_plan* plan, int segment, long long* begin, long long* end);
 
 #ifdef __cplusplus
 }

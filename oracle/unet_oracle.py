@@ -132,16 +132,35 @@ class Net:
             t = t + (_bf16_round(t) - t).detach()              # activations stored in bf16
         return t
 
-    def forward(self, imgs_nhwc, dropout_masks=None, dropout=0.2, keep_intermediates=False):
+    def forward(self, imgs_nhwc, dropout_masks=None, dropout=0.2, keep_intermediates=False, forced_acts=None):
         """imgs_nhwc: [N,H,W,C] array/tensor.  dropout_masks: {'conv3a': keep[N,H,W,C], 'conv4a': ...} with 0/1
-        entries (None and dropout>0 draws fresh masks; dropout == 0 disables).  Returns sigmoid map [N,H,W,n_cl]."""
+        entries (None and dropout>0 draws fresh masks; dropout == 0 disables).  Returns sigmoid map [N,H,W,n_cl].
+
+        forced_acts (name -> NHWC array of the layer's stored output, e.g. read back from the GPU) turns the pass into
+        the reference's backward EVALUATED AT A GIVEN FORWARD STATE: every layer output takes the forced value, ReLU /
+        dropout gates are the forced tensor's non-zero pattern and max-pool routing follows the forced values, while
+        gradients flow through the oracle's own fp32 operators.  (Gradients of a ReLU network are discontinuous in
+        the forward state -- a gate that flips re-routes a whole gradient element -- so backward parity between two
+        precisions is only meaningful at a common forward state; the forward itself is compared separately.)"""
         x = torch.as_tensor(np.asarray(imgs_nhwc), dtype=self.dtype).permute(0, 3, 1, 2)
         acts = OrderedDict()
 
+        def forced(name):
+            return torch.as_tensor(np.asarray(forced_acts[name]), dtype=self.dtype).permute(0, 3, 1, 2)
+
         def conv(name, t):
             k, b = self._w(name)
+            dropped = name in ("conv3a", "conv4a") and dropout > 0
+            if forced_acts is not None:
+                yf = forced(name)
+                y = (_conv3x3(t, k, b)) * (yf > 0).to(self.dtype)
+                if dropped:
+                    y = y / (1.0 - dropout)
+                y = y + (yf - y).detach()
+                acts[name] = y
+                return y
             y = F.relu(_conv3x3(t, k, b))
-            if name in ("conv3a", "conv4a") and dropout > 0:   # model.py:60,66 (learning phase forced, model.py:40)
+            if dropped:                                        # model.py:60,66 (learning phase forced, model.py:40)
                 if dropout_masks is not None:
                     keep = torch.as_tensor(np.asarray(dropout_masks[name]), dtype=self.dtype).permute(0, 3, 1, 2)
                 else:
@@ -156,7 +175,11 @@ class Net:
                 u = F.interpolate(t, scale_factor=2, mode="nearest")          # UpSampling2D (model.py:76)
             else:
                 k, b = self._w(name_t)
-                u = self._act(_tconv2x2(t, k, b))
+                u = _tconv2x2(t, k, b)
+                if forced_acts is not None:
+                    u = u + (forced(name_t) - u).detach()
+                else:
+                    u = self._act(u)
                 acts[name_t] = u
             return torch.cat([u, skip], dim=1)                                # up first, skip second (model.py:76,79)
 
@@ -206,11 +229,12 @@ def specificity(y_true, y_pred, smooth=1.0):
 
 
 def loss_and_grads(weights, imgs, msks, use_upsampling=False, dropout_masks=None, dropout=0.2,
-                   dtype=torch.float32, emulate_bf16=False, keep_act_grads=False):
+                   dtype=torch.float32, emulate_bf16=False, keep_act_grads=False, forced_acts=None):
     """One forward/backward (test_dist.py:204-212,246-248).  Returns dict with loss, dice, preds, grads (TF layouts,
-    numpy) and optionally the activations and their gradients keyed by layer name (NHWC numpy)."""
+    numpy) and optionally the activations and their gradients keyed by layer name (NHWC numpy).
+    forced_acts: see Net.forward (backward evaluated at a given forward state)."""
     net = Net(weights, use_upsampling, dtype, emulate_bf16)
-    preds = net.forward(imgs, dropout_masks, dropout, keep_intermediates=True)
+    preds = net.forward(imgs, dropout_masks, dropout, keep_intermediates=True, forced_acts=forced_acts)
     y = torch.as_tensor(np.asarray(msks), dtype=dtype)
     if keep_act_grads:
         for a in net.acts.values():

@@ -31,7 +31,7 @@ int unetb200_conv3x3_fwd(const void* x0, int C0, const void* x1, int C1, const v
                          void* y, int N, int H, int W, int Cout, int relu, float drop_keep, uint64_t drop_seed,
                          uint32_t drop_stream, void* stream) {
   ConvSrc s0{x0, C0}, s1{x1, x1 ? C1 : 0};
-  DropoutCfg d{drop_keep <= 0.0f ? 1.0f : drop_keep, drop_seed, drop_stream};
+  DropoutCfg d{drop_keep <= 0.0f ? 1.0f : drop_keep, drop_seed, drop_stream, nullptr};
   return conv3x3_fwd(s0, s1, w_packed, bias, y, N, H, W, Cout, relu, d, S(stream));
 }
 

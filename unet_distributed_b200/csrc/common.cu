@@ -1,8 +1,11 @@
 #include "common.h"
 
+#include <atomic>
 #include <cstdarg>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
+#include <vector>
 
 namespace ub {
 
@@ -71,6 +74,82 @@ int make_tmap_bf16(CUtensorMap* out, const void* base, int rank, const uint64_t*
   }
   return UB_OK;
 }
+
+// ------------------------------------------------------------------------------------------------ launch accounting
+namespace {
+struct ProfRec {
+  cudaEvent_t e0, e1;
+  int kind;
+  double flops, bytes;
+};
+std::atomic<long long> g_launches{0};
+bool g_prof_on = false;
+std::vector<ProfRec> g_prof;
+std::mutex g_prof_mu;
+}  // namespace
+
+void note_api_call(const char* expr_text) {
+  // "cudaGetLastError()" is checked exactly once after every kernel launch in this library
+  if (expr_text[4] == 'G' && expr_text[7] == 'L' && std::strcmp(expr_text, "cudaGetLastError()") == 0) {
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+  }
+}
+long long launch_count() { return g_launches.load(std::memory_order_relaxed); }
+bool profiling_enabled() { return g_prof_on; }
+
+void prof_begin(int kind, double flops, double bytes, cudaStream_t stream) {
+  if (!g_prof_on) return;
+  std::lock_guard<std::mutex> lk(g_prof_mu);
+  ProfRec r;
+  r.kind = kind;
+  r.flops = flops;
+  r.bytes = bytes;
+  cudaEventCreate(&r.e0);
+  cudaEventCreate(&r.e1);
+  cudaEventRecord(r.e0, stream);
+  g_prof.push_back(r);
+}
+void prof_end(cudaStream_t stream) {
+  if (!g_prof_on) return;
+  std::lock_guard<std::mutex> lk(g_prof_mu);
+  if (!g_prof.empty()) cudaEventRecord(g_prof.back().e1, stream);
+}
+
+extern "C" {
+long long unetb200_launch_count(void) { return launch_count(); }
+int unetb200_profile_enable(int on) {
+  std::lock_guard<std::mutex> lk(g_prof_mu);
+  g_prof_on = on != 0;
+  return UB_OK;
+}
+// Synchronises, then sums per kind: ms[k], flops[k], bytes[k], launches[k] (arrays of 3); clears the records.
+int unetb200_profile_collect(double* ms, double* flops, double* bytes, long long* launches) {
+  std::lock_guard<std::mutex> lk(g_prof_mu);
+  cudaError_t e = cudaDeviceSynchronize();
+  if (e != cudaSuccess) {
+    set_error("profile_collect: %s", cudaGetErrorString(e));
+    return UB_ERR_CUDA;
+  }
+  for (int k = 0; k < UB_NUM_KINDS; ++k) { ms[k] = 0; flops[k] = 0; bytes[k] = 0; launches[k] = 0; }
+  FILE* csv = nullptr;
+  if (const char* path = getenv("UNETB200_PROFILE_CSV")) csv = fopen(path, "a");
+  if (csv) fprintf(csv, "kind,gflop,mbytes,ms,tflops\n");
+  for (auto& r : g_prof) {
+    float t = 0.f;
+    cudaEventElapsedTime(&t, r.e0, r.e1);
+    if (csv) fprintf(csv, "%d,%.4f,%.3f,%.5f,%.2f\n", r.kind, r.flops * 1e-9, r.bytes * 1e-6, t, r.flops / (t * 1e-3) * 1e-12);
+    ms[r.kind] += t;
+    flops[r.kind] += r.flops;
+    bytes[r.kind] += r.bytes;
+    launches[r.kind] += 1;
+    cudaEventDestroy(r.e0);
+    cudaEventDestroy(r.e1);
+  }
+  if (csv) fclose(csv);
+  g_prof.clear();
+  return UB_OK;
+}
+}  // extern "C"
 
 int device_sm_count() {
   static int cached[64] = {0};

@@ -19,8 +19,18 @@ enum : int {
 void set_error(const char* fmt, ...);
 const char* last_error();
 
+// Launch accounting and optional per-launch timing (bench.py's roofline numbers come from here).
+enum : int { UB_KIND_IGEMM = 0, UB_KIND_WGRAD = 1, UB_KIND_OTHER = 2, UB_NUM_KINDS = 3 };
+void note_api_call(const char* expr_text);  // counts kernel launches: every launch site checks cudaGetLastError()
+long long launch_count();
+bool profiling_enabled();
+// Bracket one launch with events on `stream` when profiling is on (no-ops otherwise).
+void prof_begin(int kind, double flops, double bytes, cudaStream_t stream);
+void prof_end(cudaStream_t stream);
+
 #define UB_CHECK_CUDA(expr)                                                                        \
   do {                                                                                             \
+    ::ub::note_api_call(#expr);                                                                    \
     cudaError_t _e = (expr);                                                                       \
     if (_e != cudaSuccess) {                                                                       \
       ::ub::set_error("%s:%d: %s -> %s", __FILE__, __LINE__, #expr, cudaGetErrorString(_e));       \

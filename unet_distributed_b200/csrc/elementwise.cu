@@ -73,12 +73,12 @@ __global__ void conv_first_fwd_kernel(const float* __restrict__ x, const float* 
 // Each thread owns one 8-channel group of dz and walks pixels with a stride; partial sums go block -> ws -> final.
 __global__ void conv_first_wgrad_kernel(const float* __restrict__ x, const uint4* __restrict__ dz,
                                         float* __restrict__ ws, int N, int H, int W, int Cin, int Cout) {
-  extern __shared__ float red[];  // [9*Cin*Cout + Cout]
+  // every warp owns one row of partial sums in ws (no atomics: the reduction order is fixed, results are
+  // bit-reproducible); rows are summed by rows_reduce_kernel
   const int nout = 9 * Cin * Cout + Cout;
-  for (int i = threadIdx.x; i < nout; i += blockDim.x) red[i] = 0.0f;
-  __syncthreads();
   const int groups = Cout / 8;
   const int g = threadIdx.x % groups;
+  float* wout = ws + (static_cast<long long>(blockIdx.x) * (blockDim.x >> 5) + (threadIdx.x >> 5)) * nout;
   const long long total = static_cast<long long>(N) * H * W * groups;
   const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
   for (int ci = 0; ci < Cin; ++ci) {
@@ -121,7 +121,7 @@ __global__ void conv_first_wgrad_kernel(const float* __restrict__ x, const uint4
       for (int j = 0; j < 8; ++j) {
         float v = acc[t][j];
         for (int o = 16; o >= groups; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-        if ((threadIdx.x & 31) < groups) atomicAdd(&red[(t * Cin + ci) * Cout + g * 8 + j], v);
+        if ((threadIdx.x & 31) < groups) wout[(t * Cin + ci) * Cout + g * 8 + j] = v;
       }
     }
     if (ci == 0) {
@@ -129,23 +129,32 @@ __global__ void conv_first_wgrad_kernel(const float* __restrict__ x, const uint4
       for (int j = 0; j < 8; ++j) {
         float v = accb[j];
         for (int o = 16; o >= groups; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-        if ((threadIdx.x & 31) < groups) atomicAdd(&red[9 * Cin * Cout + g * 8 + j], v);
+        if ((threadIdx.x & 31) < groups) wout[9 * Cin * Cout + g * 8 + j] = v;
       }
     }
   }
-  __syncthreads();
-  for (int i = threadIdx.x; i < nout; i += blockDim.x) ws[static_cast<long long>(blockIdx.x) * nout + i] = red[i];
 }
 
-// out[i] = sum_b ws[b*n + i], fixed order; first n_a outputs to out_a, the rest to out_b.
-__global__ void block_partials_reduce_kernel(const float* __restrict__ ws, int nblocks, int n, float* __restrict__ out_a,
-                                             int n_a, float* __restrict__ out_b) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n) return;
+// out[i] = sum_r ws[r*n + i] over nrows rows in a fixed order (8 interleaved partial sums per column, then a fixed
+// 8-way sum); first n_a outputs go to out_a, the rest to out_b. Launch with 256 threads = 32 columns x 8 lanes.
+__global__ void rows_reduce_kernel(const float* __restrict__ ws, int nrows, int n, float* __restrict__ out_a, int n_a,
+                                   float* __restrict__ out_b) {
+  __shared__ float part[8][32];
+  const int c = threadIdx.x & 31, p = threadIdx.x >> 5;
+  const int i = blockIdx.x * 32 + c;
   float acc = 0.0f;
-  for (int b = 0; b < nblocks; ++b) acc += ws[static_cast<long long>(b) * n + i];
-  if (i < n_a) out_a[i] = acc;
-  else if (out_b) out_b[i - n_a] = acc;
+  if (i < n) {
+    for (int r = p; r < nrows; r += 8) acc += ws[static_cast<long long>(r) * n + i];
+  }
+  part[p][c] = acc;
+  __syncthreads();
+  if (p == 0 && i < n) {
+    float s = part[0][c];
+#pragma unroll
+    for (int q = 1; q < 8; ++q) s += part[q][c];
+    if (i < n_a) out_a[i] = s;
+    else if (out_b) out_b[i - n_a] = s;
+  }
 }
 
 // ------------------------------------------------------------------------------------------ pooling
@@ -298,7 +307,7 @@ __global__ void head_fwd_kernel(const uint4* __restrict__ x, const float* __rest
       for (int k = 0; k < n_cl; ++k) {
         const float z = acc[k] + sh[C * n_cl + k];
         const float p = 1.0f / (1.0f + expf(-z));
-        const float yt = __ldg(y_true + pix * n_cl + k);
+        const float yt = y_true ? __ldg(y_true + pix * n_cl + k) : 0.0f;
         p_out[pix * n_cl + k] = p;
         sI = fmaf(yt, p, sI);
         sY += yt;
@@ -330,15 +339,17 @@ __global__ void head_bwd_kernel(const uint4* __restrict__ x, const float* __rest
                                 const float* __restrict__ y_true, const float* __restrict__ p,
                                 const float* __restrict__ sums, float smooth, float grad_scale, uint4* __restrict__ dx,
                                 float* __restrict__ ws, long long P, int C, int n_cl) {
-  extern __shared__ float sh[];  // [C*n_cl] weights, then [C*n_cl + n_cl] block accumulators
+  extern __shared__ float sh[];  // [C*n_cl] weights
   const int subs = C / 8;
-  float* red = sh + C * n_cl;
   for (int i = threadIdx.x; i < C * n_cl; i += blockDim.x) sh[i] = w[i];
-  for (int i = threadIdx.x; i < C * n_cl + n_cl; i += blockDim.x) red[i] = 0.0f;
   __syncthreads();
-  const float I = sums[0], Sy = sums[1], Sp = sums[2];
-  const float ca = -2.0f / (2.0f * I + smooth);
-  const float cb = 1.0f / (Sy + Sp + smooth);
+  // sums == nullptr: y_true holds an explicit dL/dp (generic autograd path) instead of the labels
+  float ca = 1.0f, cb = 0.0f;
+  if (sums) {
+    const float I = sums[0], Sy = sums[1], Sp = sums[2];
+    ca = -2.0f / (2.0f * I + smooth);
+    cb = 1.0f / (Sy + Sp + smooth);
+  }
   const int sub = threadIdx.x % subs;
   const long long total = P * subs;
   const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
@@ -374,8 +385,10 @@ __global__ void head_bwd_kernel(const uint4* __restrict__ x, const float* __rest
     for (int j = 0; j < 8; ++j) o[j] = f[j] > 0.0f ? o[j] : 0.0f;
     dx[idx] = pack8(o);
   }
-  // reduce over lanes sharing `sub`, then one shared-memory atomic per warp and value
+  // reduce over lanes sharing `sub`; every warp then owns one row of partials in ws (fixed order, no atomics)
   const int lane = threadIdx.x & 31;
+  const int nout = C * n_cl + n_cl;
+  float* wout = ws + (static_cast<long long>(blockIdx.x) * (blockDim.x >> 5) + (threadIdx.x >> 5)) * nout;
 #pragma unroll
   for (int k = 0; k < kMaxCl; ++k) {
     if (k < n_cl) {
@@ -383,25 +396,22 @@ __global__ void head_bwd_kernel(const uint4* __restrict__ x, const float* __rest
       for (int j = 0; j < 8; ++j) {
         float v = adw[j][k];
         for (int o2 = 16; o2 >= subs; o2 >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o2);
-        if (lane < subs) atomicAdd(&red[(sub * 8 + j) * n_cl + k], v);
+        if (lane < subs) wout[(sub * 8 + j) * n_cl + k] = v;
       }
       float vb = adb[k];
       vb = warp_sum(vb);
-      if (lane == 0) atomicAdd(&red[C * n_cl + k], vb);
+      if (lane == 0) wout[C * n_cl + k] = vb;
     }
   }
-  __syncthreads();
-  const int nout = C * n_cl + n_cl;
-  for (int i = threadIdx.x; i < nout; i += blockDim.x) ws[static_cast<long long>(blockIdx.x) * nout + i] = red[i];
 }
 
 // ------------------------------------------------------------------------------------------ bias gradient (column sums)
 __global__ void colsum_kernel(const uint4* __restrict__ dz, float* __restrict__ ws, long long P, int C) {
-  extern __shared__ float red[];  // [C]
-  for (int i = threadIdx.x; i < C; i += blockDim.x) red[i] = 0.0f;
-  __syncthreads();
+  // rows of partial sums in ws: one per warp (C <= 256) or per run of C/8 consecutive threads (C > 256)
   const int groups = C / 8;
   const int g = threadIdx.x % groups;
+  const int span = groups > 32 ? groups : 32;
+  float* wout = ws + ((static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x) / span) * C;
   const long long total = P * groups;
   const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
   float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
@@ -416,10 +426,8 @@ __global__ void colsum_kernel(const uint4* __restrict__ dz, float* __restrict__ 
   for (int j = 0; j < 8; ++j) {
     float v = acc[j];
     for (int o = 16; o >= groups; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-    if (groups >= 32 || lane < groups) atomicAdd(&red[g * 8 + j], v);
+    if (groups >= 32 || lane < groups) wout[g * 8 + j] = v;
   }
-  __syncthreads();
-  for (int i = threadIdx.x; i < C; i += blockDim.x) ws[static_cast<long long>(blockIdx.x) * C + i] = red[i];
 }
 
 // ------------------------------------------------------------------------------------------ weight packing
@@ -564,7 +572,7 @@ int conv_first_fwd(const float* x, const float* w, const float* bias, void* y, i
 }
 
 long long conv_first_wgrad_ws_floats(int Cin, int Cout) {
-  return static_cast<long long>(kRedBlocks) * (9 * Cin * Cout + Cout);
+  return static_cast<long long>(kRedBlocks) * (kThreads / 32) * (9 * Cin * Cout + Cout);
 }
 
 int conv_first_wgrad(const float* x, const void* dz, float* dw, float* db, float* ws, int N, int H, int W, int Cin,
@@ -574,10 +582,9 @@ int conv_first_wgrad(const float* x, const void* dz, float* dw, float* db, float
   UB_REQUIRE(Cout % 8 == 0 && groups >= 1 && groups <= 8 && (groups & (groups - 1)) == 0,
              "conv_first_wgrad: Cout %d unsupported", Cout);
   const int nout = 9 * Cin * Cout + Cout;
-  conv_first_wgrad_kernel<<<kRedBlocks, kThreads, nout * sizeof(float), s>>>(x, reinterpret_cast<const uint4*>(dz), ws,
-                                                                             N, H, W, Cin, Cout);
+  conv_first_wgrad_kernel<<<kRedBlocks, kThreads, 0, s>>>(x, reinterpret_cast<const uint4*>(dz), ws, N, H, W, Cin, Cout);
   UB_CHECK_CUDA(cudaGetLastError());
-  block_partials_reduce_kernel<<<grid_for(nout, 128), 128, 0, s>>>(ws, kRedBlocks, nout, dw, 9 * Cin * Cout, db);
+  rows_reduce_kernel<<<grid_for(nout, 32), 256, 0, s>>>(ws, kRedBlocks * (kThreads / 32), nout, dw, 9 * Cin * Cout, db);
   UB_CHECK_CUDA(cudaGetLastError());
   return UB_OK;
 }
@@ -623,7 +630,7 @@ int upsample2x2_bwd(const void* dy, const void* x, void* dx, int N, int H, int W
 
 long long head_ws_floats(long long, int C, int n_cl) {
   const long long fwd = 3ll * kRedBlocks;
-  const long long bwd = static_cast<long long>(kRedBlocks) * (C * n_cl + n_cl);
+  const long long bwd = static_cast<long long>(kRedBlocks) * (kThreads / 32) * (C * n_cl + n_cl);
   return fwd > bwd ? fwd : bwd;
 }
 
@@ -636,7 +643,7 @@ int head_fwd(const void* x, const float* w, const float* b, const float* y_true,
   head_fwd_kernel<<<kRedBlocks, kThreads, smem, s>>>(reinterpret_cast<const uint4*>(x), w, b, y_true, p_out, ws, P, C,
                                                      n_cl);
   UB_CHECK_CUDA(cudaGetLastError());
-  block_partials_reduce_kernel<<<1, 32, 0, s>>>(ws, kRedBlocks, 3, sums, 3, nullptr);
+  rows_reduce_kernel<<<1, 256, 0, s>>>(ws, kRedBlocks, 3, sums, 3, nullptr);
   UB_CHECK_CUDA(cudaGetLastError());
   return UB_OK;
 }
@@ -653,23 +660,25 @@ int head_bwd(const void* x, const float* w, const float* y_true, const float* p,
   const int subs = C / 8;
   UB_REQUIRE(C % 8 == 0 && subs >= 1 && subs <= 32 && (subs & (subs - 1)) == 0, "head_bwd: C %d unsupported", C);
   const int nout = C * n_cl + n_cl;
-  const size_t smem = (C * n_cl + nout) * sizeof(float);
+  const size_t smem = (C * n_cl) * sizeof(float);
   head_bwd_kernel<<<kRedBlocks, kThreads, smem, s>>>(reinterpret_cast<const uint4*>(x), w, y_true, p, sums, smooth,
                                                      grad_scale, reinterpret_cast<uint4*>(dx), ws, P, C, n_cl);
   UB_CHECK_CUDA(cudaGetLastError());
-  block_partials_reduce_kernel<<<grid_for(nout, 128), 128, 0, s>>>(ws, kRedBlocks, nout, dw, C * n_cl, db);
+  rows_reduce_kernel<<<grid_for(nout, 32), 256, 0, s>>>(ws, kRedBlocks * (kThreads / 32), nout, dw, C * n_cl, db);
   UB_CHECK_CUDA(cudaGetLastError());
   return UB_OK;
 }
 
-long long colsum_ws_floats(int C) { return static_cast<long long>(kRedBlocks) * C; }
+long long colsum_ws_floats(int C) { return static_cast<long long>(kRedBlocks) * (kThreads / 32) * C; }
 
 int colsum_bf16(const void* dz, float* db, float* ws, long long P, int C, cudaStream_t s) {
   int rc = check_groups(C, "colsum_bf16");
   if (rc) return rc;
-  colsum_kernel<<<kRedBlocks, kThreads, C * sizeof(float), s>>>(reinterpret_cast<const uint4*>(dz), ws, P, C);
+  const int groups = C / 8;
+  const int rows = kRedBlocks * (kThreads / (groups > 32 ? groups : 32));
+  colsum_kernel<<<kRedBlocks, kThreads, 0, s>>>(reinterpret_cast<const uint4*>(dz), ws, P, C);
   UB_CHECK_CUDA(cudaGetLastError());
-  block_partials_reduce_kernel<<<grid_for(C, 128), 128, 0, s>>>(ws, kRedBlocks, C, db, C, nullptr);
+  rows_reduce_kernel<<<grid_for(C, 32), 256, 0, s>>>(ws, rows, C, db, C, nullptr);
   UB_CHECK_CUDA(cudaGetLastError());
   return UB_OK;
 }

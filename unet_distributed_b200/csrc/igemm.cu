@@ -195,9 +195,11 @@ igemm_kernel(const __grid_constant__ IgemmParams p, const __grid_constant__ CUte
           }
           if (e.drop_keep < 1.0f) {
             const float inv = 1.0f / e.drop_keep;
+            const unsigned long long seed =
+                e.drop_seed + (e.drop_seed_add ? static_cast<unsigned long long>(__ldg(e.drop_seed_add)) : 0ull);
 #pragma unroll
             for (int g = 0; g < 2; ++g) {
-              const uint32_t bits = dropout_keep_bits8(e.drop_seed, e.drop_stream, (drop_elem0 + c) / 8 + g, e.drop_keep);
+              const uint32_t bits = dropout_keep_bits8(seed, e.drop_stream, (drop_elem0 + c) / 8 + g, e.drop_keep);
 #pragma unroll
               for (int i = 0; i < 8; ++i) v[8 * g + i] = ((bits >> i) & 1u) ? v[8 * g + i] * inv : 0.0f;
             }
@@ -264,8 +266,17 @@ int igemm_launch(const IgemmParams& p, const CUtensorMap& a0, const CUtensorMap&
   UB_REQUIRE(num_tiles > 0, "igemm: empty problem");
   int grid = device_sm_count();
   if (grid > num_tiles) grid = num_tiles;
+  if (profiling_enabled()) {
+    const double pixels = static_cast<double>(p.N) * p.H * p.W;
+    const double kdim = static_cast<double>(p.taps_r) * p.taps_s * p.kc *
+                        (p.src_kblocks[0] + (p.num_src > 1 ? p.src_kblocks[1] : 0));
+    const double ncols = static_cast<double>(p.n_tiles) * p.block_n;
+    prof_begin(UB_KIND_IGEMM, 2.0 * pixels * kdim * ncols,
+               2.0 * pixels * (kdim / (p.taps_r * p.taps_s) + ncols), stream);
+  }
   igemm_kernel<<<grid, kThreads, smem, stream>>>(p, a0, a1, b);
   UB_CHECK_CUDA(cudaGetLastError());
+  prof_end(stream);
   return UB_OK;
 }
 

@@ -30,6 +30,7 @@ struct IgemmEpilogue {
   int d2s_cout;        // >0: depth-to-space store; GEMM column = (a*2+b)*d2s_cout + o
   float drop_keep;     // <1: dropout with keep probability drop_keep (scaled by 1/keep)
   unsigned long long drop_seed;
+  const long long* drop_seed_add;  // optional device counter added to drop_seed (graph-replayable per-step masks)
   unsigned int drop_stream;
 };
 

@@ -18,11 +18,26 @@ struct Box {
 };
 
 // 128-pixel output tile (igemm) or 64-pixel reduction block (wgrad) for an NHWC grid.
-Box pick_box(int pixels, int W) {
+// Small grids pack several images into one box. `image_aligned` (needed by the 5-D transposed-conv view, whose
+// last dimension is the merged n*H+i index) forbids boxes that straddle images unless they cover whole images.
+Box pick_box(int pixels, int H, int W, bool image_aligned = false) {
   Box b;
-  b.TW = W >= 16 ? 16 : 8;
-  b.TH = pixels == 128 ? 8 : (b.TW == 16 ? 4 : 8);
-  b.TN = pixels / (b.TW * b.TH);
+  b.TW = W > 8 ? 16 : 8;
+  const int max_th = pixels / b.TW;
+  if (H >= max_th) {
+    b.TH = max_th;
+    b.TN = 1;
+  } else {
+    int th = 1;
+    while (th < H) th <<= 1;
+    b.TH = th;
+    b.TN = max_th / th;
+    if (image_aligned && b.TN > 1 && b.TH != H) {
+      b.TW = 16;
+      b.TH = pixels / 16;
+      b.TN = 1;
+    }
+  }
   return b;
 }
 
@@ -91,7 +106,7 @@ int conv3x3_fwd(ConvSrc x0, ConvSrc x1, const void* w_packed, const float* bias,
   UB_REQUIRE(block_n != 0, "conv3x3_fwd: Cout %d must be a multiple of 32", Cout);
   IgemmParams p;
   std::memset(&p, 0, sizeof(p));
-  const Box b = pick_box(128, W);
+  const Box b = pick_box(128, H, W);
   fill_grid(p, N, H, W, b);
   p.n_tiles = Cout / block_n;
   p.block_n = block_n;
@@ -112,6 +127,7 @@ int conv3x3_fwd(ConvSrc x0, ConvSrc x1, const void* w_packed, const float* bias,
   p.epi.drop_keep = drop.keep;
   p.epi.drop_seed = drop.seed;
   p.epi.drop_stream = drop.stream;
+  p.epi.drop_seed_add = drop.seed_add;
   CUtensorMap a0, a1, bm;
   int rc = nhwc_map(&a0, x0.ptr, N, H, W, x0.C, kc, b);
   if (rc) return rc;
@@ -139,7 +155,7 @@ int conv3x3_dgrad(const void* dz, int Cout, const void* w_packed_d, DgradDst d0,
   UB_REQUIRE(block_n != 0, "conv3x3_dgrad: destination channels %d/%d must be multiples of 32", d0.C, C1);
   IgemmParams p;
   std::memset(&p, 0, sizeof(p));
-  const Box b = pick_box(128, W);
+  const Box b = pick_box(128, H, W);
   fill_grid(p, N, H, W, b);
   p.n_tiles = (d0.C + C1) / block_n;
   p.block_n = block_n;
@@ -176,7 +192,7 @@ struct WgradPlan {
 int plan_wgrad(WgradPlan& wp, int N, int H, int W, int taps_r, int taps_s, int pad, int z_C, int C0, int C1) {
   WgradParams& p = wp.p;
   std::memset(&p, 0, sizeof(p));
-  const Box b = pick_box(64, W);
+  const Box b = pick_box(64, H, W, taps_r == 2);
   p.N = N; p.H = H; p.W = W;
   p.TN = b.TN; p.TH = b.TH; p.TW = b.TW;
   p.blocks_n = cdiv(N, b.TN);
@@ -273,7 +289,7 @@ int tconv2x2_fwd(const void* x, int Cin, const void* w_packed, const float* bias
   UB_REQUIRE(block_n != 0, "tconv2x2_fwd: Cout %d must be a multiple of 32", Cout);
   IgemmParams p;
   std::memset(&p, 0, sizeof(p));
-  const Box b = pick_box(128, W);
+  const Box b = pick_box(128, H, W);
   fill_grid(p, N, H, W, b);
   p.n_tiles = 4 * Cout / block_n;
   p.block_n = block_n;
@@ -305,7 +321,7 @@ int tconv2x2_dgrad(const void* dy, int Cout, const void* w_packed_d, void* dx, i
   UB_REQUIRE(block_n != 0, "tconv2x2_dgrad: Cin %d must be a multiple of 32", Cin);
   IgemmParams p;
   std::memset(&p, 0, sizeof(p));
-  const Box b = pick_box(128, W);
+  const Box b = pick_box(128, H, W, true);
   UB_REQUIRE(b.TN == 1 || b.TH == H, "tconv2x2_dgrad: %dx%d grid needs an image-aligned tile", H, W);
   fill_grid(p, N, H, W, b);
   p.n_tiles = Cin / block_n;

@@ -15,6 +15,7 @@ struct DropoutCfg {
   float keep;  // 1.0 = off
   unsigned long long seed;
   unsigned int stream;
+  const long long* seed_add;  // optional device counter added to seed
 };
 
 // y = relu?(conv3x3_same([x0, x1]) + bias) (* dropout); w_packed = bf16 [Cout][9][C0+C1].

@@ -1,0 +1,469 @@
+// UNet step plan: the layer graph of model.py:36-130 as a fixed launch sequence over one caller-owned arena.
+// The plan owns no device memory: the caller asks for the arena size, allocates it (PyTorch does) and binds it together
+// with the flat fp32 parameter / gradient buffers whose layout (TensorFlow variable order and shapes) the plan reports.
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../include/unetb200.h"
+#include "common.h"
+#include "elementwise.cuh"
+#include "ops.cuh"
+
+using namespace ub;
+
+namespace {
+
+struct Var {
+  std::string name;
+  long long offset;
+  int rank;
+  int shape[4];
+  long long count() const {
+    long long n = 1;
+    for (int i = 0; i < rank; ++i) n *= shape[i];
+    return n;
+  }
+};
+
+struct Layer {
+  std::string name;
+  int kind;  // 0 conv3x3, 1 tconv, 2 mask
+  int cin, cout;
+  long long w_off, b_off;     // into the flat parameter buffer (floats)
+  size_t pk_fwd, pk_dgrad;    // arena offsets of the packed bf16 operands
+};
+
+constexpr size_t kAlign = 1024;
+
+}  // namespace
+
+struct unetb200_plan {
+  int N, H, W, Cin, ncl, ups;
+  float dropout;
+  std::vector<Var> vars;
+  std::vector<Layer> layers;
+  long long nparams = 0;
+  size_t arena_bytes = 0;
+  // layer indices
+  int enc_a[5], enc_b[5], dec_a[4], dec_b[4], tc[4], mask;
+  // arena offsets: activations and their gradients (bf16 NHWC)
+  size_t a[5], c[5], p[4], u[4], da[4], dc[4];
+  size_t g_a[5], g_c[5], g_p[4], g_u[4], g_da[4], g_dc[4];
+  size_t preds, sums, metrics, ws;
+  size_t ws_bytes = 0;
+  int ch[5];
+  int c4_out;      // channels of c[4] (conv5b)
+  int dc_out[4];   // channels of dc[L] (conv{9-L}b)
+  // bound buffers
+  uint8_t* arena = nullptr;
+  float* params = nullptr;
+  float* grads = nullptr;
+
+  size_t bump(size_t bytes) {
+    size_t off = arena_bytes;
+    arena_bytes += (bytes + kAlign - 1) / kAlign * kAlign;
+    return off;
+  }
+  int Hl(int L) const { return H >> L; }
+  int Wl(int L) const { return W >> L; }
+  size_t act_bytes(int L, int C) const { return static_cast<size_t>(N) * Hl(L) * Wl(L) * C * 2; }
+  void* at(size_t off) const { return arena + off; }
+  const float* W_(int li) const { return params + layers[li].w_off; }
+  const float* B_(int li) const { return params + layers[li].b_off; }
+  float* dW_(int li) const { return grads + layers[li].w_off; }
+  float* dB_(int li) const { return grads + layers[li].b_off; }
+  const void* pkf(int li) const { return arena + layers[li].pk_fwd; }
+  const void* pkd(int li) const { return arena + layers[li].pk_dgrad; }
+};
+
+namespace {
+
+int add_layer(unetb200_plan* P, const std::string& name, int kind, int cin, int cout) {
+  Layer l;
+  l.name = name;
+  l.kind = kind;
+  l.cin = cin;
+  l.cout = cout;
+  Var k, b;
+  k.name = name + "/kernel";
+  k.rank = 4;
+  if (kind == 0) { k.shape[0] = 3; k.shape[1] = 3; k.shape[2] = cin; k.shape[3] = cout; }
+  else if (kind == 1) { k.shape[0] = 2; k.shape[1] = 2; k.shape[2] = cout; k.shape[3] = cin; }
+  else { k.shape[0] = 1; k.shape[1] = 1; k.shape[2] = cin; k.shape[3] = cout; }
+  // every variable starts on a 16-byte boundary of the flat buffer (vectorised Adam, float4 bias loads)
+  P->nparams = (P->nparams + 3) / 4 * 4;
+  k.offset = P->nparams;
+  P->nparams += k.count();
+  P->nparams = (P->nparams + 3) / 4 * 4;
+  b.name = name + "/bias";
+  b.rank = 1;
+  b.shape[0] = cout; b.shape[1] = b.shape[2] = b.shape[3] = 1;
+  b.offset = P->nparams;
+  P->nparams += cout;
+  l.w_off = k.offset;
+  l.b_off = b.offset;
+  l.pk_fwd = l.pk_dgrad = 0;
+  P->vars.push_back(k);
+  P->vars.push_back(b);
+  P->layers.push_back(l);
+  return static_cast<int>(P->layers.size()) - 1;
+}
+
+size_t max_sz(size_t a, size_t b) { return a > b ? a : b; }
+
+}  // namespace
+
+extern "C" {
+
+int unetb200_plan_create(unetb200_plan** out, int N, int H, int W, int in_channels, int n_cl_out, int use_upsampling,
+                         float dropout) {
+  UB_REQUIRE(out != nullptr, "plan_create: null output");
+  UB_REQUIRE(N >= 1 && H >= 16 && W >= 16 && H % 16 == 0 && W % 16 == 0,
+             "plan_create: image %dx%d must be a multiple of 16 (four 2x2 poolings), batch %d >= 1", H, W, N);
+  UB_REQUIRE(in_channels >= 1 && in_channels <= 8, "plan_create: in_channels %d outside 1..8", in_channels);
+  UB_REQUIRE(n_cl_out >= 1 && n_cl_out <= 4, "plan_create: n_cl_out %d outside 1..4", n_cl_out);
+  UB_REQUIRE(dropout >= 0.0f && dropout < 1.0f, "plan_create: dropout %f outside [0,1)", dropout);
+  unetb200_plan* P = new unetb200_plan();
+  P->N = N; P->H = H; P->W = W; P->Cin = in_channels; P->ncl = n_cl_out; P->ups = use_upsampling ? 1 : 0;
+  P->dropout = dropout;
+  for (int L = 0; L < 5; ++L) P->ch[L] = 32 << L;
+  const int up = P->ups;
+  // ---- variables in creation order (model.py:51-120)
+  static const char* enc_names[5] = {"conv1", "conv2", "conv3", "conv4", "conv5"};
+  for (int L = 0; L < 5; ++L) {
+    const int cin = L == 0 ? in_channels : P->ch[L - 1];
+    P->enc_a[L] = add_layer(P, std::string(enc_names[L]) + "a", 0, cin, P->ch[L]);
+    const int cout_b = (L == 4 && up) ? 256 : P->ch[L];
+    P->enc_b[L] = add_layer(P, std::string(enc_names[L]) + "b", 0, P->ch[L], cout_b);
+  }
+  P->c4_out = up ? 256 : 512;
+  for (int L = 3; L >= 0; --L) {
+    const std::string idx = std::to_string(9 - L);
+    const int below = (L == 3) ? P->c4_out : P->dc_out[L + 1];  // channels of the tensor one level down
+    if (!up) P->tc[L] = add_layer(P, "transConv" + idx, 1, below, P->ch[L]);
+    else P->tc[L] = -1;
+    P->dec_a[L] = add_layer(P, "conv" + idx + "a", 0, 2 * P->ch[L], P->ch[L]);
+    P->dc_out[L] = (up && L > 0) ? P->ch[L] / 2 : P->ch[L];
+    P->dec_b[L] = add_layer(P, "conv" + idx + "b", 0, P->ch[L], P->dc_out[L]);
+  }
+  P->mask = add_layer(P, "Mask", 2, 32, n_cl_out);
+  P->nparams = (P->nparams + 3) / 4 * 4;
+
+  // ---- arena: packed weights
+  for (auto& l : P->layers) {
+    if (l.kind == 2 || l.cin < 32) continue;  // Mask and conv1a run from the fp32 master
+    const size_t bytes = static_cast<size_t>(l.kind == 0 ? 9 : 4) * l.cin * l.cout * 2;
+    l.pk_fwd = P->bump(bytes);
+    l.pk_dgrad = P->bump(bytes);
+  }
+  // ---- arena: activations and gradients
+  for (int L = 0; L < 5; ++L) {
+    P->a[L] = P->bump(P->act_bytes(L, P->ch[L]));
+    P->g_a[L] = P->bump(P->act_bytes(L, P->ch[L]));
+    const int cb = L == 4 ? P->c4_out : P->ch[L];
+    P->c[L] = P->bump(P->act_bytes(L, cb));
+    P->g_c[L] = P->bump(P->act_bytes(L, cb));
+  }
+  for (int L = 0; L < 4; ++L) {
+    P->p[L] = P->bump(P->act_bytes(L + 1, P->ch[L]));
+    P->g_p[L] = P->bump(P->act_bytes(L + 1, P->ch[L]));
+    P->u[L] = P->bump(P->act_bytes(L, P->ch[L]));
+    P->g_u[L] = P->bump(P->act_bytes(L, P->ch[L]));
+    P->da[L] = P->bump(P->act_bytes(L, P->ch[L]));
+    P->g_da[L] = P->bump(P->act_bytes(L, P->ch[L]));
+    P->dc[L] = P->bump(P->act_bytes(L, P->dc_out[L]));
+    P->g_dc[L] = P->bump(P->act_bytes(L, P->dc_out[L]));
+  }
+  const long long pixels = static_cast<long long>(N) * H * W;
+  P->preds = P->bump(static_cast<size_t>(pixels) * n_cl_out * 4);
+  P->sums = P->bump(64);
+  P->metrics = P->bump(64);
+  // ---- workspace: the largest any single op asks for (ops are serialised on one stream)
+  size_t ws = max_sz(unetb200_head_ws_bytes(pixels, 32, n_cl_out), unetb200_conv_first_wgrad_ws_bytes(in_channels, 32));
+  for (int L = 0; L < 5; ++L) {
+    ws = max_sz(ws, unetb200_bias_grad_ws_bytes(P->ch[L]));
+    const auto& la = P->layers[P->enc_a[L]];
+    const auto& lb = P->layers[P->enc_b[L]];
+    if (L > 0) ws = max_sz(ws, conv3x3_wgrad_ws_bytes(N, P->Hl(L), P->Wl(L), la.cin, la.cout));
+    ws = max_sz(ws, conv3x3_wgrad_ws_bytes(N, P->Hl(L), P->Wl(L), lb.cin, lb.cout));
+  }
+  for (int L = 0; L < 4; ++L) {
+    const auto& la = P->layers[P->dec_a[L]];
+    const auto& lb = P->layers[P->dec_b[L]];
+    ws = max_sz(ws, conv3x3_wgrad_ws_bytes(N, P->Hl(L), P->Wl(L), la.cin, la.cout));
+    ws = max_sz(ws, conv3x3_wgrad_ws_bytes(N, P->Hl(L), P->Wl(L), lb.cin, lb.cout));
+    if (!up) {
+      const auto& lt = P->layers[P->tc[L]];
+      ws = max_sz(ws, tconv2x2_wgrad_ws_bytes(N, P->Hl(L + 1), P->Wl(L + 1), lt.cin, lt.cout));
+    }
+  }
+  P->ws_bytes = ws;
+  P->ws = P->bump(ws);
+  *out = P;
+  return UB_OK;
+}
+
+void unetb200_plan_destroy(unetb200_plan* P) { delete P; }
+
+long long unetb200_plan_num_params(const unetb200_plan* P) { return P->nparams; }
+int unetb200_plan_num_variables(const unetb200_plan* P) { return static_cast<int>(P->vars.size()); }
+
+int unetb200_plan_variable(const unetb200_plan* P, int i, char* name, int name_cap, long long* offset, int* rank,
+                           int* shape4) {
+  UB_REQUIRE(i >= 0 && i < static_cast<int>(P->vars.size()), "plan_variable: index %d out of range", i);
+  const Var& v = P->vars[i];
+  if (name && name_cap > 0) {
+    std::strncpy(name, v.name.c_str(), name_cap - 1);
+    name[name_cap - 1] = 0;
+  }
+  if (offset) *offset = v.offset;
+  if (rank) *rank = v.rank;
+  if (shape4) for (int k = 0; k < 4; ++k) shape4[k] = v.shape[k];
+  return UB_OK;
+}
+
+size_t unetb200_plan_arena_bytes(const unetb200_plan* P) { return P->arena_bytes; }
+
+int unetb200_plan_bind(unetb200_plan* P, void* arena, float* params, float* grads) {
+  UB_REQUIRE(arena && params && grads, "plan_bind: null buffer");
+  UB_REQUIRE(reinterpret_cast<uintptr_t>(arena) % kAlign == 0, "plan_bind: arena must be %zu-byte aligned", kAlign);
+  UB_REQUIRE(reinterpret_cast<uintptr_t>(params) % 16 == 0 && reinterpret_cast<uintptr_t>(grads) % 16 == 0,
+             "plan_bind: parameter buffers must be 16-byte aligned");
+  P->arena = reinterpret_cast<uint8_t*>(arena);
+  P->params = params;
+  P->grads = grads;
+  return UB_OK;
+}
+
+// Arena offset of a named tensor (debugging / per-layer parity tests). Names: a1..a5, c1..c5, p1..p4, u6..u9,
+// a6..a9, c6..c9 and the same with a leading 'g' for gradients; 'preds', 'metrics'.
+int unetb200_plan_tensor(const unetb200_plan* P, const char* name, long long* offset, int* n, int* h, int* w, int* c,
+                         int* elem_bytes) {
+  std::string s(name);
+  bool grad = false;
+  if (s == "preds") {
+    *offset = static_cast<long long>(P->preds); *n = P->N; *h = P->H; *w = P->W; *c = P->ncl; *elem_bytes = 4;
+    return UB_OK;
+  }
+  if (s == "metrics") {
+    *offset = static_cast<long long>(P->metrics); *n = 1; *h = 1; *w = 1; *c = 4; *elem_bytes = 4;
+    return UB_OK;
+  }
+  if (s.size() == 3 && s[0] == 'g') { grad = true; s = s.substr(1); }
+  UB_REQUIRE(s.size() == 2 && s[1] >= '1' && s[1] <= '9', "plan_tensor: unknown tensor '%s'", name);
+  const int idx = s[1] - '0';
+  size_t off = 0;
+  int L = 0, C = 0;
+  if (idx <= 5) {
+    L = idx - 1;
+    if (s[0] == 'a') { off = grad ? P->g_a[L] : P->a[L]; C = P->ch[L]; }
+    else if (s[0] == 'c') { off = grad ? P->g_c[L] : P->c[L]; C = L == 4 ? P->c4_out : P->ch[L]; }
+    else if (s[0] == 'p' && L < 4) { off = grad ? P->g_p[L] : P->p[L]; C = P->ch[L]; L = L + 1; }
+    else { UB_REQUIRE(false, "plan_tensor: unknown tensor '%s'", name); }
+  } else {
+    L = 9 - idx;
+    if (s[0] == 'a') { off = grad ? P->g_da[L] : P->da[L]; C = P->ch[L]; }
+    else if (s[0] == 'c') { off = grad ? P->g_dc[L] : P->dc[L]; C = P->dc_out[L]; }
+    else if (s[0] == 'u') { off = grad ? P->g_u[L] : P->u[L]; C = P->ch[L]; }
+    else { UB_REQUIRE(false, "plan_tensor: unknown tensor '%s'", name); }
+  }
+  *offset = static_cast<long long>(off); *n = P->N; *h = P->Hl(L); *w = P->Wl(L); *c = C; *elem_bytes = 2;
+  return UB_OK;
+}
+
+#define RC(expr)            \
+  do {                      \
+    int _rc = (expr);       \
+    if (_rc) return _rc;    \
+  } while (0)
+
+// Refresh the bf16 GEMM operands from the fp32 master weights (after init and after every optimizer update).
+int unetb200_plan_pack_weights(unetb200_plan* P, void* stream) {
+  UB_REQUIRE(P->arena, "plan_pack_weights: plan is not bound");
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  for (size_t i = 0; i < P->layers.size(); ++i) {
+    const Layer& l = P->layers[i];
+    if (l.kind == 2 || l.cin < 32) continue;
+    const int li = static_cast<int>(i);
+    if (l.kind == 0) {
+      RC(pack_conv_fwd(P->W_(li), P->at(l.pk_fwd), 9, l.cin, l.cout, s));
+      RC(pack_conv_dgrad(P->W_(li), P->at(l.pk_dgrad), 9, l.cin, l.cout, s));
+    } else {
+      RC(pack_tconv_fwd(P->W_(li), P->at(l.pk_fwd), l.cin, l.cout, s));
+      RC(pack_tconv_dgrad(P->W_(li), P->at(l.pk_dgrad), l.cin, l.cout, s));
+    }
+  }
+  return UB_OK;
+}
+
+// Forward pass (model.py:45-120) + dice metrics (model.py:4-21,133-143) when msks != NULL.
+// imgs: fp32 [N,H,W,Cin]; msks: fp32 [N,H,W,n_cl]. Dropout masks come from Philox stream (seed + *seed_add, layer).
+int unetb200_plan_forward(unetb200_plan* P, const float* imgs, const float* msks, uint64_t seed,
+                          const long long* seed_add, void* stream) {
+  UB_REQUIRE(P->arena, "plan_forward: plan is not bound");
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  const int N = P->N;
+  const DropoutCfg no_drop{1.0f, 0, 0, nullptr};
+  // encoder
+  for (int L = 0; L < 5; ++L) {
+    const int H = P->Hl(L), W = P->Wl(L);
+    const int la = P->enc_a[L], lb = P->enc_b[L];
+    if (L == 0) {
+      RC(conv_first_fwd(imgs, P->W_(la), P->B_(la), P->at(P->a[0]), N, H, W, P->Cin, 32, s));
+    } else {
+      DropoutCfg d = no_drop;
+      if ((L == 2 || L == 3) && P->dropout > 0.0f) d = DropoutCfg{1.0f - P->dropout, seed, static_cast<unsigned>(L), seed_add};
+      RC(conv3x3_fwd(ConvSrc{P->at(P->p[L - 1]), P->ch[L - 1]}, ConvSrc{nullptr, 0}, P->pkf(la), P->B_(la),
+                     P->at(P->a[L]), N, H, W, P->ch[L], 1, d, s));
+    }
+    RC(conv3x3_fwd(ConvSrc{P->at(P->a[L]), P->ch[L]}, ConvSrc{nullptr, 0}, P->pkf(lb), P->B_(lb), P->at(P->c[L]), N, H,
+                   W, P->layers[lb].cout, 1, no_drop, s));
+    if (L < 4) RC(maxpool2x2_fwd(P->at(P->c[L]), P->at(P->p[L]), N, H, W, P->ch[L], s));
+  }
+  // decoder
+  for (int L = 3; L >= 0; --L) {
+    const int H = P->Hl(L), W = P->Wl(L);
+    const size_t below = (L == 3) ? P->c[4] : P->dc[L + 1];
+    const int below_C = (L == 3) ? P->c4_out : P->dc_out[L + 1];
+    if (P->ups) {
+      RC(upsample2x2_fwd(P->at(below), P->at(P->u[L]), N, H / 2, W / 2, below_C, s));
+    } else {
+      const int lt = P->tc[L];
+      RC(tconv2x2_fwd(P->at(below), below_C, P->pkf(lt), P->B_(lt), P->at(P->u[L]), P->ch[L], N, H / 2, W / 2, s));
+    }
+    const int la = P->dec_a[L], lb = P->dec_b[L];
+    RC(conv3x3_fwd(ConvSrc{P->at(P->u[L]), P->ch[L]}, ConvSrc{P->at(P->c[L]), P->ch[L]}, P->pkf(la), P->B_(la),
+                   P->at(P->da[L]), N, H, W, P->ch[L], 1, no_drop, s));
+    RC(conv3x3_fwd(ConvSrc{P->at(P->da[L]), P->ch[L]}, ConvSrc{nullptr, 0}, P->pkf(lb), P->B_(lb), P->at(P->dc[L]), N, H,
+                   W, P->dc_out[L], 1, no_drop, s));
+  }
+  // head
+  const long long pixels = static_cast<long long>(N) * P->H * P->W;
+  float* preds = reinterpret_cast<float*>(P->at(P->preds));
+  float* sums = reinterpret_cast<float*>(P->at(P->sums));
+  if (msks) {
+    RC(head_fwd(P->at(P->dc[0]), P->W_(P->mask), P->B_(P->mask), msks, preds, sums,
+                reinterpret_cast<float*>(P->at(P->ws)), pixels, 32, P->ncl, s));
+    RC(dice_finalize(sums, 1.0f, reinterpret_cast<float*>(P->at(P->metrics)), s));
+  } else {
+    // inference: no labels, the dice sums degenerate to {0, 0, sum p}
+    RC(head_fwd(P->at(P->dc[0]), P->W_(P->mask), P->B_(P->mask), nullptr, preds, sums,
+                reinterpret_cast<float*>(P->at(P->ws)), pixels, 32, P->ncl, s));
+  }
+  return UB_OK;
+}
+
+// Backward segments (the autodiff graph optimizer.compute_gradients builds at test_dist.py:246-248), split so the
+// caller can start the all-reduce of a gradient bucket as soon as the segment that completes it has been enqueued:
+//   segment 0: head + decoder  -> gradients of transConv6|conv6a .. Mask   (tail of the flat buffer)
+//   segment 1: conv5b, conv5a  -> the two largest tensors
+//   segment 2: encoder         -> conv1a .. conv4b
+int unetb200_plan_backward(unetb200_plan* P, const float* imgs, const float* msks, const float* dpreds,
+                           float grad_scale, int segment, void* stream) {
+  UB_REQUIRE(P->arena, "plan_backward: plan is not bound");
+  UB_REQUIRE(segment >= 0 && segment <= 2, "plan_backward: segment %d outside 0..2", segment);
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  const int N = P->N;
+  float* ws = reinterpret_cast<float*>(P->at(P->ws));
+  void* wsv = P->at(P->ws);
+  const float inv_keep = P->dropout > 0.0f ? 1.0f / (1.0f - P->dropout) : 1.0f;
+
+  if (segment == 0) {
+    const long long pixels = static_cast<long long>(N) * P->H * P->W;
+    UB_REQUIRE(msks || dpreds, "plan_backward: need the labels or an explicit dL/dpreds");
+    RC(head_bwd(P->at(P->dc[0]), P->W_(P->mask), dpreds ? dpreds : msks, reinterpret_cast<const float*>(P->at(P->preds)),
+                dpreds ? nullptr : reinterpret_cast<const float*>(P->at(P->sums)), 1.0f, grad_scale, P->at(P->g_dc[0]), P->dW_(P->mask),
+                P->dB_(P->mask), ws, pixels, 32, P->ncl, s));
+    for (int L = 0; L < 4; ++L) {
+      const int H = P->Hl(L), W = P->Wl(L);
+      const long long px = static_cast<long long>(N) * H * W;
+      const int la = P->dec_a[L], lb = P->dec_b[L];
+      // conv{9-L}b
+      RC(conv3x3_wgrad(P->at(P->g_dc[L]), P->dc_out[L], ConvSrc{P->at(P->da[L]), P->ch[L]}, ConvSrc{nullptr, 0},
+                       P->dW_(lb), wsv, P->ws_bytes, N, H, W, s));
+      RC(colsum_bf16(P->at(P->g_dc[L]), P->dB_(lb), ws, px, P->dc_out[L], s));
+      RC(conv3x3_dgrad(P->at(P->g_dc[L]), P->dc_out[L], P->pkd(lb),
+                       DgradDst{P->at(P->g_da[L]), P->ch[L], P->at(P->da[L]), 1.0f}, DgradDst{nullptr, 0, nullptr, 1.0f},
+                       N, H, W, s));
+      // conv{9-L}a over [u, skip]
+      RC(conv3x3_wgrad(P->at(P->g_da[L]), P->ch[L], ConvSrc{P->at(P->u[L]), P->ch[L]}, ConvSrc{P->at(P->c[L]), P->ch[L]},
+                       P->dW_(la), wsv, P->ws_bytes, N, H, W, s));
+      RC(colsum_bf16(P->at(P->g_da[L]), P->dB_(la), ws, px, P->ch[L], s));
+      RC(conv3x3_dgrad(P->at(P->g_da[L]), P->ch[L], P->pkd(la), DgradDst{P->at(P->g_u[L]), P->ch[L], nullptr, 1.0f},
+                       DgradDst{P->at(P->g_c[L]), P->ch[L], P->at(P->c[L]), 1.0f}, N, H, W, s));
+      // up path
+      const size_t below = (L == 3) ? P->c[4] : P->dc[L + 1];
+      const size_t g_below = (L == 3) ? P->g_c[4] : P->g_dc[L + 1];
+      const int below_C = (L == 3) ? P->c4_out : P->dc_out[L + 1];
+      if (P->ups) {
+        RC(upsample2x2_bwd(P->at(P->g_u[L]), P->at(below), P->at(g_below), N, H / 2, W / 2, below_C, 1, s));
+      } else {
+        const int lt = P->tc[L];
+        RC(tconv2x2_wgrad(P->at(P->g_u[L]), P->ch[L], P->at(below), below_C, P->dW_(lt), wsv, P->ws_bytes, N, H / 2,
+                          W / 2, s));
+        RC(colsum_bf16(P->at(P->g_u[L]), P->dB_(lt), ws, px, P->ch[L], s));
+        RC(tconv2x2_dgrad(P->at(P->g_u[L]), P->ch[L], P->pkd(lt), P->at(g_below), below_C, P->at(below), 1.0f, N, H / 2,
+                          W / 2, s));
+      }
+    }
+    return UB_OK;
+  }
+
+  if (segment == 1) {
+    const int L = 4;
+    const int H = P->Hl(L), W = P->Wl(L);
+    const long long px = static_cast<long long>(N) * H * W;
+    const int la = P->enc_a[L], lb = P->enc_b[L];
+    RC(conv3x3_wgrad(P->at(P->g_c[L]), P->c4_out, ConvSrc{P->at(P->a[L]), P->ch[L]}, ConvSrc{nullptr, 0}, P->dW_(lb), wsv,
+                     P->ws_bytes, N, H, W, s));
+    RC(colsum_bf16(P->at(P->g_c[L]), P->dB_(lb), ws, px, P->c4_out, s));
+    RC(conv3x3_dgrad(P->at(P->g_c[L]), P->c4_out, P->pkd(lb), DgradDst{P->at(P->g_a[L]), P->ch[L], P->at(P->a[L]), 1.0f},
+                     DgradDst{nullptr, 0, nullptr, 1.0f}, N, H, W, s));
+    RC(conv3x3_wgrad(P->at(P->g_a[L]), P->ch[L], ConvSrc{P->at(P->p[L - 1]), P->ch[L - 1]}, ConvSrc{nullptr, 0},
+                     P->dW_(la), wsv, P->ws_bytes, N, H, W, s));
+    RC(colsum_bf16(P->at(P->g_a[L]), P->dB_(la), ws, px, P->ch[L], s));
+    RC(conv3x3_dgrad(P->at(P->g_a[L]), P->ch[L], P->pkd(la), DgradDst{P->at(P->g_p[L - 1]), P->ch[L - 1], nullptr, 1.0f},
+                     DgradDst{nullptr, 0, nullptr, 1.0f}, N, H, W, s));
+    return UB_OK;
+  }
+
+  for (int L = 3; L >= 0; --L) {
+    const int H = P->Hl(L), W = P->Wl(L);
+    const long long px = static_cast<long long>(N) * H * W;
+    const int la = P->enc_a[L], lb = P->enc_b[L];
+    // MaxPoolGrad + skip gradient + ReluGrad of conv{L+1}b, in place in g_c[L]
+    RC(maxpool2x2_bwd(P->at(P->c[L]), P->at(P->g_p[L]), P->at(P->g_c[L]), P->at(P->g_c[L]), N, H, W, P->ch[L], s));
+    RC(conv3x3_wgrad(P->at(P->g_c[L]), P->ch[L], ConvSrc{P->at(P->a[L]), P->ch[L]}, ConvSrc{nullptr, 0}, P->dW_(lb), wsv,
+                     P->ws_bytes, N, H, W, s));
+    RC(colsum_bf16(P->at(P->g_c[L]), P->dB_(lb), ws, px, P->ch[L], s));
+    const bool dropped = (L == 2 || L == 3) && P->dropout > 0.0f;
+    RC(conv3x3_dgrad(P->at(P->g_c[L]), P->ch[L], P->pkd(lb),
+                     DgradDst{P->at(P->g_a[L]), P->ch[L], P->at(P->a[L]), dropped ? inv_keep : 1.0f},
+                     DgradDst{nullptr, 0, nullptr, 1.0f}, N, H, W, s));
+    if (L > 0) {
+      RC(conv3x3_wgrad(P->at(P->g_a[L]), P->ch[L], ConvSrc{P->at(P->p[L - 1]), P->ch[L - 1]}, ConvSrc{nullptr, 0},
+                       P->dW_(la), wsv, P->ws_bytes, N, H, W, s));
+      RC(colsum_bf16(P->at(P->g_a[L]), P->dB_(la), ws, px, P->ch[L], s));
+      RC(conv3x3_dgrad(P->at(P->g_a[L]), P->ch[L], P->pkd(la),
+                       DgradDst{P->at(P->g_p[L - 1]), P->ch[L - 1], nullptr, 1.0f}, DgradDst{nullptr, 0, nullptr, 1.0f},
+                       N, H, W, s));
+    } else {
+      RC(conv_first_wgrad(imgs, P->at(P->g_a[0]), P->dW_(la), P->dB_(la), ws, N, H, W, P->Cin, 32, s));
+    }
+  }
+  return UB_OK;
+}
+
+// Flat-buffer range [begin, end) (floats) whose gradients are complete once `segment` has run.
+int unetb200_plan_bucket(const unetb200_plan* P, int segment, long long* begin, long long* end) {
+  UB_REQUIRE(segment >= 0 && segment <= 2, "plan_bucket: segment %d outside 0..2", segment);
+  const long long conv5a = P->layers[P->enc_a[4]].w_off;
+  const long long after5 = P->ups ? P->layers[P->dec_a[3]].w_off : P->layers[P->tc[3]].w_off;
+  if (segment == 0) { *begin = after5; *end = P->nparams; }
+  else if (segment == 1) { *begin = conv5a; *end = after5; }
+  else { *begin = 0; *end = conv5a; }
+  return UB_OK;
+}
+
+}  // extern "C"

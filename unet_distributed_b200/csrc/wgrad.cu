@@ -221,8 +221,14 @@ int wgrad_launch(const WgradParams& p, const CUtensorMap& z, const CUtensorMap& 
   const int total_nt = p.x_ntiles[0] + (p.num_src > 1 ? p.x_ntiles[1] : 0);
   const long long grid = static_cast<long long>(p.splits) * p.taps_r * p.taps_s * p.m_tiles * total_nt;
   UB_REQUIRE(grid > 0 && grid < (1ll << 30), "wgrad: grid %lld", grid);
+  if (profiling_enabled()) {
+    const double pixels = static_cast<double>(p.N) * p.H * p.W;
+    const double cin = static_cast<double>(p.x_C[0]) + (p.num_src > 1 ? p.x_C[1] : 0);
+    prof_begin(UB_KIND_WGRAD, 2.0 * pixels * p.taps_r * p.taps_s * cin * p.z_C, 2.0 * pixels * (cin + p.z_C), stream);
+  }
   wgrad_kernel<<<static_cast<unsigned>(grid), kThreads, smem, stream>>>(p, z, x0, x1);
   UB_CHECK_CUDA(cudaGetLastError());
+  prof_end(stream);
   return UB_OK;
 }
 

@@ -1,0 +1,66 @@
+"""data.py of the reference (data.py:5-54): load the four .npy files and cut a shuffled epoch into batches.
+Python-3 correct (the reference shuffles a zip object and uses integer `/`, data.py:38,41-42) and seedable."""
+import numpy as np
+
+from . import settings_dist
+from .preprocess import load_data, update_channels
+
+
+def load_all_data(out_path=None):
+    """data.py:5-26.  Returns imgs_train, msks_train, imgs_test, msks_test (NHWC)."""
+    path = settings_dist.OUT_PATH if out_path is None else out_path
+    print("-" * 42)
+    print("Loading and preprocessing training data...")
+    print("-" * 42)
+    imgs_train, msks_train = load_data(path, "_train")
+    imgs_train, msks_train = update_channels(imgs_train, msks_train, settings_dist.IN_CHANNEL_NO,
+                                             settings_dist.OUT_CHANNEL_NO, settings_dist.MODE)
+    print("-" * 38)
+    print("Loading and preprocessing test data...")
+    print("-" * 38)
+    imgs_test, msks_test = load_data(path, "_test")
+    imgs_test, msks_test = update_channels(imgs_test, msks_test, settings_dist.IN_CHANNEL_NO,
+                                           settings_dist.OUT_CHANNEL_NO, settings_dist.MODE)
+    print("Training images shape: {}".format(imgs_train.shape))
+    print("Training masks shape:  {}".format(msks_train.shape))
+    print("Testing images shape:  {}".format(imgs_test.shape))
+    print("Testing masks shape:   {}".format(msks_test.shape))
+    return imgs_train, msks_train, imgs_test, msks_test
+
+
+class EpochOfBatches:
+    """Result of get_epoch when images and masks differ in channel count (a ragged pair cannot be one ndarray).
+    Indexes like the reference's array: epoch[batch_idx, 0] -> images, epoch[batch_idx, 1] -> masks."""
+
+    def __init__(self, data, labels):
+        self.data, self.labels = data, labels
+        self.shape = (data.shape[0], 2) + tuple(data.shape[1:])
+
+    def __len__(self):
+        return self.data.shape[0]
+
+    def __getitem__(self, idx):
+        if isinstance(idx, tuple):
+            b, which = idx
+            return (self.data, self.labels)[which][b]
+        return self.data[idx], self.labels[idx]
+
+
+def get_epoch(batch_size, imgs_train, msks_train, rng=None):
+    """data.py:29-54: drop the remainder, shuffle image/mask pairs together, reshape to
+    [num_batches, batch_size, H, W, C] and pair them -> array [num_batches, 2, batch_size, H, W, C].
+    Each array keeps its own channel count (the reference reshapes the labels with the image's, data.py:49).
+    rng: optional numpy Generator / seed; default = unseeded like the reference."""
+    train_size = imgs_train.shape[0]
+    epoch_length = train_size - train_size % batch_size
+    batch_count = epoch_length // batch_size
+    if not isinstance(rng, np.random.Generator):
+        rng = np.random.default_rng(rng)
+    perm = rng.permutation(train_size)[:epoch_length]
+    data = np.asarray(imgs_train)[perm]
+    labels = np.asarray(msks_train)[perm]
+    data = data.reshape((batch_count, batch_size) + tuple(imgs_train.shape[1:]))
+    labels = labels.reshape((batch_count, batch_size) + tuple(msks_train.shape[1:]))
+    if data.shape == labels.shape:
+        return np.stack([data, labels], axis=1)
+    return EpochOfBatches(data, labels)

@@ -1,0 +1,145 @@
+"""Python owner of a libunetb200 network plan: allocates the arena and the flat fp32 buffers with PyTorch (tensor
+ownership only) and drives the native launch sequence.  Mirrors the graph model.py:36-130 of the reference builds."""
+from __future__ import annotations
+
+import ctypes
+from collections import OrderedDict
+
+import numpy as np
+import torch
+
+from . import _lib
+
+
+def _ptr(t):
+    return ctypes.c_void_p(t.data_ptr()) if t is not None else None
+
+
+def _stream():
+    return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+class UNetPlan:
+    """One UNet instance for a fixed (N, H, W, in_channels) input shape on the current CUDA device."""
+
+    def __init__(self, N, H, W, in_channels=1, n_cl_out=1, use_upsampling=False, dropout=0.2, device=None):
+        if not torch.cuda.is_available():
+            raise _lib.UnetB200Error("UNetPlan needs a CUDA device (sm_100a); there is no CPU path")
+        self.device = torch.device(device if device is not None else f"cuda:{torch.cuda.current_device()}")
+        self.N, self.H, self.W = int(N), int(H), int(W)
+        self.in_channels, self.n_cl_out = int(in_channels), int(n_cl_out)
+        self.use_upsampling, self.dropout = bool(use_upsampling), float(dropout)
+        L = _lib.lib()
+        h = ctypes.c_void_p()
+        _lib.check(L.unetb200_plan_create(ctypes.byref(h), self.N, self.H, self.W, self.in_channels, self.n_cl_out,
+                                          int(self.use_upsampling), self.dropout), "unetb200_plan_create")
+        self._h = h
+        self.num_params_padded = int(L.unetb200_plan_num_params(h))
+        self.variables = OrderedDict()
+        name = ctypes.create_string_buffer(64)
+        off, rank = ctypes.c_longlong(), ctypes.c_int()
+        shape = (ctypes.c_int * 4)()
+        for i in range(L.unetb200_plan_num_variables(h)):
+            _lib.check(L.unetb200_plan_variable(h, i, name, 64, ctypes.byref(off), ctypes.byref(rank), shape),
+                       "unetb200_plan_variable")
+            self.variables[name.value.decode()] = (int(off.value), tuple(shape[k] for k in range(rank.value)))
+        self.num_params = sum(int(np.prod(s)) for _, s in self.variables.values())
+        with torch.cuda.device(self.device):
+            nbytes = int(L.unetb200_plan_arena_bytes(h))
+            self._arena_raw = torch.empty(nbytes + 1024, dtype=torch.uint8, device=self.device)
+            shift = (-self._arena_raw.data_ptr()) % 1024
+            self.arena = self._arena_raw[shift:shift + nbytes]
+            self.params = torch.zeros(self.num_params_padded, dtype=torch.float32, device=self.device)
+            self.grads = torch.zeros(self.num_params_padded, dtype=torch.float32, device=self.device)
+        self.arena_bytes = nbytes
+        self.bind(self.params, self.grads)
+        self.buckets = []
+        b, e = ctypes.c_longlong(), ctypes.c_longlong()
+        for seg in range(3):
+            _lib.check(L.unetb200_plan_bucket(h, seg, ctypes.byref(b), ctypes.byref(e)), "unetb200_plan_bucket")
+            self.buckets.append((int(b.value), int(e.value)))
+
+    def __del__(self):
+        h = getattr(self, "_h", None)
+        if h is not None and h.value:
+            try:
+                _lib.lib().unetb200_plan_destroy(h)
+            except Exception:
+                pass
+            self._h = None
+
+    # ------------------------------------------------------------------ buffers
+    def bind(self, params, grads):
+        """Use caller-provided flat fp32 buffers (e.g. views of a trainer-wide allocation)."""
+        assert params.numel() == self.num_params_padded and grads.numel() == self.num_params_padded
+        self.params, self.grads = params, grads
+        _lib.call("unetb200_plan_bind", self._h, _ptr(self.arena), _ptr(params), _ptr(grads))
+
+    def _view(self, flat, name):
+        off, shape = self.variables[name]
+        return flat[off:off + int(np.prod(shape))].view(*shape)
+
+    def param(self, name):
+        return self._view(self.params, name)
+
+    def grad(self, name):
+        return self._view(self.grads, name)
+
+    def set_weights(self, weights):
+        """weights: {TF variable name: array in TF layout}. Refreshes the packed bf16 GEMM operands."""
+        with torch.no_grad():
+            for name in self.variables:
+                w = torch.as_tensor(np.asarray(weights[name], dtype=np.float32))
+                self.param(name).copy_(w.to(self.device))
+        self.pack_weights()
+
+    def get_weights(self):
+        return OrderedDict((n, self.param(n).detach().cpu().numpy().copy()) for n in self.variables)
+
+    def get_grads(self):
+        return OrderedDict((n, self.grad(n).detach().cpu().numpy().copy()) for n in self.variables)
+
+    def tensor(self, name):
+        """View of a named arena tensor: activations 'a1'..'c9','p1'..'p4','u6'..'u9' (bf16 NHWC), their gradients
+        ('g'+name), 'preds' (fp32 NHWC) or 'metrics' (fp32 [loss, dice, sensitivity, specificity])."""
+        off = ctypes.c_longlong()
+        n, h, w, c, eb = (ctypes.c_int() for _ in range(5))
+        _lib.call("unetb200_plan_tensor", self._h, name.encode(), ctypes.byref(off), ctypes.byref(n), ctypes.byref(h),
+                  ctypes.byref(w), ctypes.byref(c), ctypes.byref(eb))
+        count = n.value * h.value * w.value * c.value
+        raw = self.arena[off.value:off.value + count * eb.value]
+        dt = torch.bfloat16 if eb.value == 2 else torch.float32
+        t = raw.view(dt)
+        return t.view(4) if name == "metrics" else t.view(n.value, h.value, w.value, c.value)
+
+    @property
+    def preds(self):
+        return self.tensor("preds")
+
+    @property
+    def metrics(self):
+        return self.tensor("metrics")
+
+    # ------------------------------------------------------------------ launches (asynchronous on the current stream)
+    def pack_weights(self):
+        _lib.call("unetb200_plan_pack_weights", self._h, _stream())
+
+    def forward(self, imgs, msks=None, seed=0, seed_add=None):
+        """imgs fp32 [N,H,W,Cin] and msks fp32 [N,H,W,n_cl] on this device, contiguous."""
+        self._check_input(imgs, self.in_channels, "imgs")
+        if msks is not None:
+            self._check_input(msks, self.n_cl_out, "msks")
+        _lib.call("unetb200_plan_forward", self._h, _ptr(imgs), _ptr(msks), ctypes.c_uint64(int(seed)),
+                  _ptr(seed_add), _stream())
+
+    def backward(self, imgs, msks=None, dpreds=None, grad_scale=1.0, segment=None):
+        segs = (0, 1, 2) if segment is None else (segment,)
+        for s in segs:
+            _lib.call("unetb200_plan_backward", self._h, _ptr(imgs), _ptr(msks), _ptr(dpreds),
+                      ctypes.c_float(grad_scale), int(s), _stream())
+
+    def _check_input(self, t, C, what):
+        want = (self.N, self.H, self.W, C)
+        if tuple(t.shape) != want or t.dtype != torch.float32 or not t.is_cuda or not t.is_contiguous():
+            raise ValueError(f"{what}: expected contiguous CUDA float32 {want}, got {tuple(t.shape)} {t.dtype} "
+                             f"{t.device}")

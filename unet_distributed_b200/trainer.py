@@ -1,0 +1,165 @@
+"""The training step of test_dist.py:380-398 on B200: forward -> fused dice loss -> backward (with the gradient
+buckets all-reduced as they complete) -> TF-style Adam with the decaying learning rate -> weight re-pack.
+No host synchronisation happens inside a step; loss / dice stay on the device until the caller reads them."""
+from __future__ import annotations
+
+import ctypes
+
+import numpy as np
+import torch
+
+from . import _lib, parallel
+from .init import initial_weights
+from .plan import UNetPlan, _ptr, _stream
+
+
+class Trainer:
+    """Owns one UNetPlan (per-GPU batch N), the Adam slots and the device-side global_step.
+
+    Flags follow test_dist.py:64-85 / settings_dist.py:17-22: learning_rate, const_learningrate, lr_fraction,
+    decay_steps, use_upsampling.  `optimizer` may be "adam" (the reference, test_dist.py:246) or "sgd" (the
+    commented alternative, test_dist.py:239-244)."""
+
+    def __init__(self, N, H=128, W=128, in_channels=1, n_cl_out=1, use_upsampling=False, dropout=0.2,
+                 learning_rate=0.0005, const_learningrate=True, lr_fraction=0.2, decay_steps=100, optimizer="adam",
+                 beta1=0.9, beta2=0.999, epsilon=1e-8, weight_seed=1234, dropout_seed=816, weights=None,
+                 use_cuda_graph=False):
+        self.world, self.rank = parallel.world()
+        self.plan = UNetPlan(N, H, W, in_channels, n_cl_out, use_upsampling, dropout)
+        p = self.plan
+        dev = p.device
+        self.m = torch.zeros_like(p.params)
+        self.v = torch.zeros_like(p.params)
+        self.step_dev = torch.zeros(1, dtype=torch.int64, device=dev)   # global_step (test_dist.py:185)
+        self.lr0, self.const_lr = float(learning_rate), bool(const_learningrate)
+        self.lr_fraction, self.decay_steps = float(lr_fraction), float(decay_steps)
+        self.beta1, self.beta2, self.eps = float(beta1), float(beta2), float(epsilon)
+        self.optimizer = optimizer
+        if optimizer not in ("adam", "sgd"):
+            raise ValueError("optimizer must be 'adam' or 'sgd'")
+        self.dropout_seed = int(dropout_seed)
+        p.set_weights(weights if weights is not None else initial_weights(p.variables, weight_seed))
+        parallel.broadcast_flat(p.params)
+        if self.world > 1:
+            p.pack_weights()
+        self.reducer = parallel.BucketedAllReduce(p.grads, p.buckets)
+        self.use_cuda_graph = bool(use_cuda_graph) and self.world == 1
+        self._graph = None
+        self._g_imgs = self._g_msks = None
+        self.steps_done = 0
+        # pinned staging for the host-facing step
+        self._h_imgs = self._h_msks = None
+        self._d_imgs = torch.empty((N, H, W, in_channels), dtype=torch.float32, device=dev)
+        self._d_msks = torch.empty((N, H, W, n_cl_out), dtype=torch.float32, device=dev)
+        self._h_metrics = torch.empty(4, dtype=torch.float32).pin_memory()
+
+    # ------------------------------------------------------------------ one optimizer step on device-resident data
+    def _enqueue_step(self, imgs, msks):
+        p = self.plan
+        p.forward(imgs, msks, seed=self.dropout_seed, seed_add=self.step_dev)
+        for seg in range(3):
+            p.backward(imgs, msks, grad_scale=1.0, segment=seg)
+            self.reducer.launch(seg)
+        self.reducer.wait()
+        self._apply_update()
+
+    def _apply_update(self):
+        p = self.plan
+        scale = 1.0 / self.world            # SyncReplicasOptimizer averages the replica gradients
+        n = ctypes.c_longlong(p.num_params_padded)
+        if self.optimizer == "adam":
+            _lib.call("unetb200_adam_step", _ptr(p.params), _ptr(self.m), _ptr(self.v), _ptr(p.grads), n,
+                      _ptr(self.step_dev), self.lr0, int(self.const_lr), self.lr_fraction, self.decay_steps,
+                      self.beta1, self.beta2, self.eps, scale, _stream())
+        else:
+            _lib.call("unetb200_sgd_step", _ptr(p.params), _ptr(p.grads), n, _ptr(self.step_dev), self.lr0,
+                      int(self.const_lr), self.lr_fraction, self.decay_steps, scale, _stream())
+        _lib.call("unetb200_step_increment", _ptr(self.step_dev), _stream())
+        p.pack_weights()
+
+    def train_step(self, imgs, msks):
+        """imgs/msks: contiguous CUDA float32 NHWC tensors for THIS replica's shard. Returns the device tensor
+        [loss, dice, sensitivity, specificity] of this step (no synchronisation)."""
+        if self.use_cuda_graph:
+            if self._graph is None:
+                self._capture(imgs, msks)
+            self._g_imgs.copy_(imgs, non_blocking=True)
+            self._g_msks.copy_(msks, non_blocking=True)
+            self._graph.replay()
+        else:
+            self._enqueue_step(imgs, msks)
+        self.steps_done += 1
+        return self.plan.metrics
+
+    def _capture(self, imgs, msks):
+        self._g_imgs, self._g_msks = imgs.clone(), msks.clone()
+        # warm-up outside capture (kernel attribute set-up, lazy module loading) on a side stream, then restore state
+        snap = [t.clone() for t in (self.plan.params, self.m, self.v, self.step_dev)]
+        s = torch.cuda.Stream()
+        s.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(s):
+            self._enqueue_step(self._g_imgs, self._g_msks)
+        torch.cuda.current_stream().wait_stream(s)
+        for dst, src in zip((self.plan.params, self.m, self.v, self.step_dev), snap):
+            dst.copy_(src)
+        self.plan.pack_weights()
+        torch.cuda.synchronize()
+        self._graph = torch.cuda.CUDAGraph()
+        before = _lib.lib().unetb200_launch_count()
+        with torch.cuda.graph(self._graph):
+            self._enqueue_step(self._g_imgs, self._g_msks)
+        # kernels of this library inside one replay (the library's launch counter only sees the capture)
+        self.graph_launches_per_step = int(_lib.lib().unetb200_launch_count() - before)
+
+    # ------------------------------------------------------------------ host-facing step (what a user calls)
+    def train_step_host(self, imgs_np, msks_np):
+        """One step fed from HOST arrays (the feed_dict of test_dist.py:394-398): copies this replica's shard from
+        pinned memory, runs the step and reads the step's [loss, dice, sens, spec] back. Returns a numpy array."""
+        if self._h_imgs is None:
+            self._h_imgs = torch.empty(self._d_imgs.shape, dtype=torch.float32).pin_memory()
+            self._h_msks = torch.empty(self._d_msks.shape, dtype=torch.float32).pin_memory()
+        self._h_imgs.numpy()[...] = imgs_np
+        self._h_msks.numpy()[...] = msks_np
+        return self.train_step_pinned(self._h_imgs, self._h_msks)
+
+    def train_step_pinned(self, h_imgs, h_msks):
+        self._d_imgs.copy_(h_imgs, non_blocking=True)
+        self._d_msks.copy_(h_msks, non_blocking=True)
+        met = self.train_step(self._d_imgs, self._d_msks)
+        self._h_metrics.copy_(met, non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+        return self._h_metrics.numpy().copy()
+
+    def h2d_bytes_per_step(self):
+        return (self._d_imgs.numel() + self._d_msks.numel()) * 4
+
+    def d2h_bytes_per_step(self):
+        return 16
+
+    # ------------------------------------------------------------------ evaluation / state
+    def predict(self, imgs, msks=None):
+        """Forward only (dropout stays on, as in the reference: model.py:40). Returns (preds, metrics)."""
+        self.plan.forward(imgs, msks, seed=self.dropout_seed, seed_add=self.step_dev)
+        return self.plan.preds, (self.plan.metrics if msks is not None else None)
+
+    def global_step(self):
+        return int(self.step_dev.item())
+
+    def state_dict(self):
+        p = self.plan
+        sd = {"global_step": self.global_step()}
+        for name in p.variables:
+            sd[name] = p.param(name).detach().cpu().numpy().copy()
+            sd[name + "/Adam"] = p._view(self.m, name).detach().cpu().numpy().copy()      # TF slot names
+            sd[name + "/Adam_1"] = p._view(self.v, name).detach().cpu().numpy().copy()
+        return sd
+
+    def load_state_dict(self, sd):
+        p = self.plan
+        for name in p.variables:
+            p.param(name).copy_(torch.as_tensor(np.asarray(sd[name], np.float32)).to(p.device))
+            if name + "/Adam" in sd:
+                p._view(self.m, name).copy_(torch.as_tensor(np.asarray(sd[name + "/Adam"], np.float32)).to(p.device))
+                p._view(self.v, name).copy_(torch.as_tensor(np.asarray(sd[name + "/Adam_1"], np.float32)).to(p.device))
+        self.step_dev.fill_(int(sd.get("global_step", 0)))
+        p.pack_weights()
