@@ -1,0 +1,159 @@
+"""Host-side logic and the C-ABI surface, without a GPU: the shared library loads and exports every symbol the
+header declares; the native planner reports the TF variable table; data / flags / settings mirror the reference."""
+import os
+import re
+import subprocess
+
+import numpy as np
+import pytest
+
+from util import O, ROOT
+
+from unet_distributed_b200 import _lib, data, parallel, preprocess, settings_dist, synthetic
+from unet_distributed_b200.init import initial_weights
+from unet_distributed_b200.plan import describe_plan
+from unet_distributed_b200.test_dist import build_parser
+
+
+def test_library_exports_every_declared_symbol():
+    protos = _lib.parse_header()
+    assert len(protos) >= 45
+    lib = _lib.lib()                                  # raises if a declared symbol is missing
+    assert lib.unetb200_version() >= 100
+    out = subprocess.run(["nm", "-D", "--defined-only", _lib.LIB_PATH], capture_output=True, text=True).stdout
+    exported = set(re.findall(r"\b(unetb200_\w+)\b", out))
+    assert set(protos) <= exported, sorted(set(protos) - exported)
+    # nothing is exported that the header does not declare
+    assert exported <= set(protos), sorted(exported - set(protos))
+
+
+def test_library_is_sm100a_tcgen05_tma():
+    sass = subprocess.run(["cuobjdump", "-sass", _lib.LIB_PATH], capture_output=True, text=True).stdout
+    assert "sm_100a" in sass
+    for mnemonic in ("UTCHMMA", "UTMALDG", "LDTM"):   # tcgen05.mma, TMA tensor loads, tcgen05.ld
+        assert mnemonic in sass, mnemonic
+
+
+def test_no_cpu_fallback():
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("CPU-only check")
+    from unet_distributed_b200.plan import UNetPlan
+    with pytest.raises(_lib.UnetB200Error):
+        UNetPlan(1, 16, 16)
+
+
+@pytest.mark.parametrize("ups,cin,ncl", [(False, 1, 1), (True, 1, 1), (False, 4, 1), (True, 4, 2)])
+def test_native_planner_variable_table(ups, cin, ncl):
+    d = describe_plan(2, 32, 32, cin, ncl, ups)
+    shapes = O.variable_shapes(ups, cin, ncl)
+    assert list(d["variables"]) == list(shapes)                       # TF creation order and names
+    for k, (off, shp) in d["variables"].items():
+        assert tuple(shp) == tuple(shapes[k]) and off % 4 == 0, k
+    assert d["num_params"] == sum(int(np.prod(s)) for s in shapes.values())
+    offs = [(off, int(np.prod(s))) for off, s in d["variables"].values()]
+    for (o0, n0), (o1, _) in zip(offs, offs[1:]):
+        assert o0 + n0 <= o1                                         # no overlap
+    assert d["num_params_padded"] >= offs[-1][0] + offs[-1][1]
+    # buckets: a partition of the flat buffer, in the order backward completes them
+    b = d["buckets"]
+    assert b[2][0] == 0 and b[2][1] == b[1][0] and b[1][1] == b[0][0] and b[0][1] == d["num_params_padded"]
+    assert b[1][0] == d["variables"]["conv5a/kernel"][0]
+    first_decoder = "conv6a/kernel" if ups else "transConv6/kernel"
+    assert b[0][0] == d["variables"][first_decoder][0]
+    assert d["arena_bytes"] > 0
+
+
+def test_planner_rejects_bad_shapes():
+    for args in ((1, 100, 100, 1, 1), (1, 128, 128, 9, 1), (1, 128, 128, 1, 5), (0, 128, 128, 1, 1)):
+        with pytest.raises(_lib.UnetB200Error):
+            describe_plan(*args)
+
+
+def test_initial_weights_follow_the_named_initialisers():
+    d = describe_plan(1, 16, 16)
+    w = initial_weights(d["variables"], seed=7)
+    assert sum(a.size for a in w.values()) == 7759521
+    assert np.abs(w["conv3b/kernel"]).max() <= np.sqrt(6 / (9 * 128))
+    assert np.abs(w["transConv8/kernel"]).max() <= np.sqrt(6 / (4 * 64 + 4 * 128))
+    assert np.all(w["conv7a/bias"] == 0)
+    w2 = initial_weights(d["variables"], seed=7)
+    assert all(np.array_equal(w[k], w2[k]) for k in w)
+
+
+def test_settings_defaults_are_the_reference_values():
+    # settings_dist.py:17-24 of the reference
+    assert settings_dist.BATCH_SIZE == 1024 and settings_dist.EPOCHS == 10
+    assert settings_dist.LEARNINGRATE == 0.0005 and settings_dist.DECAY_STEPS == 100
+    assert settings_dist.LR_FRACTION == 0.2 and settings_dist.CONST_LEARNINGRATE is True
+    assert settings_dist.USE_UPSAMPLING is False and settings_dist.MODE == 1
+    assert settings_dist.IMG_ROWS == 128 and settings_dist.IN_CHANNEL_NO == 1 and settings_dist.OUT_CHANNEL_NO == 1
+
+
+def test_flags_accept_both_spellings():
+    p = build_parser()
+    a = p.parse_args([])
+    assert a.batch_size == 1024 and a.learning_rate == 0.0005 and a.const_learningrate is True
+    assert a.use_upsampling is False and a.is_sync == 1
+    a = p.parse_args(["--learningrate", "0.001", "--use_upsampling=True", "--const_learningrate", "False",
+                      "--decay_steps", "150", "--lr_fraction", "0.25", "--batch_size", "128", "--epochs", "3"])
+    assert a.learning_rate == 0.001 and a.use_upsampling is True and a.const_learningrate is False
+    assert a.decay_steps == 150 and a.lr_fraction == 0.25 and a.batch_size == 128 and a.epochs == 3
+    assert p.parse_args(["--learning_rate", "0.002"]).learning_rate == 0.002
+
+
+def test_get_epoch_contract():
+    n, B = 37, 8
+    imgs = np.arange(n, dtype=np.float32).reshape(n, 1, 1, 1) * np.ones((1, 4, 4, 1), np.float32)
+    msks = -imgs
+    ep = data.get_epoch(B, imgs, msks, rng=3)
+    assert ep.shape == (4, 2, B, 4, 4, 1)                                # remainder dropped: 37 -> 32
+    assert np.array_equal(ep[:, 0], -ep[:, 1])                           # pairs stay together
+    ids = ep[:, 0, :, 0, 0, 0].ravel()
+    assert len(set(ids.tolist())) == 32 and not np.array_equal(ids, np.arange(32))   # shuffled, no repeats
+    assert np.array_equal(data.get_epoch(B, imgs, msks, rng=3), ep)      # seedable
+    assert np.array_equal(ep[1, 0], ep[1][0])
+    # different channel counts (config 4: 4 modalities, 1 mask channel)
+    imgs4 = np.repeat(imgs, 4, axis=3)
+    ep4 = data.get_epoch(B, imgs4, msks, rng=3)
+    assert ep4[2, 0].shape == (B, 4, 4, 4) and ep4[2, 1].shape == (B, 4, 4, 1) and len(ep4) == 4
+    assert np.array_equal(ep4[2, 0][..., 0], -ep4[2, 1][..., 0])
+
+
+def test_update_channels_and_load_data(tmp_path):
+    synthetic.write_npy_dataset(str(tmp_path), n_train=6, n_test=3, H=16, W=16, seed=1)
+    imgs, msks = preprocess.load_data(str(tmp_path), "_train")
+    assert imgs.shape == (6, 16, 16, 4) and msks.shape == (6, 16, 16, 4)
+    i1, m1 = preprocess.update_channels(imgs, msks, 1, 1, 1)
+    assert i1.dtype == np.float64 and i1.shape == (6, 16, 16, 1)        # np.zeros default dtype, like the reference
+    assert np.array_equal(i1[..., 0], imgs[..., 2]) and np.array_equal(m1[..., 0], msks.sum(axis=3))
+    assert set(np.unique(m1)) <= {0.0, 1.0}
+    i2, m2 = preprocess.update_channels(imgs, msks, 1, 1, 2)
+    assert np.array_equal(i2[..., 0], imgs[..., 0]) and np.array_equal(m2[..., 0], msks[..., 3])
+    i3, m3 = preprocess.update_channels(imgs, msks, 1, 1, 3)
+    assert np.array_equal(i3[..., 0], imgs[..., 1])
+    assert np.array_equal(m3[..., 0], msks[..., 0] + msks[..., 2] + msks[..., 3])
+    old = settings_dist.OUT_PATH
+    try:
+        settings_dist.OUT_PATH = str(tmp_path)
+        a, b, c, d = data.load_all_data()
+        assert a.shape == (6, 16, 16, 1) and b.shape == (6, 16, 16, 1) and c.shape[0] == 3 and d.shape[0] == 3
+    finally:
+        settings_dist.OUT_PATH = old
+
+
+def test_shard_range_is_the_reference_split():
+    # test_dist.py:390-392
+    for B, n in ((1024, 4), (128, 8), (130, 4), (7, 2)):
+        for r in range(n):
+            s, e = parallel.shard_range(B, n, r)
+            assert s == int(B / n) * r and e - s == int(B / n)
+
+
+def test_synthetic_slices():
+    imgs, msks = synthetic.make_slices(16, 64, 64, 1, seed=816)
+    assert imgs.shape == (16, 64, 64, 1) and imgs.dtype == np.float32 and set(np.unique(msks)) <= {0.0, 1.0}
+    assert 0 < (msks.reshape(16, -1).sum(1) == 0).sum() < 16            # some empty masks, some not
+    i2, _ = synthetic.make_slices(16, 64, 64, 1, seed=816)
+    assert np.array_equal(imgs, i2)
+    assert os.path.isdir(ROOT)

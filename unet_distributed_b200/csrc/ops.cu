@@ -238,6 +238,7 @@ size_t conv3x3_wgrad_ws_bytes(int N, int H, int W, int Cin_total, int Cout) {
   // the split count does not depend on how Cin is divided between sources beyond the tile count; use the
   // single-source plan as an upper bound (two sources never have fewer tiles, hence never more splits).
   if (plan_wgrad(wp, N, H, W, 3, 3, 1, Cout, Cin_total, 0) != UB_OK) return 0;
+  if (wp.p.splits <= 1) return 0;  // a single pixel range writes the gradient directly
   return static_cast<size_t>(wp.p.splits) * wp.nweights * sizeof(float);
 }
 
@@ -347,6 +348,7 @@ int tconv2x2_dgrad(const void* dy, int Cout, const void* w_packed_d, void* dx, i
 size_t tconv2x2_wgrad_ws_bytes(int N, int H, int W, int Cin, int Cout) {
   WgradPlan wp;
   if (plan_wgrad(wp, N, H, W, 2, 2, 0, Cout, Cin, 0) != UB_OK) return 0;
+  if (wp.p.splits <= 1) return 0;  // a single pixel range writes the gradient directly
   return static_cast<size_t>(wp.p.splits) * wp.nweights * sizeof(float);
 }
 

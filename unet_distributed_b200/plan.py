@@ -19,6 +19,34 @@ def _stream():
     return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
 
 
+def describe_plan(N, H, W, in_channels=1, n_cl_out=1, use_upsampling=False, dropout=0.2):
+    """Host-only description of a plan (no GPU needed): variable table (TF names -> (offset, shape)), padded flat
+    size, arena bytes and the three gradient buckets.  This is the native planner's own answer, not a Python copy."""
+    L = _lib.lib()
+    h = ctypes.c_void_p()
+    _lib.check(L.unetb200_plan_create(ctypes.byref(h), int(N), int(H), int(W), int(in_channels), int(n_cl_out),
+                                      int(bool(use_upsampling)), float(dropout)), "unetb200_plan_create")
+    try:
+        variables = OrderedDict()
+        name = ctypes.create_string_buffer(64)
+        off, rank = ctypes.c_longlong(), ctypes.c_int()
+        shape = (ctypes.c_int * 4)()
+        for i in range(L.unetb200_plan_num_variables(h)):
+            _lib.check(L.unetb200_plan_variable(h, i, name, 64, ctypes.byref(off), ctypes.byref(rank), shape),
+                       "unetb200_plan_variable")
+            variables[name.value.decode()] = (int(off.value), tuple(shape[k] for k in range(rank.value)))
+        buckets = []
+        b, e = ctypes.c_longlong(), ctypes.c_longlong()
+        for seg in range(3):
+            _lib.check(L.unetb200_plan_bucket(h, seg, ctypes.byref(b), ctypes.byref(e)), "unetb200_plan_bucket")
+            buckets.append((int(b.value), int(e.value)))
+        return {"variables": variables, "num_params_padded": int(L.unetb200_plan_num_params(h)),
+                "num_params": sum(int(np.prod(s)) for _, s in variables.values()),
+                "arena_bytes": int(L.unetb200_plan_arena_bytes(h)), "buckets": buckets}
+    finally:
+        L.unetb200_plan_destroy(h)
+
+
 class UNetPlan:
     """One UNet instance for a fixed (N, H, W, in_channels) input shape on the current CUDA device."""
 
