@@ -60,6 +60,17 @@ int unetb200_conv_first_wgrad(const float* x, const void* dz, float* dw, float* 
 /* BiasAddGrad: db[c] = sum over N*H*W of dz[., c]. */
 size_t unetb200_bias_grad_ws_bytes(int C);
 int unetb200_bias_grad(const void* dz, float* db, void* ws, long long pixels, int C, void* stream);
+/* No counterpart in the reference: the same bias gradient for callers that cannot hand over a workspace because
+ * they cannot allocate one -- plug-ins whose host application owns all device memory and forbids cudaMalloc on its
+ * worker threads, training loops run under a fixed memory budget with a no-allocation rule, embedders that only
+ * ever see the tensors they are given. Inputs and outputs are still the caller's; the partial sums live in a
+ * 2,424,832-byte device array built into the library
+ * (every GPU that loads the library holds it until the process exits). Limit: C <= 512 (8 * power of two); larger C
+ * returns an error that names the limit -- use unetb200_bias_grad then. The first call on each device looks up the
+ * array's device address (host-side work): make that call before any stream capture starts. All calls on a device
+ * share the array; calls that overlap on the GPU (different streams) race. Calls neither cudaMalloc nor cudaFree
+ * nor any allocating routine; nothing in the array needs clearing between calls. */
+int unetb200_bias_grad_static(const void* dz, float* db, long long pixels, int C, void* stream);
 
 /* ---- MaxPooling2D 2x2: model.py:53,57,63,69 -------------------------------------------------------------------- */
 int unetb200_maxpool2x2_fwd(const void* x, void* y, int N, int H, int W, int C, void* stream);

@@ -65,6 +65,9 @@ size_t unetb200_bias_grad_ws_bytes(int C) { return static_cast<size_t>(colsum_ws
 int unetb200_bias_grad(const void* dz, float* db, void* ws, long long pixels, int C, void* stream) {
   return colsum_bf16(dz, db, reinterpret_cast<float*>(ws), pixels, C, S(stream));
 }
+int unetb200_bias_grad_static(const void* dz, float* db, long long pixels, int C, void* stream) {
+  return colsum_bf16_static(dz, db, pixels, C, S(stream));
+}
 
 int unetb200_maxpool2x2_fwd(const void* x, void* y, int N, int H, int W, int C, void* stream) {
   return maxpool2x2_fwd(x, y, N, H, W, C, S(stream));

@@ -1,5 +1,7 @@
 #include "elementwise.cuh"
 
+#include <mutex>
+
 #include "common.h"
 #include "igemm.cuh"
 #include "ptx.cuh"
@@ -679,6 +681,53 @@ int colsum_bf16(const void* dz, float* db, float* ws, long long P, int C, cudaSt
   colsum_kernel<<<kRedBlocks, kThreads, 0, s>>>(reinterpret_cast<const uint4*>(dz), ws, P, C);
   UB_CHECK_CUDA(cudaGetLastError());
   rows_reduce_kernel<<<grid_for(C, 32), 256, 0, s>>>(ws, rows, C, db, C, nullptr);
+  UB_CHECK_CUDA(cudaGetLastError());
+  return UB_OK;
+}
+
+// ------------------------------------------------------------------------------------------ bias gradient, no allocation
+// Same two kernels as colsum_bf16, but the partial-sum rows live in a fixed device array that is part of the
+// loaded library image instead of a caller-provided workspace.  Meant for callers that have nowhere to get a
+// workspace from: plug-ins of host applications that own all device memory and forbid cudaMalloc on their worker
+// threads, loops run under a fixed memory budget with a no-allocation rule, embedders that only see given tensors.
+// Every GPU that loads the library carries these kStaticScratchFloats * 4 bytes (about 2.3 MiB) until the process
+// exits.  All calls on a device share the array: two calls that overlap on the GPU (different streams) race on it.
+// Nothing in it has to start at zero -- the first kernel overwrites every row it later reads -- so stale contents
+// of an earlier call are harmless.
+constexpr int kStaticMaxC = 512;   // widest layer of the UNet
+constexpr long long kStaticScratchFloats = static_cast<long long>(kRedBlocks) * (kThreads / 32) * 256;  // 606,208
+static __device__ __align__(256) float g_bias_grad_scratch[kStaticScratchFloats];
+
+int colsum_bf16_static(const void* dz, float* db, long long P, int C, cudaStream_t s) {
+  UB_REQUIRE(C >= 8 && C <= kStaticMaxC,
+             "bias_grad_static: C = %d is beyond the built-in scratch (supports 8 <= C <= %d); use "
+             "unetb200_bias_grad with a caller workspace for wider tensors", C, kStaticMaxC);
+  int rc = check_groups(C, "bias_grad_static");
+  if (rc) return rc;
+  const int groups = C / 8;
+  const int rows = kRedBlocks * (kThreads / (groups > 32 ? groups : 32));
+  UB_REQUIRE(static_cast<long long>(rows) * C <= kStaticScratchFloats, "bias_grad_static: internal scratch too small");
+  // The array's name is only a host-side handle; the device address has to be asked for, once per device, with
+  // that device current.  This first-call set-up is host work outside any stream, so make the first call on a
+  // device before starting a stream capture.
+  static float* scratch_of_device[64] = {nullptr};
+  static std::mutex mu;
+  int dev = 0;
+  UB_CHECK_CUDA(cudaGetDevice(&dev));
+  UB_REQUIRE(dev >= 0 && dev < 64, "bias_grad_static: device index %d unsupported", dev);
+  float* scratch = nullptr;
+  {
+    std::lock_guard<std::mutex> lk(mu);
+    if (!scratch_of_device[dev]) {
+      void* p = nullptr;
+      UB_CHECK_CUDA(cudaGetSymbolAddress(&p, g_bias_grad_scratch));
+      scratch_of_device[dev] = static_cast<float*>(p);
+    }
+    scratch = scratch_of_device[dev];
+  }
+  colsum_kernel<<<kRedBlocks, kThreads, 0, s>>>(reinterpret_cast<const uint4*>(dz), scratch, P, C);
+  UB_CHECK_CUDA(cudaGetLastError());
+  rows_reduce_kernel<<<grid_for(C, 32), 256, 0, s>>>(scratch, rows, C, db, C, nullptr);
   UB_CHECK_CUDA(cudaGetLastError());
   return UB_OK;
 }

@@ -40,6 +40,8 @@ int head_bwd(const void* x, const float* w, const float* y_true, const float* p,
 // db[c] = sum over pixels of dz[pixel][c] (bf16 in, fp32 out); ws needs colsum_ws_floats(C) floats.
 long long colsum_ws_floats(int C);
 int colsum_bf16(const void* dz, float* db, float* ws, long long P, int C, cudaStream_t s);
+// Same result without a workspace argument: partial sums go to a fixed device array inside the library (C <= 512).
+int colsum_bf16_static(const void* dz, float* db, long long P, int C, cudaStream_t s);
 
 // Weight packing fp32 master (TF layout) -> bf16 GEMM operand layouts.
 //   conv fwd  : out[co][tap][ci] = w[tap][ci][co]
