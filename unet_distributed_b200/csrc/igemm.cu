@@ -102,35 +102,39 @@ igemm_kernel(const __grid_constant__ IgemmParams p, const __grid_constant__ CUte
       }
     }
   } else if (warp == 1) {
-    // ------------------------------------------------------------ MMA issuer (one thread)
-    if (lane == 0) {
-      const uint32_t idesc = umma_idesc_bf16(128, static_cast<uint32_t>(p.block_n), 0, 0);
-      const uint32_t sw = p.kc == 64 ? UMMA_SW_128B : UMMA_SW_64B;
-      const uint32_t sbo = static_cast<uint32_t>(8 * p.kc * 2);  // 8 rows of kc bf16
-      const int ksteps = p.kc / 16;
-      int stage = 0;
-      uint32_t phase = 0;
-      int it = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
-        const int acc = it & 1;
-        mbar_wait(&bars->tmem_empty[acc], (((it >> 1) & 1) ^ 1u));
+    // ------------------------------------------------------------ MMA issuer
+    // The warp walks the uniform control flow together; one elected lane issues (bare UTCHMMAs, uniform registers).
+    const uint32_t idesc = umma_idesc_bf16(128, static_cast<uint32_t>(p.block_n), 0, 0);
+    const uint32_t sw = p.kc == 64 ? UMMA_SW_128B : UMMA_SW_64B;
+    const uint32_t sbo = static_cast<uint32_t>(8 * p.kc * 2);  // 8 rows of kc bf16
+    const uint64_t desc_hi = umma_smem_desc(0, 0, sbo, sw);
+    int stage = 0;
+    uint32_t phase = 0;
+    int it = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
+      const int acc = it & 1;
+      mbar_wait(&bars->tmem_empty[acc], (((it >> 1) & 1) ^ 1u));
+      tc_fence_after();
+      const uint32_t d_tmem = tmem_base + static_cast<uint32_t>(acc * p.block_n);
+      for (int kb = 0; kb < num_kb; ++kb) {
+        mbar_wait(&bars->full[stage], phase);
         tc_fence_after();
-        const uint32_t d_tmem = tmem_base + static_cast<uint32_t>(acc * p.block_n);
-        for (int kb = 0; kb < num_kb; ++kb) {
-          mbar_wait(&bars->full[stage], phase);
-          tc_fence_after();
-          const uint32_t sa = smem_u32(smem + stage * stage_bytes);
-          const uint32_t sb = sa + static_cast<uint32_t>(a_bytes);
-          const uint64_t adesc = umma_smem_desc(sa, 0, sbo, sw);
-          const uint64_t bdesc = umma_smem_desc(sb, 0, sbo, sw);
-          for (int k = 0; k < ksteps; ++k) {
-            umma_f16(d_tmem, adesc + static_cast<uint64_t>(2 * k), bdesc + static_cast<uint64_t>(2 * k), idesc,
-                     (kb | k) ? 1u : 0u);
+        const uint32_t sa = smem_u32(smem + stage * stage_bytes);
+        const uint64_t adesc = desc_hi + (sa >> 4);
+        const uint64_t bdesc = desc_hi + ((sa + static_cast<uint32_t>(a_bytes)) >> 4);
+        if (elect_one()) {
+          const uint32_t acc_flag = kb ? 1u : 0u;
+          umma_f16(d_tmem, adesc, bdesc, idesc, acc_flag);
+          umma_f16(d_tmem, adesc + 2, bdesc + 2, idesc, 1u);
+          if (p.kc == 64) {
+            umma_f16(d_tmem, adesc + 4, bdesc + 4, idesc, 1u);
+            umma_f16(d_tmem, adesc + 6, bdesc + 6, idesc, 1u);
           }
           umma_commit(&bars->empty[stage]);
-          if (++stage == p.stages) { stage = 0; phase ^= 1u; }
+          if (kb == num_kb - 1) umma_commit(&bars->tmem_full[acc]);
         }
-        umma_commit(&bars->tmem_full[acc]);
+        __syncwarp();
+        if (++stage == p.stages) { stage = 0; phase ^= 1u; }
       }
     }
   } else {

@@ -4,6 +4,7 @@
 #include <cstring>
 
 #include "common.h"
+#include "conv_halo.cuh"
 #include "igemm.cuh"
 #include "wgrad.cuh"
 
@@ -94,6 +95,34 @@ int pick_block_n(int ncols_per_dest) {
   return 0;
 }
 
+// Run a 3x3 conv (forward or dgrad, described by the generic params `p`) on the halo kernel when the shape allows.
+// Returns true when it took the launch (status in *rc).
+bool try_halo(const IgemmParams& p, const void* src0, int C0, const void* src1, int C1, const void* w_packed,
+              int ncols, int ktot, cudaStream_t s, int* rc) {
+  HaloParams hp;
+  std::memset(&hp, 0, sizeof(hp));
+  if (!halo_plan(hp, p.N, p.H, p.W, p.kc, ncols)) return false;
+  hp.num_src = p.num_src;
+  for (int i = 0; i < 2; ++i) {
+    hp.src_kblocks[i] = p.src_kblocks[i];
+    hp.src_ci_off[i] = p.src_ci_off[i];
+  }
+  hp.epi = p.epi;
+  const Box hb = {1, 18, 8 * hp.J + 2};
+  CUtensorMap a0, a1, bm;
+  *rc = nhwc_map(&a0, src0, p.N, p.H, p.W, C0, p.kc, hb);
+  if (*rc) return true;
+  a1 = a0;
+  if (C1) {
+    *rc = nhwc_map(&a1, src1, p.N, p.H, p.W, C1, p.kc, hb);
+    if (*rc) return true;
+  }
+  *rc = weight_map(&bm, w_packed, ncols, 9, ktot, p.kc, hp.block_n);
+  if (*rc) return true;
+  *rc = halo_launch(hp, a0, a1, bm, s);
+  return true;
+}
+
 }  // namespace
 
 // ------------------------------------------------------------------------------------------------ conv3x3 forward
@@ -128,8 +157,10 @@ int conv3x3_fwd(ConvSrc x0, ConvSrc x1, const void* w_packed, const float* bias,
   p.epi.drop_seed = drop.seed;
   p.epi.drop_stream = drop.stream;
   p.epi.drop_seed_add = drop.seed_add;
+  int rc = UB_OK;
+  if (try_halo(p, x0.ptr, x0.C, x1.ptr, C1, w_packed, Cout, x0.C + C1, s, &rc)) return rc;
   CUtensorMap a0, a1, bm;
-  int rc = nhwc_map(&a0, x0.ptr, N, H, W, x0.C, kc, b);
+  rc = nhwc_map(&a0, x0.ptr, N, H, W, x0.C, kc, b);
   if (rc) return rc;
   a1 = a0;
   if (C1) {
@@ -173,8 +204,10 @@ int conv3x3_dgrad(const void* dz, int Cout, const void* w_packed_d, DgradDst d0,
              "conv3x3_dgrad: both destinations must share the mask scale");
   if (!d0.mask && d1.mask) p.epi.mask_scale = d1.scale;
   p.epi.drop_keep = 1.0f;
+  int rc = UB_OK;
+  if (try_halo(p, dz, Cout, nullptr, 0, w_packed_d, d0.C + C1, Cout, s, &rc)) return rc;
   CUtensorMap a0, bm;
-  int rc = nhwc_map(&a0, dz, N, H, W, Cout, kc, b);
+  rc = nhwc_map(&a0, dz, N, H, W, Cout, kc, b);
   if (rc) return rc;
   rc = weight_map(&bm, w_packed_d, d0.C + C1, 9, Cout, kc, block_n);
   if (rc) return rc;

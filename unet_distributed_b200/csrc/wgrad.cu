@@ -115,7 +115,8 @@ wgrad_kernel(const __grid_constant__ WgradParams p, const __grid_constant__ CUte
       }
     }
   } else if (warp == 1) {
-    if (lane == 0 && nkb > 0) {
+    if (nkb > 0) {
+      // warp-uniform control flow, one elected lane issues
       const uint32_t idesc = umma_idesc_bf16(128, static_cast<uint32_t>(block_n), 1, 1);
       const uint32_t z_sw = p.z_atom == 64 ? UMMA_SW_128B : UMMA_SW_64B;
       const uint32_t x_sw = x_atom == 64 ? UMMA_SW_128B : UMMA_SW_64B;
@@ -123,24 +124,28 @@ wgrad_kernel(const __grid_constant__ WgradParams p, const __grid_constant__ CUte
       const uint32_t x_sbo = static_cast<uint32_t>(8 * x_atom * 2);
       const uint32_t z_kstep = static_cast<uint32_t>(16 * p.z_atom * 2) >> 4;  // 16 pixels, in 16-byte units
       const uint32_t x_kstep = static_cast<uint32_t>(16 * x_atom * 2) >> 4;
+      const uint64_t a_hi = umma_smem_desc(0, z_atom_bytes, z_sbo, z_sw);
+      const uint64_t b_hi = umma_smem_desc(0, x_atom_bytes, x_sbo, x_sw);
       int stage = 0;
       uint32_t phase = 0;
       for (int kb = 0; kb < nkb; ++kb) {
         mbar_wait(&bars->full[stage], phase);
         tc_fence_after();
         const uint32_t sa = smem_u32(smem + stage * kStageBytes);
-        const uint32_t sb = sa + kOperandBytes;
-        const uint64_t adesc = umma_smem_desc(sa, z_atom_bytes, z_sbo, z_sw);
-        const uint64_t bdesc = umma_smem_desc(sb, x_atom_bytes, x_sbo, x_sw);
+        const uint64_t adesc = a_hi + (sa >> 4);
+        const uint64_t bdesc = b_hi + ((sa + kOperandBytes) >> 4);
+        if (elect_one()) {
 #pragma unroll
-        for (int k = 0; k < kKP / 16; ++k) {
-          umma_f16(tmem_base, adesc + static_cast<uint64_t>(k * z_kstep), bdesc + static_cast<uint64_t>(k * x_kstep),
-                   idesc, (kb | k) ? 1u : 0u);
+          for (int k = 0; k < kKP / 16; ++k) {
+            umma_f16(tmem_base, adesc + static_cast<uint64_t>(k * z_kstep), bdesc + static_cast<uint64_t>(k * x_kstep),
+                     idesc, (kb | k) ? 1u : 0u);
+          }
+          umma_commit(&bars->empty[stage]);
+          if (kb == nkb - 1) umma_commit(&bars->tmem_full);
         }
-        umma_commit(&bars->empty[stage]);
+        __syncwarp();
         if (++stage == p.stages) { stage = 0; phase ^= 1u; }
       }
-      umma_commit(&bars->tmem_full);
     }
   } else {
     const int quarter = warp & 3;
