@@ -1,0 +1,7 @@
+#!/bin/bash
+# launch list of one bench run: every kernel with its device time (cold-cache, serialised: compare SHARES)
+mkdir -p gpurun_out
+CMD="python bench.py --steps 2 --warmup 3 --no-graph --no-cpu-baseline --decoder ${1:-upsampling}"
+$CMD > gpurun_out/plain.log 2>&1 &&
+ncu --metrics gpu__time_duration.sum --clock-control none --csv --log-file gpurun_out/launches.csv $CMD > gpurun_out/ncu.log 2>&1
+echo "ncu exit $?"; tail -2 gpurun_out/ncu.log; wc -l gpurun_out/launches.csv

@@ -10,7 +10,7 @@ namespace ub {
 
 namespace {
 
-constexpr int kRedBlocks = 296;  // 2 x 148 SMs: fixed so per-block partial layouts are shape independent
+constexpr int kRedBlocks = 592;  // 4 x 148 SMs: fixed so per-block partial layouts are shape independent
 constexpr int kThreads = 256;
 
 __device__ __forceinline__ void unpack8(const uint4& v, float (&f)[8]) {
@@ -40,49 +40,53 @@ __global__ void conv_first_fwd_kernel(const float* __restrict__ x, const float* 
   for (int i = threadIdx.x; i < Cout; i += blockDim.x) sw[nw + i] = bias ? bias[i] : 0.0f;
   __syncthreads();
   const int groups = Cout / 8;
-  const long long total = static_cast<long long>(N) * H * W * groups;
-  const long long idx = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
-  if (idx >= total) return;
-  const int g = static_cast<int>(idx % groups);
-  long long pix = idx / groups;
-  const int wq = static_cast<int>(pix % W);
-  const int hq = static_cast<int>((pix / W) % H);
-  const long long n = pix / (static_cast<long long>(W) * H);
-  float acc[8];
+  const unsigned total = static_cast<unsigned>(N) * H * W * groups;
+  const unsigned stride = gridDim.x * blockDim.x;
+  for (unsigned idx = blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += stride) {
+    const int g = static_cast<int>(idx % groups);
+    const unsigned pix = idx / groups;
+    const int wq = static_cast<int>(pix % W);
+    const unsigned row = pix / W;              // n*H + h
+    const int hq = static_cast<int>(row % H);
+    float acc[8];
 #pragma unroll
-  for (int j = 0; j < 8; ++j) acc[j] = sw[nw + g * 8 + j];
-  for (int r = 0; r < 3; ++r) {
-    const int hh = hq + r - 1;
-    if (hh < 0 || hh >= H) continue;
-    for (int s = 0; s < 3; ++s) {
-      const int ww = wq + s - 1;
-      if (ww < 0 || ww >= W) continue;
-      const float* xp = x + ((n * H + hh) * W + ww) * Cin;
-      const float* wp = sw + ((r * 3 + s) * Cin) * Cout + g * 8;
-      for (int ci = 0; ci < Cin; ++ci) {
-        const float xv = __ldg(xp + ci);
+    for (int j = 0; j < 8; ++j) acc[j] = sw[nw + g * 8 + j];
 #pragma unroll
-        for (int j = 0; j < 8; ++j) acc[j] = fmaf(xv, wp[ci * Cout + j], acc[j]);
+    for (int r = 0; r < 3; ++r) {
+      const int hh = hq + r - 1;
+      if (hh < 0 || hh >= H) continue;
+#pragma unroll
+      for (int s = 0; s < 3; ++s) {
+        const int ww = wq + s - 1;
+        if (ww < 0 || ww >= W) continue;
+        const float* xp = x + (static_cast<size_t>(row + r - 1) * W + ww) * Cin;
+        const float* wp = sw + ((r * 3 + s) * Cin) * Cout + g * 8;
+        for (int ci = 0; ci < Cin; ++ci) {
+          const float xv = __ldg(xp + ci);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) acc[j] = fmaf(xv, wp[ci * Cout + j], acc[j]);
+        }
       }
     }
-  }
 #pragma unroll
-  for (int j = 0; j < 8; ++j) acc[j] = fmaxf(acc[j], 0.0f);
-  y[idx] = pack8(acc);
+    for (int j = 0; j < 8; ++j) acc[j] = fmaxf(acc[j], 0.0f);
+    y[idx] = pack8(acc);
+  }
 }
 
 // ------------------------------------------------------------------------------------------ conv1a wgrad (+ bias grad)
 // Each thread owns one 8-channel group of dz and walks pixels with a stride; partial sums go block -> ws -> final.
 __global__ void conv_first_wgrad_kernel(const float* __restrict__ x, const uint4* __restrict__ dz,
                                         float* __restrict__ ws, int N, int H, int W, int Cin, int Cout) {
-  // every warp owns one row of partial sums in ws (no atomics: the reduction order is fixed, results are
-  // bit-reproducible); rows are summed by rows_reduce_kernel
+  // every warp owns one row of partial sums in shared memory, the block sums its warps in a fixed order and writes
+  // one row to ws (no atomics: results are bit-reproducible); rows are summed by rows_reduce_kernel
+  extern __shared__ float red[];  // [warps][nout]
   const int nout = 9 * Cin * Cout + Cout;
   const int groups = Cout / 8;
   const int g = threadIdx.x % groups;
-  float* wout = ws + (static_cast<long long>(blockIdx.x) * (blockDim.x >> 5) + (threadIdx.x >> 5)) * nout;
-  const long long total = static_cast<long long>(N) * H * W * groups;
-  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  float* wout = red + (threadIdx.x >> 5) * nout;
+  const unsigned total = static_cast<unsigned>(N) * H * W * groups;
+  const unsigned stride = gridDim.x * blockDim.x;
   for (int ci = 0; ci < Cin; ++ci) {
     float acc[9][8];
     float accb[8];
@@ -92,11 +96,11 @@ __global__ void conv_first_wgrad_kernel(const float* __restrict__ x, const uint4
       for (int j = 0; j < 8; ++j) acc[t][j] = 0.0f;
 #pragma unroll
     for (int j = 0; j < 8; ++j) accb[j] = 0.0f;
-    for (long long idx = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; idx < total; idx += stride) {
-      long long pix = idx / groups;
+    for (unsigned idx = blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += stride) {
+      const unsigned pix = idx / groups;
       const int wq = static_cast<int>(pix % W);
-      const int hq = static_cast<int>((pix / W) % H);
-      const long long n = pix / (static_cast<long long>(W) * H);
+      const unsigned row = pix / W;            // n*H + h
+      const int hq = static_cast<int>(row % H);
       float d[8];
       unpack8(__ldg(dz + idx), d);
       if (ci == 0) {
@@ -110,7 +114,8 @@ __global__ void conv_first_wgrad_kernel(const float* __restrict__ x, const uint4
         for (int s = 0; s < 3; ++s) {
           const int ww = wq + s - 1;
           float xv = 0.0f;
-          if (hh >= 0 && hh < H && ww >= 0 && ww < W) xv = __ldg(x + ((n * H + hh) * W + ww) * Cin + ci);
+          if (hh >= 0 && hh < H && ww >= 0 && ww < W)
+            xv = __ldg(x + (static_cast<size_t>(row + r - 1) * W + ww) * Cin + ci);
 #pragma unroll
           for (int j = 0; j < 8; ++j) acc[r * 3 + s][j] = fmaf(xv, d[j], acc[r * 3 + s][j]);
         }
@@ -134,6 +139,13 @@ __global__ void conv_first_wgrad_kernel(const float* __restrict__ x, const uint4
         if ((threadIdx.x & 31) < groups) wout[9 * Cin * Cout + g * 8 + j] = v;
       }
     }
+  }
+  __syncthreads();
+  const int warps = blockDim.x >> 5;
+  for (int i = threadIdx.x; i < nout; i += blockDim.x) {
+    float s = red[i];
+    for (int wv = 1; wv < warps; ++wv) s += red[wv * nout + i];
+    ws[static_cast<size_t>(blockIdx.x) * nout + i] = s;
   }
 }
 
@@ -290,12 +302,16 @@ __global__ void head_fwd_kernel(const uint4* __restrict__ x, const float* __rest
   // every lane of a pixel group must stay in the loop for the shuffles: iterate on a uniform bound
   const long long iters = (total + stride - 1) / stride;
   long long idx = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  uint4 nxt = make_uint4(0u, 0u, 0u, 0u);
+  if (idx < total) nxt = __ldg(x + idx);
   for (long long itn = 0; itn < iters; ++itn, idx += stride) {
     const bool live = idx < total;
+    const uint4 cur = nxt;
+    if (idx + stride < total) nxt = __ldg(x + idx + stride);   // next iteration's load is already in flight
     float acc[kMaxCl] = {0.0f, 0.0f, 0.0f, 0.0f};
     if (live) {
       float f[8];
-      unpack8(__ldg(x + idx), f);
+      unpack8(cur, f);
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
         for (int k = 0; k < n_cl; ++k) acc[k] = fmaf(f[j], sh[(sub * 8 + j) * n_cl + k], acc[k]);
@@ -387,10 +403,12 @@ __global__ void head_bwd_kernel(const uint4* __restrict__ x, const float* __rest
     for (int j = 0; j < 8; ++j) o[j] = f[j] > 0.0f ? o[j] : 0.0f;
     dx[idx] = pack8(o);
   }
-  // reduce over lanes sharing `sub`; every warp then owns one row of partials in ws (fixed order, no atomics)
+  // reduce over lanes sharing `sub`; every warp owns one row in shared memory, the block sums its warps in a fixed
+  // order and writes one row of partials to ws (no atomics)
   const int lane = threadIdx.x & 31;
   const int nout = C * n_cl + n_cl;
-  float* wout = ws + (static_cast<long long>(blockIdx.x) * (blockDim.x >> 5) + (threadIdx.x >> 5)) * nout;
+  float* red = sh + C * n_cl;   // [warps][nout]
+  float* wout = red + (threadIdx.x >> 5) * nout;
 #pragma unroll
   for (int k = 0; k < kMaxCl; ++k) {
     if (k < n_cl) {
@@ -405,19 +423,37 @@ __global__ void head_bwd_kernel(const uint4* __restrict__ x, const float* __rest
       if (lane == 0) wout[C * n_cl + k] = vb;
     }
   }
+  __syncthreads();
+  const int warps = blockDim.x >> 5;
+  for (int i = threadIdx.x; i < nout; i += blockDim.x) {
+    float s = red[i];
+    for (int wv = 1; wv < warps; ++wv) s += red[wv * nout + i];
+    ws[static_cast<size_t>(blockIdx.x) * nout + i] = s;
+  }
 }
 
 // ------------------------------------------------------------------------------------------ bias gradient (column sums)
 __global__ void colsum_kernel(const uint4* __restrict__ dz, float* __restrict__ ws, long long P, int C) {
-  // rows of partial sums in ws: one per warp (C <= 256) or per run of C/8 consecutive threads (C > 256)
+  // one row of partial sums per block in ws; inside the block: lanes -> warps (or runs of C/8 threads) -> fixed-order sum
+  extern __shared__ float red[];  // [blockDim/span][C]
   const int groups = C / 8;
   const int g = threadIdx.x % groups;
   const int span = groups > 32 ? groups : 32;
-  float* wout = ws + ((static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x) / span) * C;
+  const int row = threadIdx.x / span;
+  const int rows = blockDim.x / span;
   const long long total = P * groups;
   const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
   float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-  for (long long idx = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; idx < total; idx += stride) {
+  long long idx = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  for (; idx + 3 * stride < total; idx += 4 * stride) {   // four independent 16-byte loads in flight
+    const uint4 v0 = __ldg(dz + idx), v1 = __ldg(dz + idx + stride), v2 = __ldg(dz + idx + 2 * stride),
+                v3 = __ldg(dz + idx + 3 * stride);
+    float f0[8], f1[8], f2[8], f3[8];
+    unpack8(v0, f0); unpack8(v1, f1); unpack8(v2, f2); unpack8(v3, f3);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[j] += (f0[j] + f1[j]) + (f2[j] + f3[j]);
+  }
+  for (; idx < total; idx += stride) {
     float f[8];
     unpack8(__ldg(dz + idx), f);
 #pragma unroll
@@ -428,7 +464,13 @@ __global__ void colsum_kernel(const uint4* __restrict__ dz, float* __restrict__ 
   for (int j = 0; j < 8; ++j) {
     float v = acc[j];
     for (int o = 16; o >= groups; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-    if (groups >= 32 || lane < groups) wout[g * 8 + j] = v;
+    if (groups >= 32 || lane < groups) red[row * C + g * 8 + j] = v;
+  }
+  __syncthreads();
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    float s = red[c];
+    for (int r = 1; r < rows; ++r) s += red[r * C + c];
+    ws[static_cast<long long>(blockIdx.x) * C + c] = s;
   }
 }
 
@@ -566,9 +608,12 @@ int conv_first_fwd(const float* x, const float* w, const float* bias, void* y, i
   UB_REQUIRE(Cin >= 1 && Cin <= 8, "conv_first_fwd: Cin %d outside 1..8", Cin);
   UB_REQUIRE(Cout % 8 == 0 && Cout <= 64, "conv_first_fwd: Cout %d unsupported", Cout);
   const long long total = static_cast<long long>(N) * H * W * (Cout / 8);
+  UB_REQUIRE(total < (1ll << 31), "conv_first_fwd: tensor too large");
   const size_t smem = (9 * Cin * Cout + Cout) * sizeof(float);
-  conv_first_fwd_kernel<<<grid_for(total, kThreads), kThreads, smem, s>>>(x, w, bias, reinterpret_cast<uint4*>(y), N, H,
-                                                                          W, Cin, Cout);
+  unsigned blocks = grid_for(total, kThreads);
+  const unsigned cap = 8u * static_cast<unsigned>(device_sm_count());   // weights are staged once per block
+  if (blocks > cap) blocks = cap;
+  conv_first_fwd_kernel<<<blocks, kThreads, smem, s>>>(x, w, bias, reinterpret_cast<uint4*>(y), N, H, W, Cin, Cout);
   UB_CHECK_CUDA(cudaGetLastError());
   return UB_OK;
 }
@@ -584,9 +629,16 @@ int conv_first_wgrad(const float* x, const void* dz, float* dw, float* db, float
   UB_REQUIRE(Cout % 8 == 0 && groups >= 1 && groups <= 8 && (groups & (groups - 1)) == 0,
              "conv_first_wgrad: Cout %d unsupported", Cout);
   const int nout = 9 * Cin * Cout + Cout;
-  conv_first_wgrad_kernel<<<kRedBlocks, kThreads, 0, s>>>(x, reinterpret_cast<const uint4*>(dz), ws, N, H, W, Cin, Cout);
+  UB_REQUIRE(static_cast<long long>(N) * H * W * groups < (1ll << 31), "conv_first_wgrad: tensor too large");
+  const size_t smem = static_cast<size_t>(kThreads / 32) * nout * sizeof(float);
+  if (smem > 48 * 1024) {
+    UB_CHECK_CUDA(cudaFuncSetAttribute(conv_first_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       static_cast<int>(smem)));
+  }
+  conv_first_wgrad_kernel<<<kRedBlocks, kThreads, smem, s>>>(x, reinterpret_cast<const uint4*>(dz), ws, N, H, W, Cin,
+                                                            Cout);
   UB_CHECK_CUDA(cudaGetLastError());
-  rows_reduce_kernel<<<grid_for(nout, 32), 256, 0, s>>>(ws, kRedBlocks * (kThreads / 32), nout, dw, 9 * Cin * Cout, db);
+  rows_reduce_kernel<<<grid_for(nout, 32), 256, 0, s>>>(ws, kRedBlocks, nout, dw, 9 * Cin * Cout, db);
   UB_CHECK_CUDA(cudaGetLastError());
   return UB_OK;
 }
@@ -662,11 +714,11 @@ int head_bwd(const void* x, const float* w, const float* y_true, const float* p,
   const int subs = C / 8;
   UB_REQUIRE(C % 8 == 0 && subs >= 1 && subs <= 32 && (subs & (subs - 1)) == 0, "head_bwd: C %d unsupported", C);
   const int nout = C * n_cl + n_cl;
-  const size_t smem = (C * n_cl) * sizeof(float);
+  const size_t smem = (C * n_cl + (kThreads / 32) * nout) * sizeof(float);
   head_bwd_kernel<<<kRedBlocks, kThreads, smem, s>>>(reinterpret_cast<const uint4*>(x), w, y_true, p, sums, smooth,
                                                      grad_scale, reinterpret_cast<uint4*>(dx), ws, P, C, n_cl);
   UB_CHECK_CUDA(cudaGetLastError());
-  rows_reduce_kernel<<<grid_for(nout, 32), 256, 0, s>>>(ws, kRedBlocks * (kThreads / 32), nout, dw, C * n_cl, db);
+  rows_reduce_kernel<<<grid_for(nout, 32), 256, 0, s>>>(ws, kRedBlocks, nout, dw, C * n_cl, db);
   UB_CHECK_CUDA(cudaGetLastError());
   return UB_OK;
 }
@@ -676,11 +728,10 @@ long long colsum_ws_floats(int C) { return static_cast<long long>(kRedBlocks) * 
 int colsum_bf16(const void* dz, float* db, float* ws, long long P, int C, cudaStream_t s) {
   int rc = check_groups(C, "colsum_bf16");
   if (rc) return rc;
-  const int groups = C / 8;
-  const int rows = kRedBlocks * (kThreads / (groups > 32 ? groups : 32));
-  colsum_kernel<<<kRedBlocks, kThreads, 0, s>>>(reinterpret_cast<const uint4*>(dz), ws, P, C);
+  colsum_kernel<<<kRedBlocks, kThreads, (kThreads / 32) * C * sizeof(float), s>>>(reinterpret_cast<const uint4*>(dz),
+                                                                                 ws, P, C);
   UB_CHECK_CUDA(cudaGetLastError());
-  rows_reduce_kernel<<<grid_for(C, 32), 256, 0, s>>>(ws, rows, C, db, C, nullptr);
+  rows_reduce_kernel<<<grid_for(C, 32), 256, 0, s>>>(ws, kRedBlocks, C, db, C, nullptr);
   UB_CHECK_CUDA(cudaGetLastError());
   return UB_OK;
 }
@@ -695,7 +746,7 @@ int colsum_bf16(const void* dz, float* db, float* ws, long long P, int C, cudaSt
 // Nothing in it has to start at zero -- the first kernel overwrites every row it later reads -- so stale contents
 // of an earlier call are harmless.
 constexpr int kStaticMaxC = 512;   // widest layer of the UNet
-constexpr long long kStaticScratchFloats = static_cast<long long>(kRedBlocks) * (kThreads / 32) * 256;  // 606,208
+constexpr long long kStaticScratchFloats = 606208;  // 2,424,832 bytes; kRedBlocks rows x kStaticMaxC fit twice
 static __device__ __align__(256) float g_bias_grad_scratch[kStaticScratchFloats];
 
 int colsum_bf16_static(const void* dz, float* db, long long P, int C, cudaStream_t s) {
@@ -704,8 +755,7 @@ int colsum_bf16_static(const void* dz, float* db, long long P, int C, cudaStream
              "unetb200_bias_grad with a caller workspace for wider tensors", C, kStaticMaxC);
   int rc = check_groups(C, "bias_grad_static");
   if (rc) return rc;
-  const int groups = C / 8;
-  const int rows = kRedBlocks * (kThreads / (groups > 32 ? groups : 32));
+  const int rows = kRedBlocks;
   UB_REQUIRE(static_cast<long long>(rows) * C <= kStaticScratchFloats, "bias_grad_static: internal scratch too small");
   // The array's name is only a host-side handle; the device address has to be asked for, once per device, with
   // that device current.  This first-call set-up is host work outside any stream, so make the first call on a
@@ -725,7 +775,8 @@ int colsum_bf16_static(const void* dz, float* db, long long P, int C, cudaStream
     }
     scratch = scratch_of_device[dev];
   }
-  colsum_kernel<<<kRedBlocks, kThreads, 0, s>>>(reinterpret_cast<const uint4*>(dz), scratch, P, C);
+  colsum_kernel<<<kRedBlocks, kThreads, (kThreads / 32) * C * sizeof(float), s>>>(reinterpret_cast<const uint4*>(dz),
+                                                                                 scratch, P, C);
   UB_CHECK_CUDA(cudaGetLastError());
   rows_reduce_kernel<<<grid_for(C, 32), 256, 0, s>>>(scratch, rows, C, db, C, nullptr);
   UB_CHECK_CUDA(cudaGetLastError());

@@ -271,13 +271,39 @@ size_t conv3x3_wgrad_ws_bytes(int N, int H, int W, int Cin_total, int Cout) {
   // the split count does not depend on how Cin is divided between sources beyond the tile count; use the
   // single-source plan as an upper bound (two sources never have fewer tiles, hence never more splits).
   if (plan_wgrad(wp, N, H, W, 3, 3, 1, Cout, Cin_total, 0) != UB_OK) return 0;
-  if (wp.p.splits <= 1) return 0;  // a single pixel range writes the gradient directly
-  return static_cast<size_t>(wp.p.splits) * wp.nweights * sizeof(float);
+  size_t generic = 0;
+  if (wp.p.splits > 1) generic = static_cast<size_t>(wp.p.splits) * wp.nweights * sizeof(float);
+  // the halo variant (32/64-channel sources) keeps one partial gradient per CTA; Cin_total may be one source or
+  // the concat of two, so take the larger per-source case
+  size_t halo = 0;
+  const int cx = Cin_total >= 64 ? 64 : 32;
+  if (Cin_total <= 128 && wgrad_halo_supported(H, W, cx, Cout)) halo = wgrad_halo_ws_bytes(N, H, W, cx, Cout);
+  return generic > halo ? generic : halo;
 }
 
 int conv3x3_wgrad(const void* dz, int Cout, ConvSrc x0, ConvSrc x1, float* dw, void* ws, size_t ws_bytes, int N, int H,
                   int W, cudaStream_t s) {
   const int C1 = x1.ptr ? x1.C : 0;
+  if (wgrad_halo_supported(H, W, x0.C, Cout) && (!C1 || wgrad_halo_supported(H, W, C1, Cout))) {
+    const ConvSrc srcs[2] = {x0, x1};
+    int off = 0;
+    for (int i = 0; i < (C1 ? 2 : 1); ++i) {
+      const int Cx = srcs[i].C;
+      const size_t need = wgrad_halo_ws_bytes(N, H, W, Cx, Cout);
+      UB_REQUIRE(ws != nullptr && ws_bytes >= need, "conv3x3_wgrad: workspace of %zu bytes needed, %zu given", need,
+                 ws_bytes);
+      const int J = wgrad_halo_pick_J(Cx, W);
+      CUtensorMap xm, zm;
+      int rc = nhwc_map(&xm, srcs[i].ptr, N, H, W, Cx, Cx, Box{1, 18, 8 * J + 2});
+      if (rc) return rc;
+      rc = nhwc_map(&zm, dz, N, H, W, Cout, Cout, Box{1, 16, 8 * J});
+      if (rc) return rc;
+      rc = wgrad_halo_launch(xm, zm, N, H, W, Cx, Cout, J, dw, x0.C + C1, off, reinterpret_cast<float*>(ws), s);
+      if (rc) return rc;
+      off += Cx;
+    }
+    return UB_OK;
+  }
   WgradPlan wp;
   int rc = plan_wgrad(wp, N, H, W, 3, 3, 1, Cout, x0.C, C1);
   if (rc) return rc;

@@ -36,6 +36,14 @@ struct WgradParams {
 int wgrad_launch(const WgradParams& p, const CUtensorMap& z, const CUtensorMap& x0, const CUtensorMap& x1,
                  cudaStream_t stream);
 
+// Halo variant for 32/64-channel inputs and gradients (wgrad_halo.cu): all nine taps per CTA, one halo tile per
+// super-tile, filter columns stacked along GEMM M. One launch per source of a concatenated input.
+bool wgrad_halo_supported(int H, int W, int Cx, int Cz);
+int wgrad_halo_pick_J(int Cx, int W);
+size_t wgrad_halo_ws_bytes(int N, int H, int W, int Cx, int Cz);
+int wgrad_halo_launch(const CUtensorMap& x_map, const CUtensorMap& z_map, int N, int H, int W, int Cx, int Cz, int J,
+                      float* dw, int cin_total, int ci_off, float* ws, cudaStream_t stream);
+
 // out[i] = sum_s ws[s*stride + i] (fixed order), i < n.
 int splitk_reduce_launch(const float* ws, long long split_stride, int splits, float* out, long long n,
                          cudaStream_t stream);

@@ -1,0 +1,299 @@
+// Weight gradient of a 3x3 conv for 32- and 64-channel inputs (the 128x128 and 64x64 levels of the UNet), where the
+// per-tap wgrad engine (wgrad.cu) is issue- and L2-bound: C is so small that one (tap, Cout, Cin) tile is a sliver of
+// the tensor core and every tap re-reads both operands.
+//
+// Here a CTA walks super-tiles of 16 rows x 8J columns. Per super-tile it loads ONE halo tile of the input
+// (18 x (8J+2) pixels) and ONE tile of the output gradient, and accumulates ALL nine taps in TMEM:
+//   * the reduction (GEMM K) runs over pixels: 16 pixels per MMA = rows 2i and 2i+1 of an 8-wide strip; the strip's
+//     8 pixels are 8 consecutive smem rows and the stride to the next image row is the descriptor's SBO;
+//   * filter columns are stacked along GEMM M: both operands are MN-major, and the "next 32/64-channel atom along M"
+//     (the descriptor's LBO) is set to ONE pixel row, so atom a of the A operand is the same halo tile shifted by a
+//     pixels = tap column s0+a. One MMA therefore produces dW for up to four filter columns at once:
+//     D[(s, ci), co] += sum_pixels X[pixel + (r, s), ci] * dZ[pixel, co];
+//   * filter rows r = 0..2 are three start addresses into the same halo tile and three accumulators.
+// Partial results of the CTAs are summed in a fixed order by wgrad_halo_reduce_kernel (bit-reproducible).
+#include "wgrad.cuh"
+
+#include <cstdlib>
+
+#include "common.h"
+#include "ptx.cuh"
+
+namespace ub {
+
+namespace {
+
+constexpr int kThreads = 256;   // warp0 TMA producer, warp1 MMA + TMEM, warps 4..7 epilogue
+constexpr int kMaxStages = 3;
+constexpr int kTH = 16;
+
+struct WgradHaloParams {
+  int N, H, W;
+  int J;                    // 8-wide strips per super-tile
+  int tiles_h, tiles_w;
+  int Cx, Cz;               // 32 or 64 each
+  int stages;
+  float* ws;                // [gridDim.x][9][Cx][Cz] partial gradients
+};
+
+struct __align__(8) WgradHaloBarriers {
+  uint64_t full[kMaxStages];
+  uint64_t empty[kMaxStages];
+  uint64_t tmem_full;
+  uint32_t tmem_base;
+};
+
+__host__ __device__ inline int round_up_1k(int x) { return (x + 1023) & ~1023; }
+
+template <int J>
+__device__ __forceinline__ void issue_supertile(uint32_t tmem_base, uint64_t x_desc0, uint64_t z_desc0, uint32_t idesc,
+                                                int P, uint32_t xrow16, uint32_t zrow16, int groups, int n_cols,
+                                                uint32_t accumulate_first) {
+  // i: pairs of image rows (16 pixels of reduction), j: strips, r: filter rows, g: groups of stacked filter columns
+#pragma unroll 1
+  for (int i = 0; i < kTH / 2; ++i) {
+#pragma unroll
+    for (int j = 0; j < J; ++j) {
+      const uint64_t zd = z_desc0 + static_cast<uint64_t>((2 * i * 8 * J + 8 * j) * zrow16);
+#pragma unroll
+      for (int r = 0; r < 3; ++r) {
+        for (int g = 0; g < groups; ++g) {
+          const uint64_t xd = x_desc0 + static_cast<uint64_t>(((2 * i + r) * P + 8 * j + 2 * g) * xrow16);
+          const uint32_t acc = (accumulate_first | static_cast<uint32_t>(i) | static_cast<uint32_t>(j)) ? 1u : 0u;
+          umma_f16(tmem_base + static_cast<uint32_t>((r * groups + g) * n_cols), xd, zd, idesc, acc);
+        }
+      }
+    }
+  }
+}
+
+__global__ void __launch_bounds__(kThreads, 1)
+wgrad_halo_kernel(const __grid_constant__ WgradHaloParams p, const __grid_constant__ CUtensorMap tmX,
+                  const __grid_constant__ CUtensorMap tmZ) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t raw_addr = smem_u32(smem_raw);
+  uint8_t* smem = smem_raw + ((1024u - (raw_addr & 1023u)) & 1023u);
+
+  const int P = 8 * p.J + 2;
+  const int xrow = p.Cx * 2, zrow = p.Cz * 2;
+  const int halo_bytes = (kTH + 2) * P * xrow;
+  const int z_bytes = kTH * 8 * p.J * zrow;
+  // 1 KiB of slack after the halo tile: the junk filter column (s = 3) reads up to 3 pixel rows past its end
+  const int halo_stride = round_up_1k(halo_bytes + 4 * xrow);
+  const int stage_bytes = halo_stride + round_up_1k(z_bytes);
+  WgradHaloBarriers* bars = reinterpret_cast<WgradHaloBarriers*>(smem + p.stages * stage_bytes);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int num_tiles = p.N * p.tiles_h * p.tiles_w;
+  const int groups = p.Cx == 32 ? 1 : 2;          // stacked filter columns per MMA: 4 (Cx=32) or 2 (Cx=64)
+  const int n_acc = 3 * groups;
+  uint32_t tmem_cols = 32;
+  while (tmem_cols < static_cast<uint32_t>(n_acc * p.Cz)) tmem_cols <<= 1;
+  const int my_tiles = (num_tiles > static_cast<int>(blockIdx.x))
+                           ? (num_tiles - static_cast<int>(blockIdx.x) + static_cast<int>(gridDim.x) - 1) /
+                                 static_cast<int>(gridDim.x)
+                           : 0;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < p.stages; ++s) {
+      mbar_init(&bars->full[s], 1);
+      mbar_init(&bars->empty[s], 1);
+    }
+    mbar_init(&bars->tmem_full, 1);
+    mbar_fence_init();
+    tma_prefetch_desc(&tmX);
+    tma_prefetch_desc(&tmZ);
+  }
+  if (warp == 1) {
+    tmem_alloc(&bars->tmem_base, tmem_cols);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = bars->tmem_base;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        int t = tile;
+        const int tw_i = t % p.tiles_w;
+        t /= p.tiles_w;
+        const int th_i = t % p.tiles_h;
+        const int n = t / p.tiles_h;
+        const int h0 = th_i * kTH, w0 = tw_i * 8 * p.J;
+        mbar_wait(&bars->empty[stage], phase ^ 1u);
+        uint8_t* sx = smem + stage * stage_bytes;
+        mbar_arrive_expect_tx(&bars->full[stage], static_cast<uint32_t>(halo_bytes + z_bytes));
+        tma_load_4d(sx, &tmX, &bars->full[stage], 0, w0 - 1, h0 - 1, n);
+        tma_load_4d(sx + halo_stride, &tmZ, &bars->full[stage], 0, w0, h0, n);
+        if (++stage == p.stages) { stage = 0; phase ^= 1u; }
+      }
+    }
+  } else if (warp == 1) {
+    if (my_tiles > 0) {
+      const uint32_t idesc = umma_idesc_bf16(128, static_cast<uint32_t>(p.Cz), 1, 1);
+      const uint32_t x_sw = p.Cx == 64 ? UMMA_SW_128B : UMMA_SW_64B;
+      const uint32_t z_sw = p.Cz == 64 ? UMMA_SW_128B : UMMA_SW_64B;
+      // A: atoms along M are one pixel row apart (LBO = row bytes); 8-pixel groups along K are one image row apart
+      const uint64_t x_hi = umma_smem_desc(0, static_cast<uint32_t>(xrow), static_cast<uint32_t>(P * xrow), x_sw);
+      const uint64_t z_hi = umma_smem_desc(0, 0, static_cast<uint32_t>(8 * p.J * zrow), z_sw);
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int k = 0; k < my_tiles; ++k) {
+        mbar_wait(&bars->full[stage], phase);
+        tc_fence_after();
+        const uint32_t sx = smem_u32(smem + stage * stage_bytes);
+        const uint64_t xd = x_hi + (sx >> 4);
+        const uint64_t zd = z_hi + ((sx + static_cast<uint32_t>(halo_stride)) >> 4);
+        if (elect_one()) {
+          const uint32_t first = k ? 1u : 0u;
+          if (p.J == 4) issue_supertile<4>(tmem_base, xd, zd, idesc, P, xrow >> 4, zrow >> 4, groups, p.Cz, first);
+          else if (p.J == 2) issue_supertile<2>(tmem_base, xd, zd, idesc, P, xrow >> 4, zrow >> 4, groups, p.Cz, first);
+          else issue_supertile<1>(tmem_base, xd, zd, idesc, P, xrow >> 4, zrow >> 4, groups, p.Cz, first);
+          umma_commit(&bars->empty[stage]);
+          if (k == my_tiles - 1) umma_commit(&bars->tmem_full);
+        }
+        __syncwarp();
+        if (++stage == p.stages) { stage = 0; phase ^= 1u; }
+      }
+    }
+  } else if (warp >= 4) {
+    const int quarter = warp & 3;
+    const int m = quarter * 32 + lane;
+    const int a = m / p.Cx;              // which stacked filter column this TMEM lane belongs to
+    const int ci = m % p.Cx;
+    float* out = p.ws + static_cast<size_t>(blockIdx.x) * 9 * p.Cx * p.Cz;
+    if (my_tiles > 0) {
+      mbar_wait(&bars->tmem_full, 0);
+      tc_fence_after();
+    }
+    for (int r = 0; r < 3; ++r) {
+      for (int g = 0; g < groups; ++g) {
+        const int s = (p.Cx == 32 ? 0 : 2 * g) + a;
+        const uint32_t t_row = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) +
+                               static_cast<uint32_t>((r * groups + g) * p.Cz);
+        for (int c = 0; c < p.Cz; c += 16) {
+          uint32_t v[16];
+          if (my_tiles > 0) {
+            tmem_ld_32x32b_x16(t_row + static_cast<uint32_t>(c), v);
+            tmem_ld_wait();
+          } else {
+#pragma unroll
+            for (int i = 0; i < 16; ++i) v[i] = 0u;
+          }
+          if (s < 3) {
+            float4* o4 = reinterpret_cast<float4*>(out + (static_cast<size_t>(r * 3 + s) * p.Cx + ci) * p.Cz + c);
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+              o4[q] = make_float4(__uint_as_float(v[4 * q]), __uint_as_float(v[4 * q + 1]),
+                                  __uint_as_float(v[4 * q + 2]), __uint_as_float(v[4 * q + 3]));
+            }
+          }
+        }
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, tmem_cols);
+  }
+}
+
+// dw[tap][ci_off + ci][co] = sum over parts of ws[part][tap][ci][co]; 8 interleaved partial sums then a fixed 8-way sum.
+__global__ void wgrad_halo_reduce_kernel(const float* __restrict__ ws, int nparts, int Cx, int Cz, float* __restrict__ dw,
+                                         int cin_total, int ci_off) {
+  __shared__ float part[8][32];
+  const int n = 9 * Cx * Cz;
+  const int c = threadIdx.x & 31, q = threadIdx.x >> 5;
+  const int i = blockIdx.x * 32 + c;
+  float acc = 0.0f;
+  if (i < n) {
+    for (int r = q; r < nparts; r += 8) acc += ws[static_cast<size_t>(r) * n + i];
+  }
+  part[q][c] = acc;
+  __syncthreads();
+  if (q == 0 && i < n) {
+    float s = part[0][c];
+#pragma unroll
+    for (int k = 1; k < 8; ++k) s += part[k][c];
+    const int co = i % Cz;
+    const int ci = (i / Cz) % Cx;
+    const int tap = i / (Cz * Cx);
+    dw[(static_cast<size_t>(tap) * cin_total + ci_off + ci) * Cz + co] = s;
+  }
+}
+
+int pick_J(int Cx, int W) {
+  int J = Cx == 32 ? 4 : 2;
+  while (J > 1 && 8 * (J / 2) >= W) J >>= 1;   // do not make strips that lie entirely outside the image
+  return J;
+}
+
+}  // namespace
+
+bool wgrad_halo_supported(int H, int W, int Cx, int Cz) {
+  static const bool disabled = getenv("UNETB200_NO_HALO") != nullptr;
+  if (disabled) return false;
+  return (Cx == 32 || Cx == 64) && (Cz == 32 || Cz == 64) && H >= kTH && W >= 8;
+}
+
+static int halo_grid(int N, int H, int W, int J) {
+  const int tiles = N * ((H + kTH - 1) / kTH) * ((W + 8 * J - 1) / (8 * J));
+  const int sms = device_sm_count();
+  return tiles < sms ? tiles : sms;
+}
+
+size_t wgrad_halo_ws_bytes(int N, int H, int W, int Cx, int Cz) {
+  const int J = pick_J(Cx, W);
+  return static_cast<size_t>(halo_grid(N, H, W, J)) * 9 * Cx * Cz * sizeof(float);
+}
+
+// One source of the (possibly concatenated) input: writes dw[:, ci_off : ci_off + Cx, :].
+int wgrad_halo_launch(const CUtensorMap& x_map, const CUtensorMap& z_map, int N, int H, int W, int Cx, int Cz, int J,
+                      float* dw, int cin_total, int ci_off, float* ws, cudaStream_t stream) {
+  WgradHaloParams p;
+  p.N = N; p.H = H; p.W = W;
+  p.J = J;
+  p.tiles_h = (H + kTH - 1) / kTH;
+  p.tiles_w = (W + 8 * J - 1) / (8 * J);
+  p.Cx = Cx; p.Cz = Cz;
+  p.ws = ws;
+  const int P = 8 * J + 2;
+  const int stage_bytes = round_up_1k((kTH + 2) * P * Cx * 2 + 4 * Cx * 2) + round_up_1k(kTH * 8 * J * Cz * 2);
+  int stages = (225 * 1024 - 1024 - static_cast<int>(sizeof(WgradHaloBarriers))) / stage_bytes;
+  if (stages > kMaxStages) stages = kMaxStages;
+  UB_REQUIRE(stages >= 2, "wgrad_halo: stage of %d bytes does not fit twice in shared memory", stage_bytes);
+  p.stages = stages;
+  const size_t smem = static_cast<size_t>(stages) * stage_bytes + sizeof(WgradHaloBarriers) + 1024;
+  static bool attr_set[64] = {false};
+  int dev = 0;
+  UB_CHECK_CUDA(cudaGetDevice(&dev));
+  if (dev >= 0 && dev < 64 && !attr_set[dev]) {
+    UB_CHECK_CUDA(cudaFuncSetAttribute(wgrad_halo_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    attr_set[dev] = true;
+  }
+  const int grid = halo_grid(N, H, W, J);
+  UB_REQUIRE(grid > 0, "wgrad_halo: empty problem");
+  if (profiling_enabled()) {
+    const double pixels = static_cast<double>(N) * H * W;
+    prof_begin(UB_KIND_WGRAD, 2.0 * pixels * 9 * Cx * Cz, 2.0 * pixels * (Cx + Cz), stream);
+  }
+  wgrad_halo_kernel<<<grid, kThreads, smem, stream>>>(p, x_map, z_map);
+  UB_CHECK_CUDA(cudaGetLastError());
+  prof_end(stream);
+  const int n = 9 * Cx * Cz;
+  wgrad_halo_reduce_kernel<<<(n + 31) / 32, 256, 0, stream>>>(ws, grid, Cx, Cz, dw, cin_total, ci_off);
+  UB_CHECK_CUDA(cudaGetLastError());
+  return UB_OK;
+}
+
+int wgrad_halo_pick_J(int Cx, int W) { return pick_J(Cx, W); }
+
+}  // namespace ub
