@@ -504,6 +504,34 @@ __global__ void pack_tconv_dgrad_kernel(const float* __restrict__ w, __nv_bfloat
   const int c = static_cast<int>(i / (4ll * Cout));
   out[i] = __float2bfloat16(w[(static_cast<long long>(ab) * Cout + o) * Cin + c]);
 }
+__global__ void pack_all_kernel(const PackSeg* __restrict__ segs, int nseg, long long total,
+                                const float* __restrict__ params, uint8_t* __restrict__ arena) {
+  const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i >= total) return;
+  int lo = 0, hi = nseg - 1;
+  while (lo < hi) {   // last segment whose start <= i
+    const int mid = (lo + hi + 1) >> 1;
+    if (segs[mid].start <= i) lo = mid; else hi = mid - 1;
+  }
+  const PackSeg sg = segs[lo];
+  const unsigned e = static_cast<unsigned>(i - sg.start);
+  const unsigned taps = sg.taps, cin = sg.cin, cout = sg.cout;
+  unsigned src;
+  if (sg.kind == 0) {          // out[co][tap][ci] = w[tap][ci][co]
+    const unsigned ci = e % cin, tap = (e / cin) % taps, co = e / (cin * taps);
+    src = (tap * cin + ci) * cout + co;
+  } else if (sg.kind == 1) {   // out[ci][tap][co] = w[T-1-tap][ci][co]
+    const unsigned co = e % cout, tap = (e / cout) % taps, ci = e / (cout * taps);
+    src = ((taps - 1 - tap) * cin + ci) * cout + co;
+  } else if (sg.kind == 2) {   // out[(ab*Cout+o)][c] = w[ab][o][c]
+    src = e;
+  } else {                     // out[c][ab][o] = w[ab][o][c]
+    const unsigned o = e % cout, ab = (e / cout) % 4u, c = e / (4u * cout);
+    src = (ab * cout + o) * cin + c;
+  }
+  reinterpret_cast<__nv_bfloat16*>(arena + sg.dst)[e] = __float2bfloat16(params[sg.src + src]);
+}
+
 __global__ void cast_f32_bf16_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ y, long long n) {
   const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
   if (i < n) y[i] = __float2bfloat16(x[i]);
@@ -591,6 +619,8 @@ __global__ void dropout_mask_kernel(unsigned char* __restrict__ keep, long long 
   for (int i = 0; i < 8; ++i) keep[g * 8 + i] = (bits >> i) & 1u;
 }
 
+#include "level0.cuh"
+
 int check_groups(int C, const char* what) {
   const int groups = C / 8;
   if (C % 8 != 0 || groups < 1 || groups > 256 || (groups & (groups - 1)) != 0) {
@@ -609,6 +639,19 @@ int conv_first_fwd(const float* x, const float* w, const float* bias, void* y, i
   UB_REQUIRE(Cout % 8 == 0 && Cout <= 64, "conv_first_fwd: Cout %d unsupported", Cout);
   const long long total = static_cast<long long>(N) * H * W * (Cout / 8);
   UB_REQUIRE(total < (1ll << 31), "conv_first_fwd: tensor too large");
+  if (Cout == 32 && (Cin == 1 || Cin == 4)) {   // thread-per-pixel fast path (the network's conv1a)
+    const unsigned P = static_cast<unsigned>(static_cast<long long>(N) * H * W);
+    unsigned blocks = grid_for(P, kThreads);
+    const unsigned cap = 8u * static_cast<unsigned>(device_sm_count());
+    if (blocks > cap) blocks = cap;
+    if (Cin == 1) {
+      conv_first32_fwd_kernel<1><<<blocks, kThreads, 0, s>>>(x, w, bias, reinterpret_cast<uint4*>(y), H, W, P);
+    } else {
+      conv_first32_fwd_kernel<4><<<blocks, kThreads, 0, s>>>(x, w, bias, reinterpret_cast<uint4*>(y), H, W, P);
+    }
+    UB_CHECK_CUDA(cudaGetLastError());
+    return UB_OK;
+  }
   const size_t smem = (9 * Cin * Cout + Cout) * sizeof(float);
   unsigned blocks = grid_for(total, kThreads);
   const unsigned cap = 8u * static_cast<unsigned>(device_sm_count());   // weights are staged once per block
@@ -693,9 +736,20 @@ int head_fwd(const void* x, const float* w, const float* b, const float* y_true,
   UB_REQUIRE(n_cl >= 1 && n_cl <= kMaxCl, "head_fwd: n_cl_out %d outside 1..%d", n_cl, kMaxCl);
   const int subs = C / 8;
   UB_REQUIRE(C % 8 == 0 && subs >= 1 && subs <= 32 && (subs & (subs - 1)) == 0, "head_fwd: C %d unsupported", C);
-  const size_t smem = (C * n_cl + n_cl + 3 * (kThreads / 32)) * sizeof(float);
-  head_fwd_kernel<<<kRedBlocks, kThreads, smem, s>>>(reinterpret_cast<const uint4*>(x), w, b, y_true, p_out, ws, P, C,
-                                                     n_cl);
+  if (C == 32 && P < (1ll << 31)) {   // thread-per-pixel fast path (the network's Mask layer)
+    const uint4* xv = reinterpret_cast<const uint4*>(x);
+    const unsigned Pu = static_cast<unsigned>(P);
+    switch (n_cl) {
+      case 1: head32_fwd_kernel<1><<<kRedBlocks, kThreads, 0, s>>>(xv, w, b, y_true, p_out, ws, Pu); break;
+      case 2: head32_fwd_kernel<2><<<kRedBlocks, kThreads, 0, s>>>(xv, w, b, y_true, p_out, ws, Pu); break;
+      case 3: head32_fwd_kernel<3><<<kRedBlocks, kThreads, 0, s>>>(xv, w, b, y_true, p_out, ws, Pu); break;
+      default: head32_fwd_kernel<4><<<kRedBlocks, kThreads, 0, s>>>(xv, w, b, y_true, p_out, ws, Pu); break;
+    }
+  } else {
+    const size_t smem = (C * n_cl + n_cl + 3 * (kThreads / 32)) * sizeof(float);
+    head_fwd_kernel<<<kRedBlocks, kThreads, smem, s>>>(reinterpret_cast<const uint4*>(x), w, b, y_true, p_out, ws, P, C,
+                                                       n_cl);
+  }
   UB_CHECK_CUDA(cudaGetLastError());
   rows_reduce_kernel<<<1, 256, 0, s>>>(ws, kRedBlocks, 3, sums, 3, nullptr);
   UB_CHECK_CUDA(cudaGetLastError());
@@ -714,9 +768,15 @@ int head_bwd(const void* x, const float* w, const float* y_true, const float* p,
   const int subs = C / 8;
   UB_REQUIRE(C % 8 == 0 && subs >= 1 && subs <= 32 && (subs & (subs - 1)) == 0, "head_bwd: C %d unsupported", C);
   const int nout = C * n_cl + n_cl;
-  const size_t smem = (C * n_cl + (kThreads / 32) * nout) * sizeof(float);
-  head_bwd_kernel<<<kRedBlocks, kThreads, smem, s>>>(reinterpret_cast<const uint4*>(x), w, y_true, p, sums, smooth,
-                                                     grad_scale, reinterpret_cast<uint4*>(dx), ws, P, C, n_cl);
+  if (C == 32 && n_cl == 1 && P < (1ll << 31)) {   // thread-per-pixel fast path
+    head32_bwd_kernel<<<kRedBlocks, kThreads, 0, s>>>(reinterpret_cast<const uint4*>(x), w, y_true, p, sums, smooth,
+                                                      grad_scale, reinterpret_cast<uint4*>(dx), ws,
+                                                      static_cast<unsigned>(P));
+  } else {
+    const size_t smem = (C * n_cl + (kThreads / 32) * nout) * sizeof(float);
+    head_bwd_kernel<<<kRedBlocks, kThreads, smem, s>>>(reinterpret_cast<const uint4*>(x), w, y_true, p, sums, smooth,
+                                                       grad_scale, reinterpret_cast<uint4*>(dx), ws, P, C, n_cl);
+  }
   UB_CHECK_CUDA(cudaGetLastError());
   rows_reduce_kernel<<<grid_for(nout, 32), 256, 0, s>>>(ws, kRedBlocks, nout, dw, C * n_cl, db);
   UB_CHECK_CUDA(cudaGetLastError());
@@ -779,6 +839,14 @@ int colsum_bf16_static(const void* dz, float* db, long long P, int C, cudaStream
                                                                                  scratch, P, C);
   UB_CHECK_CUDA(cudaGetLastError());
   rows_reduce_kernel<<<grid_for(C, 32), 256, 0, s>>>(scratch, rows, C, db, C, nullptr);
+  UB_CHECK_CUDA(cudaGetLastError());
+  return UB_OK;
+}
+
+int pack_all(const PackSeg* segs_dev, int nseg, long long total, const float* params, void* arena, cudaStream_t s) {
+  if (nseg <= 0 || total <= 0) return UB_OK;
+  pack_all_kernel<<<grid_for(total, kThreads), kThreads, 0, s>>>(segs_dev, nseg, total, params,
+                                                                 reinterpret_cast<uint8_t*>(arena));
   UB_CHECK_CUDA(cudaGetLastError());
   return UB_OK;
 }

@@ -53,6 +53,16 @@ int pack_conv_dgrad(const float* w, void* out, int taps, int Cin, int Cout, cuda
 int pack_tconv_fwd(const float* w, void* out, int Cin, int Cout, cudaStream_t s);
 int pack_tconv_dgrad(const float* w, void* out, int Cin, int Cout, cudaStream_t s);
 
+// All repacks of a network in one launch: a device table of segments, one thread per packed element.
+struct PackSeg {
+  long long start;   // first packed-element index of this segment (segments are sorted by start)
+  long long src;     // float offset of the TF-layout master inside the flat parameter buffer
+  long long dst;     // byte offset of the packed bf16 operand inside the arena
+  int kind;          // 0 conv fwd, 1 conv dgrad, 2 tconv fwd, 3 tconv dgrad
+  int taps, cin, cout;
+};
+int pack_all(const PackSeg* segs_dev, int nseg, long long total, const float* params, void* arena, cudaStream_t s);
+
 // TF-1.4 AdamOptimizer on a flat fp32 buffer. step_ptr holds the number of updates applied so far (device int64).
 //   lr = const_lr ? lr0 : lr0 * lr_fraction^(step/decay_steps);  t = step+1
 //   lr_t = lr*sqrt(1-b2^t)/(1-b1^t); m = b1 m + (1-b1) g; v = b2 v + (1-b2) g^2; theta -= lr_t m/(sqrt(v)+eps)

@@ -1,0 +1,175 @@
+// Thread-per-pixel kernels for the 32-channel full-resolution level (conv1a forward, the 1x1 Mask head forward and
+// backward). The generic kernels in elementwise.cu split a pixel over four threads and carry run-time channel
+// loops; at 128x128x128 images these ops each touch a 134 MB tensor once and were instruction-bound (ncu: 150 M and
+// 90 M warp instructions for conv1a / head forward). Here every thread owns one pixel's 32 channels (64 contiguous
+// bytes = four 16-byte accesses), all loops are compile-time, indices are 32-bit.
+// Included inside elementwise.cu's anonymous namespace (uses its helpers).
+#pragma once
+
+// ---------------------------------------------------------------------------------------------- conv1a forward, Cout = 32
+template <int CIN>
+__global__ void __launch_bounds__(256)
+conv_first32_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ bias,
+                        uint4* __restrict__ y, int H, int W, unsigned P) {
+  __shared__ float4 sw4[9 * CIN * 8 + 8];   // [tap][ci][32 channels] then bias, as float4
+  float* sw = reinterpret_cast<float*>(sw4);
+  for (int i = threadIdx.x; i < 9 * CIN * 32; i += blockDim.x) sw[i] = w[i];
+  for (int i = threadIdx.x; i < 32; i += blockDim.x) sw[9 * CIN * 32 + i] = bias ? bias[i] : 0.0f;
+  __syncthreads();
+  const unsigned stride = gridDim.x * blockDim.x;
+  for (unsigned pix = blockIdx.x * blockDim.x + threadIdx.x; pix < P; pix += stride) {
+    const int wq = static_cast<int>(pix % W);
+    const unsigned row = pix / W;                 // n*H + h
+    const int hq = static_cast<int>(row % H);
+    float xv[9][CIN];
+#pragma unroll
+    for (int r = 0; r < 3; ++r) {
+#pragma unroll
+      for (int s = 0; s < 3; ++s) {
+        const int hh = hq + r - 1, ww = wq + s - 1;
+        const bool in = hh >= 0 && hh < H && ww >= 0 && ww < W;
+        const float* xp = x + (static_cast<size_t>(row + r - 1) * W + ww) * CIN;
+#pragma unroll
+        for (int ci = 0; ci < CIN; ++ci) xv[r * 3 + s][ci] = in ? __ldg(xp + ci) : 0.0f;
+      }
+    }
+    float4 acc[8];
+#pragma unroll
+    for (int q = 0; q < 8; ++q) acc[q] = sw4[9 * CIN * 8 + q];
+#pragma unroll
+    for (int t = 0; t < 9; ++t) {
+#pragma unroll
+      for (int ci = 0; ci < CIN; ++ci) {
+        const float v = xv[t][ci];
+#pragma unroll
+        for (int q = 0; q < 8; ++q) {
+          const float4 wv = sw4[(t * CIN + ci) * 8 + q];
+          acc[q].x = fmaf(v, wv.x, acc[q].x); acc[q].y = fmaf(v, wv.y, acc[q].y);
+          acc[q].z = fmaf(v, wv.z, acc[q].z); acc[q].w = fmaf(v, wv.w, acc[q].w);
+        }
+      }
+    }
+    uint4* yp = y + static_cast<size_t>(pix) * 4;
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const float4 a = acc[2 * q], b = acc[2 * q + 1];
+      uint4 o;
+      o.x = pack_bf16x2(fmaxf(a.x, 0.f), fmaxf(a.y, 0.f)); o.y = pack_bf16x2(fmaxf(a.z, 0.f), fmaxf(a.w, 0.f));
+      o.z = pack_bf16x2(fmaxf(b.x, 0.f), fmaxf(b.y, 0.f)); o.w = pack_bf16x2(fmaxf(b.z, 0.f), fmaxf(b.w, 0.f));
+      yp[q] = o;
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------- head forward, C = 32
+template <int NCL>
+__global__ void __launch_bounds__(256)
+head32_fwd_kernel(const uint4* __restrict__ x, const float* __restrict__ w, const float* __restrict__ b,
+                  const float* __restrict__ y_true, float* __restrict__ p_out, float* __restrict__ ws, unsigned P) {
+  __shared__ float sw[32 * NCL + NCL];
+  __shared__ float wred[8 * 3];
+  for (int i = threadIdx.x; i < 32 * NCL; i += blockDim.x) sw[i] = w[i];
+  for (int i = threadIdx.x; i < NCL; i += blockDim.x) sw[32 * NCL + i] = b ? b[i] : 0.0f;
+  __syncthreads();
+  float sI = 0.0f, sY = 0.0f, sP = 0.0f;
+  const unsigned stride = gridDim.x * blockDim.x;
+  for (unsigned pix = blockIdx.x * blockDim.x + threadIdx.x; pix < P; pix += stride) {
+    const uint4* xp = x + static_cast<size_t>(pix) * 4;
+    const uint4 v0 = __ldg(xp), v1 = __ldg(xp + 1), v2 = __ldg(xp + 2), v3 = __ldg(xp + 3);
+    float f[32];
+    {
+      float t8[8];
+      unpack8(v0, t8);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) f[j] = t8[j];
+      unpack8(v1, t8);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) f[8 + j] = t8[j];
+      unpack8(v2, t8);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) f[16 + j] = t8[j];
+      unpack8(v3, t8);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) f[24 + j] = t8[j];
+    }
+#pragma unroll
+    for (int k = 0; k < NCL; ++k) {
+      float z = sw[32 * NCL + k];
+#pragma unroll
+      for (int c = 0; c < 32; ++c) z = fmaf(f[c], sw[c * NCL + k], z);
+      const float p = 1.0f / (1.0f + expf(-z));
+      const float yt = y_true ? __ldg(y_true + static_cast<size_t>(pix) * NCL + k) : 0.0f;
+      p_out[static_cast<size_t>(pix) * NCL + k] = p;
+      sI = fmaf(yt, p, sI);
+      sY += yt;
+      sP += p;
+    }
+  }
+  sI = warp_sum(sI); sY = warp_sum(sY); sP = warp_sum(sP);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (lane == 0) { wred[warp * 3 + 0] = sI; wred[warp * 3 + 1] = sY; wred[warp * 3 + 2] = sP; }
+  __syncthreads();
+  if (threadIdx.x < 3) {
+    float a = 0.0f;
+    for (int wv = 0; wv < static_cast<int>(blockDim.x >> 5); ++wv) a += wred[wv * 3 + threadIdx.x];
+    ws[blockIdx.x * 3 + threadIdx.x] = a;
+  }
+}
+
+// ---------------------------------------------------------------------------------------------- head backward, C = 32, one class
+// dl = (ca*y + cb) * p(1-p) * scale (dice) or y * p(1-p) * scale (explicit dL/dp in y when sums == nullptr);
+// dx = dl * w masked by x > 0; dW[c] += x[c]*dl, db += dl -> ws[block][33].
+__global__ void __launch_bounds__(256)
+head32_bwd_kernel(const uint4* __restrict__ x, const float* __restrict__ w, const float* __restrict__ y_true,
+                  const float* __restrict__ p, const float* __restrict__ sums, float smooth, float grad_scale,
+                  uint4* __restrict__ dx, float* __restrict__ ws, unsigned P) {
+  __shared__ float sw[32];
+  __shared__ float red[8][33];
+  if (threadIdx.x < 32) sw[threadIdx.x] = w[threadIdx.x];
+  __syncthreads();
+  float ca = 1.0f, cb = 0.0f;
+  if (sums) {
+    const float I = sums[0], Sy = sums[1], Sp = sums[2];
+    ca = -2.0f / (2.0f * I + smooth);
+    cb = 1.0f / (Sy + Sp + smooth);
+  }
+  float adw[32];
+#pragma unroll
+  for (int c = 0; c < 32; ++c) adw[c] = 0.0f;
+  float adb = 0.0f;
+  const unsigned stride = gridDim.x * blockDim.x;
+  for (unsigned pix = blockIdx.x * blockDim.x + threadIdx.x; pix < P; pix += stride) {
+    const uint4* xp = x + static_cast<size_t>(pix) * 4;
+    const uint4 v[4] = {__ldg(xp), __ldg(xp + 1), __ldg(xp + 2), __ldg(xp + 3)};
+    const float pv = __ldg(p + pix);
+    const float yt = __ldg(y_true + pix);
+    const float dl = (ca * yt + cb) * pv * (1.0f - pv) * grad_scale;
+    adb += dl;
+    uint4* dp = dx + static_cast<size_t>(pix) * 4;
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      float f[8], o[8];
+      unpack8(v[q], f);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        adw[8 * q + j] = fmaf(f[j], dl, adw[8 * q + j]);
+        o[j] = f[j] > 0.0f ? dl * sw[8 * q + j] : 0.0f;
+      }
+      dp[q] = pack8(o);
+    }
+  }
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+#pragma unroll
+  for (int c = 0; c < 32; ++c) {
+    const float s = warp_sum(adw[c]);
+    if (lane == 0) red[warp][c] = s;
+  }
+  adb = warp_sum(adb);
+  if (lane == 0) red[warp][32] = adb;
+  __syncthreads();
+  if (threadIdx.x < 33) {
+    float s = red[0][threadIdx.x];
+    for (int wv = 1; wv < static_cast<int>(blockDim.x >> 5); ++wv) s += red[wv][threadIdx.x];
+    ws[static_cast<size_t>(blockIdx.x) * 33 + threadIdx.x] = s;
+  }
+}

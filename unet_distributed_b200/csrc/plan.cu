@@ -51,6 +51,9 @@ struct unetb200_plan {
   size_t a[5], c[5], p[4], u[4], da[4], dc[4];
   size_t g_a[5], g_c[5], g_p[4], g_u[4], g_da[4], g_dc[4];
   size_t preds, sums, metrics, ws;
+  std::vector<PackSeg> pack_segs;
+  long long pack_total = 0;
+  size_t pack_table = 0;
   size_t ws_bytes = 0;
   int ch[5];
   int c4_out;      // channels of c[4] (conv5b)
@@ -200,6 +203,25 @@ int unetb200_plan_create(unetb200_plan** out, int N, int H, int W, int in_channe
   }
   P->ws_bytes = ws;
   P->ws = P->bump(ws);
+  // ---- one table for all weight repacks (uploaded at bind time, walked by a single kernel)
+  long long start = 0;
+  for (const auto& l : P->layers) {
+    if (l.kind == 2 || l.cin < 32) continue;
+    const int taps = l.kind == 0 ? 9 : 4;
+    const long long count = static_cast<long long>(taps) * l.cin * l.cout;
+    for (int d = 0; d < 2; ++d) {
+      PackSeg sg;
+      sg.start = start;
+      sg.src = l.w_off;
+      sg.dst = static_cast<long long>(d == 0 ? l.pk_fwd : l.pk_dgrad);
+      sg.kind = (l.kind == 0 ? 0 : 2) + d;
+      sg.taps = taps; sg.cin = l.cin; sg.cout = l.cout;
+      P->pack_segs.push_back(sg);
+      start += count;
+    }
+  }
+  P->pack_total = start;
+  P->pack_table = P->bump(P->pack_segs.size() * sizeof(PackSeg));
   *out = P;
   return UB_OK;
 }
@@ -233,6 +255,9 @@ int unetb200_plan_bind(unetb200_plan* P, void* arena, float* params, float* grad
   P->arena = reinterpret_cast<uint8_t*>(arena);
   P->params = params;
   P->grads = grads;
+  // the repack table lives in the arena; binding is a set-up call, so a synchronous copy is fine here
+  UB_CHECK_CUDA(cudaMemcpy(P->at(P->pack_table), P->pack_segs.data(), P->pack_segs.size() * sizeof(PackSeg),
+                           cudaMemcpyHostToDevice));
   return UB_OK;
 }
 
@@ -282,19 +307,8 @@ int unetb200_plan_tensor(const unetb200_plan* P, const char* name, long long* of
 int unetb200_plan_pack_weights(unetb200_plan* P, void* stream) {
   UB_REQUIRE(P->arena, "plan_pack_weights: plan is not bound");
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
-  for (size_t i = 0; i < P->layers.size(); ++i) {
-    const Layer& l = P->layers[i];
-    if (l.kind == 2 || l.cin < 32) continue;
-    const int li = static_cast<int>(i);
-    if (l.kind == 0) {
-      RC(pack_conv_fwd(P->W_(li), P->at(l.pk_fwd), 9, l.cin, l.cout, s));
-      RC(pack_conv_dgrad(P->W_(li), P->at(l.pk_dgrad), 9, l.cin, l.cout, s));
-    } else {
-      RC(pack_tconv_fwd(P->W_(li), P->at(l.pk_fwd), l.cin, l.cout, s));
-      RC(pack_tconv_dgrad(P->W_(li), P->at(l.pk_dgrad), l.cin, l.cout, s));
-    }
-  }
-  return UB_OK;
+  return pack_all(reinterpret_cast<const PackSeg*>(P->at(P->pack_table)), static_cast<int>(P->pack_segs.size()),
+                  P->pack_total, P->params, P->arena, s);
 }
 
 // Forward pass (model.py:45-120) + dice metrics (model.py:4-21,133-143) when msks != NULL.
