@@ -9,7 +9,7 @@ namespace ub {
 
 namespace {
 
-constexpr int kThreads = 256;  // warp0 halo TMA, warp1 MMA + TMEM, warp2 weight TMA, warp3 idle, warps4..7 epilogue
+constexpr int kThreads = 384;  // warp0 halo TMA, warp1 MMA + TMEM, warp2 weight TMA, warp3 idle, warps4..11 epilogue
 constexpr int kHaloStages = 2;
 constexpr int kMaxBStages = 4;
 constexpr int kTH = 16;        // image rows per super-tile
@@ -88,7 +88,7 @@ conv_halo_kernel(const __grid_constant__ HaloParams p, const __grid_constant__ C
     }
     for (int a = 0; a < 2; ++a) {
       mbar_init(&bars->tmem_full[a], 1);
-      mbar_init(&bars->tmem_empty[a], 4);
+      mbar_init(&bars->tmem_empty[a], 8);
     }
     mbar_fence_init();
     tma_prefetch_desc(&tmA0);
@@ -206,11 +206,18 @@ conv_halo_kernel(const __grid_constant__ HaloParams p, const __grid_constant__ C
       __syncwarp();
     }
   } else if (warp >= 4) {
-    // ------------------------------------------------------------ epilogue: one TMEM lane quarter per warp
+    // ------------------------------------------------------------ epilogue: 8 warps, two per TMEM lane quarter
+    // Work items are (pixel tile j, 16-column chunk); the two warps of a quarter take alternate items. The gate
+    // tensor of the NEXT item (dgrad: the producer's forward output) is requested before the current item's
+    // accumulators are read, so its latency hides behind the TMEM load and the stores.
     const int quarter = warp & 3;
+    const int half = (warp - 4) >> 2;
     const int m = quarter * 32 + lane;
     const int th = m >> 3, twl = m & 7;
     const IgemmEpilogue& e = p.epi;
+    const int chunks = p.block_n >> 4;
+    const int items = p.J * chunks;
+    const bool has_aux = (e.aux[0] != nullptr) || (e.aux[1] != nullptr);
     int it = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
       const int a = p.acc_double ? (it & 1) : 0;
@@ -218,73 +225,86 @@ conv_halo_kernel(const __grid_constant__ HaloParams p, const __grid_constant__ C
       int n, h0, w0, nt;
       decode_tile(p, tile, n, h0, w0, nt);
       const int h = h0 + th;
+      const size_t row_pix = (static_cast<size_t>(n) * p.H + h) * p.W;
+      uint4 ax0 = make_uint4(0u, 0u, 0u, 0u), ax1 = ax0;
+      auto aux_ptr = [&](int item) -> const uint4* {
+        const int j = item / chunks, c = (item - j * chunks) << 4;
+        const int w = w0 + 8 * j + twl;
+        const int col = nt * p.block_n + c;
+        const int slot = col >= e.split_col ? 1 : 0;
+        if (!(h < p.H && w < p.W) || e.aux[slot] == nullptr) return nullptr;
+        const int ch = slot ? col - e.split_col : col;
+        return reinterpret_cast<const uint4*>(reinterpret_cast<const __nv_bfloat16*>(e.aux[slot]) +
+                                              (row_pix + w) * e.aux_C[slot] + e.aux_coff[slot] + ch);
+      };
+      if (has_aux && half < items) {
+        const uint4* ap = aux_ptr(half);
+        if (ap) { ax0 = __ldg(ap); ax1 = __ldg(ap + 1); }
+      }
       mbar_wait(&bars->tmem_full[a], fparity);
       tc_fence_after();
-      for (int j = 0; j < p.J; ++j) {
+      for (int item = half; item < items; item += 2) {
+        const int j = item / chunks, c = (item - j * chunks) << 4;
         const int w = w0 + 8 * j + twl;
         const bool valid = (h < p.H) && (w < p.W);
-        const size_t pix = (static_cast<size_t>(n) * p.H + h) * p.W + w;
-        const uint32_t t_row = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) +
-                               static_cast<uint32_t>((a * p.J + j) * p.block_n);
-        for (int c = 0; c < p.block_n; c += 16) {
-          uint32_t r[16];
-          tmem_ld_32x32b_x16(t_row + static_cast<uint32_t>(c), r);
-          tmem_ld_wait();
-          if (!valid) continue;
-          const int col = nt * p.block_n + c;
-          const int slot = col >= e.split_col ? 1 : 0;
-          const int ch = slot ? col - e.split_col : col;
-          float v[16];
+        const size_t pix = row_pix + w;
+        const uint4 cur0 = ax0, cur1 = ax1;
+        if (has_aux && item + 2 < items) {
+          const uint4* ap = aux_ptr(item + 2);
+          if (ap) { ax0 = __ldg(ap); ax1 = __ldg(ap + 1); }
+        }
+        uint32_t r[16];
+        tmem_ld_32x32b_x16(tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) +
+                               static_cast<uint32_t>((a * p.J + j) * p.block_n + c), r);
+        tmem_ld_wait();
+        if (!valid) continue;
+        const int col = nt * p.block_n + c;
+        const int slot = col >= e.split_col ? 1 : 0;
+        const int ch = slot ? col - e.split_col : col;
+        float v[16];
 #pragma unroll
-          for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
-          if (e.bias) {
-            const float4* bp = reinterpret_cast<const float4*>(e.bias + col);
+        for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
+        if (e.bias) {
+          const float4* bp = reinterpret_cast<const float4*>(e.bias + col);
 #pragma unroll
-            for (int q = 0; q < 4; ++q) {
-              const float4 bq = __ldg(bp + q);
-              v[4 * q + 0] += bq.x; v[4 * q + 1] += bq.y; v[4 * q + 2] += bq.z; v[4 * q + 3] += bq.w;
-            }
+          for (int q = 0; q < 4; ++q) {
+            const float4 bq = __ldg(bp + q);
+            v[4 * q + 0] += bq.x; v[4 * q + 1] += bq.y; v[4 * q + 2] += bq.z; v[4 * q + 3] += bq.w;
           }
-          if (e.relu) {
+        }
+        if (e.relu) {
 #pragma unroll
-            for (int i = 0; i < 16; ++i) v[i] = fmaxf(v[i], 0.0f);
-          }
-          const size_t elem0 = pix * e.dst_C[slot] + e.dst_coff[slot] + ch;
-          if (e.drop_keep < 1.0f) {
-            const float inv = 1.0f / e.drop_keep;
-            const unsigned long long seed =
-                e.drop_seed + (e.drop_seed_add ? static_cast<unsigned long long>(__ldg(e.drop_seed_add)) : 0ull);
-#pragma unroll
-            for (int g = 0; g < 2; ++g) {
-              const uint32_t bits = dropout_keep_bits8(seed, e.drop_stream, elem0 / 8 + g, e.drop_keep);
-#pragma unroll
-              for (int i = 0; i < 8; ++i) v[8 * g + i] = ((bits >> i) & 1u) ? v[8 * g + i] * inv : 0.0f;
-            }
-          }
-          if (e.aux[slot]) {
-            const uint4* ap = reinterpret_cast<const uint4*>(reinterpret_cast<const __nv_bfloat16*>(e.aux[slot]) +
-                                                             pix * e.aux_C[slot] + e.aux_coff[slot] + ch);
-#pragma unroll
-            for (int g = 0; g < 2; ++g) {
-              const uint4 av = __ldg(ap + g);
-              const uint32_t aw[4] = {av.x, av.y, av.z, av.w};
-#pragma unroll
-              for (int i = 0; i < 4; ++i) {
-                v[8 * g + 2 * i] = bf16_lo(aw[i]) > 0.0f ? v[8 * g + 2 * i] * e.mask_scale : 0.0f;
-                v[8 * g + 2 * i + 1] = bf16_hi(aw[i]) > 0.0f ? v[8 * g + 2 * i + 1] * e.mask_scale : 0.0f;
-              }
-            }
-          }
-          uint4* dp = reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(e.dst[slot]) + elem0);
+          for (int i = 0; i < 16; ++i) v[i] = fmaxf(v[i], 0.0f);
+        }
+        const size_t elem0 = pix * e.dst_C[slot] + e.dst_coff[slot] + ch;
+        if (e.drop_keep < 1.0f) {
+          const float inv = 1.0f / e.drop_keep;
+          const unsigned long long seed =
+              e.drop_seed + (e.drop_seed_add ? static_cast<unsigned long long>(__ldg(e.drop_seed_add)) : 0ull);
 #pragma unroll
           for (int g = 0; g < 2; ++g) {
-            uint4 o;
-            o.x = pack_bf16x2(v[8 * g + 0], v[8 * g + 1]);
-            o.y = pack_bf16x2(v[8 * g + 2], v[8 * g + 3]);
-            o.z = pack_bf16x2(v[8 * g + 4], v[8 * g + 5]);
-            o.w = pack_bf16x2(v[8 * g + 6], v[8 * g + 7]);
-            dp[g] = o;
+            const uint32_t bits = dropout_keep_bits8(seed, e.drop_stream, elem0 / 8 + g, e.drop_keep);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) v[8 * g + i] = ((bits >> i) & 1u) ? v[8 * g + i] * inv : 0.0f;
           }
+        }
+        if (e.aux[slot]) {
+          const uint32_t aw[8] = {cur0.x, cur0.y, cur0.z, cur0.w, cur1.x, cur1.y, cur1.z, cur1.w};
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            v[2 * i] = bf16_lo(aw[i]) > 0.0f ? v[2 * i] * e.mask_scale : 0.0f;
+            v[2 * i + 1] = bf16_hi(aw[i]) > 0.0f ? v[2 * i + 1] * e.mask_scale : 0.0f;
+          }
+        }
+        uint4* dp = reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(e.dst[slot]) + elem0);
+#pragma unroll
+        for (int g = 0; g < 2; ++g) {
+          uint4 o;
+          o.x = pack_bf16x2(v[8 * g + 0], v[8 * g + 1]);
+          o.y = pack_bf16x2(v[8 * g + 2], v[8 * g + 3]);
+          o.z = pack_bf16x2(v[8 * g + 4], v[8 * g + 5]);
+          o.w = pack_bf16x2(v[8 * g + 6], v[8 * g + 7]);
+          dp[g] = o;
         }
       }
       tc_fence_before();

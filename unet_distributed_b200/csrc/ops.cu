@@ -278,7 +278,16 @@ size_t conv3x3_wgrad_ws_bytes(int N, int H, int W, int Cin_total, int Cout) {
   size_t halo = 0;
   const int cx = Cin_total >= 64 ? 64 : 32;
   if (Cin_total <= 128 && wgrad_halo_supported(H, W, cx, Cout)) halo = wgrad_halo_ws_bytes(N, H, W, cx, Cout);
-  return generic > halo ? generic : halo;
+  // the row variant (wide layers) splits the pixel range further because it has three times fewer CTAs per range
+  size_t row = 0;
+  if (wgrad_row_supported(H, W, Cout, Cin_total, 0)) {
+    WgradRowParams rp;
+    std::memset(&rp, 0, sizeof(rp));
+    wgrad_row_plan(rp, N, H, W, Cout, Cin_total, 0);
+    if (rp.splits > 1) row = static_cast<size_t>(rp.splits) * wp.nweights * sizeof(float);
+  }
+  size_t need = generic > halo ? generic : halo;
+  return need > row ? need : row;
 }
 
 int conv3x3_wgrad(const void* dz, int Cout, ConvSrc x0, ConvSrc x1, float* dw, void* ws, size_t ws_bytes, int N, int H,
@@ -302,6 +311,39 @@ int conv3x3_wgrad(const void* dz, int Cout, ConvSrc x0, ConvSrc x1, float* dw, v
       if (rc) return rc;
       off += Cx;
     }
+    return UB_OK;
+  }
+  if (wgrad_row_supported(H, W, Cout, x0.C, C1)) {
+    WgradRowParams rp;
+    std::memset(&rp, 0, sizeof(rp));
+    int rc = wgrad_row_plan(rp, N, H, W, Cout, x0.C, C1);
+    if (rc) return rc;
+    const long long cin = x0.C + C1;
+    const long long nweights = 9 * cin * Cout;
+    rp.out_tap_stride = cin * Cout;
+    rp.out_n_stride = Cout;
+    rp.out_split_stride = nweights;
+    if (rp.splits > 1) {
+      const size_t need = static_cast<size_t>(rp.splits) * nweights * sizeof(float);
+      UB_REQUIRE(ws != nullptr && ws_bytes >= need, "conv3x3_wgrad: workspace of %zu bytes needed, %zu given", need,
+                 ws_bytes);
+      rp.out = reinterpret_cast<float*>(ws);
+    } else {
+      rp.out = dw;
+    }
+    CUtensorMap zm, xm0, xm1;
+    rc = nhwc_map(&zm, dz, N, H, W, Cout, 64, Box{1, 8, 8});
+    if (rc) return rc;
+    rc = nhwc_map(&xm0, x0.ptr, N, H, W, x0.C, 64, Box{1, 8, 10});
+    if (rc) return rc;
+    xm1 = xm0;
+    if (C1) {
+      rc = nhwc_map(&xm1, x1.ptr, N, H, W, C1, 64, Box{1, 8, 10});
+      if (rc) return rc;
+    }
+    rc = wgrad_row_launch(rp, zm, xm0, xm1, s);
+    if (rc) return rc;
+    if (rp.splits > 1) return splitk_reduce_launch(rp.out, nweights, rp.splits, dw, nweights, s);
     return UB_OK;
   }
   WgradPlan wp;

@@ -44,6 +44,23 @@ size_t wgrad_halo_ws_bytes(int N, int H, int W, int Cx, int Cz);
 int wgrad_halo_launch(const CUtensorMap& x_map, const CUtensorMap& z_map, int N, int H, int W, int Cx, int Cz, int J,
                       float* dw, int cin_total, int ci_off, float* ws, cudaStream_t stream);
 
+// Row variant for wide layers (wgrad_row.cu): one CTA = one filter row (three taps) of a 128 x 128 tile.
+struct WgradRowParams {
+  int N, H, W;
+  int blocks_h, blocks_w;   // 8 x 8 pixel blocks per image
+  int splits;
+  int z_C, m_tiles;
+  int num_src;
+  int x_block_n[2], x_ntiles[2], x_col_off[2];
+  int stages;
+  float* out;
+  long long out_split_stride, out_tap_stride, out_n_stride;   // output channel (M) stride is 1
+};
+bool wgrad_row_supported(int H, int W, int Cz, int C0, int C1);
+int wgrad_row_plan(WgradRowParams& p, int N, int H, int W, int Cz, int C0, int C1);
+int wgrad_row_launch(const WgradRowParams& p, const CUtensorMap& z, const CUtensorMap& x0, const CUtensorMap& x1,
+                     cudaStream_t stream);
+
 // out[i] = sum_s ws[s*stride + i] (fixed order), i < n.
 int splitk_reduce_launch(const float* ws, long long split_stride, int splits, float* out, long long n,
                          cudaStream_t stream);
