@@ -10,14 +10,14 @@ namespace ub {
 namespace {
 
 constexpr int kThreads = 384;  // warp0 halo TMA, warp1 MMA + TMEM, warp2 weight TMA, warp3 idle, warps4..11 epilogue
-constexpr int kHaloStages = 2;
+constexpr int kMaxHaloStages = 4;
 constexpr int kMaxBStages = 4;
 constexpr int kTH = 16;        // image rows per super-tile
 constexpr int kSmemBudget = 225 * 1024;
 
 struct __align__(8) HaloBarriers {
-  uint64_t halo_full[kHaloStages];
-  uint64_t halo_empty[kHaloStages];
+  uint64_t halo_full[kMaxHaloStages];
+  uint64_t halo_empty[kMaxHaloStages];
   uint64_t b_full[kMaxBStages];
   uint64_t b_empty[kMaxBStages];
   uint64_t tmem_full[2];
@@ -26,6 +26,18 @@ struct __align__(8) HaloBarriers {
 };
 
 __host__ __device__ inline int round_up_1k(int x) { return (x + 1023) & ~1023; }
+
+// Optional wait-time accounting (UNETB200_HALO_TIMING=1): cycles each role spends blocked, summed over CTAs.
+// [0] MMA on tmem_empty, [1] MMA on halo_full, [2] MMA on b_full, [3] MMA total, [4] epilogue(warp4) on tmem_full,
+// [5] epilogue(warp4) total, [6] halo producer on halo_empty, [7] CTAs
+__device__ unsigned long long g_halo_timing[8];
+
+__device__ __forceinline__ void timed_wait(uint64_t* bar, uint32_t parity, bool on, unsigned long long& acc) {
+  if (!on) { mbar_wait(bar, parity); return; }
+  const long long t0 = clock64();
+  mbar_wait(bar, parity);
+  acc += static_cast<unsigned long long>(clock64() - t0);
+}
 
 __device__ __forceinline__ void decode_tile(const HaloParams& p, int tile, int& n, int& h0, int& w0, int& nt) {
   nt = tile % p.n_tiles;
@@ -52,6 +64,132 @@ __device__ __forceinline__ void issue_tap(uint32_t d0, int block_n, uint64_t ade
   }
 }
 
+// Epilogue of one CTA's tiles, specialised at compile time so that a 16-column chunk costs tens of instructions, not
+// hundreds (ncu: the run-time-generic version executed 33 M warp instructions for conv1b and was the bottleneck of
+// every 32/64-channel layer). Work items are (pixel tile j, 16-column chunk); the two warps of a TMEM lane quarter
+// take alternate items. BIAS_RELU: forward conv (bias + ReLU, bias may be null); DROP: Philox dropout after ReLU;
+// AUX: dgrad, gate by the producer's stored output (two destinations possible). The gate of the NEXT item is
+// requested before the current accumulators are read so that its latency hides behind the TMEM load and the stores.
+template <int BN, bool BIAS_RELU, bool DROP, bool AUX>
+__device__ __forceinline__ void halo_epilogue(const HaloParams& p, HaloBarriers* bars, uint32_t tmem_base, int warp,
+                                              int lane, int num_tiles) {
+  constexpr int kChunks = BN / 16;
+  const IgemmEpilogue& e = p.epi;
+  const int quarter = warp & 3;
+  const int half = (warp - 4) >> 2;
+  const int m = quarter * 32 + lane;
+  const int th = m >> 3, twl = m & 7;
+  const int items = p.J * kChunks;
+  const uint32_t t_lane = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16);
+  unsigned long long seed = 0;
+  if (DROP) seed = e.drop_seed + (e.drop_seed_add ? static_cast<unsigned long long>(__ldg(e.drop_seed_add)) : 0ull);
+  const float inv_keep = DROP ? 1.0f / e.drop_keep : 1.0f;
+  int it = 0;
+  unsigned long long t_wait = 0;
+  const long long t_begin = clock64();
+  for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
+    const int a = p.acc_double ? (it & 1) : 0;
+    const uint32_t fparity = p.acc_double ? ((it >> 1) & 1) : (it & 1);
+    int n, h0, w0, nt;
+    decode_tile(p, tile, n, h0, w0, nt);
+    const int h = h0 + th;
+    const int wbase = w0 + twl;
+    const bool row_ok = h < p.H;
+    const size_t pix0 = (static_cast<size_t>(n) * p.H + h) * p.W + wbase;   // pixel of strip j = pix0 + 8 j
+    const int col_tile = nt * BN;
+    // per-destination byte bases of this thread's pixel row (strip 0)
+    const char* aux_b[2] = {nullptr, nullptr};
+    char* dst_b[2];
+#pragma unroll
+    for (int sl = 0; sl < 2; ++sl) {
+      dst_b[sl] = reinterpret_cast<char*>(e.dst[sl]) + (pix0 * e.dst_C[sl] + e.dst_coff[sl]) * 2;
+      if (AUX && e.aux[sl]) {
+        aux_b[sl] = reinterpret_cast<const char*>(e.aux[sl]) + (pix0 * e.aux_C[sl] + e.aux_coff[sl]) * 2;
+      }
+    }
+    uint4 ax0 = make_uint4(0u, 0u, 0u, 0u), ax1 = ax0;
+    auto load_aux = [&](int item) {
+      const int j = item / kChunks, c = (item % kChunks) * 16;
+      const int col = col_tile + c;
+      const int sl = col >= e.split_col ? 1 : 0;
+      if (row_ok && (wbase + 8 * j) < p.W && aux_b[sl]) {
+        const int ch = sl ? col - e.split_col : col;
+        const uint4* ap = reinterpret_cast<const uint4*>(aux_b[sl] + (static_cast<size_t>(8 * j) * e.aux_C[sl] + ch) * 2);
+        ax0 = __ldg(ap);
+        ax1 = __ldg(ap + 1);
+      }
+    };
+    if (AUX && half < items) load_aux(half);
+    timed_wait(&bars->tmem_full[a], fparity, p.timing != 0, t_wait);
+    tc_fence_after();
+    for (int item = half; item < items; item += 2) {
+      const int j = item / kChunks, c = (item % kChunks) * 16;
+      const bool valid = row_ok && (wbase + 8 * j) < p.W;
+      const uint4 cur0 = ax0, cur1 = ax1;
+      if (AUX && item + 2 < items) load_aux(item + 2);
+      uint32_t r[16];
+      tmem_ld_32x32b_x16(t_lane + static_cast<uint32_t>((a * p.J + j) * BN + c), r);
+      tmem_ld_wait();
+      if (!valid) continue;
+      const int col = col_tile + c;
+      const int sl = (AUX && col >= e.split_col) ? 1 : 0;
+      const int ch = sl ? col - e.split_col : col;
+      float v[16];
+#pragma unroll
+      for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
+      if (BIAS_RELU) {
+        if (e.bias) {
+          const float4* bp = reinterpret_cast<const float4*>(e.bias + col);
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            const float4 bq = __ldg(bp + q);
+            v[4 * q + 0] += bq.x; v[4 * q + 1] += bq.y; v[4 * q + 2] += bq.z; v[4 * q + 3] += bq.w;
+          }
+        }
+        if (e.relu) {
+#pragma unroll
+          for (int i = 0; i < 16; ++i) v[i] = fmaxf(v[i], 0.0f);
+        }
+      }
+      const size_t off = (static_cast<size_t>(8 * j) * e.dst_C[sl] + ch) * 2;   // bytes from dst_b[sl]
+      if (DROP) {
+        const size_t elem0 = (pix0 + 8 * j) * e.dst_C[sl] + e.dst_coff[sl] + ch;
+#pragma unroll
+        for (int g = 0; g < 2; ++g) {
+          const uint32_t bits = dropout_keep_bits8(seed, e.drop_stream, elem0 / 8 + g, e.drop_keep);
+#pragma unroll
+          for (int i = 0; i < 8; ++i) v[8 * g + i] = ((bits >> i) & 1u) ? v[8 * g + i] * inv_keep : 0.0f;
+        }
+      }
+      if (AUX) {
+        if (aux_b[sl]) {
+          const uint32_t aw[8] = {cur0.x, cur0.y, cur0.z, cur0.w, cur1.x, cur1.y, cur1.z, cur1.w};
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            v[2 * i] = bf16_lo(aw[i]) > 0.0f ? v[2 * i] * e.mask_scale : 0.0f;
+            v[2 * i + 1] = bf16_hi(aw[i]) > 0.0f ? v[2 * i + 1] * e.mask_scale : 0.0f;
+          }
+        }
+      }
+      uint4* dp = reinterpret_cast<uint4*>(dst_b[sl] + off);
+      uint4 o0, o1;
+      o0.x = pack_bf16x2(v[0], v[1]);   o0.y = pack_bf16x2(v[2], v[3]);
+      o0.z = pack_bf16x2(v[4], v[5]);   o0.w = pack_bf16x2(v[6], v[7]);
+      o1.x = pack_bf16x2(v[8], v[9]);   o1.y = pack_bf16x2(v[10], v[11]);
+      o1.z = pack_bf16x2(v[12], v[13]); o1.w = pack_bf16x2(v[14], v[15]);
+      dp[0] = o0;
+      dp[1] = o1;
+    }
+    tc_fence_before();
+    __syncwarp();
+    if (lane == 0) mbar_arrive(&bars->tmem_empty[a]);
+  }
+  if (p.timing && warp == 4 && lane == 0) {
+    atomicAdd(&g_halo_timing[4], t_wait);
+    atomicAdd(&g_halo_timing[5], static_cast<unsigned long long>(clock64() - t_begin));
+  }
+}
+
 __global__ void __launch_bounds__(kThreads, 1)
 conv_halo_kernel(const __grid_constant__ HaloParams p, const __grid_constant__ CUtensorMap tmA0,
                  const __grid_constant__ CUtensorMap tmA1, const __grid_constant__ CUtensorMap tmB) {
@@ -66,7 +204,7 @@ conv_halo_kernel(const __grid_constant__ HaloParams p, const __grid_constant__ C
   const int btile_bytes = p.block_n * rowbytes;
   const int bstage_bytes = p.tpb * btile_bytes;    // multiple of 1024 (block_n >= 32, kc >= 32 -> >= 2048)
   uint8_t* halo_base = smem;
-  uint8_t* b_base = smem + kHaloStages * halo_stride;
+  uint8_t* b_base = smem + p.h_stages * halo_stride;
   HaloBarriers* bars = reinterpret_cast<HaloBarriers*>(b_base + p.b_stages * bstage_bytes);
 
   const int warp = threadIdx.x >> 5;
@@ -78,7 +216,7 @@ conv_halo_kernel(const __grid_constant__ HaloParams p, const __grid_constant__ C
   while (tmem_cols < static_cast<uint32_t>(acc_sets * p.J * p.block_n)) tmem_cols <<= 1;
 
   if (threadIdx.x == 0) {
-    for (int s = 0; s < kHaloStages; ++s) {
+    for (int s = 0; s < p.h_stages; ++s) {
       mbar_init(&bars->halo_full[s], 1);
       mbar_init(&bars->halo_empty[s], 1);
     }
@@ -109,18 +247,23 @@ conv_halo_kernel(const __grid_constant__ HaloParams p, const __grid_constant__ C
     if (lane == 0) {
       int hs = 0;
       uint32_t hphase = 0;
+      unsigned long long t_prod = 0;
       for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
         int n, h0, w0, nt;
         decode_tile(p, tile, n, h0, w0, nt);
         for (int src = 0; src < p.num_src; ++src) {
           const CUtensorMap* tmA = src == 0 ? &tmA0 : &tmA1;
           for (int cb = 0; cb < p.src_kblocks[src]; ++cb) {
-            mbar_wait(&bars->halo_empty[hs], hphase ^ 1u);
+            timed_wait(&bars->halo_empty[hs], hphase ^ 1u, p.timing != 0, t_prod);
             mbar_arrive_expect_tx(&bars->halo_full[hs], static_cast<uint32_t>(halo_bytes));
             tma_load_4d(halo_base + hs * halo_stride, tmA, &bars->halo_full[hs], cb * p.kc, w0 - 1, h0 - 1, n);
-            if (++hs == kHaloStages) { hs = 0; hphase ^= 1u; }
+            if (++hs == p.h_stages) { hs = 0; hphase ^= 1u; }
           }
         }
+      }
+      if (p.timing) {
+        atomicAdd(&g_halo_timing[6], t_prod);
+        atomicAdd(&g_halo_timing[7], 1ull);
       }
     }
   } else if (warp == 2) {
@@ -160,19 +303,21 @@ conv_halo_kernel(const __grid_constant__ HaloParams p, const __grid_constant__ C
     const uint32_t row16 = static_cast<uint32_t>(rowbytes >> 4);  // one halo row, in 16-byte units
     int hs = 0, bs = 0, it = 0;
     uint32_t hphase = 0, bphase = 0;
+    unsigned long long t_e = 0, t_h = 0, t_b = 0;
+    const long long t_mma0 = clock64();
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
       const int a = p.acc_double ? (it & 1) : 0;
       const uint32_t eparity = p.acc_double ? (((it >> 1) & 1) ^ 1u) : ((it & 1) ^ 1u);
-      mbar_wait(&bars->tmem_empty[a], eparity);
+      timed_wait(&bars->tmem_empty[a], eparity, p.timing != 0, t_e);
       tc_fence_after();
       const uint32_t d0 = tmem_base + static_cast<uint32_t>(a * p.J * p.block_n);
       uint32_t started = 0;  // 0 until the first MMA of every accumulator has been issued
       for (int src = 0; src < p.num_src; ++src) {
         for (int cb = 0; cb < p.src_kblocks[src]; ++cb) {
-          mbar_wait(&bars->halo_full[hs], hphase);
+          timed_wait(&bars->halo_full[hs], hphase, p.timing != 0, t_h);
           const uint64_t a_base = desc_hi_a + (smem_u32(halo_base + hs * halo_stride) >> 4);
           for (int tg = 0; tg < tap_groups; ++tg) {
-            mbar_wait(&bars->b_full[bs], bphase);
+            timed_wait(&bars->b_full[bs], bphase, p.timing != 0, t_b);
             tc_fence_after();
             const uint64_t b_stage = desc_hi_b + (smem_u32(b_base + bs * bstage_bytes) >> 4);
             if (elect_one()) {
@@ -199,118 +344,34 @@ conv_halo_kernel(const __grid_constant__ HaloParams p, const __grid_constant__ C
             started = 1;
             if (++bs == p.b_stages) { bs = 0; bphase ^= 1u; }
           }
-          if (++hs == kHaloStages) { hs = 0; hphase ^= 1u; }
+          if (++hs == p.h_stages) { hs = 0; hphase ^= 1u; }
         }
       }
       if (elect_one()) umma_commit(&bars->tmem_full[a]);
       __syncwarp();
     }
+    if (p.timing && lane == 0) {
+      atomicAdd(&g_halo_timing[0], t_e);
+      atomicAdd(&g_halo_timing[1], t_h);
+      atomicAdd(&g_halo_timing[2], t_b);
+      atomicAdd(&g_halo_timing[3], static_cast<unsigned long long>(clock64() - t_mma0));
+    }
   } else if (warp >= 4) {
     // ------------------------------------------------------------ epilogue: 8 warps, two per TMEM lane quarter
-    // Work items are (pixel tile j, 16-column chunk); the two warps of a quarter take alternate items. The gate
-    // tensor of the NEXT item (dgrad: the producer's forward output) is requested before the current item's
-    // accumulators are read, so its latency hides behind the TMEM load and the stores.
-    const int quarter = warp & 3;
-    const int half = (warp - 4) >> 2;
-    const int m = quarter * 32 + lane;
-    const int th = m >> 3, twl = m & 7;
     const IgemmEpilogue& e = p.epi;
-    const int chunks = p.block_n >> 4;
-    const int items = p.J * chunks;
-    const bool has_aux = (e.aux[0] != nullptr) || (e.aux[1] != nullptr);
-    int it = 0;
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
-      const int a = p.acc_double ? (it & 1) : 0;
-      const uint32_t fparity = p.acc_double ? ((it >> 1) & 1) : (it & 1);
-      int n, h0, w0, nt;
-      decode_tile(p, tile, n, h0, w0, nt);
-      const int h = h0 + th;
-      const size_t row_pix = (static_cast<size_t>(n) * p.H + h) * p.W;
-      uint4 ax0 = make_uint4(0u, 0u, 0u, 0u), ax1 = ax0;
-      auto aux_ptr = [&](int item) -> const uint4* {
-        const int j = item / chunks, c = (item - j * chunks) << 4;
-        const int w = w0 + 8 * j + twl;
-        const int col = nt * p.block_n + c;
-        const int slot = col >= e.split_col ? 1 : 0;
-        if (!(h < p.H && w < p.W) || e.aux[slot] == nullptr) return nullptr;
-        const int ch = slot ? col - e.split_col : col;
-        return reinterpret_cast<const uint4*>(reinterpret_cast<const __nv_bfloat16*>(e.aux[slot]) +
-                                              (row_pix + w) * e.aux_C[slot] + e.aux_coff[slot] + ch);
-      };
-      if (has_aux && half < items) {
-        const uint4* ap = aux_ptr(half);
-        if (ap) { ax0 = __ldg(ap); ax1 = __ldg(ap + 1); }
-      }
-      mbar_wait(&bars->tmem_full[a], fparity);
-      tc_fence_after();
-      for (int item = half; item < items; item += 2) {
-        const int j = item / chunks, c = (item - j * chunks) << 4;
-        const int w = w0 + 8 * j + twl;
-        const bool valid = (h < p.H) && (w < p.W);
-        const size_t pix = row_pix + w;
-        const uint4 cur0 = ax0, cur1 = ax1;
-        if (has_aux && item + 2 < items) {
-          const uint4* ap = aux_ptr(item + 2);
-          if (ap) { ax0 = __ldg(ap); ax1 = __ldg(ap + 1); }
-        }
-        uint32_t r[16];
-        tmem_ld_32x32b_x16(tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) +
-                               static_cast<uint32_t>((a * p.J + j) * p.block_n + c), r);
-        tmem_ld_wait();
-        if (!valid) continue;
-        const int col = nt * p.block_n + c;
-        const int slot = col >= e.split_col ? 1 : 0;
-        const int ch = slot ? col - e.split_col : col;
-        float v[16];
-#pragma unroll
-        for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
-        if (e.bias) {
-          const float4* bp = reinterpret_cast<const float4*>(e.bias + col);
-#pragma unroll
-          for (int q = 0; q < 4; ++q) {
-            const float4 bq = __ldg(bp + q);
-            v[4 * q + 0] += bq.x; v[4 * q + 1] += bq.y; v[4 * q + 2] += bq.z; v[4 * q + 3] += bq.w;
-          }
-        }
-        if (e.relu) {
-#pragma unroll
-          for (int i = 0; i < 16; ++i) v[i] = fmaxf(v[i], 0.0f);
-        }
-        const size_t elem0 = pix * e.dst_C[slot] + e.dst_coff[slot] + ch;
-        if (e.drop_keep < 1.0f) {
-          const float inv = 1.0f / e.drop_keep;
-          const unsigned long long seed =
-              e.drop_seed + (e.drop_seed_add ? static_cast<unsigned long long>(__ldg(e.drop_seed_add)) : 0ull);
-#pragma unroll
-          for (int g = 0; g < 2; ++g) {
-            const uint32_t bits = dropout_keep_bits8(seed, e.drop_stream, elem0 / 8 + g, e.drop_keep);
-#pragma unroll
-            for (int i = 0; i < 8; ++i) v[8 * g + i] = ((bits >> i) & 1u) ? v[8 * g + i] * inv : 0.0f;
-          }
-        }
-        if (e.aux[slot]) {
-          const uint32_t aw[8] = {cur0.x, cur0.y, cur0.z, cur0.w, cur1.x, cur1.y, cur1.z, cur1.w};
-#pragma unroll
-          for (int i = 0; i < 8; ++i) {
-            v[2 * i] = bf16_lo(aw[i]) > 0.0f ? v[2 * i] * e.mask_scale : 0.0f;
-            v[2 * i + 1] = bf16_hi(aw[i]) > 0.0f ? v[2 * i + 1] * e.mask_scale : 0.0f;
-          }
-        }
-        uint4* dp = reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(e.dst[slot]) + elem0);
-#pragma unroll
-        for (int g = 0; g < 2; ++g) {
-          uint4 o;
-          o.x = pack_bf16x2(v[8 * g + 0], v[8 * g + 1]);
-          o.y = pack_bf16x2(v[8 * g + 2], v[8 * g + 3]);
-          o.z = pack_bf16x2(v[8 * g + 4], v[8 * g + 5]);
-          o.w = pack_bf16x2(v[8 * g + 6], v[8 * g + 7]);
-          dp[g] = o;
-        }
-      }
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&bars->tmem_empty[a]);
-    }
+    const bool aux = (e.aux[0] != nullptr) || (e.aux[1] != nullptr);
+    const bool drop = e.drop_keep < 1.0f;
+#define UB_EPI(BN)                                                                                         \
+    do {                                                                                                   \
+      if (aux) halo_epilogue<BN, false, false, true>(p, bars, tmem_base, warp, lane, num_tiles);           \
+      else if (drop) halo_epilogue<BN, true, true, false>(p, bars, tmem_base, warp, lane, num_tiles);      \
+      else if (e.bias || e.relu) halo_epilogue<BN, true, false, false>(p, bars, tmem_base, warp, lane, num_tiles); \
+      else halo_epilogue<BN, false, false, false>(p, bars, tmem_base, warp, lane, num_tiles);              \
+    } while (0)
+    if (p.block_n == 32) UB_EPI(32);
+    else if (p.block_n == 64) UB_EPI(64);
+    else UB_EPI(128);
+#undef UB_EPI
   }
 
   tc_fence_before();
@@ -324,7 +385,7 @@ conv_halo_kernel(const __grid_constant__ HaloParams p, const __grid_constant__ C
 size_t halo_smem_bytes(const HaloParams& p) {
   const int P = 8 * p.J + 2;
   const int halo_stride = round_up_1k((kTH + 2) * P * p.kc * 2);
-  return static_cast<size_t>(kHaloStages) * halo_stride + static_cast<size_t>(p.b_stages) * p.tpb * p.block_n * p.kc * 2 +
+  return static_cast<size_t>(p.h_stages) * halo_stride + static_cast<size_t>(p.b_stages) * p.tpb * p.block_n * p.kc * 2 +
          sizeof(HaloBarriers) + 1024;
 }
 
@@ -350,10 +411,16 @@ bool halo_plan(HaloParams& p, int N, int H, int W, int kc, int ncols) {
     p.acc_double = (2 * J * block_n <= 512) ? 1 : 0;
     p.tpb = (9 * btile <= 36 * 1024) ? 9 : ((3 * btile <= 48 * 1024) ? 3 : 1);
     const int P = 8 * J + 2;
-    const int halo = kHaloStages * round_up_1k((kTH + 2) * P * kc * 2);
-    int stages = (kSmemBudget - halo - 1024 - static_cast<int>(sizeof(HaloBarriers))) / (p.tpb * btile);
-    if (stages > kMaxBStages) stages = kMaxBStages;
-    if (stages >= 2) {
+    const int halo_stride = round_up_1k((kTH + 2) * P * kc * 2);
+    const int budget = kSmemBudget - 1024 - static_cast<int>(sizeof(HaloBarriers));
+    // at least two weight stages; then as many halo stages as fit (the halo load is the long-latency one: a box of
+    // up to 612 rows), then the rest to the weight ring
+    int hst = (budget - 2 * p.tpb * btile) / halo_stride;
+    if (hst > kMaxHaloStages) hst = kMaxHaloStages;
+    if (hst >= 2) {
+      int stages = (budget - hst * halo_stride) / (p.tpb * btile);
+      if (stages > kMaxBStages) stages = kMaxBStages;
+      p.h_stages = hst;
       p.b_stages = stages;
       break;
     }
@@ -385,6 +452,22 @@ int halo_launch(const HaloParams& p, const CUtensorMap& a0, const CUtensorMap& a
     const double kdim = 9.0 * p.kc * (p.src_kblocks[0] + (p.num_src > 1 ? p.src_kblocks[1] : 0));
     const double ncols = static_cast<double>(p.n_tiles) * p.block_n;
     prof_begin(UB_KIND_IGEMM, 2.0 * pixels * kdim * ncols, 2.0 * pixels * (kdim / 9.0 + ncols), stream);
+  }
+  static const bool timing = getenv("UNETB200_HALO_TIMING") != nullptr;
+  if (timing) {
+    HaloParams pt = p;
+    pt.timing = 1;
+    unsigned long long z[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    cudaMemcpyToSymbol(g_halo_timing, z, sizeof(z));
+    conv_halo_kernel<<<grid, kThreads, smem, stream>>>(pt, a0, a1, b);
+    cudaStreamSynchronize(stream);
+    cudaMemcpyFromSymbol(z, g_halo_timing, sizeof(z));
+    const double c = static_cast<double>(z[7] ? z[7] : 1);
+    fprintf(stderr, "[halo timing] N%d %dx%d kc%d bn%d J%d srcs%d tiles%d grid%d | per CTA cycles: mma_total %.0f (wait tmem_empty %.0f, "
+            "halo_full %.0f, b_full %.0f) epi_total %.0f (wait tmem_full %.0f) halo_producer wait %.0f\n",
+            p.N, p.H, p.W, p.kc, p.block_n, p.J, p.num_src, num_tiles, grid, z[3] / c, z[0] / c, z[1] / c, z[2] / c, z[5] / c,
+            z[4] / c, z[6] / c);
+    return UB_OK;
   }
   conv_halo_kernel<<<grid, kThreads, smem, stream>>>(p, a0, a1, b);
   UB_CHECK_CUDA(cudaGetLastError());

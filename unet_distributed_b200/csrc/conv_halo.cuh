@@ -28,6 +28,8 @@ struct HaloParams {
   int kc;                 // 64 (SWIZZLE_128B) or 32 (SWIZZLE_64B)
   int tpb;                // taps per weight stage: 9, 3 or 1
   int b_stages;
+  int h_stages;           // halo ring depth (2..4)
+  int timing;             // debug: accumulate per-role wait cycles (UNETB200_HALO_TIMING)
   int acc_double;         // two accumulator sets: epilogue overlaps the next super-tile's MMAs
   IgemmEpilogue epi;      // d2s_cout must be 0
 };
