@@ -140,7 +140,7 @@ def run_reference(args):
     if rank != 0:
         return 0
     cores = os.cpu_count() or 1
-    sample = 16
+    sample = 8
     value, ms = cpu_train_images_per_sec(args.decoder, args.size, args.channels, sample, args.steps, args.warmup, cores)
     line = {
         "impl": "reference", "metric": "train images/sec", "value": value, "unit": "images/s", "n_gpus": args.gpus,
@@ -154,7 +154,7 @@ def run_reference(args):
                                    "restatement of the reference (oracle/unet_oracle.py); TF 1.4 is not installable"},
         "e2e": {"value": value, "unit": "images/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
     return 0
 
 
@@ -175,7 +175,7 @@ def run_b200(args):
     ups = args.decoder == "upsampling"
     tr = Trainer(N, S, S, C, 1, ups, dropout=0.2, learning_rate=0.0005,
                  const_learningrate=bool(args.const_learningrate), lr_fraction=args.lr_fraction,
-                 decay_steps=args.decay_steps, use_cuda_graph=(world == 1 and not args.no_graph))
+                 decay_steps=args.decay_steps, use_cuda_graph=(not args.no_graph))
     # synthetic batches: a few distinct ones per rank, rotated (inputs are far smaller than the per-step working set)
     nb = 4
     base_imgs, base_msks = make_slices(min(N, 64), S, S, C, seed=816 + rank)
@@ -233,26 +233,49 @@ def run_b200(args):
     ms_e2e_step = float(ms_e2e.item()) / args.steps
 
     # ---- per-kernel-class timing for the roofline (events around every tile-engine launch; graph replay off)
+    # every rank runs these steps (they contain the gradient all-reduce); only rank 0's records are reported
     roof = None
-    if rank == 0:
-        tr_prof = tr
-        if tr.use_cuda_graph:
-            tr.use_cuda_graph = False
-        for i in range(2):
-            tr_prof.train_step(*d_batches[i % nb])
-        torch.cuda.synchronize()
-        L.unetb200_profile_enable(1)
-        psteps = 3
-        for i in range(psteps):
-            tr_prof.train_step(*d_batches[i % nb])
-        ms = (ctypes.c_double * 3)()
-        fl = (ctypes.c_double * 3)()
-        by = (ctypes.c_double * 3)()
-        ln = (ctypes.c_longlong * 3)()
-        _lib.check(L.unetb200_profile_collect(ms, fl, by, ln), "profile_collect")
-        L.unetb200_profile_enable(0)
-        roof = {"igemm": (ms[0], fl[0], by[0], ln[0]), "wgrad": (ms[1], fl[1], by[1], ln[1]), "steps": psteps}
+    if tr.use_cuda_graph:
+        tr.use_cuda_graph = False
+    for i in range(2):
+        tr.train_step(*d_batches[i % nb])
+    torch.cuda.synchronize()
+    L.unetb200_profile_enable(1)
+    psteps = 3
+    for i in range(psteps):
+        tr.train_step(*d_batches[i % nb])
+    ms = (ctypes.c_double * 3)()
+    fl = (ctypes.c_double * 3)()
+    by = (ctypes.c_double * 3)()
+    ln = (ctypes.c_longlong * 3)()
+    _lib.check(L.unetb200_profile_collect(ms, fl, by, ln), "profile_collect")
+    L.unetb200_profile_enable(0)
+    roof = {"igemm": (ms[0], fl[0], by[0], ln[0]), "wgrad": (ms[1], fl[1], by[1], ln[1]), "steps": psteps}
     barrier()
+
+    # ---- the gradient all-reduce alone (the three buckets back to back), for bus bandwidth against NVLink
+    allreduce = None
+    if world > 1:
+        for _ in range(3):
+            for seg in range(3):
+                tr.reducer.launch(seg)
+            tr.reducer.wait()
+        barrier()
+        a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        reps = 20
+        a0.record()
+        for _ in range(reps):
+            for seg in range(3):
+                tr.reducer.launch(seg)
+            tr.reducer.wait()
+        a1.record()
+        barrier()
+        t_ar = torch.tensor([a0.elapsed_time(a1) / reps], device=dev)
+        dist.all_reduce(t_ar, op=dist.ReduceOp.MAX)
+        nbytes = tr.reducer.bytes_per_step()
+        alg = nbytes / (float(t_ar.item()) * 1e-3) / 1e9
+        allreduce = {"bytes_per_step": nbytes, "ms": float(t_ar.item()), "alg_gbs": alg,
+                     "bus_gbs": alg * 2 * (world - 1) / world, "nvlink_peak_gbs_per_direction": 900, "buckets": 3}
 
     if rank == 0:
         peaks = load_peaks()
@@ -280,7 +303,7 @@ def run_b200(args):
                 "workload": f"UNet {S}x{S}x{C} {args.decoder} decoder (BASELINE configs[{1 if ups else 0}] shape), "
                             f"bs{N} per GPU, Adam, dropout 0.2, train step fwd+dice+bwd+allreduce+Adam",
                 "decoder": args.decoder, "per_gpu_batch": N, "global_batch": gb, "image": [S, S, C],
-                "parallelism": f"dp{world}", "cuda_graph": bool(world == 1 and not args.no_graph),
+                "parallelism": f"dp{world}", "cuda_graph": bool(not args.no_graph),
                 "l2": "no explicit flush: one step touches >2.5 GB of activations and gradients (L2 is 126 MB); "
                       "input batches rotate",
                 "const_learningrate": bool(args.const_learningrate)},
@@ -298,7 +321,7 @@ def run_b200(args):
                           "launches_per_step": wg_n / roof["steps"], "ms_per_step": wg_ms / roof["steps"]},
                 "whole_step": ({"achieved": value * gflop_img / 1e3 / world, "unit": "TFLOP/s per GPU",
                                 "frac": value * gflop_img / 1e3 / world / peak_tf} if gflop_img else None)},
-            "loss": float(metrics_last[0]), "dice": float(metrics_last[1]),
+            "loss": float(metrics_last[0]), "dice": float(metrics_last[1]), "allreduce": allreduce,
         }
         if world == 1 and not args.no_cpu_baseline:
             cores = os.cpu_count() or 1
@@ -307,15 +330,28 @@ def run_b200(args):
                 "value": cpu_v, "unit": "images/s", "cores": cores, "kind": "port",
                 "sample": "3 timed steps of 32 images (of the bs128 workload) after 1 warm-up, torch-CPU fp32 "
                           "restatement of the reference's train step (oracle/unet_oracle.py)"}
-        print(json.dumps(line), flush=True)
+        emit(line)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
     return 0
 
 
+_REAL_STDOUT = None
+
+
+def emit(line):
+    """The ONE JSON line goes to the real stdout; everything else this process (or NCCL) prints goes to stderr."""
+    data = (json.dumps(line) + "\n").encode()
+    os.write(_REAL_STDOUT if _REAL_STDOUT is not None else 1, data)
+
+
 def main():
+    global _REAL_STDOUT
     args = parse_args()
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
     if args.impl == "reference":
         return run_reference(args)
     return run_b200(args)

@@ -70,10 +70,11 @@ __device__ __forceinline__ void issue_tap(uint32_t d0, int block_n, uint64_t ade
 // take alternate items. BIAS_RELU: forward conv (bias + ReLU, bias may be null); DROP: Philox dropout after ReLU;
 // AUX: dgrad, gate by the producer's stored output (two destinations possible). The gate of the NEXT item is
 // requested before the current accumulators are read so that its latency hides behind the TMEM load and the stores.
-template <int BN, bool BIAS_RELU, bool DROP, bool AUX>
+template <int BN, bool BIAS_RELU, bool DROP, bool AUX, bool GIN>
 __device__ __forceinline__ void halo_epilogue(const HaloParams& p, HaloBarriers* bars, uint32_t tmem_base, int warp,
                                               int lane, int num_tiles) {
   constexpr int kChunks = BN / 16;
+  constexpr int kMaxItems = 8;   // per warp: J * kChunks / 2 <= 8 for every plan halo_plan() produces
   const IgemmEpilogue& e = p.epi;
   const int quarter = warp & 3;
   const int half = (warp - 4) >> 2;
@@ -120,9 +121,31 @@ __device__ __forceinline__ void halo_epilogue(const HaloParams& p, HaloBarriers*
       }
     };
     if (AUX && half < items) load_aux(half);
+    // GIN: the producer's ReLU gates as bits -- all of this warp's items of the tile are requested up front (one
+    // 2-byte load each), so their latency overlaps the MMAs of this very tile
+    uint32_t gb[kMaxItems];
+    if (GIN) {
+#pragma unroll
+      for (int k = 0; k < kMaxItems; ++k) {
+        const int item = half + 2 * k;
+        gb[k] = 0xFFFFu;
+        if (item < items) {
+          const int j = item / kChunks, c = (item % kChunks) * 16;
+          const int col = col_tile + c;
+          const int sl = col >= e.split_col ? 1 : 0;
+          if (row_ok && (wbase + 8 * j) < p.W && e.gate_in[sl]) {
+            const int ch = sl ? col - e.split_col : col;
+            gb[k] = __ldg(e.gate_in[sl] + (((pix0 + 8 * j) * e.aux_C[sl] + e.aux_coff[sl] + ch) >> 4));
+          }
+        }
+      }
+    }
     timed_wait(&bars->tmem_full[a], fparity, p.timing != 0, t_wait);
     tc_fence_after();
-    for (int item = half; item < items; item += 2) {
+#pragma unroll
+    for (int k = 0; k < kMaxItems; ++k) {
+      const int item = half + 2 * k;
+      if (item >= items) break;
       const int j = item / kChunks, c = (item % kChunks) * 16;
       const bool valid = row_ok && (wbase + 8 * j) < p.W;
       const uint4 cur0 = ax0, cur1 = ax1;
@@ -132,7 +155,7 @@ __device__ __forceinline__ void halo_epilogue(const HaloParams& p, HaloBarriers*
       tmem_ld_wait();
       if (!valid) continue;
       const int col = col_tile + c;
-      const int sl = (AUX && col >= e.split_col) ? 1 : 0;
+      const int sl = ((AUX || GIN) && col >= e.split_col) ? 1 : 0;
       const int ch = sl ? col - e.split_col : col;
       float v[16];
 #pragma unroll
@@ -159,6 +182,21 @@ __device__ __forceinline__ void halo_epilogue(const HaloParams& p, HaloBarriers*
           const uint32_t bits = dropout_keep_bits8(seed, e.drop_stream, elem0 / 8 + g, e.drop_keep);
 #pragma unroll
           for (int i = 0; i < 8; ++i) v[8 * g + i] = ((bits >> i) & 1u) ? v[8 * g + i] * inv_keep : 0.0f;
+        }
+      }
+      if (BIAS_RELU) {
+        if (e.gate_out) {
+          uint32_t bits = 0;
+#pragma unroll
+          for (int i = 0; i < 16; ++i) bits |= (v[i] > 0.0f ? 1u : 0u) << i;
+          e.gate_out[((pix0 + 8 * j) * e.dst_C[0] + e.dst_coff[0] + ch) >> 4] = static_cast<unsigned short>(bits);
+        }
+      }
+      if (GIN) {
+        if (e.gate_in[sl]) {
+          const uint32_t b = gb[k];
+#pragma unroll
+          for (int i = 0; i < 16; ++i) v[i] = ((b >> i) & 1u) ? v[i] * e.mask_scale : 0.0f;
         }
       }
       if (AUX) {
@@ -360,13 +398,15 @@ conv_halo_kernel(const __grid_constant__ HaloParams p, const __grid_constant__ C
     // ------------------------------------------------------------ epilogue: 8 warps, two per TMEM lane quarter
     const IgemmEpilogue& e = p.epi;
     const bool aux = (e.aux[0] != nullptr) || (e.aux[1] != nullptr);
+    const bool gin = (e.gate_in[0] != nullptr) || (e.gate_in[1] != nullptr);
     const bool drop = e.drop_keep < 1.0f;
 #define UB_EPI(BN)                                                                                         \
     do {                                                                                                   \
-      if (aux) halo_epilogue<BN, false, false, true>(p, bars, tmem_base, warp, lane, num_tiles);           \
-      else if (drop) halo_epilogue<BN, true, true, false>(p, bars, tmem_base, warp, lane, num_tiles);      \
-      else if (e.bias || e.relu) halo_epilogue<BN, true, false, false>(p, bars, tmem_base, warp, lane, num_tiles); \
-      else halo_epilogue<BN, false, false, false>(p, bars, tmem_base, warp, lane, num_tiles);              \
+      if (gin) halo_epilogue<BN, false, false, false, true>(p, bars, tmem_base, warp, lane, num_tiles);    \
+      else if (aux) halo_epilogue<BN, false, false, true, false>(p, bars, tmem_base, warp, lane, num_tiles); \
+      else if (drop) halo_epilogue<BN, true, true, false, false>(p, bars, tmem_base, warp, lane, num_tiles); \
+      else if (e.bias || e.relu) halo_epilogue<BN, true, false, false, false>(p, bars, tmem_base, warp, lane, num_tiles); \
+      else halo_epilogue<BN, false, false, false, false>(p, bars, tmem_base, warp, lane, num_tiles);       \
     } while (0)
     if (p.block_n == 32) UB_EPI(32);
     else if (p.block_n == 64) UB_EPI(64);

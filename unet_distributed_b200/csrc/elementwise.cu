@@ -153,19 +153,28 @@ __global__ void conv_first_wgrad_kernel(const float* __restrict__ x, const uint4
 // 8-way sum); first n_a outputs go to out_a, the rest to out_b. Launch with 256 threads = 32 columns x 8 lanes.
 __global__ void rows_reduce_kernel(const float* __restrict__ ws, int nrows, int n, float* __restrict__ out_a, int n_a,
                                    float* __restrict__ out_b) {
-  __shared__ float part[8][32];
+  __shared__ float part[32][32];
+  const int lanes = blockDim.x >> 5;   // row lanes per column (any block of 32*k threads, k <= 32)
   const int c = threadIdx.x & 31, p = threadIdx.x >> 5;
   const int i = blockIdx.x * 32 + c;
   float acc = 0.0f;
   if (i < n) {
-    for (int r = p; r < nrows; r += 8) acc += ws[static_cast<long long>(r) * n + i];
+    // each lane walks its rows in order; four loads are in flight, summed in the same order every time
+    int r = p;
+    for (; r + 3 * lanes < nrows; r += 4 * lanes) {
+      const float v0 = ws[static_cast<long long>(r) * n + i];
+      const float v1 = ws[static_cast<long long>(r + lanes) * n + i];
+      const float v2 = ws[static_cast<long long>(r + 2 * lanes) * n + i];
+      const float v3 = ws[static_cast<long long>(r + 3 * lanes) * n + i];
+      acc += v0; acc += v1; acc += v2; acc += v3;
+    }
+    for (; r < nrows; r += lanes) acc += ws[static_cast<long long>(r) * n + i];
   }
   part[p][c] = acc;
   __syncthreads();
   if (p == 0 && i < n) {
     float s = part[0][c];
-#pragma unroll
-    for (int q = 1; q < 8; ++q) s += part[q][c];
+    for (int q = 1; q < lanes; ++q) s += part[q][c];
     if (i < n_a) out_a[i] = s;
     else if (out_b) out_b[i - n_a] = s;
   }
@@ -633,9 +642,13 @@ int check_groups(int C, const char* what) {
 }  // namespace
 
 // ============================================================================================ host launchers
+bool conv_first_fwd_writes_gates(int Cin, int Cout) { return Cout == 32 && (Cin == 1 || Cin == 4); }
+
 int conv_first_fwd(const float* x, const float* w, const float* bias, void* y, int N, int H, int W, int Cin, int Cout,
-                   cudaStream_t s) {
+                   cudaStream_t s, unsigned short* gate_out) {
   UB_REQUIRE(Cin >= 1 && Cin <= 8, "conv_first_fwd: Cin %d outside 1..8", Cin);
+  UB_REQUIRE(gate_out == nullptr || conv_first_fwd_writes_gates(Cin, Cout),
+             "conv_first_fwd: gate bits are only written for Cout 32 and Cin 1 or 4");
   UB_REQUIRE(Cout % 8 == 0 && Cout <= 64, "conv_first_fwd: Cout %d unsupported", Cout);
   const long long total = static_cast<long long>(N) * H * W * (Cout / 8);
   UB_REQUIRE(total < (1ll << 31), "conv_first_fwd: tensor too large");
@@ -645,9 +658,11 @@ int conv_first_fwd(const float* x, const float* w, const float* bias, void* y, i
     const unsigned cap = 8u * static_cast<unsigned>(device_sm_count());
     if (blocks > cap) blocks = cap;
     if (Cin == 1) {
-      conv_first32_fwd_kernel<1><<<blocks, kThreads, 0, s>>>(x, w, bias, reinterpret_cast<uint4*>(y), H, W, P);
+      conv_first32_fwd_kernel<1><<<blocks, kThreads, 0, s>>>(x, w, bias, reinterpret_cast<uint4*>(y),
+                                                             reinterpret_cast<unsigned int*>(gate_out), H, W, P);
     } else {
-      conv_first32_fwd_kernel<4><<<blocks, kThreads, 0, s>>>(x, w, bias, reinterpret_cast<uint4*>(y), H, W, P);
+      conv_first32_fwd_kernel<4><<<blocks, kThreads, 0, s>>>(x, w, bias, reinterpret_cast<uint4*>(y),
+                                                             reinterpret_cast<unsigned int*>(gate_out), H, W, P);
     }
     UB_CHECK_CUDA(cudaGetLastError());
     return UB_OK;
@@ -681,7 +696,7 @@ int conv_first_wgrad(const float* x, const void* dz, float* dw, float* db, float
   conv_first_wgrad_kernel<<<kRedBlocks, kThreads, smem, s>>>(x, reinterpret_cast<const uint4*>(dz), ws, N, H, W, Cin,
                                                             Cout);
   UB_CHECK_CUDA(cudaGetLastError());
-  rows_reduce_kernel<<<grid_for(nout, 32), 256, 0, s>>>(ws, kRedBlocks, nout, dw, 9 * Cin * Cout, db);
+  rows_reduce_kernel<<<grid_for(nout, 32), 1024, 0, s>>>(ws, kRedBlocks, nout, dw, 9 * Cin * Cout, db);
   UB_CHECK_CUDA(cudaGetLastError());
   return UB_OK;
 }
@@ -751,7 +766,7 @@ int head_fwd(const void* x, const float* w, const float* b, const float* y_true,
                                                        n_cl);
   }
   UB_CHECK_CUDA(cudaGetLastError());
-  rows_reduce_kernel<<<1, 256, 0, s>>>(ws, kRedBlocks, 3, sums, 3, nullptr);
+  rows_reduce_kernel<<<1, 1024, 0, s>>>(ws, kRedBlocks, 3, sums, 3, nullptr);
   UB_CHECK_CUDA(cudaGetLastError());
   return UB_OK;
 }
@@ -778,7 +793,7 @@ int head_bwd(const void* x, const float* w, const float* y_true, const float* p,
                                                        grad_scale, reinterpret_cast<uint4*>(dx), ws, P, C, n_cl);
   }
   UB_CHECK_CUDA(cudaGetLastError());
-  rows_reduce_kernel<<<grid_for(nout, 32), 256, 0, s>>>(ws, kRedBlocks, nout, dw, C * n_cl, db);
+  rows_reduce_kernel<<<grid_for(nout, 32), 1024, 0, s>>>(ws, kRedBlocks, nout, dw, C * n_cl, db);
   UB_CHECK_CUDA(cudaGetLastError());
   return UB_OK;
 }
@@ -791,7 +806,7 @@ int colsum_bf16(const void* dz, float* db, float* ws, long long P, int C, cudaSt
   colsum_kernel<<<kRedBlocks, kThreads, (kThreads / 32) * C * sizeof(float), s>>>(reinterpret_cast<const uint4*>(dz),
                                                                                  ws, P, C);
   UB_CHECK_CUDA(cudaGetLastError());
-  rows_reduce_kernel<<<grid_for(C, 32), 256, 0, s>>>(ws, kRedBlocks, C, db, C, nullptr);
+  rows_reduce_kernel<<<grid_for(C, 32), 1024, 0, s>>>(ws, kRedBlocks, C, db, C, nullptr);
   UB_CHECK_CUDA(cudaGetLastError());
   return UB_OK;
 }
@@ -838,7 +853,7 @@ int colsum_bf16_static(const void* dz, float* db, long long P, int C, cudaStream
   colsum_kernel<<<kRedBlocks, kThreads, (kThreads / 32) * C * sizeof(float), s>>>(reinterpret_cast<const uint4*>(dz),
                                                                                  scratch, P, C);
   UB_CHECK_CUDA(cudaGetLastError());
-  rows_reduce_kernel<<<grid_for(C, 32), 256, 0, s>>>(scratch, rows, C, db, C, nullptr);
+  rows_reduce_kernel<<<grid_for(C, 32), 1024, 0, s>>>(scratch, rows, C, db, C, nullptr);
   UB_CHECK_CUDA(cudaGetLastError());
   return UB_OK;
 }

@@ -7,8 +7,10 @@
 namespace ub {
 
 // conv1a: direct 3x3 'same' conv on the fp32 network input (Cin in 1..8), fp32 HWIO weights, bias, ReLU -> bf16.
+// gate_out (optional, only for Cout == 32 and Cin in {1, 4}): ReLU gates as bits, uint16 per 16 channels.
 int conv_first_fwd(const float* x, const float* w_hwio, const float* bias, void* y_bf16, int N, int H, int W, int Cin,
-                   int Cout, cudaStream_t s);
+                   int Cout, cudaStream_t s, unsigned short* gate_out = nullptr);
+bool conv_first_fwd_writes_gates(int Cin, int Cout);
 // dW[3][3][Cin][Cout] and db[Cout] from fp32 x and bf16 dz; ws needs conv_first_wgrad_ws_floats() floats.
 long long conv_first_wgrad_ws_floats(int Cin, int Cout);
 int conv_first_wgrad(const float* x, const void* dz_bf16, float* dw, float* db, float* ws, int N, int H, int W, int Cin,

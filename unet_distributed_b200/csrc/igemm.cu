@@ -208,6 +208,17 @@ igemm_kernel(const __grid_constant__ IgemmParams p, const __grid_constant__ CUte
               for (int i = 0; i < 8; ++i) v[8 * g + i] = ((bits >> i) & 1u) ? v[8 * g + i] * inv : 0.0f;
             }
           }
+          if (e.gate_out && e.d2s_cout == 0) {   // ReLU gates of this output as bits (see igemm.cuh)
+            uint32_t bits = 0;
+#pragma unroll
+            for (int i = 0; i < 16; ++i) bits |= (v[i] > 0.0f ? 1u : 0u) << i;
+            e.gate_out[(drop_elem0 + c) >> 4] = static_cast<unsigned short>(bits);
+          }
+          if (e.gate_in[slot]) {
+            const uint32_t b = __ldg(e.gate_in[slot] + ((pix * e.aux_C[slot] + e.aux_coff[slot] + ch0 + c) >> 4));
+#pragma unroll
+            for (int i = 0; i < 16; ++i) v[i] = ((b >> i) & 1u) ? v[i] * e.mask_scale : 0.0f;
+          }
           if (aux) {
             const uint4* ap = reinterpret_cast<const uint4*>(aux + c);
 #pragma unroll

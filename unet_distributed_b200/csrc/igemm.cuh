@@ -23,6 +23,11 @@ struct IgemmEpilogue {
   int dst_coff[2];
   int aux_C[2];
   int aux_coff[2];
+  // ReLU gates as bits: one uint16 per (pixel, 16-channel group), bit i = channel 16g+i is > 0. A forward epilogue
+  // can write them next to its output (gate_out); a dgrad epilogue reads them (gate_in) instead of re-reading the
+  // producer's whole activation tensor through `aux` -- 1/16 of the bytes and one 2-byte load per 16 columns.
+  unsigned short* gate_out;
+  const unsigned short* gate_in[2];
   int split_col;       // GEMM columns >= split_col go to slot 1
   const float* bias;   // fp32 per GEMM column (tconv: per column modulo d2s_cout), or null
   int relu;

@@ -10,7 +10,7 @@
 template <int CIN>
 __global__ void __launch_bounds__(256)
 conv_first32_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ bias,
-                        uint4* __restrict__ y, int H, int W, unsigned P) {
+                        uint4* __restrict__ y, unsigned int* __restrict__ gate, int H, int W, unsigned P) {
   __shared__ float4 sw4[9 * CIN * 8 + 8];   // [tap][ci][32 channels] then bias, as float4
   float* sw = reinterpret_cast<float*>(sw4);
   for (int i = threadIdx.x; i < 9 * CIN * 32; i += blockDim.x) sw[i] = w[i];
@@ -48,6 +48,17 @@ conv_first32_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w
           acc[q].z = fmaf(v, wv.z, acc[q].z); acc[q].w = fmaf(v, wv.w, acc[q].w);
         }
       }
+    }
+    if (gate) {   // ReLU gates as bits: two uint16 (16 channels each) per pixel = one 32-bit word
+      unsigned int bits = 0;
+#pragma unroll
+      for (int q = 0; q < 8; ++q) {
+        bits |= (acc[q].x > 0.f ? 1u : 0u) << (4 * q);
+        bits |= (acc[q].y > 0.f ? 1u : 0u) << (4 * q + 1);
+        bits |= (acc[q].z > 0.f ? 1u : 0u) << (4 * q + 2);
+        bits |= (acc[q].w > 0.f ? 1u : 0u) << (4 * q + 3);
+      }
+      gate[pix] = bits;
     }
     uint4* yp = y + static_cast<size_t>(pix) * 4;
 #pragma unroll

@@ -127,7 +127,7 @@ bool try_halo(const IgemmParams& p, const void* src0, int C0, const void* src1, 
 
 // ------------------------------------------------------------------------------------------------ conv3x3 forward
 int conv3x3_fwd(ConvSrc x0, ConvSrc x1, const void* w_packed, const float* bias, void* y, int N, int H, int W, int Cout,
-                int relu, DropoutCfg drop, cudaStream_t s) {
+                int relu, DropoutCfg drop, cudaStream_t s, unsigned short* gate_out) {
   const int C1 = x1.ptr ? x1.C : 0;
   const int kc = pick_kc(x0.C, C1);
   UB_REQUIRE(kc != 0, "conv3x3_fwd: input channels %d/%d must be multiples of 32", x0.C, C1);
@@ -157,6 +157,7 @@ int conv3x3_fwd(ConvSrc x0, ConvSrc x1, const void* w_packed, const float* bias,
   p.epi.drop_seed = drop.seed;
   p.epi.drop_stream = drop.stream;
   p.epi.drop_seed_add = drop.seed_add;
+  p.epi.gate_out = gate_out;
   int rc = UB_OK;
   if (try_halo(p, x0.ptr, x0.C, x1.ptr, C1, w_packed, Cout, x0.C + C1, s, &rc)) return rc;
   CUtensorMap a0, a1, bm;
@@ -196,13 +197,15 @@ int conv3x3_dgrad(const void* dz, int Cout, const void* w_packed_d, DgradDst d0,
   p.src_kblocks[0] = Cout / kc;
   p.kc = kc;
   p.stages = igemm_pick_stages(block_n, kc);
-  p.epi.dst[0] = d0.ptr; p.epi.dst_C[0] = d0.C; p.epi.aux[0] = d0.mask; p.epi.aux_C[0] = d0.C;
-  p.epi.dst[1] = d1.ptr; p.epi.dst_C[1] = C1; p.epi.aux[1] = d1.mask; p.epi.aux_C[1] = C1;
+  p.epi.dst[0] = d0.ptr; p.epi.dst_C[0] = d0.C; p.epi.aux[0] = d0.gate ? nullptr : d0.mask; p.epi.aux_C[0] = d0.C;
+  p.epi.dst[1] = d1.ptr; p.epi.dst_C[1] = C1; p.epi.aux[1] = d1.gate ? nullptr : d1.mask; p.epi.aux_C[1] = C1;
+  p.epi.gate_in[0] = d0.gate;
+  p.epi.gate_in[1] = C1 ? d1.gate : nullptr;
   p.epi.split_col = C1 ? d0.C : INT_MAX;
   p.epi.mask_scale = d0.scale;
   UB_REQUIRE(!C1 || !d0.mask || !d1.mask || d0.scale == d1.scale,
              "conv3x3_dgrad: both destinations must share the mask scale");
-  if (!d0.mask && d1.mask) p.epi.mask_scale = d1.scale;
+  if (!(d0.mask || d0.gate) && (d1.mask || d1.gate)) p.epi.mask_scale = d1.scale;
   p.epi.drop_keep = 1.0f;
   int rc = UB_OK;
   if (try_halo(p, dz, Cout, nullptr, 0, w_packed_d, d0.C + C1, Cout, s, &rc)) return rc;
@@ -416,7 +419,7 @@ int tconv2x2_fwd(const void* x, int Cin, const void* w_packed, const float* bias
 }
 
 int tconv2x2_dgrad(const void* dy, int Cout, const void* w_packed_d, void* dx, int Cin, const void* mask, float scale,
-                   int N, int H, int W, cudaStream_t s) {
+                   int N, int H, int W, cudaStream_t s, const unsigned short* gate) {
   const int kc = pick_kc(Cout, 0);
   UB_REQUIRE(kc != 0, "tconv2x2_dgrad: Cout %d must be a multiple of 32", Cout);
   const int block_n = pick_block_n(Cin);
@@ -434,7 +437,8 @@ int tconv2x2_dgrad(const void* dy, int Cout, const void* w_packed_d, void* dx, i
   p.src_kblocks[0] = Cout / kc;
   p.kc = kc;
   p.stages = igemm_pick_stages(block_n, kc);
-  p.epi.dst[0] = dx; p.epi.dst_C[0] = Cin; p.epi.aux[0] = mask; p.epi.aux_C[0] = Cin;
+  p.epi.dst[0] = dx; p.epi.dst_C[0] = Cin; p.epi.aux[0] = gate ? nullptr : mask; p.epi.aux_C[0] = Cin;
+  p.epi.gate_in[0] = gate;
   p.epi.split_col = INT_MAX;
   p.epi.mask_scale = scale;
   p.epi.drop_keep = 1.0f;

@@ -20,7 +20,7 @@ struct DropoutCfg {
 
 // y = relu?(conv3x3_same([x0, x1]) + bias) (* dropout); w_packed = bf16 [Cout][9][C0+C1].
 int conv3x3_fwd(ConvSrc x0, ConvSrc x1, const void* w_packed, const float* bias, void* y, int N, int H, int W, int Cout,
-                int relu, DropoutCfg drop, cudaStream_t s);
+                int relu, DropoutCfg drop, cudaStream_t s, unsigned short* gate_out = nullptr);
 
 // dx_k = conv3x3_same(dz, flipped weights)[channels of source k] * (mask_k > 0 ? scale_k : 0)   (mask optional)
 // w_packed_d = bf16 [C0+C1][9][Cout] (tap-flipped).
@@ -29,6 +29,7 @@ struct DgradDst {
   int C;
   const void* mask;  // same shape as ptr, or null
   float scale;
+  const unsigned short* gate = nullptr;  // ReLU gates of the producer as bits (takes precedence over mask)
 };
 int conv3x3_dgrad(const void* dz, int Cout, const void* w_packed_d, DgradDst d0, DgradDst d1, int N, int H, int W,
                   cudaStream_t s);
@@ -44,7 +45,7 @@ int tconv2x2_fwd(const void* x, int Cin, const void* w_packed, const float* bias
                  cudaStream_t s);
 // dx[n,i,j,c] = sum_{a,b,o} dy[n,2i+a,2j+b,o] w[a,b,o,c], masked by (mask>0). w_packed_d = bf16 [Cin][4][Cout].
 int tconv2x2_dgrad(const void* dy, int Cout, const void* w_packed_d, void* dx, int Cin, const void* mask, float scale,
-                   int N, int H, int W, cudaStream_t s);
+                   int N, int H, int W, cudaStream_t s, const unsigned short* gate = nullptr);
 // dw fp32 [2][2][Cout][Cin].
 size_t tconv2x2_wgrad_ws_bytes(int N, int H, int W, int Cin, int Cout);
 int tconv2x2_wgrad(const void* dy, int Cout, const void* x, int Cin, float* dw, void* ws, size_t ws_bytes, int N, int H,

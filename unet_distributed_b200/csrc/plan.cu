@@ -35,6 +35,7 @@ struct Layer {
 };
 
 constexpr size_t kAlign = 1024;
+constexpr size_t kNoGate = ~static_cast<size_t>(0);
 
 }  // namespace
 
@@ -50,6 +51,9 @@ struct unetb200_plan {
   // arena offsets: activations and their gradients (bf16 NHWC)
   size_t a[5], c[5], p[4], u[4], da[4], dc[4];
   size_t g_a[5], g_c[5], g_p[4], g_u[4], g_da[4], g_dc[4];
+  // ReLU gates of the activations the backward pass masks by, one bit per element (uint16 per 16 channels); kNoGate
+  // where nothing consumes them (the consumer then reads the activation tensor itself)
+  size_t gt_a[5], gt_c[5], gt_da[4], gt_dc[4];
   size_t preds, sums, metrics, ws;
   std::vector<PackSeg> pack_segs;
   long long pack_total = 0;
@@ -72,6 +76,9 @@ struct unetb200_plan {
   int Wl(int L) const { return W >> L; }
   size_t act_bytes(int L, int C) const { return static_cast<size_t>(N) * Hl(L) * Wl(L) * C * 2; }
   void* at(size_t off) const { return arena + off; }
+  unsigned short* gate(size_t off) const {
+    return off == kNoGate ? nullptr : reinterpret_cast<unsigned short*>(arena + off);
+  }
   const float* W_(int li) const { return params + layers[li].w_off; }
   const float* B_(int li) const { return params + layers[li].b_off; }
   float* dW_(int li) const { return grads + layers[li].w_off; }
@@ -177,6 +184,17 @@ int unetb200_plan_create(unetb200_plan** out, int N, int H, int W, int in_channe
     P->g_da[L] = P->bump(P->act_bytes(L, P->ch[L]));
     P->dc[L] = P->bump(P->act_bytes(L, P->dc_out[L]));
     P->g_dc[L] = P->bump(P->act_bytes(L, P->dc_out[L]));
+  }
+  // ---- arena: ReLU gate bits (1/16 of the activation they describe)
+  for (int L = 0; L < 5; ++L) {
+    const bool a_gates = L > 0 || conv_first_fwd_writes_gates(in_channels, 32);
+    P->gt_a[L] = a_gates ? P->bump(P->act_bytes(L, P->ch[L]) / 16) : kNoGate;
+    const bool c_gates = L < 4 || !up;   // c[4] is masked by the transposed-conv dgrad only
+    P->gt_c[L] = c_gates ? P->bump(P->act_bytes(L, L == 4 ? P->c4_out : P->ch[L]) / 16) : kNoGate;
+  }
+  for (int L = 0; L < 4; ++L) {
+    P->gt_da[L] = P->bump(P->act_bytes(L, P->ch[L]) / 16);
+    P->gt_dc[L] = (!up && L > 0) ? P->bump(P->act_bytes(L, P->dc_out[L]) / 16) : kNoGate;
   }
   const long long pixels = static_cast<long long>(N) * H * W;
   P->preds = P->bump(static_cast<size_t>(pixels) * n_cl_out * 4);
@@ -324,15 +342,15 @@ int unetb200_plan_forward(unetb200_plan* P, const float* imgs, const float* msks
     const int H = P->Hl(L), W = P->Wl(L);
     const int la = P->enc_a[L], lb = P->enc_b[L];
     if (L == 0) {
-      RC(conv_first_fwd(imgs, P->W_(la), P->B_(la), P->at(P->a[0]), N, H, W, P->Cin, 32, s));
+      RC(conv_first_fwd(imgs, P->W_(la), P->B_(la), P->at(P->a[0]), N, H, W, P->Cin, 32, s, P->gate(P->gt_a[0])));
     } else {
       DropoutCfg d = no_drop;
       if ((L == 2 || L == 3) && P->dropout > 0.0f) d = DropoutCfg{1.0f - P->dropout, seed, static_cast<unsigned>(L), seed_add};
       RC(conv3x3_fwd(ConvSrc{P->at(P->p[L - 1]), P->ch[L - 1]}, ConvSrc{nullptr, 0}, P->pkf(la), P->B_(la),
-                     P->at(P->a[L]), N, H, W, P->ch[L], 1, d, s));
+                     P->at(P->a[L]), N, H, W, P->ch[L], 1, d, s, P->gate(P->gt_a[L])));
     }
     RC(conv3x3_fwd(ConvSrc{P->at(P->a[L]), P->ch[L]}, ConvSrc{nullptr, 0}, P->pkf(lb), P->B_(lb), P->at(P->c[L]), N, H,
-                   W, P->layers[lb].cout, 1, no_drop, s));
+                   W, P->layers[lb].cout, 1, no_drop, s, P->gate(P->gt_c[L])));
     if (L < 4) RC(maxpool2x2_fwd(P->at(P->c[L]), P->at(P->p[L]), N, H, W, P->ch[L], s));
   }
   // decoder
@@ -348,9 +366,9 @@ int unetb200_plan_forward(unetb200_plan* P, const float* imgs, const float* msks
     }
     const int la = P->dec_a[L], lb = P->dec_b[L];
     RC(conv3x3_fwd(ConvSrc{P->at(P->u[L]), P->ch[L]}, ConvSrc{P->at(P->c[L]), P->ch[L]}, P->pkf(la), P->B_(la),
-                   P->at(P->da[L]), N, H, W, P->ch[L], 1, no_drop, s));
+                   P->at(P->da[L]), N, H, W, P->ch[L], 1, no_drop, s, P->gate(P->gt_da[L])));
     RC(conv3x3_fwd(ConvSrc{P->at(P->da[L]), P->ch[L]}, ConvSrc{nullptr, 0}, P->pkf(lb), P->B_(lb), P->at(P->dc[L]), N, H,
-                   W, P->dc_out[L], 1, no_drop, s));
+                   W, P->dc_out[L], 1, no_drop, s, P->gate(P->gt_dc[L])));
   }
   // head
   const long long pixels = static_cast<long long>(N) * P->H * P->W;
@@ -398,14 +416,15 @@ int unetb200_plan_backward(unetb200_plan* P, const float* imgs, const float* msk
                        P->dW_(lb), wsv, P->ws_bytes, N, H, W, s));
       RC(colsum_bf16(P->at(P->g_dc[L]), P->dB_(lb), ws, px, P->dc_out[L], s));
       RC(conv3x3_dgrad(P->at(P->g_dc[L]), P->dc_out[L], P->pkd(lb),
-                       DgradDst{P->at(P->g_da[L]), P->ch[L], P->at(P->da[L]), 1.0f}, DgradDst{nullptr, 0, nullptr, 1.0f},
+                       DgradDst{P->at(P->g_da[L]), P->ch[L], P->at(P->da[L]), 1.0f, P->gate(P->gt_da[L])},
+                       DgradDst{nullptr, 0, nullptr, 1.0f},
                        N, H, W, s));
       // conv{9-L}a over [u, skip]
       RC(conv3x3_wgrad(P->at(P->g_da[L]), P->ch[L], ConvSrc{P->at(P->u[L]), P->ch[L]}, ConvSrc{P->at(P->c[L]), P->ch[L]},
                        P->dW_(la), wsv, P->ws_bytes, N, H, W, s));
       RC(colsum_bf16(P->at(P->g_da[L]), P->dB_(la), ws, px, P->ch[L], s));
       RC(conv3x3_dgrad(P->at(P->g_da[L]), P->ch[L], P->pkd(la), DgradDst{P->at(P->g_u[L]), P->ch[L], nullptr, 1.0f},
-                       DgradDst{P->at(P->g_c[L]), P->ch[L], P->at(P->c[L]), 1.0f}, N, H, W, s));
+                       DgradDst{P->at(P->g_c[L]), P->ch[L], P->at(P->c[L]), 1.0f, P->gate(P->gt_c[L])}, N, H, W, s));
       // up path
       const size_t below = (L == 3) ? P->c[4] : P->dc[L + 1];
       const size_t g_below = (L == 3) ? P->g_c[4] : P->g_dc[L + 1];
@@ -418,7 +437,7 @@ int unetb200_plan_backward(unetb200_plan* P, const float* imgs, const float* msk
                           W / 2, s));
         RC(colsum_bf16(P->at(P->g_u[L]), P->dB_(lt), ws, px, P->ch[L], s));
         RC(tconv2x2_dgrad(P->at(P->g_u[L]), P->ch[L], P->pkd(lt), P->at(g_below), below_C, P->at(below), 1.0f, N, H / 2,
-                          W / 2, s));
+                          W / 2, s, P->gate(L == 3 ? P->gt_c[4] : P->gt_dc[L + 1])));
       }
     }
     return UB_OK;
@@ -432,7 +451,7 @@ int unetb200_plan_backward(unetb200_plan* P, const float* imgs, const float* msk
     RC(conv3x3_wgrad(P->at(P->g_c[L]), P->c4_out, ConvSrc{P->at(P->a[L]), P->ch[L]}, ConvSrc{nullptr, 0}, P->dW_(lb), wsv,
                      P->ws_bytes, N, H, W, s));
     RC(colsum_bf16(P->at(P->g_c[L]), P->dB_(lb), ws, px, P->c4_out, s));
-    RC(conv3x3_dgrad(P->at(P->g_c[L]), P->c4_out, P->pkd(lb), DgradDst{P->at(P->g_a[L]), P->ch[L], P->at(P->a[L]), 1.0f},
+    RC(conv3x3_dgrad(P->at(P->g_c[L]), P->c4_out, P->pkd(lb), DgradDst{P->at(P->g_a[L]), P->ch[L], P->at(P->a[L]), 1.0f, P->gate(P->gt_a[L])},
                      DgradDst{nullptr, 0, nullptr, 1.0f}, N, H, W, s));
     RC(conv3x3_wgrad(P->at(P->g_a[L]), P->ch[L], ConvSrc{P->at(P->p[L - 1]), P->ch[L - 1]}, ConvSrc{nullptr, 0},
                      P->dW_(la), wsv, P->ws_bytes, N, H, W, s));
@@ -453,7 +472,7 @@ int unetb200_plan_backward(unetb200_plan* P, const float* imgs, const float* msk
     RC(colsum_bf16(P->at(P->g_c[L]), P->dB_(lb), ws, px, P->ch[L], s));
     const bool dropped = (L == 2 || L == 3) && P->dropout > 0.0f;
     RC(conv3x3_dgrad(P->at(P->g_c[L]), P->ch[L], P->pkd(lb),
-                     DgradDst{P->at(P->g_a[L]), P->ch[L], P->at(P->a[L]), dropped ? inv_keep : 1.0f},
+                     DgradDst{P->at(P->g_a[L]), P->ch[L], P->at(P->a[L]), dropped ? inv_keep : 1.0f, P->gate(P->gt_a[L])},
                      DgradDst{nullptr, 0, nullptr, 1.0f}, N, H, W, s));
     if (L > 0) {
       RC(conv3x3_wgrad(P->at(P->g_a[L]), P->ch[L], ConvSrc{P->at(P->p[L - 1]), P->ch[L - 1]}, ConvSrc{nullptr, 0},

@@ -209,20 +209,20 @@ wgrad_halo_kernel(const __grid_constant__ WgradHaloParams p, const __grid_consta
 // dw[tap][ci_off + ci][co] = sum over parts of ws[part][tap][ci][co]; 8 interleaved partial sums then a fixed 8-way sum.
 __global__ void wgrad_halo_reduce_kernel(const float* __restrict__ ws, int nparts, int Cx, int Cz, float* __restrict__ dw,
                                          int cin_total, int ci_off) {
-  __shared__ float part[8][32];
+  __shared__ float part[32][32];
+  const int lanes = blockDim.x >> 5;
   const int n = 9 * Cx * Cz;
   const int c = threadIdx.x & 31, q = threadIdx.x >> 5;
   const int i = blockIdx.x * 32 + c;
   float acc = 0.0f;
   if (i < n) {
-    for (int r = q; r < nparts; r += 8) acc += ws[static_cast<size_t>(r) * n + i];
+    for (int r = q; r < nparts; r += lanes) acc += ws[static_cast<size_t>(r) * n + i];
   }
   part[q][c] = acc;
   __syncthreads();
   if (q == 0 && i < n) {
     float s = part[0][c];
-#pragma unroll
-    for (int k = 1; k < 8; ++k) s += part[k][c];
+    for (int k = 1; k < lanes; ++k) s += part[k][c];
     const int co = i % Cz;
     const int ci = (i / Cz) % Cx;
     const int tap = i / (Cz * Cx);
@@ -289,7 +289,7 @@ int wgrad_halo_launch(const CUtensorMap& x_map, const CUtensorMap& z_map, int N,
   UB_CHECK_CUDA(cudaGetLastError());
   prof_end(stream);
   const int n = 9 * Cx * Cz;
-  wgrad_halo_reduce_kernel<<<(n + 31) / 32, 256, 0, stream>>>(ws, grid, Cx, Cz, dw, cin_total, ci_off);
+  wgrad_halo_reduce_kernel<<<(n + 31) / 32, 1024, 0, stream>>>(ws, grid, Cx, Cz, dw, cin_total, ci_off);
   UB_CHECK_CUDA(cudaGetLastError());
   return UB_OK;
 }

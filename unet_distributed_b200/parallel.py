@@ -8,6 +8,7 @@ launched as soon as the backward segment that completes it has been enqueued (ov
 The helpers are backend-agnostic (NCCL on GPUs, gloo in the CPU tests)."""
 from __future__ import annotations
 
+import datetime
 import os
 
 import torch
@@ -42,7 +43,10 @@ def init_from_env(backend=None):
         torch.cuda.set_device(local)
     if not dist.is_initialized():
         kw = {"device_id": torch.device("cuda", local)} if backend == "nccl" else {}
-        dist.init_process_group(backend=backend, rank=rank, world_size=ws, **kw)
+        # a mismatched collective should fail in minutes, not after the 10-minute default
+        dist.init_process_group(backend=backend, rank=rank, world_size=ws,
+                                timeout=datetime.timedelta(seconds=int(os.environ.get("UNETB200_DIST_TIMEOUT", "180"))),
+                                **kw)
     return ws, rank, local
 
 

@@ -43,7 +43,7 @@ class Trainer:
         if self.world > 1:
             p.pack_weights()
         self.reducer = parallel.BucketedAllReduce(p.grads, p.buckets)
-        self.use_cuda_graph = bool(use_cuda_graph) and self.world == 1
+        self.use_cuda_graph = bool(use_cuda_graph)
         self._graph = None
         self._g_imgs = self._g_msks = None
         self.steps_done = 0
@@ -54,14 +54,23 @@ class Trainer:
         self._h_metrics = torch.empty(4, dtype=torch.float32).pin_memory()
 
     # ------------------------------------------------------------------ one optimizer step on device-resident data
-    def _enqueue_step(self, imgs, msks):
+    def _piece(self, i, imgs, msks):
+        """The step in four launch sequences; the gradient all-reduces go between them (eager NCCL calls)."""
         p = self.plan
-        p.forward(imgs, msks, seed=self.dropout_seed, seed_add=self.step_dev)
+        if i == 0:
+            p.forward(imgs, msks, seed=self.dropout_seed, seed_add=self.step_dev)
+            p.backward(imgs, msks, grad_scale=1.0, segment=0)
+        elif i < 3:
+            p.backward(imgs, msks, grad_scale=1.0, segment=i)
+        else:
+            self._apply_update()
+
+    def _enqueue_step(self, imgs, msks):
         for seg in range(3):
-            p.backward(imgs, msks, grad_scale=1.0, segment=seg)
+            self._piece(seg, imgs, msks)
             self.reducer.launch(seg)
         self.reducer.wait()
-        self._apply_update()
+        self._piece(3, imgs, msks)
 
     def _apply_update(self):
         p = self.plan
@@ -85,7 +94,14 @@ class Trainer:
                 self._capture(imgs, msks)
             self._g_imgs.copy_(imgs, non_blocking=True)
             self._g_msks.copy_(msks, non_blocking=True)
-            self._graph.replay()
+            if self.world == 1:
+                self._graph.replay()
+            else:   # four graphs with the bucket all-reduces between them (NCCL stays outside the graphs)
+                for seg in range(3):
+                    self._graph[seg].replay()
+                    self.reducer.launch(seg)
+                self.reducer.wait()
+                self._graph[3].replay()
         else:
             self._enqueue_step(imgs, msks)
         self.steps_done += 1
@@ -104,10 +120,20 @@ class Trainer:
             dst.copy_(src)
         self.plan.pack_weights()
         torch.cuda.synchronize()
-        self._graph = torch.cuda.CUDAGraph()
         before = _lib.lib().unetb200_launch_count()
-        with torch.cuda.graph(self._graph):
-            self._enqueue_step(self._g_imgs, self._g_msks)
+        if self.world == 1:
+            self._graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(self._graph):
+                self._enqueue_step(self._g_imgs, self._g_msks)
+        else:
+            graphs = []
+            for i in range(4):
+                g = torch.cuda.CUDAGraph()
+                # thread_local: the NCCL watchdog thread may query events while this thread captures
+                with torch.cuda.graph(g, capture_error_mode="thread_local"):
+                    self._piece(i, self._g_imgs, self._g_msks)
+                graphs.append(g)
+            self._graph = graphs
         # kernels of this library inside one replay (the library's launch counter only sees the capture)
         self.graph_launches_per_step = int(_lib.lib().unetb200_launch_count() - before)
 
