@@ -50,17 +50,83 @@ __device__ __forceinline__ void decode_tile(const HaloParams& p, int tile, int& 
   w0 = tw_i * 8 * p.J;
 }
 
-// All MMAs of one filter tap: J pixel tiles x KSTEPS K slices, fully unrolled (descriptor = base + constant).
-template <int J, int KSTEPS>
-__device__ __forceinline__ void issue_tap(uint32_t d0, int block_n, uint64_t adesc0, uint32_t strip16, uint64_t bdesc,
-                                          uint32_t idesc, uint32_t started) {
+__device__ __forceinline__ uint64_t desc_pair(uint32_t lo, uint32_t hi) {
+  return (static_cast<uint64_t>(hi) << 32) | lo;
+}
+
+// MMA issuer of one CTA, specialised on the plan (J pixel strips, KC channels per block, BN columns) so that every
+// operand descriptor of a k-block is "stage base + compile-time constant": measured with csrc/mma_rate.cu, an SS-mode
+// 128xNx16 MMA costs 32 + N/4 cycles (40 / 48 / 64 for N = 32 / 64 / 128) when the issuing lane keeps up, and each
+// extra scalar instruction between two MMAs costs ~4 cycles of a single warp's dependent-issue latency -- the
+// run-time-generic loop (tap / 3, 64-bit descriptor adds, R2UR moves) ran at 62 / 60 / 92 cycles per MMA.
+// The whole warp walks the (uniform) control flow and waits; one elected lane issues.
+template <int J, int KC, int BN>
+__device__ __forceinline__ void halo_mma_role(const HaloParams& p, HaloBarriers* bars, uint32_t halo_addr,
+                                              uint32_t halo_stride, uint32_t b_addr, uint32_t tmem_base,
+                                              int num_tiles, int lane) {
+  constexpr int P = 8 * J + 2;                      // halo pitch in pixels
+  constexpr uint32_t ROW16 = KC * 2 / 16;           // one halo row, in 16-byte units
+  constexpr int KSTEPS = KC / 16;
+  constexpr int BTILE = BN * KC * 2;
+  constexpr int TPB = (9 * BTILE <= 36 * 1024) ? 9 : 3;   // must match halo_plan()
+  constexpr int TAP_GROUPS = 9 / TPB;
+  constexpr uint32_t BSTAGE = TPB * BTILE;
+  constexpr uint32_t SW = KC == 64 ? UMMA_SW_128B : UMMA_SW_64B;
+  const uint32_t idesc = umma_idesc_bf16(128, BN, 0, 0);
+  const uint32_t a_hi = static_cast<uint32_t>(umma_smem_desc(0, 0, P * KC * 2, SW) >> 32);   // SBO = next image row
+  const uint32_t b_hi = static_cast<uint32_t>(umma_smem_desc(0, 0, 8 * KC * 2, SW) >> 32);
+  const int total_kb = p.src_kblocks[0] + (p.num_src > 1 ? p.src_kblocks[1] : 0);
+  int hs = 0, bs = 0, it = 0;
+  uint32_t hphase = 0, bphase = 0;
+  unsigned long long t_e = 0, t_h = 0, t_b = 0;
+  const long long t_mma0 = clock64();
+  for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
+    const int a = p.acc_double ? (it & 1) : 0;
+    const uint32_t eparity = p.acc_double ? (((it >> 1) & 1) ^ 1u) : ((it & 1) ^ 1u);
+    timed_wait(&bars->tmem_empty[a], eparity, p.timing != 0, t_e);
+    tc_fence_after();
+    const uint32_t d0 = tmem_base + static_cast<uint32_t>(a * J * BN);
+    for (int kb = 0; kb < total_kb; ++kb) {
+      timed_wait(&bars->halo_full[hs], hphase, p.timing != 0, t_h);
+      const uint32_t a_lo = (halo_addr + static_cast<uint32_t>(hs) * halo_stride) >> 4;
+      const uint32_t fresh = kb == 0 ? 0u : 1u;   // accumulate flag of the very first MMA of each accumulator
 #pragma unroll
-  for (int j = 0; j < J; ++j) {
+      for (int tg = 0; tg < TAP_GROUPS; ++tg) {
+        timed_wait(&bars->b_full[bs], bphase, p.timing != 0, t_b);
+        tc_fence_after();
+        const uint32_t b_lo = (b_addr + static_cast<uint32_t>(bs) * BSTAGE) >> 4;
+        if (elect_one()) {
 #pragma unroll
-    for (int k = 0; k < KSTEPS; ++k) {
-      umma_f16(d0 + static_cast<uint32_t>(j * block_n), adesc0 + static_cast<uint64_t>(j * strip16 + 2 * k),
-               bdesc + static_cast<uint64_t>(2 * k), idesc, (started | static_cast<uint32_t>(k)) ? 1u : 0u);
+          for (int t = 0; t < TPB; ++t) {
+            const int tap = tg * TPB + t;
+            const int r = tap / 3, s = tap % 3;
+#pragma unroll
+            for (int j = 0; j < J; ++j) {
+#pragma unroll
+              for (int k = 0; k < KSTEPS; ++k) {
+                umma_f16(d0 + static_cast<uint32_t>(j * BN),
+                         desc_pair(a_lo + static_cast<uint32_t>((r * P + s + 8 * j) * ROW16 + 2 * k), a_hi),
+                         desc_pair(b_lo + static_cast<uint32_t>(t * (BTILE >> 4) + 2 * k), b_hi), idesc,
+                         (tap == 0 && k == 0) ? fresh : 1u);
+              }
+            }
+          }
+          umma_commit(&bars->b_empty[bs]);
+          if (tg == TAP_GROUPS - 1) umma_commit(&bars->halo_empty[hs]);
+        }
+        __syncwarp();
+        if (++bs == p.b_stages) { bs = 0; bphase ^= 1u; }
+      }
+      if (++hs == p.h_stages) { hs = 0; hphase ^= 1u; }
     }
+    if (elect_one()) umma_commit(&bars->tmem_full[a]);
+    __syncwarp();
+  }
+  if (p.timing && lane == 0) {
+    atomicAdd(&g_halo_timing[0], t_e);
+    atomicAdd(&g_halo_timing[1], t_h);
+    atomicAdd(&g_halo_timing[2], t_b);
+    atomicAdd(&g_halo_timing[3], static_cast<unsigned long long>(clock64() - t_mma0));
   }
 }
 
@@ -228,6 +294,150 @@ __device__ __forceinline__ void halo_epilogue(const HaloParams& p, HaloBarriers*
   }
 }
 
+// Lean epilogue for the shapes the UNet step actually runs (full super-tiles, one N tile, no dropout, gates as bits):
+// everything that does not depend on the item is hoisted out of the item loop or made a compile-time constant.
+// ncu on conv1b forward (128 x 128x128 x 32 -> 32) showed the generic epilogue above executing 235 warp
+// instructions per (32 pixels x 16 columns) item -- 46 IMAD, 25 ISETP, 20 IADD3, 19 BRA, 19 R2UR -- with only two
+// epilogue warps per scheduler, i.e. latency-bound at ~1100 cycles per item while the MMAs of a super-tile need ~720.
+//   FWD   : v + bias -> cvt.rn.relu.bf16x2 (ReLU inside the conversion) -> store; the ReLU gates come from the
+//           packed words: w + 0x7fff7fff sets bit 15 / 31 iff the low / high bf16 is non-zero.
+//   !FWD  : dgrad; per slot optional gate bits (prefetched for the whole tile before the accumulators are ready).
+//   SPLIT : columns [BN/2, BN) go to destination 1 (the skip connection's gradient).
+__device__ __forceinline__ uint32_t pack_bf16x2_relu(float lo, float hi) {
+  uint32_t d;
+  asm("cvt.rn.relu.bf16x2.f32 %0, %1, %2;" : "=r"(d) : "f"(hi), "f"(lo));
+  return d;
+}
+
+template <int J, int BN, bool FWD, bool SPLIT>
+__device__ __forceinline__ void halo_epilogue_fast(const HaloParams& p, HaloBarriers* bars, uint32_t tmem_base,
+                                                   int warp, int lane, int num_tiles) {
+  static_assert(!SPLIT || BN >= 64, "split destinations need 32-column halves");
+  constexpr int kCl = BN / 32;              // 16-column chunks per warp (the two warps of a quarter interleave)
+  constexpr int kItems = J * kCl;
+  constexpr bool kBiasRegs = FWD && BN <= 64;
+  const IgemmEpilogue& e = p.epi;
+  const int quarter = warp & 3;
+  const int half = (warp - 4) >> 2;
+  const int m = quarter * 32 + lane;
+  const int th = m >> 3, twl = m & 7;
+  const uint32_t t_lane = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + static_cast<uint32_t>(half * 16);
+  float bias_r[kBiasRegs ? kCl : 1][16];
+  if (kBiasRegs) {
+#pragma unroll
+    for (int cl = 0; cl < kCl; ++cl) {
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        float4 b = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (e.bias) b = __ldg(reinterpret_cast<const float4*>(e.bias + half * 16 + 32 * cl) + q);
+        bias_r[cl][4 * q + 0] = b.x; bias_r[cl][4 * q + 1] = b.y; bias_r[cl][4 * q + 2] = b.z; bias_r[cl][4 * q + 3] = b.w;
+      }
+    }
+  }
+  const float scale = e.mask_scale;
+  const bool scaled = scale != 1.0f;
+  constexpr int kSlots = SPLIT ? 2 : 1;
+  uint32_t strip_b[kSlots], gstrip[kSlots];   // bytes / gate words between two 8-pixel strips
+#pragma unroll
+  for (int sl = 0; sl < kSlots; ++sl) {
+    strip_b[sl] = static_cast<uint32_t>(16 * e.dst_C[sl]);
+    gstrip[sl] = static_cast<uint32_t>((FWD ? e.dst_C[sl] : e.aux_C[sl]) >> 1);
+  }
+  int it = 0;
+  unsigned long long t_wait = 0;
+  const long long t_begin = clock64();
+  for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
+    const int a = p.acc_double ? (it & 1) : 0;
+    const uint32_t fparity = p.acc_double ? ((it >> 1) & 1) : (it & 1);
+    int n, h0, w0, nt;
+    decode_tile(p, tile, n, h0, w0, nt);
+    const size_t pix0 = (static_cast<size_t>(n) * p.H + (h0 + th)) * p.W + (w0 + twl);
+    char* dst_b[kSlots];
+    const unsigned short* gin_b[kSlots];
+    unsigned short* gout_b = nullptr;
+#pragma unroll
+    for (int sl = 0; sl < kSlots; ++sl) {
+      dst_b[sl] = reinterpret_cast<char*>(e.dst[sl]) + (pix0 * e.dst_C[sl] + e.dst_coff[sl] + half * 16) * 2;
+      gin_b[sl] = nullptr;
+      if (!FWD && e.gate_in[sl]) gin_b[sl] = e.gate_in[sl] + ((pix0 * e.aux_C[sl] + e.aux_coff[sl]) >> 4) + half;
+    }
+    if (FWD && e.gate_out) gout_b = e.gate_out + ((pix0 * e.dst_C[0] + e.dst_coff[0]) >> 4) + half;
+    uint32_t gb[kItems];
+    if (!FWD) {
+#pragma unroll
+      for (int k = 0; k < kItems; ++k) {
+        const int j = k / kCl, cl = k % kCl;
+        const int sl = (SPLIT && 32 * cl >= BN / 2) ? 1 : 0;
+        gb[k] = 0xFFFFu;
+        if (gin_b[sl]) gb[k] = __ldg(gin_b[sl] + j * gstrip[sl] + (2 * cl - sl * (BN / 32)));
+      }
+    }
+    timed_wait(&bars->tmem_full[a], fparity, p.timing != 0, t_wait);
+    tc_fence_after();
+    const uint32_t t_acc = t_lane + static_cast<uint32_t>(a * J * BN);
+#pragma unroll
+    for (int k = 0; k < kItems; ++k) {
+      const int j = k / kCl, cl = k % kCl;
+      const int sl = (SPLIT && 32 * cl >= BN / 2) ? 1 : 0;
+      uint32_t r[16];
+      tmem_ld_32x32b_x16(t_acc + static_cast<uint32_t>(j * BN + 32 * cl), r);
+      tmem_ld_wait();
+      uint32_t w[8];
+      if (FWD) {
+        float v[16];
+        if (kBiasRegs) {
+#pragma unroll
+          for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]) + bias_r[kBiasRegs ? cl : 0][i];
+        } else {
+#pragma unroll
+          for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
+          if (e.bias) {
+            const float4* bp = reinterpret_cast<const float4*>(e.bias + half * 16 + 32 * cl);
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+              const float4 bq = __ldg(bp + q);
+              v[4 * q + 0] += bq.x; v[4 * q + 1] += bq.y; v[4 * q + 2] += bq.z; v[4 * q + 3] += bq.w;
+            }
+          }
+        }
+#pragma unroll
+        for (int i = 0; i < 8; ++i) w[i] = pack_bf16x2_relu(v[2 * i], v[2 * i + 1]);
+        if (gout_b) {
+          uint32_t acc = 0;
+#pragma unroll
+          for (int i = 0; i < 8; ++i) acc |= ((w[i] + 0x7FFF7FFFu) >> (15 - 2 * i)) & (0x00010001u << (2 * i));
+          gout_b[j * gstrip[0] + 2 * cl] = static_cast<unsigned short>((acc & 0xFFFFu) | (acc >> 15));
+        }
+      } else {
+        float v[16];
+#pragma unroll
+        for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
+        if (gin_b[sl]) {
+          const uint32_t b = gb[k];
+          if (scaled) {
+#pragma unroll
+            for (int i = 0; i < 16; ++i) v[i] *= scale;
+          }
+#pragma unroll
+          for (int i = 0; i < 16; ++i) v[i] = ((b >> i) & 1u) ? v[i] : 0.0f;
+        }
+#pragma unroll
+        for (int i = 0; i < 8; ++i) w[i] = pack_bf16x2(v[2 * i], v[2 * i + 1]);
+      }
+      uint4* dp = reinterpret_cast<uint4*>(dst_b[sl] + j * strip_b[sl] + (32 * cl - sl * (BN / 2)) * 2);
+      dp[0] = make_uint4(w[0], w[1], w[2], w[3]);
+      dp[1] = make_uint4(w[4], w[5], w[6], w[7]);
+    }
+    tc_fence_before();
+    __syncwarp();
+    if (lane == 0) mbar_arrive(&bars->tmem_empty[a]);
+  }
+  if (p.timing && warp == 4 && lane == 0) {
+    atomicAdd(&g_halo_timing[4], t_wait);
+    atomicAdd(&g_halo_timing[5], static_cast<unsigned long long>(clock64() - t_begin));
+  }
+}
+
 __global__ void __launch_bounds__(kThreads, 1)
 conv_halo_kernel(const __grid_constant__ HaloParams p, const __grid_constant__ CUtensorMap tmA0,
                  const __grid_constant__ CUtensorMap tmA1, const __grid_constant__ CUtensorMap tmB) {
@@ -328,81 +538,48 @@ conv_halo_kernel(const __grid_constant__ HaloParams p, const __grid_constant__ C
       }
     }
   } else if (warp == 1) {
-    // ------------------------------------------------------------ MMA issuer
-    // The whole warp walks the (uniform) control flow and waits; one elected lane issues, so the compiler keeps
-    // descriptors in uniform registers and emits bare UTCHMMAs. The 32/64-channel layers issue N=32/64 MMAs that
-    // last 16-48 cycles each: the issue loop has to stay at a handful of instructions per MMA.
-    const uint32_t idesc = umma_idesc_bf16(128, static_cast<uint32_t>(p.block_n), 0, 0);
-    const uint32_t sw = p.kc == 64 ? UMMA_SW_128B : UMMA_SW_64B;
-    const uint32_t a_sbo = static_cast<uint32_t>(P * rowbytes);   // next image row of the halo tile
-    const uint32_t b_sbo = static_cast<uint32_t>(8 * rowbytes);
-    const uint64_t desc_hi_a = umma_smem_desc(0, 0, a_sbo, sw);   // everything but the start address
-    const uint64_t desc_hi_b = umma_smem_desc(0, 0, b_sbo, sw);
-    const uint32_t row16 = static_cast<uint32_t>(rowbytes >> 4);  // one halo row, in 16-byte units
-    int hs = 0, bs = 0, it = 0;
-    uint32_t hphase = 0, bphase = 0;
-    unsigned long long t_e = 0, t_h = 0, t_b = 0;
-    const long long t_mma0 = clock64();
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
-      const int a = p.acc_double ? (it & 1) : 0;
-      const uint32_t eparity = p.acc_double ? (((it >> 1) & 1) ^ 1u) : ((it & 1) ^ 1u);
-      timed_wait(&bars->tmem_empty[a], eparity, p.timing != 0, t_e);
-      tc_fence_after();
-      const uint32_t d0 = tmem_base + static_cast<uint32_t>(a * p.J * p.block_n);
-      uint32_t started = 0;  // 0 until the first MMA of every accumulator has been issued
-      for (int src = 0; src < p.num_src; ++src) {
-        for (int cb = 0; cb < p.src_kblocks[src]; ++cb) {
-          timed_wait(&bars->halo_full[hs], hphase, p.timing != 0, t_h);
-          const uint64_t a_base = desc_hi_a + (smem_u32(halo_base + hs * halo_stride) >> 4);
-          for (int tg = 0; tg < tap_groups; ++tg) {
-            timed_wait(&bars->b_full[bs], bphase, p.timing != 0, t_b);
-            tc_fence_after();
-            const uint64_t b_stage = desc_hi_b + (smem_u32(b_base + bs * bstage_bytes) >> 4);
-            if (elect_one()) {
-              for (int t = 0; t < p.tpb; ++t) {
-                const int tap = tg * p.tpb + t;
-                const int r = tap / 3, s = tap - 3 * r;
-                const uint64_t bdesc = b_stage + static_cast<uint32_t>(t * (btile_bytes >> 4));
-                const uint64_t adesc0 = a_base + static_cast<uint32_t>((r * P + s)) * row16;
-                if (p.kc == 64) {
-                  if (p.J == 4) issue_tap<4, 4>(d0, p.block_n, adesc0, 8 * row16, bdesc, idesc, started);
-                  else if (p.J == 2) issue_tap<2, 4>(d0, p.block_n, adesc0, 8 * row16, bdesc, idesc, started);
-                  else issue_tap<1, 4>(d0, p.block_n, adesc0, 8 * row16, bdesc, idesc, started);
-                } else {
-                  if (p.J == 4) issue_tap<4, 2>(d0, p.block_n, adesc0, 8 * row16, bdesc, idesc, started);
-                  else if (p.J == 2) issue_tap<2, 2>(d0, p.block_n, adesc0, 8 * row16, bdesc, idesc, started);
-                  else issue_tap<1, 2>(d0, p.block_n, adesc0, 8 * row16, bdesc, idesc, started);
-                }
-                started = 1;
-              }
-              umma_commit(&bars->b_empty[bs]);
-              if (tg == tap_groups - 1) umma_commit(&bars->halo_empty[hs]);
-            }
-            __syncwarp();
-            started = 1;
-            if (++bs == p.b_stages) { bs = 0; bphase ^= 1u; }
-          }
-          if (++hs == p.h_stages) { hs = 0; hphase ^= 1u; }
-        }
-      }
-      if (elect_one()) umma_commit(&bars->tmem_full[a]);
-      __syncwarp();
+    // ------------------------------------------------------------ MMA issuer (see halo_mma_role)
+    const uint32_t ha = smem_u32(halo_base), ba = smem_u32(b_base);
+    const uint32_t hst = static_cast<uint32_t>(halo_stride);
+#define UB_MMA(JJ, KK, NN) halo_mma_role<JJ, KK, NN>(p, bars, ha, hst, ba, tmem_base, num_tiles, lane)
+#define UB_MMA_J(KK, NN)                        \
+    do {                                        \
+      if (p.J == 4) UB_MMA(4, KK, NN);          \
+      else if (p.J == 2) UB_MMA(2, KK, NN);     \
+      else UB_MMA(1, KK, NN);                   \
+    } while (0)
+    if (p.kc == 64) {
+      if (p.block_n == 32) UB_MMA_J(64, 32);
+      else if (p.block_n == 64) UB_MMA_J(64, 64);
+      else UB_MMA_J(64, 128);
+    } else {
+      if (p.block_n == 32) UB_MMA_J(32, 32);
+      else if (p.block_n == 64) UB_MMA_J(32, 64);
+      else UB_MMA_J(32, 128);
     }
-    if (p.timing && lane == 0) {
-      atomicAdd(&g_halo_timing[0], t_e);
-      atomicAdd(&g_halo_timing[1], t_h);
-      atomicAdd(&g_halo_timing[2], t_b);
-      atomicAdd(&g_halo_timing[3], static_cast<unsigned long long>(clock64() - t_mma0));
-    }
+#undef UB_MMA_J
+#undef UB_MMA
   } else if (warp >= 4) {
     // ------------------------------------------------------------ epilogue: 8 warps, two per TMEM lane quarter
     const IgemmEpilogue& e = p.epi;
     const bool aux = (e.aux[0] != nullptr) || (e.aux[1] != nullptr);
     const bool gin = (e.gate_in[0] != nullptr) || (e.gate_in[1] != nullptr);
     const bool drop = e.drop_keep < 1.0f;
+#define UB_FAST(JJ, BN)                                                                                    \
+    do {                                                                                                   \
+      if (p.fast_epi == 1) halo_epilogue_fast<JJ, BN, true, false>(p, bars, tmem_base, warp, lane, num_tiles);       \
+      else if (p.fast_epi == 2) halo_epilogue_fast<JJ, BN, false, false>(p, bars, tmem_base, warp, lane, num_tiles); \
+      else halo_epilogue_fast<JJ, (BN >= 64 ? BN : 64), false, true>(p, bars, tmem_base, warp, lane, num_tiles);     \
+    } while (0)
 #define UB_EPI(BN)                                                                                         \
     do {                                                                                                   \
-      if (gin) halo_epilogue<BN, false, false, false, true>(p, bars, tmem_base, warp, lane, num_tiles);    \
+      if (p.fast_epi) {                                                                                    \
+        if (p.J == 4) UB_FAST(4, BN);                                                                      \
+        else if (p.J == 2) UB_FAST(2, BN);                                                                 \
+        else UB_FAST(1, BN);                                                                               \
+      }                                                                                                    \
+      else if (gin && aux) halo_epilogue<BN, false, false, true, true>(p, bars, tmem_base, warp, lane, num_tiles); \
+      else if (gin) halo_epilogue<BN, false, false, false, true>(p, bars, tmem_base, warp, lane, num_tiles);    \
       else if (aux) halo_epilogue<BN, false, false, true, false>(p, bars, tmem_base, warp, lane, num_tiles); \
       else if (drop) halo_epilogue<BN, true, true, false, false>(p, bars, tmem_base, warp, lane, num_tiles); \
       else if (e.bias || e.relu) halo_epilogue<BN, true, false, false, false>(p, bars, tmem_base, warp, lane, num_tiles); \
@@ -412,6 +589,7 @@ conv_halo_kernel(const __grid_constant__ HaloParams p, const __grid_constant__ C
     else if (p.block_n == 64) UB_EPI(64);
     else UB_EPI(128);
 #undef UB_EPI
+#undef UB_FAST
   }
 
   tc_fence_before();
@@ -471,10 +649,10 @@ bool halo_plan(HaloParams& p, int N, int H, int W, int kc, int ncols) {
   return true;
 }
 
-int halo_launch(const HaloParams& p, const CUtensorMap& a0, const CUtensorMap& a1, const CUtensorMap& b,
+int halo_launch(const HaloParams& p_in, const CUtensorMap& a0, const CUtensorMap& a1, const CUtensorMap& b,
                 cudaStream_t stream) {
-  UB_REQUIRE(p.epi.d2s_cout == 0, "conv_halo: depth-to-space epilogue is not supported here");
-  const size_t smem = halo_smem_bytes(p);
+  UB_REQUIRE(p_in.epi.d2s_cout == 0, "conv_halo: depth-to-space epilogue is not supported here");
+  const size_t smem = halo_smem_bytes(p_in);
   UB_REQUIRE(smem <= 227 * 1024, "conv_halo: %zu bytes of shared memory requested", smem);
   static bool attr_set[64] = {false};
   int dev = 0;
@@ -483,8 +661,25 @@ int halo_launch(const HaloParams& p, const CUtensorMap& a0, const CUtensorMap& a
     UB_CHECK_CUDA(cudaFuncSetAttribute(conv_halo_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
     attr_set[dev] = true;
   }
-  const int num_tiles = p.N * p.tiles_h * p.tiles_w * p.n_tiles;
+  const int num_tiles = p_in.N * p_in.tiles_h * p_in.tiles_w * p_in.n_tiles;
   UB_REQUIRE(num_tiles > 0, "conv_halo: empty problem");
+  HaloParams p = p_in;
+  {
+    // the lean epilogue covers full super-tiles of one N tile without dropout or tensor masks (see halo_epilogue_fast)
+    static const bool no_fast = getenv("UNETB200_NO_FAST_EPI") != nullptr;
+    const IgemmEpilogue& e = p.epi;
+    const bool full = p.n_tiles == 1 && p.H % kTH == 0 && p.W % (8 * p.J) == 0;
+    const bool plain = e.drop_keep >= 1.0f && !e.aux[0] && !e.aux[1];
+    const bool gates_in = e.gate_in[0] || e.gate_in[1];
+    p.fast_epi = 0;
+    if (!no_fast && full && plain) {
+      if (e.relu && !gates_in && e.split_col >= p.block_n) p.fast_epi = 1;
+      else if (!e.relu && !e.bias && !e.gate_out) {
+        if (e.split_col >= p.block_n) p.fast_epi = 2;
+        else if (e.split_col == p.block_n / 2 && p.block_n >= 64) p.fast_epi = 3;
+      }
+    }
+  }
   int grid = device_sm_count();
   if (grid > num_tiles) grid = num_tiles;
   if (profiling_enabled()) {
