@@ -45,25 +45,59 @@ struct __align__(8) WgradHaloBarriers {
 
 __host__ __device__ inline int round_up_1k(int x) { return (x + 1023) & ~1023; }
 
-template <int J>
-__device__ __forceinline__ void issue_supertile(uint32_t tmem_base, uint64_t x_desc0, uint64_t z_desc0, uint32_t idesc,
-                                                int P, uint32_t xrow16, uint32_t zrow16, int groups, int n_cols,
-                                                uint32_t accumulate_first) {
-  // i: pairs of image rows (16 pixels of reduction), j: strips, r: filter rows, g: groups of stacked filter columns
-#pragma unroll 1
-  for (int i = 0; i < kTH / 2; ++i) {
+__device__ __forceinline__ uint64_t desc_pair(uint32_t lo, uint32_t hi) {
+  return (static_cast<uint64_t>(hi) << 32) | lo;
+}
+
+// MMA issuer, specialised on (J, Cx, Cz): every descriptor of a super-tile is "stage base + compile-time constant"
+// (csrc/mma_rate.cu: a 128 x 32 x 16 SS MMA retires every 40 cycles only if the issuing lane spends no more than a
+// few scalar instructions per MMA; the run-time-generic loop with 64-bit descriptor arithmetic ran at ~75).
+template <int J, int CX, int CZ>
+__device__ __forceinline__ void wgrad_halo_mma_role(WgradHaloBarriers* bars, uint32_t smem_addr, uint32_t stage_bytes,
+                                                    uint32_t halo_stride, int stages, uint32_t tmem_base, int my_tiles) {
+  constexpr int P = 8 * J + 2;
+  constexpr uint32_t XROW = CX * 2, ZROW = CZ * 2;
+  constexpr int GROUPS = CX == 32 ? 1 : 2;
+  const uint32_t idesc = umma_idesc_bf16(128, CZ, 1, 1);
+  // A: atoms along M are one pixel row apart (LBO = row bytes); 8-pixel groups along K are one image row apart
+  const uint32_t x_hi =
+      static_cast<uint32_t>(umma_smem_desc(0, XROW, P * XROW, CX == 64 ? UMMA_SW_128B : UMMA_SW_64B) >> 32);
+  const uint32_t z_hi =
+      static_cast<uint32_t>(umma_smem_desc(0, 0, 8 * J * ZROW, CZ == 64 ? UMMA_SW_128B : UMMA_SW_64B) >> 32);
+  // LBO lives in bits [16,30) of the low word
+  const uint32_t x_lo_const = static_cast<uint32_t>(umma_smem_desc(0, XROW, P * XROW, UMMA_SW_NONE) & 0xFFFFFFFFu);
+  int stage = 0;
+  uint32_t phase = 0;
+  for (int k = 0; k < my_tiles; ++k) {
+    mbar_wait(&bars->full[stage], phase);
+    tc_fence_after();
+    const uint32_t sx = smem_addr + static_cast<uint32_t>(stage) * stage_bytes;
+    const uint32_t x_lo = x_lo_const + (sx >> 4);
+    const uint32_t z_lo = (sx + halo_stride) >> 4;
+    if (elect_one()) {
+      const uint32_t first = k ? 1u : 0u;
+      // i: pairs of image rows (16 pixels of reduction), j: strips, r: filter rows, g: groups of stacked filter columns
 #pragma unroll
-    for (int j = 0; j < J; ++j) {
-      const uint64_t zd = z_desc0 + static_cast<uint64_t>((2 * i * 8 * J + 8 * j) * zrow16);
+      for (int i = 0; i < kTH / 2; ++i) {
 #pragma unroll
-      for (int r = 0; r < 3; ++r) {
-        for (int g = 0; g < groups; ++g) {
-          const uint64_t xd = x_desc0 + static_cast<uint64_t>(((2 * i + r) * P + 8 * j + 2 * g) * xrow16);
-          const uint32_t acc = (accumulate_first | static_cast<uint32_t>(i) | static_cast<uint32_t>(j)) ? 1u : 0u;
-          umma_f16(tmem_base + static_cast<uint32_t>((r * groups + g) * n_cols), xd, zd, idesc, acc);
+        for (int j = 0; j < J; ++j) {
+#pragma unroll
+          for (int r = 0; r < 3; ++r) {
+#pragma unroll
+            for (int g = 0; g < GROUPS; ++g) {
+              umma_f16(tmem_base + static_cast<uint32_t>((r * GROUPS + g) * CZ),
+                       desc_pair(x_lo + static_cast<uint32_t>(((2 * i + r) * P + 8 * j + 2 * g) * (XROW >> 4)), x_hi),
+                       desc_pair(z_lo + static_cast<uint32_t>((2 * i * 8 * J + 8 * j) * (ZROW >> 4)), z_hi), idesc,
+                       (i == 0 && j == 0) ? first : 1u);
+            }
+          }
         }
       }
+      umma_commit(&bars->empty[stage]);
+      if (k == my_tiles - 1) umma_commit(&bars->tmem_full);
     }
+    __syncwarp();
+    if (++stage == stages) { stage = 0; phase ^= 1u; }
   }
 }
 
@@ -135,31 +169,25 @@ wgrad_halo_kernel(const __grid_constant__ WgradHaloParams p, const __grid_consta
     }
   } else if (warp == 1) {
     if (my_tiles > 0) {
-      const uint32_t idesc = umma_idesc_bf16(128, static_cast<uint32_t>(p.Cz), 1, 1);
-      const uint32_t x_sw = p.Cx == 64 ? UMMA_SW_128B : UMMA_SW_64B;
-      const uint32_t z_sw = p.Cz == 64 ? UMMA_SW_128B : UMMA_SW_64B;
-      // A: atoms along M are one pixel row apart (LBO = row bytes); 8-pixel groups along K are one image row apart
-      const uint64_t x_hi = umma_smem_desc(0, static_cast<uint32_t>(xrow), static_cast<uint32_t>(P * xrow), x_sw);
-      const uint64_t z_hi = umma_smem_desc(0, 0, static_cast<uint32_t>(8 * p.J * zrow), z_sw);
-      int stage = 0;
-      uint32_t phase = 0;
-      for (int k = 0; k < my_tiles; ++k) {
-        mbar_wait(&bars->full[stage], phase);
-        tc_fence_after();
-        const uint32_t sx = smem_u32(smem + stage * stage_bytes);
-        const uint64_t xd = x_hi + (sx >> 4);
-        const uint64_t zd = z_hi + ((sx + static_cast<uint32_t>(halo_stride)) >> 4);
-        if (elect_one()) {
-          const uint32_t first = k ? 1u : 0u;
-          if (p.J == 4) issue_supertile<4>(tmem_base, xd, zd, idesc, P, xrow >> 4, zrow >> 4, groups, p.Cz, first);
-          else if (p.J == 2) issue_supertile<2>(tmem_base, xd, zd, idesc, P, xrow >> 4, zrow >> 4, groups, p.Cz, first);
-          else issue_supertile<1>(tmem_base, xd, zd, idesc, P, xrow >> 4, zrow >> 4, groups, p.Cz, first);
-          umma_commit(&bars->empty[stage]);
-          if (k == my_tiles - 1) umma_commit(&bars->tmem_full);
-        }
-        __syncwarp();
-        if (++stage == p.stages) { stage = 0; phase ^= 1u; }
+      const uint32_t sa = smem_u32(smem);
+#define UB_WH(JJ, CX, CZ)                                                                                 \
+      wgrad_halo_mma_role<JJ, CX, CZ>(bars, sa, static_cast<uint32_t>(stage_bytes),                       \
+                                      static_cast<uint32_t>(halo_stride), p.stages, tmem_base, my_tiles)
+#define UB_WH_J(CX, CZ)                        \
+      do {                                     \
+        if (p.J == 4) UB_WH(4, CX, CZ);        \
+        else if (p.J == 2) UB_WH(2, CX, CZ);   \
+        else UB_WH(1, CX, CZ);                 \
+      } while (0)
+      if (p.Cx == 32) {
+        if (p.Cz == 32) UB_WH_J(32, 32);
+        else UB_WH_J(32, 64);
+      } else {
+        if (p.Cz == 32) UB_WH_J(64, 32);
+        else UB_WH_J(64, 64);
       }
+#undef UB_WH_J
+#undef UB_WH
     }
   } else if (warp >= 4) {
     const int quarter = warp & 3;
