@@ -5,6 +5,7 @@
 
 #include "common.h"
 #include "conv_halo.cuh"
+#include "elementwise.cuh"
 #include "igemm.cuh"
 #include "wgrad.cuh"
 
@@ -269,7 +270,7 @@ int plan_wgrad(WgradPlan& wp, int N, int H, int W, int taps_r, int taps_s, int p
 
 }  // namespace
 
-size_t conv3x3_wgrad_ws_bytes(int N, int H, int W, int Cin_total, int Cout) {
+size_t conv3x3_wgrad_ws_bytes(int N, int H, int W, int Cin_total, int Cout, bool with_bias) {
   WgradPlan wp;
   // the split count does not depend on how Cin is divided between sources beyond the tile count; use the
   // single-source plan as an upper bound (two sources never have fewer tiles, hence never more splits).
@@ -290,11 +291,23 @@ size_t conv3x3_wgrad_ws_bytes(int N, int H, int W, int Cin_total, int Cout) {
     if (rp.splits > 1) row = static_cast<size_t>(rp.splits) * wp.nweights * sizeof(float);
   }
   size_t need = generic > halo ? generic : halo;
-  return need > row ? need : row;
+  if (row > need) need = row;
+  // the optional bias gradient of the non-halo paths reuses the workspace after the split-K reduction
+  const size_t bias = with_bias ? static_cast<size_t>(colsum_ws_floats(Cout)) * sizeof(float) : 0;
+  return need > bias ? need : bias;
+}
+
+// Bias gradient for the wgrad paths that do not produce it themselves.
+static int bias_grad_after(const void* dz, int Cout, float* db, void* ws, size_t ws_bytes, int N, int H, int W,
+                           cudaStream_t s) {
+  const size_t need = static_cast<size_t>(colsum_ws_floats(Cout)) * sizeof(float);
+  UB_REQUIRE(ws != nullptr && ws_bytes >= need, "conv3x3_wgrad: workspace of %zu bytes needed for the bias gradient, %zu given",
+             need, ws_bytes);
+  return colsum_bf16(dz, db, reinterpret_cast<float*>(ws), static_cast<long long>(N) * H * W, Cout, s);
 }
 
 int conv3x3_wgrad(const void* dz, int Cout, ConvSrc x0, ConvSrc x1, float* dw, void* ws, size_t ws_bytes, int N, int H,
-                  int W, cudaStream_t s) {
+                  int W, cudaStream_t s, float* db) {
   const int C1 = x1.ptr ? x1.C : 0;
   if (wgrad_halo_supported(H, W, x0.C, Cout) && (!C1 || wgrad_halo_supported(H, W, C1, Cout))) {
     const ConvSrc srcs[2] = {x0, x1};
@@ -310,7 +323,8 @@ int conv3x3_wgrad(const void* dz, int Cout, ConvSrc x0, ConvSrc x1, float* dw, v
       if (rc) return rc;
       rc = nhwc_map(&zm, dz, N, H, W, Cout, Cout, Box{1, 16, 8 * J});
       if (rc) return rc;
-      rc = wgrad_halo_launch(xm, zm, N, H, W, Cx, Cout, J, dw, x0.C + C1, off, reinterpret_cast<float*>(ws), s);
+      rc = wgrad_halo_launch(xm, zm, N, H, W, Cx, Cout, J, dw, x0.C + C1, off, reinterpret_cast<float*>(ws), s,
+                             i == 0 ? db : nullptr);   // fused: one extra MMA per K step against a tile of ones
       if (rc) return rc;
       off += Cx;
     }
@@ -346,8 +360,11 @@ int conv3x3_wgrad(const void* dz, int Cout, ConvSrc x0, ConvSrc x1, float* dw, v
     }
     rc = wgrad_row_launch(rp, zm, xm0, xm1, s);
     if (rc) return rc;
-    if (rp.splits > 1) return splitk_reduce_launch(rp.out, nweights, rp.splits, dw, nweights, s);
-    return UB_OK;
+    if (rp.splits > 1) {
+      rc = splitk_reduce_launch(rp.out, nweights, rp.splits, dw, nweights, s);
+      if (rc) return rc;
+    }
+    return db ? bias_grad_after(dz, Cout, db, ws, ws_bytes, N, H, W, s) : UB_OK;
   }
   WgradPlan wp;
   int rc = plan_wgrad(wp, N, H, W, 3, 3, 1, Cout, x0.C, C1);
@@ -381,8 +398,11 @@ int conv3x3_wgrad(const void* dz, int Cout, ConvSrc x0, ConvSrc x1, float* dw, v
   }
   rc = wgrad_launch(p, zm, xm0, xm1, s);
   if (rc) return rc;
-  if (p.splits > 1) return splitk_reduce_launch(p.out, wp.nweights, p.splits, dw, wp.nweights, s);
-  return UB_OK;
+  if (p.splits > 1) {
+    rc = splitk_reduce_launch(p.out, wp.nweights, p.splits, dw, wp.nweights, s);
+    if (rc) return rc;
+  }
+  return db ? bias_grad_after(dz, Cout, db, ws, ws_bytes, N, H, W, s) : UB_OK;
 }
 
 // ------------------------------------------------------------------------------------------------ transposed conv

@@ -35,9 +35,10 @@ int conv3x3_dgrad(const void* dz, int Cout, const void* w_packed_d, DgradDst d0,
                   cudaStream_t s);
 
 // dw (fp32 [3][3][C0+C1][Cout]) = correlation of [x0,x1] with dz over all pixels. ws: conv3x3_wgrad_ws_bytes().
-size_t conv3x3_wgrad_ws_bytes(int N, int H, int W, int Cin_total, int Cout);
+size_t conv3x3_wgrad_ws_bytes(int N, int H, int W, int Cin_total, int Cout, bool with_bias = false);
+// db (optional): also the bias gradient sum_pixels dz, fused into the halo kernel where that one runs.
 int conv3x3_wgrad(const void* dz, int Cout, ConvSrc x0, ConvSrc x1, float* dw, void* ws, size_t ws_bytes, int N, int H,
-                  int W, cudaStream_t s);
+                  int W, cudaStream_t s, float* db = nullptr);
 
 // Conv2DTranspose 2x2 stride 2: y[n,2i+a,2j+b,o] = sum_c x[n,i,j,c] w[a,b,o,c] + bias[o].
 // w_packed = bf16 [4*Cout][Cin] (cast of the TF layout); (N,H,W) is the input grid.

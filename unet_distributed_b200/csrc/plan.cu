@@ -206,14 +206,14 @@ int unetb200_plan_create(unetb200_plan** out, int N, int H, int W, int in_channe
     ws = max_sz(ws, unetb200_bias_grad_ws_bytes(P->ch[L]));
     const auto& la = P->layers[P->enc_a[L]];
     const auto& lb = P->layers[P->enc_b[L]];
-    if (L > 0) ws = max_sz(ws, conv3x3_wgrad_ws_bytes(N, P->Hl(L), P->Wl(L), la.cin, la.cout));
-    ws = max_sz(ws, conv3x3_wgrad_ws_bytes(N, P->Hl(L), P->Wl(L), lb.cin, lb.cout));
+    if (L > 0) ws = max_sz(ws, conv3x3_wgrad_ws_bytes(N, P->Hl(L), P->Wl(L), la.cin, la.cout, true));
+    ws = max_sz(ws, conv3x3_wgrad_ws_bytes(N, P->Hl(L), P->Wl(L), lb.cin, lb.cout, true));
   }
   for (int L = 0; L < 4; ++L) {
     const auto& la = P->layers[P->dec_a[L]];
     const auto& lb = P->layers[P->dec_b[L]];
-    ws = max_sz(ws, conv3x3_wgrad_ws_bytes(N, P->Hl(L), P->Wl(L), la.cin, la.cout));
-    ws = max_sz(ws, conv3x3_wgrad_ws_bytes(N, P->Hl(L), P->Wl(L), lb.cin, lb.cout));
+    ws = max_sz(ws, conv3x3_wgrad_ws_bytes(N, P->Hl(L), P->Wl(L), la.cin, la.cout, true));
+    ws = max_sz(ws, conv3x3_wgrad_ws_bytes(N, P->Hl(L), P->Wl(L), lb.cin, lb.cout, true));
     if (!up) {
       const auto& lt = P->layers[P->tc[L]];
       ws = max_sz(ws, tconv2x2_wgrad_ws_bytes(N, P->Hl(L + 1), P->Wl(L + 1), lt.cin, lt.cout));
@@ -413,16 +413,14 @@ int unetb200_plan_backward(unetb200_plan* P, const float* imgs, const float* msk
       const int la = P->dec_a[L], lb = P->dec_b[L];
       // conv{9-L}b
       RC(conv3x3_wgrad(P->at(P->g_dc[L]), P->dc_out[L], ConvSrc{P->at(P->da[L]), P->ch[L]}, ConvSrc{nullptr, 0},
-                       P->dW_(lb), wsv, P->ws_bytes, N, H, W, s));
-      RC(colsum_bf16(P->at(P->g_dc[L]), P->dB_(lb), ws, px, P->dc_out[L], s));
+                       P->dW_(lb), wsv, P->ws_bytes, N, H, W, s, P->dB_(lb)));
       RC(conv3x3_dgrad(P->at(P->g_dc[L]), P->dc_out[L], P->pkd(lb),
                        DgradDst{P->at(P->g_da[L]), P->ch[L], P->at(P->da[L]), 1.0f, P->gate(P->gt_da[L])},
                        DgradDst{nullptr, 0, nullptr, 1.0f},
                        N, H, W, s));
       // conv{9-L}a over [u, skip]
       RC(conv3x3_wgrad(P->at(P->g_da[L]), P->ch[L], ConvSrc{P->at(P->u[L]), P->ch[L]}, ConvSrc{P->at(P->c[L]), P->ch[L]},
-                       P->dW_(la), wsv, P->ws_bytes, N, H, W, s));
-      RC(colsum_bf16(P->at(P->g_da[L]), P->dB_(la), ws, px, P->ch[L], s));
+                       P->dW_(la), wsv, P->ws_bytes, N, H, W, s, P->dB_(la)));
       RC(conv3x3_dgrad(P->at(P->g_da[L]), P->ch[L], P->pkd(la), DgradDst{P->at(P->g_u[L]), P->ch[L], nullptr, 1.0f},
                        DgradDst{P->at(P->g_c[L]), P->ch[L], P->at(P->c[L]), 1.0f, P->gate(P->gt_c[L])}, N, H, W, s));
       // up path
@@ -449,13 +447,11 @@ int unetb200_plan_backward(unetb200_plan* P, const float* imgs, const float* msk
     const long long px = static_cast<long long>(N) * H * W;
     const int la = P->enc_a[L], lb = P->enc_b[L];
     RC(conv3x3_wgrad(P->at(P->g_c[L]), P->c4_out, ConvSrc{P->at(P->a[L]), P->ch[L]}, ConvSrc{nullptr, 0}, P->dW_(lb), wsv,
-                     P->ws_bytes, N, H, W, s));
-    RC(colsum_bf16(P->at(P->g_c[L]), P->dB_(lb), ws, px, P->c4_out, s));
+                     P->ws_bytes, N, H, W, s, P->dB_(lb)));
     RC(conv3x3_dgrad(P->at(P->g_c[L]), P->c4_out, P->pkd(lb), DgradDst{P->at(P->g_a[L]), P->ch[L], P->at(P->a[L]), 1.0f, P->gate(P->gt_a[L])},
                      DgradDst{nullptr, 0, nullptr, 1.0f}, N, H, W, s));
     RC(conv3x3_wgrad(P->at(P->g_a[L]), P->ch[L], ConvSrc{P->at(P->p[L - 1]), P->ch[L - 1]}, ConvSrc{nullptr, 0},
-                     P->dW_(la), wsv, P->ws_bytes, N, H, W, s));
-    RC(colsum_bf16(P->at(P->g_a[L]), P->dB_(la), ws, px, P->ch[L], s));
+                     P->dW_(la), wsv, P->ws_bytes, N, H, W, s, P->dB_(la)));
     RC(conv3x3_dgrad(P->at(P->g_a[L]), P->ch[L], P->pkd(la), DgradDst{P->at(P->g_p[L - 1]), P->ch[L - 1], nullptr, 1.0f},
                      DgradDst{nullptr, 0, nullptr, 1.0f}, N, H, W, s));
     return UB_OK;
@@ -468,16 +464,14 @@ int unetb200_plan_backward(unetb200_plan* P, const float* imgs, const float* msk
     // MaxPoolGrad + skip gradient + ReluGrad of conv{L+1}b, in place in g_c[L]
     RC(maxpool2x2_bwd(P->at(P->c[L]), P->at(P->g_p[L]), P->at(P->g_c[L]), P->at(P->g_c[L]), N, H, W, P->ch[L], s));
     RC(conv3x3_wgrad(P->at(P->g_c[L]), P->ch[L], ConvSrc{P->at(P->a[L]), P->ch[L]}, ConvSrc{nullptr, 0}, P->dW_(lb), wsv,
-                     P->ws_bytes, N, H, W, s));
-    RC(colsum_bf16(P->at(P->g_c[L]), P->dB_(lb), ws, px, P->ch[L], s));
+                     P->ws_bytes, N, H, W, s, P->dB_(lb)));
     const bool dropped = (L == 2 || L == 3) && P->dropout > 0.0f;
     RC(conv3x3_dgrad(P->at(P->g_c[L]), P->ch[L], P->pkd(lb),
                      DgradDst{P->at(P->g_a[L]), P->ch[L], P->at(P->a[L]), dropped ? inv_keep : 1.0f, P->gate(P->gt_a[L])},
                      DgradDst{nullptr, 0, nullptr, 1.0f}, N, H, W, s));
     if (L > 0) {
       RC(conv3x3_wgrad(P->at(P->g_a[L]), P->ch[L], ConvSrc{P->at(P->p[L - 1]), P->ch[L - 1]}, ConvSrc{nullptr, 0},
-                       P->dW_(la), wsv, P->ws_bytes, N, H, W, s));
-      RC(colsum_bf16(P->at(P->g_a[L]), P->dB_(la), ws, px, P->ch[L], s));
+                       P->dW_(la), wsv, P->ws_bytes, N, H, W, s, P->dB_(la)));
       RC(conv3x3_dgrad(P->at(P->g_a[L]), P->ch[L], P->pkd(la),
                        DgradDst{P->at(P->g_p[L - 1]), P->ch[L - 1], nullptr, 1.0f}, DgradDst{nullptr, 0, nullptr, 1.0f},
                        N, H, W, s));

@@ -42,7 +42,7 @@ bool wgrad_halo_supported(int H, int W, int Cx, int Cz);
 int wgrad_halo_pick_J(int Cx, int W);
 size_t wgrad_halo_ws_bytes(int N, int H, int W, int Cx, int Cz);
 int wgrad_halo_launch(const CUtensorMap& x_map, const CUtensorMap& z_map, int N, int H, int W, int Cx, int Cz, int J,
-                      float* dw, int cin_total, int ci_off, float* ws, cudaStream_t stream);
+                      float* dw, int cin_total, int ci_off, float* ws, cudaStream_t stream, float* db = nullptr);
 
 // Row variant for wide layers (wgrad_row.cu): one CTA = one filter row (three taps) of a 128 x 128 tile.
 struct WgradRowParams {

@@ -26,6 +26,7 @@ namespace {
 constexpr int kThreads = 256;   // warp0 TMA producer, warp1 MMA + TMEM, warps 4..7 epilogue
 constexpr int kMaxStages = 3;
 constexpr int kTH = 16;
+constexpr int kOnesBytes = 4096;   // bf16 1.0 tile: covers every address an A descriptor of this kernel can form from it
 
 struct WgradHaloParams {
   int N, H, W;
@@ -33,7 +34,8 @@ struct WgradHaloParams {
   int tiles_h, tiles_w;
   int Cx, Cz;               // 32 or 64 each
   int stages;
-  float* ws;                // [gridDim.x][9][Cx][Cz] partial gradients
+  float* ws;                // [gridDim.x][9*Cx*Cz (+ Cz)] partial gradients (+ partial bias gradient)
+  int with_bias;            // also reduce dZ over pixels (one extra MMA per K step against a tile of ones)
 };
 
 struct __align__(8) WgradHaloBarriers {
@@ -54,7 +56,8 @@ __device__ __forceinline__ uint64_t desc_pair(uint32_t lo, uint32_t hi) {
 // few scalar instructions per MMA; the run-time-generic loop with 64-bit descriptor arithmetic ran at ~75).
 template <int J, int CX, int CZ>
 __device__ __forceinline__ void wgrad_halo_mma_role(WgradHaloBarriers* bars, uint32_t smem_addr, uint32_t stage_bytes,
-                                                    uint32_t halo_stride, int stages, uint32_t tmem_base, int my_tiles) {
+                                                    uint32_t halo_stride, int stages, uint32_t tmem_base, int my_tiles,
+                                                    uint32_t ones_addr, bool with_bias) {
   constexpr int P = 8 * J + 2;
   constexpr uint32_t XROW = CX * 2, ZROW = CZ * 2;
   constexpr int GROUPS = CX == 32 ? 1 : 2;
@@ -66,6 +69,10 @@ __device__ __forceinline__ void wgrad_halo_mma_role(WgradHaloBarriers* bars, uin
       static_cast<uint32_t>(umma_smem_desc(0, 0, 8 * J * ZROW, CZ == 64 ? UMMA_SW_128B : UMMA_SW_64B) >> 32);
   // LBO lives in bits [16,30) of the low word
   const uint32_t x_lo_const = static_cast<uint32_t>(umma_smem_desc(0, XROW, P * XROW, UMMA_SW_NONE) & 0xFFFFFFFFu);
+  // Bias gradient on the tensor core: A = ones (every row of the extra accumulator becomes sum_p dZ[p, co]).
+  // The ones tile is K-major with a single 8-row group stride of 0 ... any layout of a constant tile is the same tile;
+  // it is addressed like an X atom set with zero strides so that the footprint stays inside kOnesBytes.
+  const uint64_t ones_desc = umma_smem_desc(ones_addr, 0, 0, CX == 64 ? UMMA_SW_128B : UMMA_SW_64B);
   int stage = 0;
   uint32_t phase = 0;
   for (int k = 0; k < my_tiles; ++k) {
@@ -91,6 +98,11 @@ __device__ __forceinline__ void wgrad_halo_mma_role(WgradHaloBarriers* bars, uin
                        (i == 0 && j == 0) ? first : 1u);
             }
           }
+          if (with_bias) {
+            umma_f16(tmem_base + static_cast<uint32_t>(3 * GROUPS * CZ), ones_desc,
+                     desc_pair(z_lo + static_cast<uint32_t>((2 * i * 8 * J + 8 * j) * (ZROW >> 4)), z_hi), idesc,
+                     (i == 0 && j == 0) ? first : 1u);
+          }
         }
       }
       umma_commit(&bars->empty[stage]);
@@ -115,7 +127,8 @@ wgrad_halo_kernel(const __grid_constant__ WgradHaloParams p, const __grid_consta
   // 1 KiB of slack after the halo tile: the junk filter column (s = 3) reads up to 3 pixel rows past its end
   const int halo_stride = round_up_1k(halo_bytes + 4 * xrow);
   const int stage_bytes = halo_stride + round_up_1k(z_bytes);
-  WgradHaloBarriers* bars = reinterpret_cast<WgradHaloBarriers*>(smem + p.stages * stage_bytes);
+  uint8_t* ones = smem + p.stages * stage_bytes;
+  WgradHaloBarriers* bars = reinterpret_cast<WgradHaloBarriers*>(ones + kOnesBytes);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -123,7 +136,7 @@ wgrad_halo_kernel(const __grid_constant__ WgradHaloParams p, const __grid_consta
   const int groups = p.Cx == 32 ? 1 : 2;          // stacked filter columns per MMA: 4 (Cx=32) or 2 (Cx=64)
   const int n_acc = 3 * groups;
   uint32_t tmem_cols = 32;
-  while (tmem_cols < static_cast<uint32_t>(n_acc * p.Cz)) tmem_cols <<= 1;
+  while (tmem_cols < static_cast<uint32_t>((n_acc + (p.with_bias ? 1 : 0)) * p.Cz)) tmem_cols <<= 1;
   const int my_tiles = (num_tiles > static_cast<int>(blockIdx.x))
                            ? (num_tiles - static_cast<int>(blockIdx.x) + static_cast<int>(gridDim.x) - 1) /
                                  static_cast<int>(gridDim.x)
@@ -142,6 +155,11 @@ wgrad_halo_kernel(const __grid_constant__ WgradHaloParams p, const __grid_consta
   if (warp == 1) {
     tmem_alloc(&bars->tmem_base, tmem_cols);
     tmem_relinquish();
+  }
+  if (p.with_bias) {
+    uint32_t* o32 = reinterpret_cast<uint32_t*>(ones);
+    for (int i = threadIdx.x; i < kOnesBytes / 4; i += blockDim.x) o32[i] = 0x3F803F80u;   // two bf16 1.0
+    fence_proxy_async_smem();
   }
   tc_fence_before();
   __syncthreads();
@@ -172,7 +190,8 @@ wgrad_halo_kernel(const __grid_constant__ WgradHaloParams p, const __grid_consta
       const uint32_t sa = smem_u32(smem);
 #define UB_WH(JJ, CX, CZ)                                                                                 \
       wgrad_halo_mma_role<JJ, CX, CZ>(bars, sa, static_cast<uint32_t>(stage_bytes),                       \
-                                      static_cast<uint32_t>(halo_stride), p.stages, tmem_base, my_tiles)
+                                      static_cast<uint32_t>(halo_stride), p.stages, tmem_base, my_tiles,      \
+                                      smem_u32(ones), p.with_bias != 0)
 #define UB_WH_J(CX, CZ)                        \
       do {                                     \
         if (p.J == 4) UB_WH(4, CX, CZ);        \
@@ -194,7 +213,8 @@ wgrad_halo_kernel(const __grid_constant__ WgradHaloParams p, const __grid_consta
     const int m = quarter * 32 + lane;
     const int a = m / p.Cx;              // which stacked filter column this TMEM lane belongs to
     const int ci = m % p.Cx;
-    float* out = p.ws + static_cast<size_t>(blockIdx.x) * 9 * p.Cx * p.Cz;
+    const int n_out = 9 * p.Cx * p.Cz + (p.with_bias ? p.Cz : 0);
+    float* out = p.ws + static_cast<size_t>(blockIdx.x) * n_out;
     if (my_tiles > 0) {
       mbar_wait(&bars->tmem_full, 0);
       tc_fence_after();
@@ -224,6 +244,23 @@ wgrad_halo_kernel(const __grid_constant__ WgradHaloParams p, const __grid_consta
         }
       }
     }
+    if (p.with_bias && warp == 4) {   // every row of the bias accumulator holds the same sums; lane 0 stores row 0
+      const uint32_t t_row = tmem_base + static_cast<uint32_t>(n_acc * p.Cz);
+      for (int c = 0; c < p.Cz; c += 16) {
+        uint32_t v[16];
+        if (my_tiles > 0) {
+          tmem_ld_32x32b_x16(t_row + static_cast<uint32_t>(c), v);
+          tmem_ld_wait();
+        } else {
+#pragma unroll
+          for (int i = 0; i < 16; ++i) v[i] = 0u;
+        }
+        if (lane == 0) {
+#pragma unroll
+          for (int i = 0; i < 16; ++i) out[9 * p.Cx * p.Cz + c + i] = __uint_as_float(v[i]);
+        }
+      }
+    }
   }
 
   tc_fence_before();
@@ -236,10 +273,11 @@ wgrad_halo_kernel(const __grid_constant__ WgradHaloParams p, const __grid_consta
 
 // dw[tap][ci_off + ci][co] = sum over parts of ws[part][tap][ci][co]; 8 interleaved partial sums then a fixed 8-way sum.
 __global__ void wgrad_halo_reduce_kernel(const float* __restrict__ ws, int nparts, int Cx, int Cz, float* __restrict__ dw,
-                                         int cin_total, int ci_off) {
+                                         int cin_total, int ci_off, float* __restrict__ db) {
   __shared__ float part[32][32];
   const int lanes = blockDim.x >> 5;
-  const int n = 9 * Cx * Cz;
+  const int nw = 9 * Cx * Cz;
+  const int n = nw + (db ? Cz : 0);
   const int c = threadIdx.x & 31, q = threadIdx.x >> 5;
   const int i = blockIdx.x * 32 + c;
   float acc = 0.0f;
@@ -251,10 +289,14 @@ __global__ void wgrad_halo_reduce_kernel(const float* __restrict__ ws, int npart
   if (q == 0 && i < n) {
     float s = part[0][c];
     for (int k = 1; k < lanes; ++k) s += part[k][c];
-    const int co = i % Cz;
-    const int ci = (i / Cz) % Cx;
-    const int tap = i / (Cz * Cx);
-    dw[(static_cast<size_t>(tap) * cin_total + ci_off + ci) * Cz + co] = s;
+    if (i >= nw) {
+      db[i - nw] = s;
+    } else {
+      const int co = i % Cz;
+      const int ci = (i / Cz) % Cx;
+      const int tap = i / (Cz * Cx);
+      dw[(static_cast<size_t>(tap) * cin_total + ci_off + ci) * Cz + co] = s;
+    }
   }
 }
 
@@ -280,12 +322,12 @@ static int halo_grid(int N, int H, int W, int J) {
 
 size_t wgrad_halo_ws_bytes(int N, int H, int W, int Cx, int Cz) {
   const int J = pick_J(Cx, W);
-  return static_cast<size_t>(halo_grid(N, H, W, J)) * 9 * Cx * Cz * sizeof(float);
+  return static_cast<size_t>(halo_grid(N, H, W, J)) * (9 * Cx * Cz + Cz) * sizeof(float);
 }
 
 // One source of the (possibly concatenated) input: writes dw[:, ci_off : ci_off + Cx, :].
 int wgrad_halo_launch(const CUtensorMap& x_map, const CUtensorMap& z_map, int N, int H, int W, int Cx, int Cz, int J,
-                      float* dw, int cin_total, int ci_off, float* ws, cudaStream_t stream) {
+                      float* dw, int cin_total, int ci_off, float* ws, cudaStream_t stream, float* db) {
   WgradHaloParams p;
   p.N = N; p.H = H; p.W = W;
   p.J = J;
@@ -293,13 +335,14 @@ int wgrad_halo_launch(const CUtensorMap& x_map, const CUtensorMap& z_map, int N,
   p.tiles_w = (W + 8 * J - 1) / (8 * J);
   p.Cx = Cx; p.Cz = Cz;
   p.ws = ws;
+  p.with_bias = db ? 1 : 0;
   const int P = 8 * J + 2;
   const int stage_bytes = round_up_1k((kTH + 2) * P * Cx * 2 + 4 * Cx * 2) + round_up_1k(kTH * 8 * J * Cz * 2);
-  int stages = (225 * 1024 - 1024 - static_cast<int>(sizeof(WgradHaloBarriers))) / stage_bytes;
+  int stages = (225 * 1024 - 1024 - kOnesBytes - static_cast<int>(sizeof(WgradHaloBarriers))) / stage_bytes;
   if (stages > kMaxStages) stages = kMaxStages;
   UB_REQUIRE(stages >= 2, "wgrad_halo: stage of %d bytes does not fit twice in shared memory", stage_bytes);
   p.stages = stages;
-  const size_t smem = static_cast<size_t>(stages) * stage_bytes + sizeof(WgradHaloBarriers) + 1024;
+  const size_t smem = static_cast<size_t>(stages) * stage_bytes + kOnesBytes + sizeof(WgradHaloBarriers) + 1024;
   static bool attr_set[64] = {false};
   int dev = 0;
   UB_CHECK_CUDA(cudaGetDevice(&dev));
@@ -316,8 +359,8 @@ int wgrad_halo_launch(const CUtensorMap& x_map, const CUtensorMap& z_map, int N,
   wgrad_halo_kernel<<<grid, kThreads, smem, stream>>>(p, x_map, z_map);
   UB_CHECK_CUDA(cudaGetLastError());
   prof_end(stream);
-  const int n = 9 * Cx * Cz;
-  wgrad_halo_reduce_kernel<<<(n + 31) / 32, 1024, 0, stream>>>(ws, grid, Cx, Cz, dw, cin_total, ci_off);
+  const int n = 9 * Cx * Cz + (db ? Cz : 0);
+  wgrad_halo_reduce_kernel<<<(n + 31) / 32, 1024, 0, stream>>>(ws, grid, Cx, Cz, dw, cin_total, ci_off, db);
   UB_CHECK_CUDA(cudaGetLastError());
   return UB_OK;
 }
