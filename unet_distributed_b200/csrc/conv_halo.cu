@@ -424,9 +424,10 @@ __device__ __forceinline__ void halo_epilogue_fast(const HaloParams& p, HaloBarr
 #pragma unroll
         for (int i = 0; i < 8; ++i) w[i] = pack_bf16x2(v[2 * i], v[2 * i + 1]);
       }
-      uint4* dp = reinterpret_cast<uint4*>(dst_b[sl] + j * strip_b[sl] + (32 * cl - sl * (BN / 2)) * 2);
-      dp[0] = make_uint4(w[0], w[1], w[2], w[3]);
-      dp[1] = make_uint4(w[4], w[5], w[6], w[7]);
+      U32x8 o;
+#pragma unroll
+      for (int i = 0; i < 8; ++i) o.v[i] = w[i];
+      st_global_v8(dst_b[sl] + j * strip_b[sl] + (32 * cl - sl * (BN / 2)) * 2, o);   // one full sector per lane
     }
     tc_fence_before();
     __syncwarp();
@@ -668,7 +669,9 @@ int halo_launch(const HaloParams& p_in, const CUtensorMap& a0, const CUtensorMap
     // the lean epilogue covers full super-tiles of one N tile without dropout or tensor masks (see halo_epilogue_fast)
     static const bool no_fast = getenv("UNETB200_NO_FAST_EPI") != nullptr;
     const IgemmEpilogue& e = p.epi;
-    const bool full = p.n_tiles == 1 && p.H % kTH == 0 && p.W % (8 * p.J) == 0;
+    const bool aligned = reinterpret_cast<uintptr_t>(e.dst[0]) % 32 == 0 && reinterpret_cast<uintptr_t>(e.dst[1]) % 32 == 0 &&
+                         e.dst_coff[0] % 16 == 0 && e.dst_coff[1] % 16 == 0 && e.dst_C[0] % 16 == 0 && e.dst_C[1] % 16 == 0;
+    const bool full = aligned && p.n_tiles == 1 && p.H % kTH == 0 && p.W % (8 * p.J) == 0;
     const bool plain = e.drop_keep >= 1.0f && !e.aux[0] && !e.aux[1];
     const bool gates_in = e.gate_in[0] || e.gate_in[1];
     p.fast_epi = 0;

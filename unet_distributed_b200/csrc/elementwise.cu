@@ -652,7 +652,9 @@ int conv_first_fwd(const float* x, const float* w, const float* bias, void* y, i
   UB_REQUIRE(Cout % 8 == 0 && Cout <= 64, "conv_first_fwd: Cout %d unsupported", Cout);
   const long long total = static_cast<long long>(N) * H * W * (Cout / 8);
   UB_REQUIRE(total < (1ll << 31), "conv_first_fwd: tensor too large");
-  if (Cout == 32 && (Cin == 1 || Cin == 4)) {   // thread-per-pixel fast path (the network's conv1a)
+  const bool y32 = reinterpret_cast<uintptr_t>(y) % 32 == 0;   // the fast path stores 32 bytes per instruction
+  UB_REQUIRE(gate_out == nullptr || y32, "conv_first_fwd: gate bits need a 32-byte aligned output tensor");
+  if (y32 && Cout == 32 && (Cin == 1 || Cin == 4)) {   // thread-per-pixel fast path (the network's conv1a)
     const unsigned P = static_cast<unsigned>(static_cast<long long>(N) * H * W);
     unsigned blocks = grid_for(P, kThreads);
     const unsigned cap = 8u * static_cast<unsigned>(device_sm_count());
@@ -688,6 +690,16 @@ int conv_first_wgrad(const float* x, const void* dz, float* dw, float* db, float
              "conv_first_wgrad: Cout %d unsupported", Cout);
   const int nout = 9 * Cin * Cout + Cout;
   UB_REQUIRE(static_cast<long long>(N) * H * W * groups < (1ll << 31), "conv_first_wgrad: tensor too large");
+  if (Cout == 32 && (Cin == 1 || Cin == 4) && W % 8 == 0) {   // strip kernel (level0.cuh)
+    const unsigned n_strips = static_cast<unsigned>(N) * H * (W / 8);
+    const uint4* dz4 = reinterpret_cast<const uint4*>(dz);
+    if (Cin == 1) conv_first32_wgrad_kernel<1><<<kRedBlocks, 128, 0, s>>>(x, dz4, ws, H, W, n_strips);
+    else conv_first32_wgrad_kernel<4><<<kRedBlocks, 128, 0, s>>>(x, dz4, ws, H, W, n_strips);
+    UB_CHECK_CUDA(cudaGetLastError());
+    rows_reduce_kernel<<<grid_for(nout, 32), 1024, 0, s>>>(ws, kRedBlocks, nout, dw, 9 * Cin * Cout, db);
+    UB_CHECK_CUDA(cudaGetLastError());
+    return UB_OK;
+  }
   const size_t smem = static_cast<size_t>(kThreads / 32) * nout * sizeof(float);
   if (smem > 48 * 1024) {
     UB_CHECK_CUDA(cudaFuncSetAttribute(conv_first_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,

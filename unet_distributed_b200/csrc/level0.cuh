@@ -62,12 +62,17 @@ conv_first32_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w
     }
     uint4* yp = y + static_cast<size_t>(pix) * 4;
 #pragma unroll
-    for (int q = 0; q < 4; ++q) {
-      const float4 a = acc[2 * q], b = acc[2 * q + 1];
-      uint4 o;
-      o.x = pack_bf16x2(fmaxf(a.x, 0.f), fmaxf(a.y, 0.f)); o.y = pack_bf16x2(fmaxf(a.z, 0.f), fmaxf(a.w, 0.f));
-      o.z = pack_bf16x2(fmaxf(b.x, 0.f), fmaxf(b.y, 0.f)); o.w = pack_bf16x2(fmaxf(b.z, 0.f), fmaxf(b.w, 0.f));
-      yp[q] = o;
+    for (int q2 = 0; q2 < 2; ++q2) {   // two 32-byte stores per pixel
+      U32x8 o;
+#pragma unroll
+      for (int q = 0; q < 2; ++q) {
+        const float4 a = acc[4 * q2 + 2 * q], b = acc[4 * q2 + 2 * q + 1];
+        o.v[4 * q + 0] = pack_bf16x2(fmaxf(a.x, 0.f), fmaxf(a.y, 0.f));
+        o.v[4 * q + 1] = pack_bf16x2(fmaxf(a.z, 0.f), fmaxf(a.w, 0.f));
+        o.v[4 * q + 2] = pack_bf16x2(fmaxf(b.x, 0.f), fmaxf(b.y, 0.f));
+        o.v[4 * q + 3] = pack_bf16x2(fmaxf(b.z, 0.f), fmaxf(b.w, 0.f));
+      }
+      st_global_v8(yp + 2 * q2, o);
     }
   }
 }
@@ -182,5 +187,99 @@ head32_bwd_kernel(const uint4* __restrict__ x, const float* __restrict__ w, cons
     float s = red[0][threadIdx.x];
     for (int wv = 1; wv < static_cast<int>(blockDim.x >> 5); ++wv) s += red[wv][threadIdx.x];
     ws[static_cast<size_t>(blockIdx.x) * 33 + threadIdx.x] = s;
+  }
+}
+
+// ---------------------------------------------------------------------------------------------- conv1a wgrad, Cout = 32
+// dW[3][3][CIN][32] and db[32] from the fp32 network input and bf16 dz. The generic kernel spends ~170 instructions
+// per (pixel, 8-channel group) on index arithmetic and nine boundary-checked input loads (ncu: 137 us for a 134 MB
+// read). Here a thread owns one 8-channel group of a strip of 8 consecutive pixels of an image row: the 3 x 10 input
+// window is loaded once per strip, the eight 16-byte dz loads are issued back to back, and the 72 + 8 accumulators
+// stay in registers across strips. Lanes l and l^4, l^8, l^16 hold the same channel group; warps, then blocks, are
+// summed in a fixed order (bit-reproducible): block -> ws[block][nout] -> rows_reduce_kernel.
+template <int CIN>
+__global__ void __launch_bounds__(128)
+conv_first32_wgrad_kernel(const float* __restrict__ x, const uint4* __restrict__ dz, float* __restrict__ ws, int H,
+                          int W, unsigned n_strips) {
+  constexpr int kNout = 9 * CIN * 32 + 32;
+  __shared__ float red[4][kNout];
+  const int g = threadIdx.x & 3;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const unsigned strips_w = static_cast<unsigned>(W) >> 3;
+  const unsigned first = (blockIdx.x * blockDim.x + threadIdx.x) >> 2;
+  const unsigned step = (gridDim.x * blockDim.x) >> 2;
+  for (int ci = 0; ci < CIN; ++ci) {
+    float acc[9][8];
+    float accb[8];
+#pragma unroll
+    for (int t = 0; t < 9; ++t)
+#pragma unroll
+      for (int j = 0; j < 8; ++j) acc[t][j] = 0.0f;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) accb[j] = 0.0f;
+    for (unsigned sidx = first; sidx < n_strips; sidx += step) {
+      const unsigned row = sidx / strips_w;                       // n*H + h
+      const int w0 = static_cast<int>(sidx - row * strips_w) * 8;
+      const int hq = static_cast<int>(row % static_cast<unsigned>(H));
+      uint4 q[8];
+      const uint4* dp = dz + (static_cast<size_t>(row) * W + w0) * 4 + g;
+#pragma unroll
+      for (int k = 0; k < 8; ++k) q[k] = __ldg(dp + 4 * k);
+      float xr[3][10];
+#pragma unroll
+      for (int r = 0; r < 3; ++r) {
+        const int hh = hq + r - 1;
+        const bool row_in = hh >= 0 && hh < H;
+        const float* xp = x + (static_cast<size_t>(row + r - 1) * W + w0 - 1) * CIN + ci;
+#pragma unroll
+        for (int c = 0; c < 10; ++c) {
+          const int ww = w0 - 1 + c;
+          xr[r][c] = (row_in && ww >= 0 && ww < W) ? __ldg(xp + c * CIN) : 0.0f;
+        }
+      }
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        float d[8];
+        unpack8(q[k], d);
+        if (ci == 0) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) accb[j] += d[j];
+        }
+#pragma unroll
+        for (int r = 0; r < 3; ++r) {
+#pragma unroll
+          for (int sx = 0; sx < 3; ++sx) {
+            const float xv = xr[r][k + sx];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) acc[r * 3 + sx][j] = fmaf(xv, d[j], acc[r * 3 + sx][j]);
+          }
+        }
+      }
+    }
+#pragma unroll
+    for (int t = 0; t < 9; ++t) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        float v = acc[t][j];
+        v += __shfl_xor_sync(0xffffffffu, v, 16);
+        v += __shfl_xor_sync(0xffffffffu, v, 8);
+        v += __shfl_xor_sync(0xffffffffu, v, 4);
+        if (lane < 4) red[warp][(t * CIN + ci) * 32 + g * 8 + j] = v;
+      }
+    }
+    if (ci == 0) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        float v = accb[j];
+        v += __shfl_xor_sync(0xffffffffu, v, 16);
+        v += __shfl_xor_sync(0xffffffffu, v, 8);
+        v += __shfl_xor_sync(0xffffffffu, v, 4);
+        if (lane < 4) red[warp][9 * CIN * 32 + g * 8 + j] = v;
+      }
+    }
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < kNout; i += blockDim.x) {
+    ws[static_cast<size_t>(blockIdx.x) * kNout + i] = (red[0][i] + red[1][i]) + (red[2][i] + red[3][i]);
   }
 }

@@ -173,6 +173,25 @@ __host__ __device__ __forceinline__ uint32_t umma_idesc_bf16(uint32_t m, uint32_
   return d;
 }
 
+// ---------------------------------------------------------------- 256-bit global accesses (sm_100+, 32-byte aligned)
+// One full 32-byte sector per lane and instruction: half the LSU wavefronts and L2 requests of two 16-byte accesses.
+struct __align__(32) U32x8 {
+  uint32_t v[8];
+};
+__device__ __forceinline__ void st_global_v8(void* p, const U32x8& a) {
+  asm volatile("st.global.v8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(p), "r"(a.v[0]), "r"(a.v[1]),
+               "r"(a.v[2]), "r"(a.v[3]), "r"(a.v[4]), "r"(a.v[5]), "r"(a.v[6]), "r"(a.v[7])
+               : "memory");
+}
+__device__ __forceinline__ U32x8 ld_global_nc_v8(const void* p) {
+  U32x8 a;
+  asm volatile("ld.global.nc.v8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+               : "=r"(a.v[0]), "=r"(a.v[1]), "=r"(a.v[2]), "=r"(a.v[3]), "=r"(a.v[4]), "=r"(a.v[5]), "=r"(a.v[6]),
+                 "=r"(a.v[7])
+               : "l"(p));
+  return a;
+}
+
 // ---------------------------------------------------------------- small helpers
 __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
   __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
