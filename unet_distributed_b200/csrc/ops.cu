@@ -1,6 +1,7 @@
 #include "ops.cuh"
 
 #include <climits>
+#include <cstdlib>
 #include <cstring>
 
 #include "common.h"
@@ -257,7 +258,8 @@ int plan_wgrad(WgradPlan& wp, int N, int H, int W, int taps_r, int taps_s, int p
   }
   const int total_pb = p.blocks_n * p.blocks_h * p.blocks_w;
   const int base = taps_r * taps_s * p.m_tiles * total_nt;
-  int splits = cdiv(2 * device_sm_count(), base);
+  static const int waves = getenv("UNETB200_WGRAD_WAVES") ? atoi(getenv("UNETB200_WGRAD_WAVES")) : 1;
+  int splits = waves == 1 ? device_sm_count() / base : cdiv(waves * device_sm_count(), base);
   const int max_splits = total_pb / 8 > 1 ? total_pb / 8 : 1;
   if (splits > max_splits) splits = max_splits;
   if (splits < 1) splits = 1;

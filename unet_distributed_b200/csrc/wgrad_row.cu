@@ -209,7 +209,10 @@ int wgrad_row_plan(WgradRowParams& p, int N, int H, int W, int Cz, int C0, int C
   }
   const int total_pb = N * p.blocks_h * p.blocks_w;
   const int base = 3 * p.m_tiles * total_nt;
-  int splits = (2 * device_sm_count() + base - 1) / base;
+  // one CTA per SM (216 KB of shared memory): a second wave pays prologue, epilogue and a second set of partials
+  // (measured: 1 wave 1.01 ms, 2 waves 1.13 ms, 3 waves 1.16 ms of wgrad time per step)
+  static const int waves = getenv("UNETB200_ROW_WAVES") ? atoi(getenv("UNETB200_ROW_WAVES")) : 1;
+  int splits = waves == 1 ? device_sm_count() / base : (waves * device_sm_count() + base - 1) / base;
   const int max_splits = total_pb / 8 > 1 ? total_pb / 8 : 1;
   if (splits > max_splits) splits = max_splits;
   if (splits < 1) splits = 1;
