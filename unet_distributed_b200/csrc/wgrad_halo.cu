@@ -26,7 +26,7 @@ namespace {
 constexpr int kThreads = 256;   // warp0 TMA producer, warp1 MMA + TMEM, warps 4..7 epilogue
 constexpr int kMaxStages = 3;
 constexpr int kTH = 16;
-constexpr int kOnesBytes = 4096;   // bf16 1.0 tile: covers every address an A descriptor of this kernel can form from it
+constexpr int kBiasScratch = 4096; // [128 threads][8] fp32: per-thread column sums of dZ before the CTA-level sum
 
 struct WgradHaloParams {
   int N, H, W;
@@ -35,7 +35,7 @@ struct WgradHaloParams {
   int Cx, Cz;               // 32 or 64 each
   int stages;
   float* ws;                // [gridDim.x][9*Cx*Cz (+ Cz)] partial gradients (+ partial bias gradient)
-  int with_bias;            // also reduce dZ over pixels (one extra MMA per K step against a tile of ones)
+  int with_bias;            // also reduce dZ over pixels (the otherwise idle epilogue warps sum the smem tile)
 };
 
 struct __align__(8) WgradHaloBarriers {
@@ -56,8 +56,7 @@ __device__ __forceinline__ uint64_t desc_pair(uint32_t lo, uint32_t hi) {
 // few scalar instructions per MMA; the run-time-generic loop with 64-bit descriptor arithmetic ran at ~75).
 template <int J, int CX, int CZ>
 __device__ __forceinline__ void wgrad_halo_mma_role(WgradHaloBarriers* bars, uint32_t smem_addr, uint32_t stage_bytes,
-                                                    uint32_t halo_stride, int stages, uint32_t tmem_base, int my_tiles,
-                                                    uint32_t ones_addr, bool with_bias) {
+                                                    uint32_t halo_stride, int stages, uint32_t tmem_base, int my_tiles) {
   constexpr int P = 8 * J + 2;
   constexpr uint32_t XROW = CX * 2, ZROW = CZ * 2;
   constexpr int GROUPS = CX == 32 ? 1 : 2;
@@ -69,10 +68,6 @@ __device__ __forceinline__ void wgrad_halo_mma_role(WgradHaloBarriers* bars, uin
       static_cast<uint32_t>(umma_smem_desc(0, 0, 8 * J * ZROW, CZ == 64 ? UMMA_SW_128B : UMMA_SW_64B) >> 32);
   // LBO lives in bits [16,30) of the low word
   const uint32_t x_lo_const = static_cast<uint32_t>(umma_smem_desc(0, XROW, P * XROW, UMMA_SW_NONE) & 0xFFFFFFFFu);
-  // Bias gradient on the tensor core: A = ones (every row of the extra accumulator becomes sum_p dZ[p, co]).
-  // The ones tile is K-major with a single 8-row group stride of 0 ... any layout of a constant tile is the same tile;
-  // it is addressed like an X atom set with zero strides so that the footprint stays inside kOnesBytes.
-  const uint64_t ones_desc = umma_smem_desc(ones_addr, 0, 0, CX == 64 ? UMMA_SW_128B : UMMA_SW_64B);
   int stage = 0;
   uint32_t phase = 0;
   for (int k = 0; k < my_tiles; ++k) {
@@ -98,11 +93,6 @@ __device__ __forceinline__ void wgrad_halo_mma_role(WgradHaloBarriers* bars, uin
                        (i == 0 && j == 0) ? first : 1u);
             }
           }
-          if (with_bias) {
-            umma_f16(tmem_base + static_cast<uint32_t>(3 * GROUPS * CZ), ones_desc,
-                     desc_pair(z_lo + static_cast<uint32_t>((2 * i * 8 * J + 8 * j) * (ZROW >> 4)), z_hi), idesc,
-                     (i == 0 && j == 0) ? first : 1u);
-          }
         }
       }
       umma_commit(&bars->empty[stage]);
@@ -127,8 +117,8 @@ wgrad_halo_kernel(const __grid_constant__ WgradHaloParams p, const __grid_consta
   // 1 KiB of slack after the halo tile: the junk filter column (s = 3) reads up to 3 pixel rows past its end
   const int halo_stride = round_up_1k(halo_bytes + 4 * xrow);
   const int stage_bytes = halo_stride + round_up_1k(z_bytes);
-  uint8_t* ones = smem + p.stages * stage_bytes;
-  WgradHaloBarriers* bars = reinterpret_cast<WgradHaloBarriers*>(ones + kOnesBytes);
+  float* bias_scratch = reinterpret_cast<float*>(smem + p.stages * stage_bytes);
+  WgradHaloBarriers* bars = reinterpret_cast<WgradHaloBarriers*>(smem + p.stages * stage_bytes + kBiasScratch);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -136,7 +126,7 @@ wgrad_halo_kernel(const __grid_constant__ WgradHaloParams p, const __grid_consta
   const int groups = p.Cx == 32 ? 1 : 2;          // stacked filter columns per MMA: 4 (Cx=32) or 2 (Cx=64)
   const int n_acc = 3 * groups;
   uint32_t tmem_cols = 32;
-  while (tmem_cols < static_cast<uint32_t>((n_acc + (p.with_bias ? 1 : 0)) * p.Cz)) tmem_cols <<= 1;
+  while (tmem_cols < static_cast<uint32_t>(n_acc * p.Cz)) tmem_cols <<= 1;
   const int my_tiles = (num_tiles > static_cast<int>(blockIdx.x))
                            ? (num_tiles - static_cast<int>(blockIdx.x) + static_cast<int>(gridDim.x) - 1) /
                                  static_cast<int>(gridDim.x)
@@ -145,7 +135,7 @@ wgrad_halo_kernel(const __grid_constant__ WgradHaloParams p, const __grid_consta
   if (threadIdx.x == 0) {
     for (int s = 0; s < p.stages; ++s) {
       mbar_init(&bars->full[s], 1);
-      mbar_init(&bars->empty[s], 1);
+      mbar_init(&bars->empty[s], p.with_bias ? 5 : 1);   // MMA commit (+ the four column-summing warps)
     }
     mbar_init(&bars->tmem_full, 1);
     mbar_fence_init();
@@ -155,11 +145,6 @@ wgrad_halo_kernel(const __grid_constant__ WgradHaloParams p, const __grid_consta
   if (warp == 1) {
     tmem_alloc(&bars->tmem_base, tmem_cols);
     tmem_relinquish();
-  }
-  if (p.with_bias) {
-    uint32_t* o32 = reinterpret_cast<uint32_t*>(ones);
-    for (int i = threadIdx.x; i < kOnesBytes / 4; i += blockDim.x) o32[i] = 0x3F803F80u;   // two bf16 1.0
-    fence_proxy_async_smem();
   }
   tc_fence_before();
   __syncthreads();
@@ -190,8 +175,7 @@ wgrad_halo_kernel(const __grid_constant__ WgradHaloParams p, const __grid_consta
       const uint32_t sa = smem_u32(smem);
 #define UB_WH(JJ, CX, CZ)                                                                                 \
       wgrad_halo_mma_role<JJ, CX, CZ>(bars, sa, static_cast<uint32_t>(stage_bytes),                       \
-                                      static_cast<uint32_t>(halo_stride), p.stages, tmem_base, my_tiles,      \
-                                      smem_u32(ones), p.with_bias != 0)
+                                      static_cast<uint32_t>(halo_stride), p.stages, tmem_base, my_tiles)
 #define UB_WH_J(CX, CZ)                        \
       do {                                     \
         if (p.J == 4) UB_WH(4, CX, CZ);        \
@@ -215,6 +199,41 @@ wgrad_halo_kernel(const __grid_constant__ WgradHaloParams p, const __grid_consta
     const int ci = m % p.Cx;
     const int n_out = 9 * p.Cx * p.Cz + (p.with_bias ? p.Cz : 0);
     float* out = p.ws + static_cast<size_t>(blockIdx.x) * n_out;
+    if (p.with_bias) {
+      // Bias gradient: while the tensor core works on a stage, these four warps sum its dZ tile over pixels.
+      // Thread t owns the 16-byte channel chunk q = t % chunks of every (128 / chunks)-th pixel row; the TMA swizzle
+      // (64-byte rows: chunk ^= (row >> 1) & 3, 128-byte rows: chunk ^= row & 7) is undone per row.
+      const int t = threadIdx.x - 128;
+      const int chunks = p.Cz >> 3;
+      const int q = t & (chunks - 1);
+      const int rows = kTH * 8 * p.J;
+      float bsum[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) bsum[j] = 0.0f;
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int k = 0; k < my_tiles; ++k) {
+        mbar_wait(&bars->full[stage], phase);
+        const uint8_t* zt = smem + stage * stage_bytes + halo_stride;
+        for (int row = t / chunks; row < rows; row += 128 / chunks) {
+          const int phys = p.Cz == 64 ? (q ^ (row & 7)) : (q ^ ((row >> 1) & 3));
+          const uint4 v = *reinterpret_cast<const uint4*>(zt + row * zrow + phys * 16);
+          bsum[0] += bf16_lo(v.x); bsum[1] += bf16_hi(v.x); bsum[2] += bf16_lo(v.y); bsum[3] += bf16_hi(v.y);
+          bsum[4] += bf16_lo(v.z); bsum[5] += bf16_hi(v.z); bsum[6] += bf16_lo(v.w); bsum[7] += bf16_hi(v.w);
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&bars->empty[stage]);
+        if (++stage == p.stages) { stage = 0; phase ^= 1u; }
+      }
+#pragma unroll
+      for (int j = 0; j < 8; ++j) bias_scratch[t * 8 + j] = bsum[j];
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+      if (t < p.Cz) {   // channel t = chunk (t / 8), element (t % 8): sum the threads that own that chunk in a fixed order
+        float acc = 0.0f;
+        for (int u = t >> 3; u < 128; u += chunks) acc += bias_scratch[u * 8 + (t & 7)];
+        out[9 * p.Cx * p.Cz + t] = acc;
+      }
+    }
     if (my_tiles > 0) {
       mbar_wait(&bars->tmem_full, 0);
       tc_fence_after();
@@ -241,23 +260,6 @@ wgrad_halo_kernel(const __grid_constant__ WgradHaloParams p, const __grid_consta
                                   __uint_as_float(v[4 * q + 2]), __uint_as_float(v[4 * q + 3]));
             }
           }
-        }
-      }
-    }
-    if (p.with_bias && warp == 4) {   // every row of the bias accumulator holds the same sums; lane 0 stores row 0
-      const uint32_t t_row = tmem_base + static_cast<uint32_t>(n_acc * p.Cz);
-      for (int c = 0; c < p.Cz; c += 16) {
-        uint32_t v[16];
-        if (my_tiles > 0) {
-          tmem_ld_32x32b_x16(t_row + static_cast<uint32_t>(c), v);
-          tmem_ld_wait();
-        } else {
-#pragma unroll
-          for (int i = 0; i < 16; ++i) v[i] = 0u;
-        }
-        if (lane == 0) {
-#pragma unroll
-          for (int i = 0; i < 16; ++i) out[9 * p.Cx * p.Cz + c + i] = __uint_as_float(v[i]);
         }
       }
     }
@@ -338,11 +340,11 @@ int wgrad_halo_launch(const CUtensorMap& x_map, const CUtensorMap& z_map, int N,
   p.with_bias = db ? 1 : 0;
   const int P = 8 * J + 2;
   const int stage_bytes = round_up_1k((kTH + 2) * P * Cx * 2 + 4 * Cx * 2) + round_up_1k(kTH * 8 * J * Cz * 2);
-  int stages = (225 * 1024 - 1024 - kOnesBytes - static_cast<int>(sizeof(WgradHaloBarriers))) / stage_bytes;
+  int stages = (225 * 1024 - 1024 - kBiasScratch - static_cast<int>(sizeof(WgradHaloBarriers))) / stage_bytes;
   if (stages > kMaxStages) stages = kMaxStages;
   UB_REQUIRE(stages >= 2, "wgrad_halo: stage of %d bytes does not fit twice in shared memory", stage_bytes);
   p.stages = stages;
-  const size_t smem = static_cast<size_t>(stages) * stage_bytes + kOnesBytes + sizeof(WgradHaloBarriers) + 1024;
+  const size_t smem = static_cast<size_t>(stages) * stage_bytes + kBiasScratch + sizeof(WgradHaloBarriers) + 1024;
   static bool attr_set[64] = {false};
   int dev = 0;
   UB_CHECK_CUDA(cudaGetDevice(&dev));
