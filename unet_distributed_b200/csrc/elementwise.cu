@@ -1,5 +1,7 @@
 #include "elementwise.cuh"
 
+#include <initializer_list>
+
 #include <mutex>
 
 #include "common.h"
@@ -513,32 +515,58 @@ __global__ void pack_tconv_dgrad_kernel(const float* __restrict__ w, __nv_bfloat
   const int c = static_cast<int>(i / (4ll * Cout));
   out[i] = __float2bfloat16(w[(static_cast<long long>(ab) * Cout + o) * Cin + c]);
 }
-__global__ void pack_all_kernel(const PackSeg* __restrict__ segs, int nseg, long long total,
-                                const float* __restrict__ params, uint8_t* __restrict__ arena) {
-  const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
-  if (i >= total) return;
-  int lo = 0, hi = nseg - 1;
-  while (lo < hi) {   // last segment whose start <= i
-    const int mid = (lo + hi + 1) >> 1;
-    if (segs[mid].start <= i) lo = mid; else hi = mid - 1;
+__global__ void __launch_bounds__(256)
+pack_all_kernel(const PackLayer* __restrict__ layers, int nlayers, const float* __restrict__ params,
+                uint8_t* __restrict__ arena) {
+  __shared__ float tile[32][33];
+  int li = 0;
+  while (li + 1 < nlayers && layers[li + 1].tile_start <= static_cast<int>(blockIdx.x)) ++li;   // block-uniform
+  const PackLayer L = layers[li];
+  const int t = static_cast<int>(blockIdx.x) - L.tile_start;
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const float* w = params + L.src;
+  __nv_bfloat16* out_f = reinterpret_cast<__nv_bfloat16*>(arena + L.dst_fwd);
+  __nv_bfloat16* out_d = reinterpret_cast<__nv_bfloat16*>(arena + L.dst_dgrad);
+  if (L.kind == 0) {
+    // master w[tap][ci][co]; fwd out[co][tap][ci] (transposed), dgrad out[ci][T-1-tap][co] (straight)
+    const int tiles_co = L.cout >> 5, tiles_ci = L.cin >> 5;
+    const int co0 = (t % tiles_co) << 5;
+    const int ci0 = ((t / tiles_co) % tiles_ci) << 5;
+    const int tap = t / (tiles_co * tiles_ci);
+#pragma unroll
+    for (int r = 0; r < 4; ++r) {
+      const int ci = ci0 + ty + 8 * r;
+      const float v = w[(static_cast<size_t>(tap) * L.cin + ci) * L.cout + co0 + tx];
+      tile[ty + 8 * r][tx] = v;
+      out_d[(static_cast<size_t>(ci) * L.taps + (L.taps - 1 - tap)) * L.cout + co0 + tx] = __float2bfloat16(v);
+    }
+    __syncthreads();
+#pragma unroll
+    for (int r = 0; r < 4; ++r) {
+      const int co = co0 + ty + 8 * r;
+      out_f[(static_cast<size_t>(co) * L.taps + tap) * L.cin + ci0 + tx] = __float2bfloat16(tile[tx][ty + 8 * r]);
+    }
+  } else {
+    // master w[ab][o][c]; fwd out[ab*Cout + o][c] (straight), dgrad out[c][ab][o] (transposed)
+    const int tiles_c = L.cin >> 5, tiles_o = L.cout >> 5;
+    const int c0 = (t % tiles_c) << 5;
+    const int o0 = ((t / tiles_c) % tiles_o) << 5;
+    const int ab = t / (tiles_c * tiles_o);
+#pragma unroll
+    for (int r = 0; r < 4; ++r) {
+      const int o = o0 + ty + 8 * r;
+      const size_t idx = (static_cast<size_t>(ab) * L.cout + o) * L.cin + c0 + tx;
+      const float v = w[idx];
+      tile[ty + 8 * r][tx] = v;
+      out_f[idx] = __float2bfloat16(v);
+    }
+    __syncthreads();
+#pragma unroll
+    for (int r = 0; r < 4; ++r) {
+      const int c = c0 + ty + 8 * r;
+      out_d[(static_cast<size_t>(c) * 4 + ab) * L.cout + o0 + tx] = __float2bfloat16(tile[tx][ty + 8 * r]);
+    }
   }
-  const PackSeg sg = segs[lo];
-  const unsigned e = static_cast<unsigned>(i - sg.start);
-  const unsigned taps = sg.taps, cin = sg.cin, cout = sg.cout;
-  unsigned src;
-  if (sg.kind == 0) {          // out[co][tap][ci] = w[tap][ci][co]
-    const unsigned ci = e % cin, tap = (e / cin) % taps, co = e / (cin * taps);
-    src = (tap * cin + ci) * cout + co;
-  } else if (sg.kind == 1) {   // out[ci][tap][co] = w[T-1-tap][ci][co]
-    const unsigned co = e % cout, tap = (e / cout) % taps, ci = e / (cout * taps);
-    src = ((taps - 1 - tap) * cin + ci) * cout + co;
-  } else if (sg.kind == 2) {   // out[(ab*Cout+o)][c] = w[ab][o][c]
-    src = e;
-  } else {                     // out[c][ab][o] = w[ab][o][c]
-    const unsigned o = e % cout, ab = (e / cout) % 4u, c = e / (4u * cout);
-    src = (ab * cout + o) * cin + c;
-  }
-  reinterpret_cast<__nv_bfloat16*>(arena + sg.dst)[e] = __float2bfloat16(params[sg.src + src]);
 }
 
 __global__ void cast_f32_bf16_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ y, long long n) {
@@ -629,6 +657,7 @@ __global__ void dropout_mask_kernel(unsigned char* __restrict__ keep, long long 
 }
 
 #include "level0.cuh"
+#include "pool.cuh"
 
 int check_groups(int C, const char* what) {
   const int groups = C / 8;
@@ -713,8 +742,25 @@ int conv_first_wgrad(const float* x, const void* dz, float* dw, float* db, float
   return UB_OK;
 }
 
+// The 16-channel / 256-bit kernels (pool.cuh) apply when every tensor is 32-byte aligned, C % 16 == 0 and the fine
+// tensor has fewer than 2^32 32-byte units.
+static bool v8_ok(int C, long long fine_pixels, std::initializer_list<const void*> ptrs) {
+  if (C % 16 != 0 || fine_pixels * (C / 16) >= (1ll << 32)) return false;
+  for (const void* p : ptrs) {
+    if (reinterpret_cast<uintptr_t>(p) % 32 != 0) return false;
+  }
+  return true;
+}
+
 int maxpool2x2_fwd(const void* x, void* y, int N, int H, int W, int C, cudaStream_t s) {
   UB_REQUIRE(C % 8 == 0 && H % 2 == 0 && W % 2 == 0, "maxpool2x2_fwd: shape %dx%dx%d unsupported", H, W, C);
+  if (v8_ok(C, static_cast<long long>(N) * H * W, {x, y})) {
+    const unsigned groups = C / 16, total16 = static_cast<unsigned>(N) * (H / 2) * (W / 2) * groups;
+    maxpool_fwd_v8_kernel<<<grid_for(total16, 256), 256, 0, s>>>(reinterpret_cast<const U32x8*>(x),
+                                                                 reinterpret_cast<U32x8*>(y), total16, groups, W / 2, H / 2);
+    UB_CHECK_CUDA(cudaGetLastError());
+    return UB_OK;
+  }
   const long long total = static_cast<long long>(N) * (H / 2) * (W / 2) * (C / 8);
   maxpool_fwd_kernel<<<grid_for(total, kThreads), kThreads, 0, s>>>(reinterpret_cast<const uint4*>(x),
                                                                     reinterpret_cast<uint4*>(y), N, H, W, C);
@@ -725,6 +771,14 @@ int maxpool2x2_fwd(const void* x, void* y, int N, int H, int W, int C, cudaStrea
 int maxpool2x2_bwd(const void* x, const void* dpool, const void* skip_grad, void* dz_full, int N, int H, int W, int C,
                    cudaStream_t s) {
   UB_REQUIRE(C % 8 == 0 && H % 2 == 0 && W % 2 == 0, "maxpool2x2_bwd: shape %dx%dx%d unsupported", H, W, C);
+  if (v8_ok(C, static_cast<long long>(N) * H * W, {x, dpool, skip_grad, dz_full})) {
+    const unsigned groups = C / 16, total16 = static_cast<unsigned>(N) * (H / 2) * (W / 2) * groups;
+    maxpool_bwd_v8_kernel<<<grid_for(total16, 256), 256, 0, s>>>(
+        reinterpret_cast<const U32x8*>(x), reinterpret_cast<const U32x8*>(dpool),
+        reinterpret_cast<const U32x8*>(skip_grad), reinterpret_cast<U32x8*>(dz_full), total16, groups, W / 2, H / 2);
+    UB_CHECK_CUDA(cudaGetLastError());
+    return UB_OK;
+  }
   const long long total = static_cast<long long>(N) * (H / 2) * (W / 2) * (C / 8);
   maxpool_bwd_kernel<<<grid_for(total, kThreads), kThreads, 0, s>>>(
       reinterpret_cast<const uint4*>(x), reinterpret_cast<const uint4*>(dpool),
@@ -735,6 +789,13 @@ int maxpool2x2_bwd(const void* x, const void* dpool, const void* skip_grad, void
 
 int upsample2x2_fwd(const void* x, void* y, int N, int H, int W, int C, cudaStream_t s) {
   UB_REQUIRE(C % 8 == 0, "upsample2x2_fwd: C %d", C);
+  if (v8_ok(C, static_cast<long long>(N) * 4 * H * W, {x, y})) {
+    const unsigned groups = C / 16, total16 = static_cast<unsigned>(N) * H * W * groups;
+    upsample_fwd_v8_kernel<<<grid_for(total16, 256), 256, 0, s>>>(reinterpret_cast<const U32x8*>(x),
+                                                                  reinterpret_cast<U32x8*>(y), total16, groups, W, H);
+    UB_CHECK_CUDA(cudaGetLastError());
+    return UB_OK;
+  }
   const long long total = static_cast<long long>(N) * (2 * H) * (2 * W) * (C / 8);
   upsample_fwd_kernel<<<grid_for(total, kThreads), kThreads, 0, s>>>(reinterpret_cast<const uint4*>(x),
                                                                      reinterpret_cast<uint4*>(y), N, H, W, C);
@@ -744,6 +805,14 @@ int upsample2x2_fwd(const void* x, void* y, int N, int H, int W, int C, cudaStre
 
 int upsample2x2_bwd(const void* dy, const void* x, void* dx, int N, int H, int W, int C, int relu_mask, cudaStream_t s) {
   UB_REQUIRE(C % 8 == 0, "upsample2x2_bwd: C %d", C);
+  if (v8_ok(C, static_cast<long long>(N) * 4 * H * W, {dy, x, dx})) {
+    const unsigned groups = C / 16, total16 = static_cast<unsigned>(N) * H * W * groups;
+    upsample_bwd_v8_kernel<<<grid_for(total16, 256), 256, 0, s>>>(
+        reinterpret_cast<const U32x8*>(dy), reinterpret_cast<const U32x8*>(x), reinterpret_cast<U32x8*>(dx), total16,
+        groups, W, H, relu_mask);
+    UB_CHECK_CUDA(cudaGetLastError());
+    return UB_OK;
+  }
   const long long total = static_cast<long long>(N) * H * W * (C / 8);
   upsample_bwd_kernel<<<grid_for(total, kThreads), kThreads, 0, s>>>(
       reinterpret_cast<const uint4*>(dy), reinterpret_cast<const uint4*>(x), reinterpret_cast<uint4*>(dx), N, H, W, C,
@@ -870,10 +939,11 @@ int colsum_bf16_static(const void* dz, float* db, long long P, int C, cudaStream
   return UB_OK;
 }
 
-int pack_all(const PackSeg* segs_dev, int nseg, long long total, const float* params, void* arena, cudaStream_t s) {
-  if (nseg <= 0 || total <= 0) return UB_OK;
-  pack_all_kernel<<<grid_for(total, kThreads), kThreads, 0, s>>>(segs_dev, nseg, total, params,
-                                                                 reinterpret_cast<uint8_t*>(arena));
+int pack_all(const PackLayer* layers_dev, int nlayers, int total_tiles, const float* params, void* arena,
+             cudaStream_t s) {
+  if (nlayers <= 0 || total_tiles <= 0) return UB_OK;
+  pack_all_kernel<<<static_cast<unsigned>(total_tiles), 256, 0, s>>>(layers_dev, nlayers, params,
+                                                                     reinterpret_cast<uint8_t*>(arena));
   UB_CHECK_CUDA(cudaGetLastError());
   return UB_OK;
 }

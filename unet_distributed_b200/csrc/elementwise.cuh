@@ -55,15 +55,19 @@ int pack_conv_dgrad(const float* w, void* out, int taps, int Cin, int Cout, cuda
 int pack_tconv_fwd(const float* w, void* out, int Cin, int Cout, cudaStream_t s);
 int pack_tconv_dgrad(const float* w, void* out, int Cin, int Cout, cudaStream_t s);
 
-// All repacks of a network in one launch: a device table of segments, one thread per packed element.
-struct PackSeg {
-  long long start;   // first packed-element index of this segment (segments are sorted by start)
-  long long src;     // float offset of the TF-layout master inside the flat parameter buffer
-  long long dst;     // byte offset of the packed bf16 operand inside the arena
-  int kind;          // 0 conv fwd, 1 conv dgrad, 2 tconv fwd, 3 tconv dgrad
-  int taps, cin, cout;
+// All repacks of a network in one launch. A block owns one 32 x 32 tile of one tap of one layer: it reads the fp32
+// master once (coalesced), writes the operand whose layout matches the master's straight away and the transposed
+// one through shared memory, so both global sides move 64-128 contiguous bytes per warp row.
+struct PackLayer {
+  long long src;        // float offset of the TF-layout master inside the flat parameter buffer
+  long long dst_fwd;    // byte offsets of the packed bf16 operands inside the arena
+  long long dst_dgrad;
+  int kind;             // 0 conv3x3 (w[tap][ci][co]), 1 transposed conv (w[ab][o][c])
+  int taps, cin, cout;  // multiples of 32 channels
+  int tile_start;       // first block of this layer (layers sorted by tile_start)
 };
-int pack_all(const PackSeg* segs_dev, int nseg, long long total, const float* params, void* arena, cudaStream_t s);
+int pack_all(const PackLayer* layers_dev, int nlayers, int total_tiles, const float* params, void* arena,
+             cudaStream_t s);
 
 // TF-1.4 AdamOptimizer on a flat fp32 buffer. step_ptr holds the number of updates applied so far (device int64).
 //   lr = const_lr ? lr0 : lr0 * lr_fraction^(step/decay_steps);  t = step+1

@@ -55,8 +55,8 @@ struct unetb200_plan {
   // where nothing consumes them (the consumer then reads the activation tensor itself)
   size_t gt_a[5], gt_c[5], gt_da[4], gt_dc[4];
   size_t preds, sums, metrics, ws;
-  std::vector<PackSeg> pack_segs;
-  long long pack_total = 0;
+  std::vector<PackLayer> pack_layers;
+  int pack_tiles = 0;
   size_t pack_table = 0;
   size_t ws_bytes = 0;
   int ch[5];
@@ -222,24 +222,22 @@ int unetb200_plan_create(unetb200_plan** out, int N, int H, int W, int in_channe
   P->ws_bytes = ws;
   P->ws = P->bump(ws);
   // ---- one table for all weight repacks (uploaded at bind time, walked by a single kernel)
-  long long start = 0;
+  int tile = 0;
   for (const auto& l : P->layers) {
     if (l.kind == 2 || l.cin < 32) continue;
-    const int taps = l.kind == 0 ? 9 : 4;
-    const long long count = static_cast<long long>(taps) * l.cin * l.cout;
-    for (int d = 0; d < 2; ++d) {
-      PackSeg sg;
-      sg.start = start;
-      sg.src = l.w_off;
-      sg.dst = static_cast<long long>(d == 0 ? l.pk_fwd : l.pk_dgrad);
-      sg.kind = (l.kind == 0 ? 0 : 2) + d;
-      sg.taps = taps; sg.cin = l.cin; sg.cout = l.cout;
-      P->pack_segs.push_back(sg);
-      start += count;
-    }
+    PackLayer pl;
+    pl.src = l.w_off;
+    pl.dst_fwd = static_cast<long long>(l.pk_fwd);
+    pl.dst_dgrad = static_cast<long long>(l.pk_dgrad);
+    pl.kind = l.kind;
+    pl.taps = l.kind == 0 ? 9 : 4;
+    pl.cin = l.cin; pl.cout = l.cout;
+    pl.tile_start = tile;
+    P->pack_layers.push_back(pl);
+    tile += pl.taps * (l.cin / 32) * (l.cout / 32);
   }
-  P->pack_total = start;
-  P->pack_table = P->bump(P->pack_segs.size() * sizeof(PackSeg));
+  P->pack_tiles = tile;
+  P->pack_table = P->bump(P->pack_layers.size() * sizeof(PackLayer));
   *out = P;
   return UB_OK;
 }
@@ -274,7 +272,7 @@ int unetb200_plan_bind(unetb200_plan* P, void* arena, float* params, float* grad
   P->params = params;
   P->grads = grads;
   // the repack table lives in the arena; binding is a set-up call, so a synchronous copy is fine here
-  UB_CHECK_CUDA(cudaMemcpy(P->at(P->pack_table), P->pack_segs.data(), P->pack_segs.size() * sizeof(PackSeg),
+  UB_CHECK_CUDA(cudaMemcpy(P->at(P->pack_table), P->pack_layers.data(), P->pack_layers.size() * sizeof(PackLayer),
                            cudaMemcpyHostToDevice));
   return UB_OK;
 }
@@ -325,8 +323,8 @@ int unetb200_plan_tensor(const unetb200_plan* P, const char* name, long long* of
 int unetb200_plan_pack_weights(unetb200_plan* P, void* stream) {
   UB_REQUIRE(P->arena, "plan_pack_weights: plan is not bound");
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
-  return pack_all(reinterpret_cast<const PackSeg*>(P->at(P->pack_table)), static_cast<int>(P->pack_segs.size()),
-                  P->pack_total, P->params, P->arena, s);
+  return pack_all(reinterpret_cast<const PackLayer*>(P->at(P->pack_table)), static_cast<int>(P->pack_layers.size()),
+                  P->pack_tiles, P->params, P->arena, s);
 }
 
 // Forward pass (model.py:45-120) + dice metrics (model.py:4-21,133-143) when msks != NULL.
