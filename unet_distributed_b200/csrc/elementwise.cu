@@ -832,7 +832,7 @@ int head_fwd(const void* x, const float* w, const float* b, const float* y_true,
   UB_REQUIRE(n_cl >= 1 && n_cl <= kMaxCl, "head_fwd: n_cl_out %d outside 1..%d", n_cl, kMaxCl);
   const int subs = C / 8;
   UB_REQUIRE(C % 8 == 0 && subs >= 1 && subs <= 32 && (subs & (subs - 1)) == 0, "head_fwd: C %d unsupported", C);
-  if (C == 32 && P < (1ll << 31)) {   // thread-per-pixel fast path (the network's Mask layer)
+  if (C == 32 && P < (1ll << 31) && reinterpret_cast<uintptr_t>(x) % 32 == 0) {   // thread-per-pixel fast path (the network's Mask layer)
     const uint4* xv = reinterpret_cast<const uint4*>(x);
     const unsigned Pu = static_cast<unsigned>(P);
     switch (n_cl) {
@@ -864,7 +864,8 @@ int head_bwd(const void* x, const float* w, const float* y_true, const float* p,
   const int subs = C / 8;
   UB_REQUIRE(C % 8 == 0 && subs >= 1 && subs <= 32 && (subs & (subs - 1)) == 0, "head_bwd: C %d unsupported", C);
   const int nout = C * n_cl + n_cl;
-  if (C == 32 && n_cl == 1 && P < (1ll << 31)) {   // thread-per-pixel fast path
+  if (C == 32 && n_cl == 1 && P < (1ll << 31) && reinterpret_cast<uintptr_t>(x) % 32 == 0 &&
+      reinterpret_cast<uintptr_t>(dx) % 32 == 0) {   // thread-per-pixel fast path
     head32_bwd_kernel<<<kRedBlocks, kThreads, 0, s>>>(reinterpret_cast<const uint4*>(x), w, y_true, p, sums, smooth,
                                                       grad_scale, reinterpret_cast<uint4*>(dx), ws,
                                                       static_cast<unsigned>(P));

@@ -91,22 +91,12 @@ head32_fwd_kernel(const uint4* __restrict__ x, const float* __restrict__ w, cons
   const unsigned stride = gridDim.x * blockDim.x;
   for (unsigned pix = blockIdx.x * blockDim.x + threadIdx.x; pix < P; pix += stride) {
     const uint4* xp = x + static_cast<size_t>(pix) * 4;
-    const uint4 v0 = __ldg(xp), v1 = __ldg(xp + 1), v2 = __ldg(xp + 2), v3 = __ldg(xp + 3);
+    const U32x8 v0 = ld_global_nc_v8(xp), v1 = ld_global_nc_v8(xp + 2);   // 64 bytes per pixel, two sector loads
     float f[32];
-    {
-      float t8[8];
-      unpack8(v0, t8);
 #pragma unroll
-      for (int j = 0; j < 8; ++j) f[j] = t8[j];
-      unpack8(v1, t8);
-#pragma unroll
-      for (int j = 0; j < 8; ++j) f[8 + j] = t8[j];
-      unpack8(v2, t8);
-#pragma unroll
-      for (int j = 0; j < 8; ++j) f[16 + j] = t8[j];
-      unpack8(v3, t8);
-#pragma unroll
-      for (int j = 0; j < 8; ++j) f[24 + j] = t8[j];
+    for (int j = 0; j < 8; ++j) {
+      f[2 * j] = bf16_lo(v0.v[j]); f[2 * j + 1] = bf16_hi(v0.v[j]);
+      f[16 + 2 * j] = bf16_lo(v1.v[j]); f[16 + 2 * j + 1] = bf16_hi(v1.v[j]);
     }
 #pragma unroll
     for (int k = 0; k < NCL; ++k) {
@@ -156,22 +146,24 @@ head32_bwd_kernel(const uint4* __restrict__ x, const float* __restrict__ w, cons
   const unsigned stride = gridDim.x * blockDim.x;
   for (unsigned pix = blockIdx.x * blockDim.x + threadIdx.x; pix < P; pix += stride) {
     const uint4* xp = x + static_cast<size_t>(pix) * 4;
-    const uint4 v[4] = {__ldg(xp), __ldg(xp + 1), __ldg(xp + 2), __ldg(xp + 3)};
+    const U32x8 v[2] = {ld_global_nc_v8(xp), ld_global_nc_v8(xp + 2)};
     const float pv = __ldg(p + pix);
     const float yt = __ldg(y_true + pix);
     const float dl = (ca * yt + cb) * pv * (1.0f - pv) * grad_scale;
     adb += dl;
     uint4* dp = dx + static_cast<size_t>(pix) * 4;
 #pragma unroll
-    for (int q = 0; q < 4; ++q) {
-      float f[8], o[8];
-      unpack8(v[q], f);
+    for (int q = 0; q < 2; ++q) {
+      U32x8 o;
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
-        adw[8 * q + j] = fmaf(f[j], dl, adw[8 * q + j]);
-        o[j] = f[j] > 0.0f ? dl * sw[8 * q + j] : 0.0f;
+        const float f0 = bf16_lo(v[q].v[j]), f1 = bf16_hi(v[q].v[j]);
+        const int c = 16 * q + 2 * j;
+        adw[c] = fmaf(f0, dl, adw[c]);
+        adw[c + 1] = fmaf(f1, dl, adw[c + 1]);
+        o.v[j] = pack_bf16x2(f0 > 0.0f ? dl * sw[c] : 0.0f, f1 > 0.0f ? dl * sw[c + 1] : 0.0f);
       }
-      dp[q] = pack8(o);
+      st_global_v8(dp + 2 * q, o);
     }
   }
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;

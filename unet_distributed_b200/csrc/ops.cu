@@ -290,7 +290,7 @@ size_t conv3x3_wgrad_ws_bytes(int N, int H, int W, int Cin_total, int Cout, bool
     WgradRowParams rp;
     std::memset(&rp, 0, sizeof(rp));
     wgrad_row_plan(rp, N, H, W, Cout, Cin_total, 0);
-    if (rp.splits > 1) row = static_cast<size_t>(rp.splits) * wp.nweights * sizeof(float);
+    if (rp.splits > 1) row = static_cast<size_t>(rp.splits) * (wp.nweights + (with_bias ? Cout : 0)) * sizeof(float);
   }
   size_t need = generic > halo ? generic : halo;
   if (row > need) need = row;
@@ -341,14 +341,20 @@ int conv3x3_wgrad(const void* dz, int Cout, ConvSrc x0, ConvSrc x1, float* dw, v
     const long long nweights = 9 * cin * Cout;
     rp.out_tap_stride = cin * Cout;
     rp.out_n_stride = Cout;
-    rp.out_split_stride = nweights;
+    // with a bias gradient every split's partial is [nweights | Cout]: one reduction produces dw and db
+    const long long per_split = nweights + (db ? Cout : 0);
+    rp.out_split_stride = per_split;
     if (rp.splits > 1) {
-      const size_t need = static_cast<size_t>(rp.splits) * nweights * sizeof(float);
+      const size_t need = static_cast<size_t>(rp.splits) * per_split * sizeof(float);
       UB_REQUIRE(ws != nullptr && ws_bytes >= need, "conv3x3_wgrad: workspace of %zu bytes needed, %zu given", need,
                  ws_bytes);
       rp.out = reinterpret_cast<float*>(ws);
+      rp.bias_out = db ? rp.out + nweights : nullptr;
+      rp.bias_split_stride = per_split;
     } else {
       rp.out = dw;
+      rp.bias_out = db;
+      rp.bias_split_stride = 0;
     }
     CUtensorMap zm, xm0, xm1;
     rc = nhwc_map(&zm, dz, N, H, W, Cout, 64, Box{1, 8, 8});
@@ -363,10 +369,10 @@ int conv3x3_wgrad(const void* dz, int Cout, ConvSrc x0, ConvSrc x1, float* dw, v
     rc = wgrad_row_launch(rp, zm, xm0, xm1, s);
     if (rc) return rc;
     if (rp.splits > 1) {
-      rc = splitk_reduce_launch(rp.out, nweights, rp.splits, dw, nweights, s);
+      rc = splitk_reduce_launch(rp.out, per_split, rp.splits, dw, per_split, s, db, nweights);
       if (rc) return rc;
     }
-    return db ? bias_grad_after(dz, Cout, db, ws, ws_bytes, N, H, W, s) : UB_OK;
+    return UB_OK;
   }
   WgradPlan wp;
   int rc = plan_wgrad(wp, N, H, W, 3, 3, 1, Cout, x0.C, C1);

@@ -193,12 +193,13 @@ wgrad_kernel(const __grid_constant__ WgradParams p, const __grid_constant__ CUte
 }
 
 __global__ void splitk_reduce_kernel(const float* __restrict__ ws, long long split_stride, int splits,
-                                     float* __restrict__ out, long long n) {
+                                     float* __restrict__ out, long long n, float* __restrict__ out_b, long long n_a) {
   const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
   if (i >= n) return;
   float acc = 0.0f;
   for (int s = 0; s < splits; ++s) acc += ws[s * split_stride + i];
-  out[i] = acc;
+  if (out_b && i >= n_a) out_b[i - n_a] = acc;
+  else out[i] = acc;
 }
 
 }  // namespace
@@ -238,11 +239,11 @@ int wgrad_launch(const WgradParams& p, const CUtensorMap& z, const CUtensorMap& 
 }
 
 int splitk_reduce_launch(const float* ws, long long split_stride, int splits, float* out, long long n,
-                         cudaStream_t stream) {
+                         cudaStream_t stream, float* out_b, long long n_a) {
   if (n <= 0) return UB_OK;
   const int threads = 256;
   const long long blocks = (n + threads - 1) / threads;
-  splitk_reduce_kernel<<<static_cast<unsigned>(blocks), threads, 0, stream>>>(ws, split_stride, splits, out, n);
+  splitk_reduce_kernel<<<static_cast<unsigned>(blocks), threads, 0, stream>>>(ws, split_stride, splits, out, n, out_b, n_a);
   UB_CHECK_CUDA(cudaGetLastError());
   return UB_OK;
 }

@@ -55,14 +55,16 @@ struct WgradRowParams {
   int stages;
   float* out;
   long long out_split_stride, out_tap_stride, out_n_stride;   // output channel (M) stride is 1
+  float* bias_out;          // optional: bias_out[split * bias_split_stride + co] = sum of dZ over the split's pixels
+  long long bias_split_stride;
 };
 bool wgrad_row_supported(int H, int W, int Cz, int C0, int C1);
 int wgrad_row_plan(WgradRowParams& p, int N, int H, int W, int Cz, int C0, int C1);
 int wgrad_row_launch(const WgradRowParams& p, const CUtensorMap& z, const CUtensorMap& x0, const CUtensorMap& x1,
                      cudaStream_t stream);
 
-// out[i] = sum_s ws[s*stride + i] (fixed order), i < n.
+// out[i] = sum_s ws[s*stride + i] (fixed order), i < n; outputs [n_a, n) go to out_b[i - n_a] when out_b is given.
 int splitk_reduce_launch(const float* ws, long long split_stride, int splits, float* out, long long n,
-                         cudaStream_t stream);
+                         cudaStream_t stream, float* out_b = nullptr, long long n_a = 0);
 
 }  // namespace ub

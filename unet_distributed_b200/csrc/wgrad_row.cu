@@ -22,6 +22,7 @@ constexpr int kMaxStages = 6;
 constexpr int kZBytes = 2 * 64 * 128;         // two 64-channel atoms x 64 pixels
 constexpr int kXAtomBytes = 8 * 10 * 128;     // one 64-channel atom x (8 rows x 10 columns)
 constexpr int kStageBytes = kZBytes + 2 * kXAtomBytes;   // 36,864
+constexpr int kBiasScratch = 4096;            // [128 threads][8] fp32 column sums of dZ
 
 struct __align__(8) RowBarriers {
   uint64_t full[kMaxStages];
@@ -36,7 +37,8 @@ wgrad_row_kernel(const __grid_constant__ WgradRowParams p, const __grid_constant
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw_addr = smem_u32(smem_raw);
   uint8_t* smem = smem_raw + ((1024u - (raw_addr & 1023u)) & 1023u);
-  RowBarriers* bars = reinterpret_cast<RowBarriers*>(smem + p.stages * kStageBytes);
+  float* bias_scratch = reinterpret_cast<float*>(smem + p.stages * kStageBytes);
+  RowBarriers* bars = reinterpret_cast<RowBarriers*>(smem + p.stages * kStageBytes + kBiasScratch);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -64,11 +66,13 @@ wgrad_row_kernel(const __grid_constant__ WgradRowParams p, const __grid_constant
   if (m_atoms > 2) m_atoms = 2;
   const int n_atoms = block_n / 64;
   const uint32_t tmem_cols = 512;   // three accumulators of up to 128 columns
+  // one CTA per (Cout tile, pixel split) also sums its dZ tiles over pixels: the bias gradient
+  const bool do_bias = p.bias_out != nullptr && ntg == 0 && r == 0;
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < p.stages; ++s) {
       mbar_init(&bars->full[s], 1);
-      mbar_init(&bars->empty[s], 1);
+      mbar_init(&bars->empty[s], do_bias ? 5 : 1);   // MMA commit (+ the four column-summing warps)
     }
     mbar_init(&bars->tmem_full, 1);
     mbar_fence_init();
@@ -142,6 +146,45 @@ wgrad_row_kernel(const __grid_constant__ WgradRowParams p, const __grid_constant
       }
     }
   } else {
+    if (do_bias) {
+      // While the tensor core works on a stage, warps 2..5 sum its dZ tile (2 atoms x 64 pixels x 128 B, 128-byte
+      // swizzle: chunk ^= pixel & 7) over pixels. Thread t: atom t/64, 16-byte chunk t%8, pixels (t/8)%8 + 8k.
+      const int t = threadIdx.x - 64;
+      const int atom = t >> 6, q = t & 7, rg = (t >> 3) & 7;
+      float bsum[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) bsum[j] = 0.0f;
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int kb = 0; kb < nkb; ++kb) {
+        mbar_wait(&bars->full[stage], phase);
+        if (atom < m_atoms) {
+          const uint8_t* zt = smem + stage * kStageBytes + atom * (kZBytes / 2);
+#pragma unroll
+          for (int k = 0; k < 8; ++k) {
+            const int px = rg + 8 * k;
+            const uint4 v = *reinterpret_cast<const uint4*>(zt + px * 128 + ((q ^ (px & 7)) << 4));
+            bsum[0] += bf16_lo(v.x); bsum[1] += bf16_hi(v.x); bsum[2] += bf16_lo(v.y); bsum[3] += bf16_hi(v.y);
+            bsum[4] += bf16_lo(v.z); bsum[5] += bf16_hi(v.z); bsum[6] += bf16_lo(v.w); bsum[7] += bf16_hi(v.w);
+          }
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&bars->empty[stage]);
+        if (++stage == p.stages) { stage = 0; phase ^= 1u; }
+      }
+#pragma unroll
+      for (int j = 0; j < 8; ++j) bias_scratch[t * 8 + j] = bsum[j];
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+      // channel c of the tile: atom c/64, chunk (c%64)/8, element c%8; its eight row-group threads in a fixed order
+      const int c = t;
+      if (m0 + c < p.z_C) {
+        const int u0 = (c >> 6) * 64 + ((c & 63) >> 3);
+        float acc = 0.0f;
+#pragma unroll
+        for (int g = 0; g < 8; ++g) acc += bias_scratch[(u0 + 8 * g) * 8 + (c & 7)];
+        p.bias_out[split * p.bias_split_stride + m0 + c] = acc;
+      }
+    }
     const int quarter = warp & 3;
     const int row = quarter * 32 + lane;
     const int co = m0 + row;
@@ -224,7 +267,7 @@ int wgrad_row_plan(WgradRowParams& p, int N, int H, int W, int Cz, int C0, int C
 
 int wgrad_row_launch(const WgradRowParams& p, const CUtensorMap& z, const CUtensorMap& x0, const CUtensorMap& x1,
                      cudaStream_t stream) {
-  const size_t smem = static_cast<size_t>(p.stages) * kStageBytes + sizeof(RowBarriers) + 1024;
+  const size_t smem = static_cast<size_t>(p.stages) * kStageBytes + kBiasScratch + sizeof(RowBarriers) + 1024;
   static bool attr_set[64] = {false};
   int dev = 0;
   UB_CHECK_CUDA(cudaGetDevice(&dev));
