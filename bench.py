@@ -237,6 +237,9 @@ def run_b200(args):
     roof = None
     if tr.use_cuda_graph:
         tr.use_cuda_graph = False
+    # kernels are timed one at a time: in the timed region above the weight gradients share the GPU with the dgrad
+    # chain (second stream), which would charge each kernel for the time it waits for SMs
+    tr.plan.side_stream(False)
     for i in range(2):
         tr.train_step(*d_batches[i % nb])
     torch.cuda.synchronize()
@@ -250,6 +253,7 @@ def run_b200(args):
     ln = (ctypes.c_longlong * 3)()
     _lib.check(L.unetb200_profile_collect(ms, fl, by, ln), "profile_collect")
     L.unetb200_profile_enable(0)
+    tr.plan.side_stream(True)
     roof = {"igemm": (ms[0], fl[0], by[0], ln[0]), "wgrad": (ms[1], fl[1], by[1], ln[1]), "steps": psteps}
     barrier()
 

@@ -167,6 +167,11 @@ int unetb200_plan_forward(unetb200_plan* plan, const float* imgs, const float* m
 int unetb200_plan_backward(unetb200_plan* plan, const float* imgs, const float* msks, const float* dpreds,
                            float grad_scale, int segment, void* stream);
 int unetb200_plan_bucket(const unetb200_plan* plan, int segment, long long* begin, long long* end);
+/* The weight gradients of plan_backward run on a second, plan-owned stream that is forked from and joined back into
+ * the caller's stream inside every segment (so the call stays stream-ordered and capturable). enable = 0 keeps all
+ * kernels on the caller's stream in program order (used when timing kernels one at a time); returns the old setting.
+ * No reference counterpart: TensorFlow's executor schedules independent ops concurrently on its own. */
+int unetb200_plan_side_stream(unetb200_plan* plan, int enable);
 
 #ifdef __cplusplus
 }

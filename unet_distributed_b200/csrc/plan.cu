@@ -1,6 +1,7 @@
 // UNet step plan: the layer graph of model.py:36-130 as a fixed launch sequence over one caller-owned arena.
 // The plan owns no device memory: the caller asks for the arena size, allocates it (PyTorch does) and binds it together
 // with the flat fp32 parameter / gradient buffers whose layout (TensorFlow variable order and shapes) the plan reports.
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -54,11 +55,19 @@ struct unetb200_plan {
   // ReLU gates of the activations the backward pass masks by, one bit per element (uint16 per 16 channels); kNoGate
   // where nothing consumes them (the consumer then reads the activation tensor itself)
   size_t gt_a[5], gt_c[5], gt_da[4], gt_dc[4];
-  size_t preds, sums, metrics, ws;
+  size_t preds, sums, metrics, ws, ws_side;
   std::vector<PackLayer> pack_layers;
   int pack_tiles = 0;
   size_t pack_table = 0;
-  size_t ws_bytes = 0;
+  size_t ws_bytes = 0;        // main-stream workspace (head, dice)
+  size_t ws_side_bytes = 0;   // weight-gradient workspace (side stream)
+  // Weight gradients run on a second stream, forked from / joined to the caller's stream with events: they depend
+  // only on tensors the main chain (dgrads, pooling) has already produced, so their CTAs fill the SMs that the tail
+  // of a persistent dgrad kernel leaves idle, and vice versa. UNETB200_NO_SIDE_STREAM=1 keeps everything in order.
+  cudaStream_t side = nullptr;
+  cudaEvent_t ev[40];
+  int n_ev = 0, ev_next = 0;
+  bool use_side = true;
   int ch[5];
   int c4_out;      // channels of c[4] (conv5b)
   int dc_out[4];   // channels of dc[L] (conv{9-L}b)
@@ -201,7 +210,9 @@ int unetb200_plan_create(unetb200_plan** out, int N, int H, int W, int in_channe
   P->sums = P->bump(64);
   P->metrics = P->bump(64);
   // ---- workspace: the largest any single op asks for (ops are serialised on one stream)
-  size_t ws = max_sz(unetb200_head_ws_bytes(pixels, 32, n_cl_out), unetb200_conv_first_wgrad_ws_bytes(in_channels, 32));
+  P->ws_bytes = unetb200_head_ws_bytes(pixels, 32, n_cl_out);
+  P->ws = P->bump(P->ws_bytes);
+  size_t ws = unetb200_conv_first_wgrad_ws_bytes(in_channels, 32);
   for (int L = 0; L < 5; ++L) {
     ws = max_sz(ws, unetb200_bias_grad_ws_bytes(P->ch[L]));
     const auto& la = P->layers[P->enc_a[L]];
@@ -219,8 +230,8 @@ int unetb200_plan_create(unetb200_plan** out, int N, int H, int W, int in_channe
       ws = max_sz(ws, tconv2x2_wgrad_ws_bytes(N, P->Hl(L + 1), P->Wl(L + 1), lt.cin, lt.cout));
     }
   }
-  P->ws_bytes = ws;
-  P->ws = P->bump(ws);
+  P->ws_side_bytes = ws;
+  P->ws_side = P->bump(ws);
   // ---- one table for all weight repacks (uploaded at bind time, walked by a single kernel)
   int tile = 0;
   for (const auto& l : P->layers) {
@@ -242,7 +253,12 @@ int unetb200_plan_create(unetb200_plan** out, int N, int H, int W, int in_channe
   return UB_OK;
 }
 
-void unetb200_plan_destroy(unetb200_plan* P) { delete P; }
+void unetb200_plan_destroy(unetb200_plan* P) {
+  if (!P) return;
+  for (int i = 0; i < P->n_ev; ++i) cudaEventDestroy(P->ev[i]);
+  if (P->side) cudaStreamDestroy(P->side);
+  delete P;
+}
 
 long long unetb200_plan_num_params(const unetb200_plan* P) { return P->nparams; }
 int unetb200_plan_num_variables(const unetb200_plan* P) { return static_cast<int>(P->vars.size()); }
@@ -271,6 +287,13 @@ int unetb200_plan_bind(unetb200_plan* P, void* arena, float* params, float* grad
   P->arena = reinterpret_cast<uint8_t*>(arena);
   P->params = params;
   P->grads = grads;
+  if (!P->side) {   // created here, never inside a stream capture
+    P->use_side = P->use_side && getenv("UNETB200_NO_SIDE_STREAM") == nullptr;
+    UB_CHECK_CUDA(cudaStreamCreateWithFlags(&P->side, cudaStreamNonBlocking));
+    for (P->n_ev = 0; P->n_ev < 40; ++P->n_ev) {
+      UB_CHECK_CUDA(cudaEventCreateWithFlags(&P->ev[P->n_ev], cudaEventDisableTiming));
+    }
+  }
   // the repack table lives in the arena; binding is a set-up call, so a synchronous copy is fine here
   UB_CHECK_CUDA(cudaMemcpy(P->at(P->pack_table), P->pack_layers.data(), P->pack_layers.size() * sizeof(PackLayer),
                            cudaMemcpyHostToDevice));
@@ -395,9 +418,31 @@ int unetb200_plan_backward(unetb200_plan* P, const float* imgs, const float* msk
   UB_REQUIRE(segment >= 0 && segment <= 2, "plan_backward: segment %d outside 0..2", segment);
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
   const int N = P->N;
-  float* ws = reinterpret_cast<float*>(P->at(P->ws));
-  void* wsv = P->at(P->ws);
+  float* ws = reinterpret_cast<float*>(P->at(P->ws));              // main stream: head
+  float* wss = reinterpret_cast<float*>(P->at(P->ws_side));         // weight-gradient stream
+  void* wsv = P->at(P->ws_side);
+  const size_t wsb = P->ws_side_bytes;
   const float inv_keep = P->dropout > 0.0f ? 1.0f / (1.0f - P->dropout) : 1.0f;
+  const bool side_on = P->use_side && P->side != nullptr;
+  cudaStream_t w = side_on ? P->side : s;   // where the weight gradients go
+  // fork: the side stream waits until the main stream has produced everything enqueued so far
+  auto fork = [&]() -> int {
+    if (!side_on) return UB_OK;
+    cudaEvent_t e = P->ev[P->ev_next];
+    P->ev_next = (P->ev_next + 1) % P->n_ev;
+    UB_CHECK_CUDA(cudaEventRecord(e, s));
+    UB_CHECK_CUDA(cudaStreamWaitEvent(w, e, 0));
+    return UB_OK;
+  };
+  // join: the main stream waits for all weight gradients enqueued so far (end of every segment)
+  auto join = [&]() -> int {
+    if (!side_on) return UB_OK;
+    cudaEvent_t e = P->ev[P->ev_next];
+    P->ev_next = (P->ev_next + 1) % P->n_ev;
+    UB_CHECK_CUDA(cudaEventRecord(e, w));
+    UB_CHECK_CUDA(cudaStreamWaitEvent(s, e, 0));
+    return UB_OK;
+  };
 
   if (segment == 0) {
     const long long pixels = static_cast<long long>(N) * P->H * P->W;
@@ -410,15 +455,19 @@ int unetb200_plan_backward(unetb200_plan* P, const float* imgs, const float* msk
       const long long px = static_cast<long long>(N) * H * W;
       const int la = P->dec_a[L], lb = P->dec_b[L];
       // conv{9-L}b
-      RC(conv3x3_wgrad(P->at(P->g_dc[L]), P->dc_out[L], ConvSrc{P->at(P->da[L]), P->ch[L]}, ConvSrc{nullptr, 0},
-                       P->dW_(lb), wsv, P->ws_bytes, N, H, W, s, P->dB_(lb)));
+      RC(fork());
+      RC(fork());
+    RC(conv3x3_wgrad(P->at(P->g_dc[L]), P->dc_out[L], ConvSrc{P->at(P->da[L]), P->ch[L]}, ConvSrc{nullptr, 0},
+                       P->dW_(lb), wsv, wsb, N, H, W, w, P->dB_(lb)));
       RC(conv3x3_dgrad(P->at(P->g_dc[L]), P->dc_out[L], P->pkd(lb),
                        DgradDst{P->at(P->g_da[L]), P->ch[L], P->at(P->da[L]), 1.0f, P->gate(P->gt_da[L])},
                        DgradDst{nullptr, 0, nullptr, 1.0f},
                        N, H, W, s));
       // conv{9-L}a over [u, skip]
-      RC(conv3x3_wgrad(P->at(P->g_da[L]), P->ch[L], ConvSrc{P->at(P->u[L]), P->ch[L]}, ConvSrc{P->at(P->c[L]), P->ch[L]},
-                       P->dW_(la), wsv, P->ws_bytes, N, H, W, s, P->dB_(la)));
+      RC(fork());
+      RC(fork());
+    RC(conv3x3_wgrad(P->at(P->g_da[L]), P->ch[L], ConvSrc{P->at(P->u[L]), P->ch[L]}, ConvSrc{P->at(P->c[L]), P->ch[L]},
+                       P->dW_(la), wsv, wsb, N, H, W, w, P->dB_(la)));
       RC(conv3x3_dgrad(P->at(P->g_da[L]), P->ch[L], P->pkd(la), DgradDst{P->at(P->g_u[L]), P->ch[L], nullptr, 1.0f},
                        DgradDst{P->at(P->g_c[L]), P->ch[L], P->at(P->c[L]), 1.0f, P->gate(P->gt_c[L])}, N, H, W, s));
       // up path
@@ -429,13 +478,14 @@ int unetb200_plan_backward(unetb200_plan* P, const float* imgs, const float* msk
         RC(upsample2x2_bwd(P->at(P->g_u[L]), P->at(below), P->at(g_below), N, H / 2, W / 2, below_C, 1, s));
       } else {
         const int lt = P->tc[L];
-        RC(tconv2x2_wgrad(P->at(P->g_u[L]), P->ch[L], P->at(below), below_C, P->dW_(lt), wsv, P->ws_bytes, N, H / 2,
-                          W / 2, s));
-        RC(colsum_bf16(P->at(P->g_u[L]), P->dB_(lt), ws, px, P->ch[L], s));
+        RC(fork());
+        RC(tconv2x2_wgrad(P->at(P->g_u[L]), P->ch[L], P->at(below), below_C, P->dW_(lt), wsv, wsb, N, H / 2, W / 2, w));
+        RC(colsum_bf16(P->at(P->g_u[L]), P->dB_(lt), wss, px, P->ch[L], w));
         RC(tconv2x2_dgrad(P->at(P->g_u[L]), P->ch[L], P->pkd(lt), P->at(g_below), below_C, P->at(below), 1.0f, N, H / 2,
                           W / 2, s, P->gate(L == 3 ? P->gt_c[4] : P->gt_dc[L + 1])));
       }
     }
+    RC(join());
     return UB_OK;
   }
 
@@ -444,14 +494,17 @@ int unetb200_plan_backward(unetb200_plan* P, const float* imgs, const float* msk
     const int H = P->Hl(L), W = P->Wl(L);
     const long long px = static_cast<long long>(N) * H * W;
     const int la = P->enc_a[L], lb = P->enc_b[L];
+    RC(fork());
     RC(conv3x3_wgrad(P->at(P->g_c[L]), P->c4_out, ConvSrc{P->at(P->a[L]), P->ch[L]}, ConvSrc{nullptr, 0}, P->dW_(lb), wsv,
-                     P->ws_bytes, N, H, W, s, P->dB_(lb)));
+                     wsb, N, H, W, w, P->dB_(lb)));
     RC(conv3x3_dgrad(P->at(P->g_c[L]), P->c4_out, P->pkd(lb), DgradDst{P->at(P->g_a[L]), P->ch[L], P->at(P->a[L]), 1.0f, P->gate(P->gt_a[L])},
                      DgradDst{nullptr, 0, nullptr, 1.0f}, N, H, W, s));
+    RC(fork());
     RC(conv3x3_wgrad(P->at(P->g_a[L]), P->ch[L], ConvSrc{P->at(P->p[L - 1]), P->ch[L - 1]}, ConvSrc{nullptr, 0},
-                     P->dW_(la), wsv, P->ws_bytes, N, H, W, s, P->dB_(la)));
+                     P->dW_(la), wsv, wsb, N, H, W, w, P->dB_(la)));
     RC(conv3x3_dgrad(P->at(P->g_a[L]), P->ch[L], P->pkd(la), DgradDst{P->at(P->g_p[L - 1]), P->ch[L - 1], nullptr, 1.0f},
                      DgradDst{nullptr, 0, nullptr, 1.0f}, N, H, W, s));
+    RC(join());
     return UB_OK;
   }
 
@@ -461,23 +514,34 @@ int unetb200_plan_backward(unetb200_plan* P, const float* imgs, const float* msk
     const int la = P->enc_a[L], lb = P->enc_b[L];
     // MaxPoolGrad + skip gradient + ReluGrad of conv{L+1}b, in place in g_c[L]
     RC(maxpool2x2_bwd(P->at(P->c[L]), P->at(P->g_p[L]), P->at(P->g_c[L]), P->at(P->g_c[L]), N, H, W, P->ch[L], s));
+    RC(fork());
     RC(conv3x3_wgrad(P->at(P->g_c[L]), P->ch[L], ConvSrc{P->at(P->a[L]), P->ch[L]}, ConvSrc{nullptr, 0}, P->dW_(lb), wsv,
-                     P->ws_bytes, N, H, W, s, P->dB_(lb)));
+                     wsb, N, H, W, w, P->dB_(lb)));
     const bool dropped = (L == 2 || L == 3) && P->dropout > 0.0f;
     RC(conv3x3_dgrad(P->at(P->g_c[L]), P->ch[L], P->pkd(lb),
                      DgradDst{P->at(P->g_a[L]), P->ch[L], P->at(P->a[L]), dropped ? inv_keep : 1.0f, P->gate(P->gt_a[L])},
                      DgradDst{nullptr, 0, nullptr, 1.0f}, N, H, W, s));
     if (L > 0) {
-      RC(conv3x3_wgrad(P->at(P->g_a[L]), P->ch[L], ConvSrc{P->at(P->p[L - 1]), P->ch[L - 1]}, ConvSrc{nullptr, 0},
-                       P->dW_(la), wsv, P->ws_bytes, N, H, W, s, P->dB_(la)));
+      RC(fork());
+      RC(fork());
+    RC(conv3x3_wgrad(P->at(P->g_a[L]), P->ch[L], ConvSrc{P->at(P->p[L - 1]), P->ch[L - 1]}, ConvSrc{nullptr, 0},
+                       P->dW_(la), wsv, wsb, N, H, W, w, P->dB_(la)));
       RC(conv3x3_dgrad(P->at(P->g_a[L]), P->ch[L], P->pkd(la),
                        DgradDst{P->at(P->g_p[L - 1]), P->ch[L - 1], nullptr, 1.0f}, DgradDst{nullptr, 0, nullptr, 1.0f},
                        N, H, W, s));
     } else {
-      RC(conv_first_wgrad(imgs, P->at(P->g_a[0]), P->dW_(la), P->dB_(la), ws, N, H, W, P->Cin, 32, s));
+      RC(fork());
+      RC(conv_first_wgrad(imgs, P->at(P->g_a[0]), P->dW_(la), P->dB_(la), wss, N, H, W, P->Cin, 32, w));
     }
   }
+  RC(join());
   return UB_OK;
+}
+
+int unetb200_plan_side_stream(unetb200_plan* P, int enable) {
+  const int old = P->use_side ? 1 : 0;
+  P->use_side = enable != 0 && getenv("UNETB200_NO_SIDE_STREAM") == nullptr;
+  return old;
 }
 
 // Flat-buffer range [begin, end) (floats) whose gradients are complete once `segment` has run.

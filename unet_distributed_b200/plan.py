@@ -149,6 +149,10 @@ class UNetPlan:
         return self.tensor("metrics")
 
     # ------------------------------------------------------------------ launches (asynchronous on the current stream)
+    def side_stream(self, enable):
+        """Run weight gradients on the plan's second stream (default) or in program order; returns the old setting."""
+        return bool(_lib.lib().unetb200_plan_side_stream(self._h, 1 if enable else 0))
+
     def pack_weights(self):
         _lib.call("unetb200_plan_pack_weights", self._h, _stream())
 
