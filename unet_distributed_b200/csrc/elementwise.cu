@@ -1,5 +1,6 @@
 #include "elementwise.cuh"
 
+#include <cstdlib>
 #include <initializer_list>
 
 #include <mutex>
@@ -744,7 +745,9 @@ int conv_first_wgrad(const float* x, const void* dz, float* dw, float* db, float
 
 // The 16-channel / 256-bit kernels (pool.cuh) apply when every tensor is 32-byte aligned, C % 16 == 0 and the fine
 // tensor has fewer than 2^32 32-byte units.
-static bool v8_ok(int C, long long fine_pixels, std::initializer_list<const void*> ptrs) {
+static bool v8_ok(int C, long long fine_pixels, std::initializer_list<const void*> ptrs, int which = 0) {
+  static const int off_mask = getenv("UNETB200_V8_OFF") ? atoi(getenv("UNETB200_V8_OFF")) : 0;
+  if (off_mask & which) return false;
   if (C % 16 != 0 || fine_pixels * (C / 16) >= (1ll << 32)) return false;
   for (const void* p : ptrs) {
     if (reinterpret_cast<uintptr_t>(p) % 32 != 0) return false;
@@ -754,7 +757,7 @@ static bool v8_ok(int C, long long fine_pixels, std::initializer_list<const void
 
 int maxpool2x2_fwd(const void* x, void* y, int N, int H, int W, int C, cudaStream_t s) {
   UB_REQUIRE(C % 8 == 0 && H % 2 == 0 && W % 2 == 0, "maxpool2x2_fwd: shape %dx%dx%d unsupported", H, W, C);
-  if (v8_ok(C, static_cast<long long>(N) * H * W, {x, y})) {
+  if (v8_ok(C, static_cast<long long>(N) * H * W, {x, y}, 1)) {
     const unsigned groups = C / 16, total16 = static_cast<unsigned>(N) * (H / 2) * (W / 2) * groups;
     maxpool_fwd_v8_kernel<<<grid_for(total16, 256), 256, 0, s>>>(reinterpret_cast<const U32x8*>(x),
                                                                  reinterpret_cast<U32x8*>(y), total16, groups, W / 2, H / 2);
@@ -771,14 +774,6 @@ int maxpool2x2_fwd(const void* x, void* y, int N, int H, int W, int C, cudaStrea
 int maxpool2x2_bwd(const void* x, const void* dpool, const void* skip_grad, void* dz_full, int N, int H, int W, int C,
                    cudaStream_t s) {
   UB_REQUIRE(C % 8 == 0 && H % 2 == 0 && W % 2 == 0, "maxpool2x2_bwd: shape %dx%dx%d unsupported", H, W, C);
-  if (v8_ok(C, static_cast<long long>(N) * H * W, {x, dpool, skip_grad, dz_full})) {
-    const unsigned groups = C / 16, total16 = static_cast<unsigned>(N) * (H / 2) * (W / 2) * groups;
-    maxpool_bwd_v8_kernel<<<grid_for(total16, 256), 256, 0, s>>>(
-        reinterpret_cast<const U32x8*>(x), reinterpret_cast<const U32x8*>(dpool),
-        reinterpret_cast<const U32x8*>(skip_grad), reinterpret_cast<U32x8*>(dz_full), total16, groups, W / 2, H / 2);
-    UB_CHECK_CUDA(cudaGetLastError());
-    return UB_OK;
-  }
   const long long total = static_cast<long long>(N) * (H / 2) * (W / 2) * (C / 8);
   maxpool_bwd_kernel<<<grid_for(total, kThreads), kThreads, 0, s>>>(
       reinterpret_cast<const uint4*>(x), reinterpret_cast<const uint4*>(dpool),
@@ -789,7 +784,7 @@ int maxpool2x2_bwd(const void* x, const void* dpool, const void* skip_grad, void
 
 int upsample2x2_fwd(const void* x, void* y, int N, int H, int W, int C, cudaStream_t s) {
   UB_REQUIRE(C % 8 == 0, "upsample2x2_fwd: C %d", C);
-  if (v8_ok(C, static_cast<long long>(N) * 4 * H * W, {x, y})) {
+  if (v8_ok(C, static_cast<long long>(N) * 4 * H * W, {x, y}, 4)) {
     const unsigned groups = C / 16, total16 = static_cast<unsigned>(N) * H * W * groups;
     upsample_fwd_v8_kernel<<<grid_for(total16, 256), 256, 0, s>>>(reinterpret_cast<const U32x8*>(x),
                                                                   reinterpret_cast<U32x8*>(y), total16, groups, W, H);
@@ -805,7 +800,7 @@ int upsample2x2_fwd(const void* x, void* y, int N, int H, int W, int C, cudaStre
 
 int upsample2x2_bwd(const void* dy, const void* x, void* dx, int N, int H, int W, int C, int relu_mask, cudaStream_t s) {
   UB_REQUIRE(C % 8 == 0, "upsample2x2_bwd: C %d", C);
-  if (v8_ok(C, static_cast<long long>(N) * 4 * H * W, {dy, x, dx})) {
+  if (v8_ok(C, static_cast<long long>(N) * 4 * H * W, {dy, x, dx}, 8)) {
     const unsigned groups = C / 16, total16 = static_cast<unsigned>(N) * H * W * groups;
     upsample_bwd_v8_kernel<<<grid_for(total16, 256), 256, 0, s>>>(
         reinterpret_cast<const U32x8*>(dy), reinterpret_cast<const U32x8*>(x), reinterpret_cast<U32x8*>(dx), total16,
