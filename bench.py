@@ -316,11 +316,14 @@ def run_b200(args):
                     "h2d_bytes_per_step": tr.h2d_bytes_per_step(), "d2h_bytes_per_step": tr.d2h_bytes_per_step()},
             "gpu_launches": int(launches),
             "roofline": {
-                "kernel": "igemm_kernel (3x3 conv / transposed conv forward + dgrad, tcgen05 implicit GEMM)",
+                "kernel": "conv_halo_kernel + igemm_kernel (3x3 conv / transposed conv forward + dgrad, tcgen05 "
+                          "implicit GEMM; every launch of the class in a step)",
                 "bound": "tensor", "achieved": achieved, "peak": peak_tf, "unit": "TFLOP/s",
                 "frac": achieved / peak_tf if peak_tf else None, "traffic": traffic,
                 "peak_source": "bf16_tflops_sustained, " + peaks["_source"],
                 "launches_per_step": ig_n / roof["steps"], "ms_per_step": ig_ms / roof["steps"],
+                "alg_gbs": (ig_by / (ig_ms * 1e-3) / 1e9 if ig_ms > 0 else 0.0),
+                "hbm_peak_gbs": float(peaks.get("hbm_gbs", FALLBACK_PEAKS.get("hbm_gbs", 0.0))),
                 "wgrad": {"achieved": (wg_fl / (wg_ms * 1e-3) / 1e12 if wg_ms > 0 else 0.0), "unit": "TFLOP/s",
                           "launches_per_step": wg_n / roof["steps"], "ms_per_step": wg_ms / roof["steps"]},
                 "whole_step": ({"achieved": value * gflop_img / 1e3 / world, "unit": "TFLOP/s per GPU",

@@ -12,7 +12,7 @@ launch = collections.OrderedDict()
 for r in rows[hi + 1:]:
     if len(r) <= vi:
         continue
-    d = launch.setdefault(r[ii], {"name": r[ki]})
+    d = launch.setdefault(r[ii], {"name": r[ki], "grid": r[hdr.index("Grid Size")].replace(",", " ")})
     v = float(r[vi].replace(",", ""))
     unit = r[ui]
     if r[mi].startswith("dram__bytes"):
@@ -41,6 +41,12 @@ lines.append(f"launches/step {len(step)}  total {tot:.1f} us (cold-cache, serial
 txt = "\n".join(lines)
 print(txt)
 open(f"profiles/{tag}_ncu_step_traffic.txt", "w").write(txt + "\n")
+with open(f"profiles/{tag}_ncu_launches_step.csv", "w") as f:
+    f.write("idx,kernel,grid,us,dram_read_bytes,dram_write_bytes\n")
+    for i, l in enumerate(step):
+        k = re.sub(r"\(.*", "", l["name"]).split("::")[-1]
+        f.write(f"{i},{k},{l.get('grid','')},{l.get('gpu__time_duration.sum',0):.2f},{l.get('dram__bytes_read.sum',0):.0f},"
+                f"{l.get('dram__bytes_write.sum',0):.0f}\n")
 conv = [agg[k] for k in agg if k.startswith("conv_halo_kernel") or k.startswith("igemm_kernel")]
 n = sum(c[0] for c in conv)
 json.dump({"igemm_dram_bytes_per_launch": sum(c[2] + c[3] for c in conv) / n, "launches": n,
