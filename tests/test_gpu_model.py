@@ -146,3 +146,26 @@ def test_deterministic_repeat(cuda_device):
         outs.append((plan.grads.clone(), plan.metrics.clone()))
     assert torch.equal(outs[0][1], outs[1][1])
     assert torch.equal(outs[0][0], outs[1][0])
+
+
+@pytest.mark.parametrize("ups", [False, True])
+def test_side_stream_on_off_identical(cuda_device, ups):
+    """Weight gradients on the plan's second stream (default) and in program order give bit-identical gradient buffers:
+    the fork/join only changes when kernels run, never what they read."""
+    from unet_distributed_b200.plan import UNetPlan
+    imgs, msks = synthetic_batch(2, 64, 64)
+    plan = UNetPlan(2, 64, 64, 1, 1, ups, 0.2)
+    plan.set_weights(O.init_weights(11, use_upsampling=ups))
+    d_imgs, d_msks = torch.tensor(imgs, device=cuda_device), torch.tensor(msks, device=cuda_device)
+    outs = []
+    for on in (True, False, True):
+        old = plan.side_stream(on)
+        assert isinstance(old, bool)
+        plan.grads.zero_()   # (the flat buffer has never-written padding between variables)
+        plan.forward(d_imgs, d_msks, seed=5)
+        plan.backward(d_imgs, d_msks)
+        torch.cuda.synchronize()
+        assert torch.isfinite(plan.grads).all() and float(plan.grads.abs().sum()) > 0.0
+        outs.append(plan.grads.clone())
+    assert torch.equal(outs[0], outs[1])
+    assert torch.equal(outs[0], outs[2])
