@@ -683,10 +683,11 @@ int conv_first_fwd(const float* x, const float* w, const float* bias, void* y, i
   const long long total = static_cast<long long>(N) * H * W * (Cout / 8);
   UB_REQUIRE(total < (1ll << 31), "conv_first_fwd: tensor too large");
   const bool y32 = reinterpret_cast<uintptr_t>(y) % 32 == 0;   // the fast path stores 32 bytes per instruction
-  UB_REQUIRE(gate_out == nullptr || y32, "conv_first_fwd: gate bits need a 32-byte aligned output tensor");
-  if (y32 && Cout == 32 && (Cin == 1 || Cin == 4)) {   // thread-per-pixel fast path (the network's conv1a)
+  UB_REQUIRE(gate_out == nullptr || (y32 && W % 2 == 0),
+             "conv_first_fwd: gate bits need a 32-byte aligned output tensor and an even width");
+  if (y32 && W % 2 == 0 && Cout == 32 && (Cin == 1 || Cin == 4)) {   // two-pixels-per-thread fast path (the network's conv1a)
     const unsigned P = static_cast<unsigned>(static_cast<long long>(N) * H * W);
-    unsigned blocks = grid_for(P, kThreads);
+    unsigned blocks = grid_for(P / 2, kThreads);
     const unsigned cap = 8u * static_cast<unsigned>(device_sm_count());
     if (blocks > cap) blocks = cap;
     if (Cin == 1) {

@@ -11,68 +11,83 @@ template <int CIN>
 __global__ void __launch_bounds__(256)
 conv_first32_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ bias,
                         uint4* __restrict__ y, unsigned int* __restrict__ gate, int H, int W, unsigned P) {
+  // A thread owns TWO horizontally adjacent pixels: every weight vector read from shared memory feeds two FMAs groups
+  // (ncu on the one-pixel version: 72 LDS.128 per pixel, short-scoreboard + MIO-throttle stalls dominate) and the
+  // 3 x 4 input window is shared. W is even (checked by the launcher), so a pair never straddles an image row.
   __shared__ float4 sw4[9 * CIN * 8 + 8];   // [tap][ci][32 channels] then bias, as float4
   float* sw = reinterpret_cast<float*>(sw4);
   for (int i = threadIdx.x; i < 9 * CIN * 32; i += blockDim.x) sw[i] = w[i];
   for (int i = threadIdx.x; i < 32; i += blockDim.x) sw[9 * CIN * 32 + i] = bias ? bias[i] : 0.0f;
   __syncthreads();
   const unsigned stride = gridDim.x * blockDim.x;
-  for (unsigned pix = blockIdx.x * blockDim.x + threadIdx.x; pix < P; pix += stride) {
+  const unsigned pairs = P >> 1;
+  for (unsigned pp = blockIdx.x * blockDim.x + threadIdx.x; pp < pairs; pp += stride) {
+    const unsigned pix = pp * 2;
     const int wq = static_cast<int>(pix % W);
     const unsigned row = pix / W;                 // n*H + h
     const int hq = static_cast<int>(row % H);
-    float xv[9][CIN];
+    float xv[3][4][CIN];
+#pragma unroll
+    for (int r = 0; r < 3; ++r) {
+      const int hh = hq + r - 1;
+      const bool row_in = hh >= 0 && hh < H;
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
+        const int ww = wq + c - 1;
+        const bool in = row_in && ww >= 0 && ww < W;
+        const float* xp = x + (static_cast<size_t>(row + r - 1) * W + ww) * CIN;
+#pragma unroll
+        for (int ci = 0; ci < CIN; ++ci) xv[r][c][ci] = in ? __ldg(xp + ci) : 0.0f;
+      }
+    }
+    float4 acc[2][8];
+#pragma unroll
+    for (int q = 0; q < 8; ++q) acc[0][q] = acc[1][q] = sw4[9 * CIN * 8 + q];
 #pragma unroll
     for (int r = 0; r < 3; ++r) {
 #pragma unroll
-      for (int s = 0; s < 3; ++s) {
-        const int hh = hq + r - 1, ww = wq + s - 1;
-        const bool in = hh >= 0 && hh < H && ww >= 0 && ww < W;
-        const float* xp = x + (static_cast<size_t>(row + r - 1) * W + ww) * CIN;
+      for (int s3 = 0; s3 < 3; ++s3) {
 #pragma unroll
-        for (int ci = 0; ci < CIN; ++ci) xv[r * 3 + s][ci] = in ? __ldg(xp + ci) : 0.0f;
-      }
-    }
-    float4 acc[8];
+        for (int ci = 0; ci < CIN; ++ci) {
+          const float v0 = xv[r][s3][ci], v1 = xv[r][s3 + 1][ci];
 #pragma unroll
-    for (int q = 0; q < 8; ++q) acc[q] = sw4[9 * CIN * 8 + q];
-#pragma unroll
-    for (int t = 0; t < 9; ++t) {
-#pragma unroll
-      for (int ci = 0; ci < CIN; ++ci) {
-        const float v = xv[t][ci];
-#pragma unroll
-        for (int q = 0; q < 8; ++q) {
-          const float4 wv = sw4[(t * CIN + ci) * 8 + q];
-          acc[q].x = fmaf(v, wv.x, acc[q].x); acc[q].y = fmaf(v, wv.y, acc[q].y);
-          acc[q].z = fmaf(v, wv.z, acc[q].z); acc[q].w = fmaf(v, wv.w, acc[q].w);
+          for (int q = 0; q < 8; ++q) {
+            const float4 wv = sw4[((r * 3 + s3) * CIN + ci) * 8 + q];
+            acc[0][q].x = fmaf(v0, wv.x, acc[0][q].x); acc[0][q].y = fmaf(v0, wv.y, acc[0][q].y);
+            acc[0][q].z = fmaf(v0, wv.z, acc[0][q].z); acc[0][q].w = fmaf(v0, wv.w, acc[0][q].w);
+            acc[1][q].x = fmaf(v1, wv.x, acc[1][q].x); acc[1][q].y = fmaf(v1, wv.y, acc[1][q].y);
+            acc[1][q].z = fmaf(v1, wv.z, acc[1][q].z); acc[1][q].w = fmaf(v1, wv.w, acc[1][q].w);
+          }
         }
       }
     }
-    if (gate) {   // ReLU gates as bits: two uint16 (16 channels each) per pixel = one 32-bit word
-      unsigned int bits = 0;
 #pragma unroll
-      for (int q = 0; q < 8; ++q) {
-        bits |= (acc[q].x > 0.f ? 1u : 0u) << (4 * q);
-        bits |= (acc[q].y > 0.f ? 1u : 0u) << (4 * q + 1);
-        bits |= (acc[q].z > 0.f ? 1u : 0u) << (4 * q + 2);
-        bits |= (acc[q].w > 0.f ? 1u : 0u) << (4 * q + 3);
+    for (int k = 0; k < 2; ++k) {
+      if (gate) {   // ReLU gates as bits: two uint16 (16 channels each) per pixel = one 32-bit word
+        unsigned int bits = 0;
+#pragma unroll
+        for (int q = 0; q < 8; ++q) {
+          bits |= (acc[k][q].x > 0.f ? 1u : 0u) << (4 * q);
+          bits |= (acc[k][q].y > 0.f ? 1u : 0u) << (4 * q + 1);
+          bits |= (acc[k][q].z > 0.f ? 1u : 0u) << (4 * q + 2);
+          bits |= (acc[k][q].w > 0.f ? 1u : 0u) << (4 * q + 3);
+        }
+        gate[pix + k] = bits;
       }
-      gate[pix] = bits;
-    }
-    uint4* yp = y + static_cast<size_t>(pix) * 4;
+      uint4* yp = y + static_cast<size_t>(pix + k) * 4;
 #pragma unroll
-    for (int q2 = 0; q2 < 2; ++q2) {   // two 32-byte stores per pixel
-      U32x8 o;
+      for (int q2 = 0; q2 < 2; ++q2) {   // two 32-byte stores per pixel
+        U32x8 o;
 #pragma unroll
-      for (int q = 0; q < 2; ++q) {
-        const float4 a = acc[4 * q2 + 2 * q], b = acc[4 * q2 + 2 * q + 1];
-        o.v[4 * q + 0] = pack_bf16x2(fmaxf(a.x, 0.f), fmaxf(a.y, 0.f));
-        o.v[4 * q + 1] = pack_bf16x2(fmaxf(a.z, 0.f), fmaxf(a.w, 0.f));
-        o.v[4 * q + 2] = pack_bf16x2(fmaxf(b.x, 0.f), fmaxf(b.y, 0.f));
-        o.v[4 * q + 3] = pack_bf16x2(fmaxf(b.z, 0.f), fmaxf(b.w, 0.f));
+        for (int q = 0; q < 2; ++q) {
+          const float4 a = acc[k][4 * q2 + 2 * q], b = acc[k][4 * q2 + 2 * q + 1];
+          o.v[4 * q + 0] = pack_bf16x2(fmaxf(a.x, 0.f), fmaxf(a.y, 0.f));
+          o.v[4 * q + 1] = pack_bf16x2(fmaxf(a.z, 0.f), fmaxf(a.w, 0.f));
+          o.v[4 * q + 2] = pack_bf16x2(fmaxf(b.x, 0.f), fmaxf(b.y, 0.f));
+          o.v[4 * q + 3] = pack_bf16x2(fmaxf(b.z, 0.f), fmaxf(b.w, 0.f));
+        }
+        st_global_v8(yp + 2 * q2, o);
       }
-      st_global_v8(yp + 2 * q2, o);
     }
   }
 }
