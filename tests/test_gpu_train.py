@@ -174,3 +174,30 @@ def test_host_step_and_sgd(cuda_device):
     for k in ("conv5b/kernel", "conv9b/kernel", "Mask/kernel"):
         assert rel_err(got[k] - weights[k], w[k] - weights[k]) < 1e-4, k
     assert tr.h2d_bytes_per_step() == (imgs.size + msks.size) * 4 and tr.global_step() == 1
+
+
+def test_pipelined_host_steps_match_synchronous(cuda_device):
+    """train_step_host(wait=False) (copy of batch k+1 overlapping step k, metrics returned one call late) runs the
+    same steps as the synchronous call: identical metrics and parameters."""
+    from unet_distributed_b200.trainer import Trainer
+    N, H, W = 2, 32, 32
+    batches = [synthetic_batch(N, H, W, seed=s) for s in (1, 2, 3, 4, 5)]
+    weights = O.init_weights(9)
+    outs = []
+    for wait in (True, False):
+        tr = Trainer(N, H, W, dropout=0.2, learning_rate=1e-3, weights=weights)
+        mets = []
+        for imgs, msks in batches:
+            m = tr.train_step_host(imgs, msks, wait=wait)
+            if m is not None:
+                mets.append(m)
+        last = tr.finish()
+        if wait:
+            assert last is None
+        else:
+            mets.append(last)
+        assert tr.finish() is None
+        outs.append((np.stack(mets), tr.plan.params.cpu().numpy(), tr.global_step()))
+    assert outs[0][2] == outs[1][2] == len(batches)
+    np.testing.assert_array_equal(outs[0][0], outs[1][0])
+    np.testing.assert_array_equal(outs[0][1], outs[1][1])

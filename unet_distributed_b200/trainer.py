@@ -47,11 +47,11 @@ class Trainer:
         self._graph = None
         self._g_imgs = self._g_msks = None
         self.steps_done = 0
-        # pinned staging for the host-facing step
-        self._h_imgs = self._h_msks = None
+        # host-facing step: two device input slots + pinned staging, created on first use (_pipeline)
+        self._slots = None
+        self._pending = None
         self._d_imgs = torch.empty((N, H, W, in_channels), dtype=torch.float32, device=dev)
         self._d_msks = torch.empty((N, H, W, n_cl_out), dtype=torch.float32, device=dev)
-        self._h_metrics = torch.empty(4, dtype=torch.float32).pin_memory()
 
     # ------------------------------------------------------------------ one optimizer step on device-resident data
     def _piece(self, i, imgs, msks):
@@ -138,23 +138,72 @@ class Trainer:
         self.graph_launches_per_step = int(_lib.lib().unetb200_launch_count() - before)
 
     # ------------------------------------------------------------------ host-facing step (what a user calls)
-    def train_step_host(self, imgs_np, msks_np):
-        """One step fed from HOST arrays (the feed_dict of test_dist.py:394-398): copies this replica's shard from
-        pinned memory, runs the step and reads the step's [loss, dice, sens, spec] back. Returns a numpy array."""
-        if self._h_imgs is None:
-            self._h_imgs = torch.empty(self._d_imgs.shape, dtype=torch.float32).pin_memory()
-            self._h_msks = torch.empty(self._d_msks.shape, dtype=torch.float32).pin_memory()
-        self._h_imgs.numpy()[...] = imgs_np
-        self._h_msks.numpy()[...] = msks_np
-        return self.train_step_pinned(self._h_imgs, self._h_msks)
+    def _pipeline(self):
+        """Two input slots + a copy stream: the host->device copy of step k+1 runs while step k computes."""
+        if self._slots is None:
+            dev = self.plan.device
+            self._copy_stream = torch.cuda.Stream(device=dev)
+            self._slots = []
+            for _ in range(2):
+                self._slots.append({
+                    "imgs": torch.empty_like(self._d_imgs), "msks": torch.empty_like(self._d_msks),
+                    "ready": torch.cuda.Event(), "free": torch.cuda.Event(), "done": torch.cuda.Event(),
+                    "h_metrics": torch.empty(4, dtype=torch.float32).pin_memory(),
+                    "h_imgs": None, "h_msks": None})
+            self._k = 0
+            self._pending = None
+        return self._slots
 
-    def train_step_pinned(self, h_imgs, h_msks):
-        self._d_imgs.copy_(h_imgs, non_blocking=True)
-        self._d_msks.copy_(h_msks, non_blocking=True)
-        met = self.train_step(self._d_imgs, self._d_msks)
-        self._h_metrics.copy_(met, non_blocking=True)
-        torch.cuda.current_stream().synchronize()
-        return self._h_metrics.numpy().copy()
+    def train_step_host(self, imgs_np, msks_np, wait=True):
+        """One step fed from HOST arrays (the feed_dict of test_dist.py:394-398): stages this replica's shard in pinned
+        memory, copies it to the device, runs the step and reads the step's [loss, dice, sens, spec] back.
+        See train_step_pinned for `wait`."""
+        slot = self._pipeline()[self._k % 2]
+        if slot["h_imgs"] is None:
+            slot["h_imgs"] = torch.empty(self._d_imgs.shape, dtype=torch.float32).pin_memory()
+            slot["h_msks"] = torch.empty(self._d_msks.shape, dtype=torch.float32).pin_memory()
+        slot["ready"].synchronize()   # the copy that last read this staging buffer (two steps ago) has finished
+        slot["h_imgs"].numpy()[...] = imgs_np
+        slot["h_msks"].numpy()[...] = msks_np
+        return self.train_step_pinned(slot["h_imgs"], slot["h_msks"], wait=wait)
+
+    def train_step_pinned(self, h_imgs, h_msks, wait=True):
+        """One step fed from pinned host tensors. wait=True (default): returns this step's metrics as a numpy array
+        (one synchronisation per step). wait=False: software-pipelined -- the step is enqueued, the PREVIOUS
+        step's metrics are returned (None on the first call) and the copy of the next batch overlaps this step's
+        kernels; call finish() for the last one. The caller must not overwrite h_imgs / h_msks before the following
+        call returns."""
+        slots = self._pipeline()
+        slot = slots[self._k % 2]
+        self._k += 1
+        cur = torch.cuda.current_stream()
+        with torch.cuda.stream(self._copy_stream):
+            self._copy_stream.wait_event(slot["free"])      # step k-2 has consumed this slot (no-op the first time)
+            slot["imgs"].copy_(h_imgs, non_blocking=True)
+            slot["msks"].copy_(h_msks, non_blocking=True)
+            slot["ready"].record(self._copy_stream)
+        cur.wait_event(slot["ready"])
+        met = self.train_step(slot["imgs"], slot["msks"])
+        slot["free"].record(cur)
+        slot["h_metrics"].copy_(met, non_blocking=True)
+        slot["done"].record(cur)
+        prev, self._pending = self._pending, slot
+        if wait:
+            self._pending = None
+            slot["done"].synchronize()
+            return slot["h_metrics"].numpy().copy()
+        if prev is None:
+            return None
+        prev["done"].synchronize()
+        return prev["h_metrics"].numpy().copy()
+
+    def finish(self):
+        """Metrics of the last pipelined step (train_step_pinned(..., wait=False)), or None if nothing is pending."""
+        prev, self._pending = self._pending, None
+        if prev is None:
+            return None
+        prev["done"].synchronize()
+        return prev["h_metrics"].numpy().copy()
 
     def h2d_bytes_per_step(self):
         return (self._d_imgs.numel() + self._d_msks.numel()) * 4
