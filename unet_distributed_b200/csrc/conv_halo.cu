@@ -309,10 +309,13 @@ __device__ __forceinline__ uint32_t pack_bf16x2_relu(float lo, float hi) {
   return d;
 }
 
-template <int J, int BN, bool FWD, bool SPLIT>
+//   POOL  : (with SPLIT) destination 0 is the coarse tensor: each 2x2 block of the gradient is summed across lanes
+//           (lane ^ 1 = next column, lane ^ 8 = next row) in fp32 and the even-row/even-column lane stores it.
+template <int J, int BN, bool FWD, bool SPLIT, bool POOL = false>
 __device__ __forceinline__ void halo_epilogue_fast(const HaloParams& p, HaloBarriers* bars, uint32_t tmem_base,
                                                    int warp, int lane, int num_tiles) {
   static_assert(!SPLIT || BN >= 64, "split destinations need 32-column halves");
+  static_assert(!POOL || (SPLIT && !FWD), "2x2 pooling of destination 0 is a split-dgrad feature");
   constexpr int kCl = BN / 32;              // 16-column chunks per warp (the two warps of a quarter interleave)
   constexpr int kItems = J * kCl;
   constexpr bool kBiasRegs = FWD && BN <= 64;
@@ -341,7 +344,7 @@ __device__ __forceinline__ void halo_epilogue_fast(const HaloParams& p, HaloBarr
 #pragma unroll
   for (int sl = 0; sl < kSlots; ++sl) {
     strip_b[sl] = static_cast<uint32_t>(16 * e.dst_C[sl]);
-    gstrip[sl] = static_cast<uint32_t>((FWD ? e.dst_C[sl] : e.aux_C[sl]) >> 1);
+    gstrip[sl] = static_cast<uint32_t>(((FWD || (POOL && sl == 0)) ? e.dst_C[sl] : e.aux_C[sl]) >> 1);
   }
   int it = 0;
   unsigned long long t_wait = 0;
@@ -362,6 +365,13 @@ __device__ __forceinline__ void halo_epilogue_fast(const HaloParams& p, HaloBarr
       if (!FWD && e.gate_in[sl]) gin_b[sl] = e.gate_in[sl] + ((pix0 * e.aux_C[sl] + e.aux_coff[sl]) >> 4) + half;
     }
     if (FWD && e.gate_out) gout_b = e.gate_out + ((pix0 * e.dst_C[0] + e.dst_coff[0]) >> 4) + half;
+    const bool pool_lane = (lane & 9) == 0;   // even row and even column of the tile
+    if (POOL) {   // destination 0 addressed on the coarse grid (this lane's 2x2 block)
+      const size_t cpix0 = (static_cast<size_t>(n) * (p.H >> 1) + ((h0 + th) >> 1)) * (p.W >> 1) + ((w0 + twl) >> 1);
+      dst_b[0] = reinterpret_cast<char*>(e.dst[0]) + (cpix0 * e.dst_C[0] + e.dst_coff[0] + half * 16) * 2;
+      gin_b[0] = nullptr;
+      if (e.gate_in[0] && pool_lane) gin_b[0] = e.gate_in[0] + ((cpix0 * e.dst_C[0] + e.dst_coff[0]) >> 4) + half;
+    }
     uint32_t gb[kItems];
     if (!FWD) {
 #pragma unroll
@@ -369,7 +379,8 @@ __device__ __forceinline__ void halo_epilogue_fast(const HaloParams& p, HaloBarr
         const int j = k / kCl, cl = k % kCl;
         const int sl = (SPLIT && 32 * cl >= BN / 2) ? 1 : 0;
         gb[k] = 0xFFFFu;
-        if (gin_b[sl]) gb[k] = __ldg(gin_b[sl] + j * gstrip[sl] + (2 * cl - sl * (BN / 32)));
+        const uint32_t gs = (POOL && sl == 0) ? (gstrip[0] >> 1) : gstrip[sl];   // coarse strips are 4 pixels apart
+        if (gin_b[sl]) gb[k] = __ldg(gin_b[sl] + j * gs + (2 * cl - sl * (BN / 32)));
       }
     }
     timed_wait(&bars->tmem_full[a], fparity, p.timing != 0, t_wait);
@@ -412,6 +423,13 @@ __device__ __forceinline__ void halo_epilogue_fast(const HaloParams& p, HaloBarr
         float v[16];
 #pragma unroll
         for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
+        if (POOL && sl == 0) {
+#pragma unroll
+          for (int i = 0; i < 16; ++i) {
+            v[i] += __shfl_xor_sync(0xffffffffu, v[i], 1);
+            v[i] += __shfl_xor_sync(0xffffffffu, v[i], 8);
+          }
+        }
         if (gin_b[sl]) {
           const uint32_t b = gb[k];
           if (scaled) {
@@ -427,7 +445,11 @@ __device__ __forceinline__ void halo_epilogue_fast(const HaloParams& p, HaloBarr
       U32x8 o;
 #pragma unroll
       for (int i = 0; i < 8; ++i) o.v[i] = w[i];
-      st_global_v8(dst_b[sl] + j * strip_b[sl] + (32 * cl - sl * (BN / 2)) * 2, o);   // one full sector per lane
+      if (POOL && sl == 0) {   // coarse strips are 4 pixels apart; one lane per 2x2 block stores
+        if (pool_lane) st_global_v8(dst_b[0] + j * (strip_b[0] >> 1) + 32 * cl * 2, o);
+      } else {
+        st_global_v8(dst_b[sl] + j * strip_b[sl] + (32 * cl - sl * (BN / 2)) * 2, o);   // one full sector per lane
+      }
     }
     tc_fence_before();
     __syncwarp();
@@ -570,7 +592,8 @@ conv_halo_kernel(const __grid_constant__ HaloParams p, const __grid_constant__ C
     do {                                                                                                   \
       if (p.fast_epi == 1) halo_epilogue_fast<JJ, BN, true, false>(p, bars, tmem_base, warp, lane, num_tiles);       \
       else if (p.fast_epi == 2) halo_epilogue_fast<JJ, BN, false, false>(p, bars, tmem_base, warp, lane, num_tiles); \
-      else halo_epilogue_fast<JJ, (BN >= 64 ? BN : 64), false, true>(p, bars, tmem_base, warp, lane, num_tiles);     \
+      else if (p.fast_epi == 3) halo_epilogue_fast<JJ, (BN >= 64 ? BN : 64), false, true>(p, bars, tmem_base, warp, lane, num_tiles); \
+      else halo_epilogue_fast<JJ, (BN >= 64 ? BN : 64), false, true, true>(p, bars, tmem_base, warp, lane, num_tiles); \
     } while (0)
 #define UB_EPI(BN)                                                                                         \
     do {                                                                                                   \
@@ -679,9 +702,11 @@ int halo_launch(const HaloParams& p_in, const CUtensorMap& a0, const CUtensorMap
       if (e.relu && !gates_in && e.split_col >= p.block_n) p.fast_epi = 1;
       else if (!e.relu && !e.bias && !e.gate_out) {
         if (e.split_col >= p.block_n) p.fast_epi = 2;
-        else if (e.split_col == p.block_n / 2 && p.block_n >= 64) p.fast_epi = 3;
+        else if (e.split_col == p.block_n / 2 && p.block_n >= 64) p.fast_epi = e.pool2_slot0 ? 4 : 3;
       }
     }
+    UB_REQUIRE(!e.pool2_slot0 || p.fast_epi == 4,
+               "conv_halo: the fused 2x2 gradient pooling needs full tiles, two equal aligned destinations and no dropout");
   }
   int grid = device_sm_count();
   if (grid > num_tiles) grid = num_tiles;

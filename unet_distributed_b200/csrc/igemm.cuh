@@ -28,6 +28,10 @@ struct IgemmEpilogue {
   // producer's whole activation tensor through `aux` -- 1/16 of the bytes and one 2-byte load per 16 columns.
   unsigned short* gate_out;
   const unsigned short* gate_in[2];
+  // dgrad, conv_halo fast path only: destination 0 is the COARSE tensor [N, H/2, W/2, dst_C[0]] and receives the sum
+  // of each 2x2 block of the gradient (ResizeNearestNeighborGrad fused into the producer); gate_in[0] then holds the
+  // coarse tensor's ReLU gates
+  int pool2_slot0;
   int split_col;       // GEMM columns >= split_col go to slot 1
   const float* bias;   // fp32 per GEMM column (tconv: per column modulo d2s_cout), or null
   int relu;

@@ -176,6 +176,17 @@ int conv3x3_fwd(ConvSrc x0, ConvSrc x1, const void* w_packed, const float* bias,
 }
 
 // ------------------------------------------------------------------------------------------------ conv3x3 dgrad
+bool conv3x3_dgrad_pool2_ok(int N, int H, int W, int Cout, int C0, int C1) {
+  static const bool no_fast = getenv("UNETB200_NO_FAST_EPI") != nullptr || getenv("UNETB200_NO_POOL2") != nullptr;
+  if (no_fast || C0 != C1 || C0 % 32 != 0) return false;
+  const int kc = pick_kc(Cout, 0);
+  if (kc == 0) return false;
+  HaloParams hp;
+  std::memset(&hp, 0, sizeof(hp));
+  if (!halo_plan(hp, N, H, W, kc, C0 + C1)) return false;
+  return hp.n_tiles == 1 && hp.block_n == C0 + C1 && hp.block_n >= 64 && H % 16 == 0 && W % (8 * hp.J) == 0;
+}
+
 int conv3x3_dgrad(const void* dz, int Cout, const void* w_packed_d, DgradDst d0, DgradDst d1, int N, int H, int W,
                   cudaStream_t s) {
   const int C1 = d1.ptr ? d1.C : 0;
@@ -202,6 +213,7 @@ int conv3x3_dgrad(const void* dz, int Cout, const void* w_packed_d, DgradDst d0,
   p.epi.dst[0] = d0.ptr; p.epi.dst_C[0] = d0.C; p.epi.aux[0] = d0.gate ? nullptr : d0.mask; p.epi.aux_C[0] = d0.C;
   p.epi.dst[1] = d1.ptr; p.epi.dst_C[1] = C1; p.epi.aux[1] = d1.gate ? nullptr : d1.mask; p.epi.aux_C[1] = C1;
   p.epi.gate_in[0] = d0.gate;
+  p.epi.pool2_slot0 = d0.pool2;
   p.epi.gate_in[1] = C1 ? d1.gate : nullptr;
   p.epi.split_col = C1 ? d0.C : INT_MAX;
   p.epi.mask_scale = d0.scale;
@@ -211,6 +223,7 @@ int conv3x3_dgrad(const void* dz, int Cout, const void* w_packed_d, DgradDst d0,
   p.epi.drop_keep = 1.0f;
   int rc = UB_OK;
   if (try_halo(p, dz, Cout, nullptr, 0, w_packed_d, d0.C + C1, Cout, s, &rc)) return rc;
+  UB_REQUIRE(!d0.pool2, "conv3x3_dgrad: fused 2x2 pooling is not available for this shape (conv3x3_dgrad_pool2_ok)");
   CUtensorMap a0, bm;
   rc = nhwc_map(&a0, dz, N, H, W, Cout, kc, b);
   if (rc) return rc;

@@ -30,7 +30,11 @@ struct DgradDst {
   const void* mask;  // same shape as ptr, or null
   float scale;
   const unsigned short* gate = nullptr;  // ReLU gates of the producer as bits (takes precedence over mask)
+  // destination 0 only: ptr is the COARSE tensor [N, H/2, W/2, C]; it receives the 2x2 block sums of the gradient
+  // (ResizeNearestNeighborGrad fused into the dgrad), gated by `gate` (coarse). Needs conv3x3_dgrad_pool2_ok().
+  int pool2 = 0;
 };
+bool conv3x3_dgrad_pool2_ok(int N, int H, int W, int Cout, int C0, int C1);
 int conv3x3_dgrad(const void* dz, int Cout, const void* w_packed_d, DgradDst d0, DgradDst d1, int N, int H, int W,
                   cudaStream_t s);
 

@@ -71,6 +71,7 @@ struct unetb200_plan {
   int ch[5];
   int c4_out;      // channels of c[4] (conv5b)
   int dc_out[4];   // channels of dc[L] (conv{9-L}b)
+  bool pool_fused[4];   // upsampling decoder: ResizeNearestNeighborGrad of level L fused into conv{9-L}a's dgrad
   // bound buffers
   uint8_t* arena = nullptr;
   float* params = nullptr;
@@ -204,6 +205,16 @@ int unetb200_plan_create(unetb200_plan** out, int N, int H, int W, int in_channe
   for (int L = 0; L < 4; ++L) {
     P->gt_da[L] = P->bump(P->act_bytes(L, P->ch[L]) / 16);
     P->gt_dc[L] = (!up && L > 0) ? P->bump(P->act_bytes(L, P->dc_out[L]) / 16) : kNoGate;
+  }
+  for (int L = 0; L < 4; ++L) {
+    // the coarse tensor below level L is c[4] (L == 3) or dc[L+1]; its gates are needed where the pooling is fused
+    P->pool_fused[L] = up && conv3x3_dgrad_pool2_ok(N, P->Hl(L), P->Wl(L), P->ch[L], P->ch[L], P->ch[L]);
+    if (!P->pool_fused[L]) continue;
+    if (L == 3) {
+      if (P->gt_c[4] == kNoGate) P->gt_c[4] = P->bump(P->act_bytes(4, P->c4_out) / 16);
+    } else if (P->gt_dc[L + 1] == kNoGate) {
+      P->gt_dc[L + 1] = P->bump(P->act_bytes(L + 1, P->dc_out[L + 1]) / 16);
+    }
   }
   const long long pixels = static_cast<long long>(N) * H * W;
   P->preds = P->bump(static_cast<size_t>(pixels) * n_cl_out * 4);
@@ -468,13 +479,19 @@ int unetb200_plan_backward(unetb200_plan* P, const float* imgs, const float* msk
       RC(fork());
     RC(conv3x3_wgrad(P->at(P->g_da[L]), P->ch[L], ConvSrc{P->at(P->u[L]), P->ch[L]}, ConvSrc{P->at(P->c[L]), P->ch[L]},
                        P->dW_(la), wsv, wsb, N, H, W, w, P->dB_(la)));
-      RC(conv3x3_dgrad(P->at(P->g_da[L]), P->ch[L], P->pkd(la), DgradDst{P->at(P->g_u[L]), P->ch[L], nullptr, 1.0f},
-                       DgradDst{P->at(P->g_c[L]), P->ch[L], P->at(P->c[L]), 1.0f, P->gate(P->gt_c[L])}, N, H, W, s));
       // up path
       const size_t below = (L == 3) ? P->c[4] : P->dc[L + 1];
       const size_t g_below = (L == 3) ? P->g_c[4] : P->g_dc[L + 1];
       const int below_C = (L == 3) ? P->c4_out : P->dc_out[L + 1];
-      if (P->ups) {
+      DgradDst d_up{P->at(P->g_u[L]), P->ch[L], nullptr, 1.0f};
+      if (P->pool_fused[L]) {   // 2x2 sums + ReluGrad of the coarse tensor straight from the dgrad epilogue
+        d_up = DgradDst{P->at(g_below), P->ch[L], nullptr, 1.0f, P->gate(L == 3 ? P->gt_c[4] : P->gt_dc[L + 1]), 1};
+      }
+      RC(conv3x3_dgrad(P->at(P->g_da[L]), P->ch[L], P->pkd(la), d_up,
+                       DgradDst{P->at(P->g_c[L]), P->ch[L], P->at(P->c[L]), 1.0f, P->gate(P->gt_c[L])}, N, H, W, s));
+      if (P->pool_fused[L]) {
+        // g_below is complete
+      } else if (P->ups) {
         RC(upsample2x2_bwd(P->at(P->g_u[L]), P->at(below), P->at(g_below), N, H / 2, W / 2, below_C, 1, s));
       } else {
         const int lt = P->tc[L];

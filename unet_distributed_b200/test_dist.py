@@ -74,9 +74,14 @@ def main(argv=None):
         batch_idx = step % num_batches
         data = np.ascontiguousarray(epoch[batch_idx, 0][start:end], dtype=np.float32)
         labels = np.ascontiguousarray(epoch[batch_idx, 1][start:end], dtype=np.float32)
-        loss_v, dice_v, _, _ = trainer.train_step_host(data, labels)
+        # steps whose numbers are printed synchronise; the others are pipelined (the copy of the next batch overlaps
+        # the kernels of this one, trainer.train_step_host)
+        report = (step + 1) % 10 == 0 or step + 1 == total
+        met = trainer.train_step_host(data, labels, wait=report)
         step += 1
-        if rank == 0 and (step % 10 == 0 or step == total):
+        if report:
+            loss_v, dice_v = float(met[0]), float(met[1])
+        if rank == 0 and report:
             dt = time.time() - t0
             print("step {}/{} (loss={:.4f}, dice={:.4f}) {:.1f} images/sec".format(
                 step, total, loss_v, dice_v, step * batch_size / dt), flush=True)
