@@ -311,11 +311,14 @@ __device__ __forceinline__ uint32_t pack_bf16x2_relu(float lo, float hi) {
 
 //   POOL  : (with SPLIT) destination 0 is the coarse tensor: each 2x2 block of the gradient is summed across lanes
 //           (lane ^ 1 = next column, lane ^ 8 = next row) in fp32 and the even-row/even-column lane stores it.
-template <int J, int BN, bool FWD, bool SPLIT, bool POOL = false>
+//   DROP  : (forward) Philox dropout after the ReLU, same element numbering as the generic epilogue.
+// With several N tiles (dgrad whose destinations split at a tile boundary) the destination is chosen per tile.
+template <int J, int BN, bool FWD, bool SPLIT, bool POOL = false, bool DROP = false>
 __device__ __forceinline__ void halo_epilogue_fast(const HaloParams& p, HaloBarriers* bars, uint32_t tmem_base,
                                                    int warp, int lane, int num_tiles) {
   static_assert(!SPLIT || BN >= 64, "split destinations need 32-column halves");
   static_assert(!POOL || (SPLIT && !FWD), "2x2 pooling of destination 0 is a split-dgrad feature");
+  static_assert(!DROP || FWD, "dropout belongs to the forward epilogue");
   constexpr int kCl = BN / 32;              // 16-column chunks per warp (the two warps of a quarter interleave)
   constexpr int kItems = J * kCl;
   constexpr bool kBiasRegs = FWD && BN <= 64;
@@ -339,6 +342,9 @@ __device__ __forceinline__ void halo_epilogue_fast(const HaloParams& p, HaloBarr
   }
   const float scale = e.mask_scale;
   const bool scaled = scale != 1.0f;
+  unsigned long long seed = 0;
+  if (DROP) seed = e.drop_seed + (e.drop_seed_add ? static_cast<unsigned long long>(__ldg(e.drop_seed_add)) : 0ull);
+  const float inv_keep = DROP ? 1.0f / e.drop_keep : 1.0f;
   constexpr int kSlots = SPLIT ? 2 : 1;
   uint32_t strip_b[kSlots], gstrip[kSlots];   // bytes / gate words between two 8-pixel strips
 #pragma unroll
@@ -358,11 +364,25 @@ __device__ __forceinline__ void halo_epilogue_fast(const HaloParams& p, HaloBarr
     char* dst_b[kSlots];
     const unsigned short* gin_b[kSlots];
     unsigned short* gout_b = nullptr;
+    if (SPLIT) {
 #pragma unroll
-    for (int sl = 0; sl < kSlots; ++sl) {
-      dst_b[sl] = reinterpret_cast<char*>(e.dst[sl]) + (pix0 * e.dst_C[sl] + e.dst_coff[sl] + half * 16) * 2;
-      gin_b[sl] = nullptr;
-      if (!FWD && e.gate_in[sl]) gin_b[sl] = e.gate_in[sl] + ((pix0 * e.aux_C[sl] + e.aux_coff[sl]) >> 4) + half;
+      for (int sl = 0; sl < kSlots; ++sl) {
+        dst_b[sl] = reinterpret_cast<char*>(e.dst[sl]) + (pix0 * e.dst_C[sl] + e.dst_coff[sl] + half * 16) * 2;
+        gin_b[sl] = nullptr;
+        if (!FWD && e.gate_in[sl]) gin_b[sl] = e.gate_in[sl] + ((pix0 * e.aux_C[sl] + e.aux_coff[sl]) >> 4) + half;
+      }
+    } else {
+      // one destination per N tile: the tile's first column decides which (warp-uniform), channels count from there
+      const int col0 = nt * BN;
+      const int sr = (!FWD && col0 >= e.split_col) ? 1 : 0;
+      const int ch0 = col0 - (sr ? e.split_col : 0) + half * 16;
+      dst_b[0] = reinterpret_cast<char*>(e.dst[sr]) + (pix0 * e.dst_C[sr] + e.dst_coff[sr] + ch0) * 2;
+      strip_b[0] = static_cast<uint32_t>(16 * e.dst_C[sr]);
+      gin_b[0] = nullptr;
+      if (!FWD && e.gate_in[sr]) {
+        gin_b[0] = e.gate_in[sr] + ((pix0 * e.aux_C[sr] + e.aux_coff[sr] + ch0) >> 4);
+        gstrip[0] = static_cast<uint32_t>(e.aux_C[sr] >> 1);
+      }
     }
     if (FWD && e.gate_out) gout_b = e.gate_out + ((pix0 * e.dst_C[0] + e.dst_coff[0]) >> 4) + half;
     const bool pool_lane = (lane & 9) == 0;   // even row and even column of the tile
@@ -409,6 +429,15 @@ __device__ __forceinline__ void halo_epilogue_fast(const HaloParams& p, HaloBarr
               const float4 bq = __ldg(bp + q);
               v[4 * q + 0] += bq.x; v[4 * q + 1] += bq.y; v[4 * q + 2] += bq.z; v[4 * q + 3] += bq.w;
             }
+          }
+        }
+        if (DROP) {   // (dropout of a negative value stays negative or zero: the ReLU in the conversion still applies)
+          const size_t elem0 = (pix0 + 8 * j) * e.dst_C[0] + e.dst_coff[0] + half * 16 + 32 * cl;
+#pragma unroll
+          for (int g = 0; g < 2; ++g) {
+            const uint32_t bits = dropout_keep_bits8(seed, e.drop_stream, elem0 / 8 + g, e.drop_keep);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) v[8 * g + i] = ((bits >> i) & 1u) ? v[8 * g + i] * inv_keep : 0.0f;
           }
         }
 #pragma unroll
@@ -591,6 +620,7 @@ conv_halo_kernel(const __grid_constant__ HaloParams p, const __grid_constant__ C
 #define UB_FAST(JJ, BN)                                                                                    \
     do {                                                                                                   \
       if (p.fast_epi == 1) halo_epilogue_fast<JJ, BN, true, false>(p, bars, tmem_base, warp, lane, num_tiles);       \
+      else if (p.fast_epi == 5) halo_epilogue_fast<JJ, BN, true, false, false, true>(p, bars, tmem_base, warp, lane, num_tiles); \
       else if (p.fast_epi == 2) halo_epilogue_fast<JJ, BN, false, false>(p, bars, tmem_base, warp, lane, num_tiles); \
       else if (p.fast_epi == 3) halo_epilogue_fast<JJ, (BN >= 64 ? BN : 64), false, true>(p, bars, tmem_base, warp, lane, num_tiles); \
       else halo_epilogue_fast<JJ, (BN >= 64 ? BN : 64), false, true, true>(p, bars, tmem_base, warp, lane, num_tiles); \
@@ -639,7 +669,10 @@ bool halo_plan(HaloParams& p, int N, int H, int W, int kc, int ncols) {
   if (H < kTH || W < 8) return false;   // small grids: several images per tile, handled by igemm
   int block_n = ncols % 256 == 0 ? 256 : ncols;
   // measured: with 256-wide tiles (16x16 level) the per-tap igemm path is as fast or faster (few super-tiles,
-  // single-buffered accumulators); the halo path pays off where the GEMM N is small
+  // single-buffered accumulators); the halo path pays off where the GEMM N is small. 256 columns on the 32x32 level
+  // and above (conv7a's dgrad: 128 + 128) run as two 128-wide N tiles: the per-tap path streams 48 KB per 512 MMA
+  // cycles there, twice what L2 delivers per SM.
+  if (ncols == 256 && H >= 32) block_n = 128;
   if (block_n != 32 && block_n != 64 && block_n != 128) return false;
   int J = W >= 25 ? 4 : (W >= 9 ? 2 : 1);
   while (J > 1 && J * block_n > 512) J >>= 1;
@@ -694,15 +727,18 @@ int halo_launch(const HaloParams& p_in, const CUtensorMap& a0, const CUtensorMap
     const IgemmEpilogue& e = p.epi;
     const bool aligned = reinterpret_cast<uintptr_t>(e.dst[0]) % 32 == 0 && reinterpret_cast<uintptr_t>(e.dst[1]) % 32 == 0 &&
                          e.dst_coff[0] % 16 == 0 && e.dst_coff[1] % 16 == 0 && e.dst_C[0] % 16 == 0 && e.dst_C[1] % 16 == 0;
-    const bool full = aligned && p.n_tiles == 1 && p.H % kTH == 0 && p.W % (8 * p.J) == 0;
-    const bool plain = e.drop_keep >= 1.0f && !e.aux[0] && !e.aux[1];
+    const bool full = aligned && p.H % kTH == 0 && p.W % (8 * p.J) == 0;
+    const bool plain = !e.aux[0] && !e.aux[1];
+    const bool dropped = e.drop_keep < 1.0f;
     const bool gates_in = e.gate_in[0] || e.gate_in[1];
+    const int ncols = p.n_tiles * p.block_n;
     p.fast_epi = 0;
     if (!no_fast && full && plain) {
-      if (e.relu && !gates_in && e.split_col >= p.block_n) p.fast_epi = 1;
-      else if (!e.relu && !e.bias && !e.gate_out) {
-        if (e.split_col >= p.block_n) p.fast_epi = 2;
-        else if (e.split_col == p.block_n / 2 && p.block_n >= 64) p.fast_epi = e.pool2_slot0 ? 4 : 3;
+      if (e.relu && !gates_in && e.split_col >= ncols && p.n_tiles == 1) p.fast_epi = dropped ? 5 : 1;
+      else if (!e.relu && !e.bias && !e.gate_out && !dropped) {
+        // one destination, or two that meet at an N-tile boundary: the destination is picked per tile
+        if (e.split_col >= ncols || e.split_col % p.block_n == 0) p.fast_epi = 2;
+        else if (p.n_tiles == 1 && e.split_col == p.block_n / 2 && p.block_n >= 64) p.fast_epi = e.pool2_slot0 ? 4 : 3;
       }
     }
     UB_REQUIRE(!e.pool2_slot0 || p.fast_epi == 4,
