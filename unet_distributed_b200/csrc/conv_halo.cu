@@ -672,7 +672,9 @@ bool halo_plan(HaloParams& p, int N, int H, int W, int kc, int ncols) {
   // single-buffered accumulators); the halo path pays off where the GEMM N is small. 256 columns on the 32x32 level
   // and above (conv7a's dgrad: 128 + 128) run as two 128-wide N tiles: the per-tap path streams 48 KB per 512 MMA
   // cycles there, twice what L2 delivers per SM.
-  if (ncols == 256 && H >= 32) block_n = 128;
+  static const int nsplit_min_h = getenv("UNETB200_HALO_NSPLIT_MINH") ? atoi(getenv("UNETB200_HALO_NSPLIT_MINH")) : 32;
+  static const int nsplit_max_cols = getenv("UNETB200_HALO_NSPLIT_MAXC") ? atoi(getenv("UNETB200_HALO_NSPLIT_MAXC")) : 256;
+  if (ncols % 128 == 0 && ncols >= 256 && ncols <= nsplit_max_cols && H >= nsplit_min_h) block_n = 128;
   if (block_n != 32 && block_n != 64 && block_n != 128) return false;
   int J = W >= 25 ? 4 : (W >= 9 ? 2 : 1);
   while (J > 1 && J * block_n > 512) J >>= 1;

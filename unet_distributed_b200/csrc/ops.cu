@@ -334,9 +334,9 @@ int conv3x3_wgrad(const void* dz, int Cout, ConvSrc x0, ConvSrc x1, float* dw, v
                  ws_bytes);
       const int J = wgrad_halo_pick_J(Cx, W);
       CUtensorMap xm, zm;
-      int rc = nhwc_map(&xm, srcs[i].ptr, N, H, W, Cx, Cx, Box{1, 18, 8 * J + 2});
+      int rc = nhwc_map(&xm, srcs[i].ptr, N, H, W, Cx, Cx, Box{1, 16, 8 * J + 2});   // column halo
       if (rc) return rc;
-      rc = nhwc_map(&zm, dz, N, H, W, Cout, Cout, Box{1, 16, 8 * J});
+      rc = nhwc_map(&zm, dz, N, H, W, Cout, Cout, Box{1, 18, 8 * J});              // row halo
       if (rc) return rc;
       rc = wgrad_halo_launch(xm, zm, N, H, W, Cx, Cout, J, dw, x0.C + C1, off, reinterpret_cast<float*>(ws), s,
                              i == 0 ? db : nullptr);   // fused: one extra MMA per K step against a tile of ones

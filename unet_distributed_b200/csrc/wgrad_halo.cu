@@ -2,15 +2,19 @@
 // per-tap wgrad engine (wgrad.cu) is issue- and L2-bound: C is so small that one (tap, Cout, Cin) tile is a sliver of
 // the tensor core and every tap re-reads both operands.
 //
-// Here a CTA walks super-tiles of 16 rows x 8J columns. Per super-tile it loads ONE halo tile of the input
-// (18 x (8J+2) pixels) and ONE tile of the output gradient, and accumulates ALL nine taps in TMEM:
-//   * the reduction (GEMM K) runs over pixels: 16 pixels per MMA = rows 2i and 2i+1 of an 8-wide strip; the strip's
+// Here a CTA walks super-tiles of 16 rows x 8J columns. Per super-tile it loads ONE tile of the input with a column
+// halo (16 x (8J+2) pixels) and ONE tile of the output gradient with a row halo (18 x 8J pixels) and accumulates ALL
+// nine taps in TMEM:
+//   dW[r, s, ci, co] = sum_q X[q + (0, s-1), ci] * dZ[q - (r-1) rows, co]        (q = p + (r-1) rows)
+//   * the reduction (GEMM K) runs over pixels q: 16 pixels per MMA = rows 2i and 2i+1 of an 8-wide strip; the strip's
 //     8 pixels are 8 consecutive smem rows and the stride to the next image row is the descriptor's SBO;
-//   * filter columns are stacked along GEMM M: both operands are MN-major, and the "next 32/64-channel atom along M"
-//     (the descriptor's LBO) is set to ONE pixel row, so atom a of the A operand is the same halo tile shifted by a
-//     pixels = tap column s0+a. One MMA therefore produces dW for up to four filter columns at once:
-//     D[(s, ci), co] += sum_pixels X[pixel + (r, s), ci] * dZ[pixel, co];
-//   * filter rows r = 0..2 are three start addresses into the same halo tile and three accumulators.
+//   * filter COLUMNS are stacked along GEMM M: both operands are MN-major, and the "next channel atom along M" (the
+//     A descriptor's LBO) is ONE pixel row, so atom a of A is the X tile shifted by a pixels = tap column s0 + a;
+//   * filter ROWS are stacked along GEMM N the same way: the B descriptor's LBO is one IMAGE row of the dZ tile, so
+//     atom a of B is dZ shifted by a rows = filter row r = 2 - a. One MMA (M = 128, N = 3*Cz) therefore produces up to
+//     4 x 3 taps: D[(s, ci), (a, co)] -- a 128 x 96 x 16 MMA costs 56 cycles (32 + N/4, csrc/mma_rate.cu) where the
+//     three 128 x 32 x 16 MMAs of the earlier row-by-row version cost 120. Operand reads from shared memory, not math,
+//     bound these layers.
 // Partial results of the CTAs are summed in a fixed order by wgrad_halo_reduce_kernel (bit-reproducible).
 #include "wgrad.cuh"
 
@@ -56,18 +60,22 @@ __device__ __forceinline__ uint64_t desc_pair(uint32_t lo, uint32_t hi) {
 // few scalar instructions per MMA; the run-time-generic loop with 64-bit descriptor arithmetic ran at ~75).
 template <int J, int CX, int CZ>
 __device__ __forceinline__ void wgrad_halo_mma_role(WgradHaloBarriers* bars, uint32_t smem_addr, uint32_t stage_bytes,
-                                                    uint32_t halo_stride, int stages, uint32_t tmem_base, int my_tiles) {
-  constexpr int P = 8 * J + 2;
+                                                    uint32_t x_stride, int stages, uint32_t tmem_base, int my_tiles) {
+  constexpr int P = 8 * J + 2;                 // X tile pitch (column halo)
+  constexpr int PZ = 8 * J;                    // dZ tile pitch
   constexpr uint32_t XROW = CX * 2, ZROW = CZ * 2;
-  constexpr int GROUPS = CX == 32 ? 1 : 2;
-  const uint32_t idesc = umma_idesc_bf16(128, CZ, 1, 1);
-  // A: atoms along M are one pixel row apart (LBO = row bytes); 8-pixel groups along K are one image row apart
-  const uint32_t x_hi =
-      static_cast<uint32_t>(umma_smem_desc(0, XROW, P * XROW, CX == 64 ? UMMA_SW_128B : UMMA_SW_64B) >> 32);
-  const uint32_t z_hi =
-      static_cast<uint32_t>(umma_smem_desc(0, 0, 8 * J * ZROW, CZ == 64 ? UMMA_SW_128B : UMMA_SW_64B) >> 32);
+  constexpr int GROUPS = CX == 32 ? 1 : 2;     // MMAs per K block: 4 stacked filter columns (Cx=32) or 2 x 2 (Cx=64)
+  constexpr uint32_t XSW = CX == 64 ? UMMA_SW_128B : UMMA_SW_64B;
+  constexpr uint32_t ZSW = CZ == 64 ? UMMA_SW_128B : UMMA_SW_64B;
+  const uint32_t idesc = umma_idesc_bf16(128, 3 * CZ, 1, 1);
+  // A: atoms along M one pixel row apart (LBO = row bytes); 8-pixel groups along K one image row apart (SBO).
+  // B: atoms along N one IMAGE row apart (LBO = PZ rows); 8-pixel groups along K one image row apart (SBO).
+  const uint32_t x_hi = static_cast<uint32_t>(umma_smem_desc(0, XROW, P * XROW, XSW) >> 32);
+  const uint32_t z_hi = static_cast<uint32_t>(umma_smem_desc(0, PZ * ZROW, PZ * ZROW, ZSW) >> 32);
   // LBO lives in bits [16,30) of the low word
   const uint32_t x_lo_const = static_cast<uint32_t>(umma_smem_desc(0, XROW, P * XROW, UMMA_SW_NONE) & 0xFFFFFFFFu);
+  const uint32_t z_lo_const =
+      static_cast<uint32_t>(umma_smem_desc(0, PZ * ZROW, PZ * ZROW, UMMA_SW_NONE) & 0xFFFFFFFFu);
   int stage = 0;
   uint32_t phase = 0;
   for (int k = 0; k < my_tiles; ++k) {
@@ -75,23 +83,21 @@ __device__ __forceinline__ void wgrad_halo_mma_role(WgradHaloBarriers* bars, uin
     tc_fence_after();
     const uint32_t sx = smem_addr + static_cast<uint32_t>(stage) * stage_bytes;
     const uint32_t x_lo = x_lo_const + (sx >> 4);
-    const uint32_t z_lo = (sx + halo_stride) >> 4;
+    const uint32_t z_lo = z_lo_const + ((sx + x_stride) >> 4);
     if (elect_one()) {
       const uint32_t first = k ? 1u : 0u;
-      // i: pairs of image rows (16 pixels of reduction), j: strips, r: filter rows, g: groups of stacked filter columns
+      // i: pairs of image rows (16 pixels of reduction), j: strips, g: groups of stacked filter columns.
+      // X rows 2i, 2i+1 of the tile meet dZ tile rows 2i + a, 2i + 1 + a (the dZ tile starts one row above).
 #pragma unroll
       for (int i = 0; i < kTH / 2; ++i) {
 #pragma unroll
         for (int j = 0; j < J; ++j) {
 #pragma unroll
-          for (int r = 0; r < 3; ++r) {
-#pragma unroll
-            for (int g = 0; g < GROUPS; ++g) {
-              umma_f16(tmem_base + static_cast<uint32_t>((r * GROUPS + g) * CZ),
-                       desc_pair(x_lo + static_cast<uint32_t>(((2 * i + r) * P + 8 * j + 2 * g) * (XROW >> 4)), x_hi),
-                       desc_pair(z_lo + static_cast<uint32_t>((2 * i * 8 * J + 8 * j) * (ZROW >> 4)), z_hi), idesc,
-                       (i == 0 && j == 0) ? first : 1u);
-            }
+          for (int g = 0; g < GROUPS; ++g) {
+            umma_f16(tmem_base + static_cast<uint32_t>(g * 3 * CZ),
+                     desc_pair(x_lo + static_cast<uint32_t>((2 * i * P + 8 * j + 2 * g) * (XROW >> 4)), x_hi),
+                     desc_pair(z_lo + static_cast<uint32_t>((2 * i * PZ + 8 * j) * (ZROW >> 4)), z_hi), idesc,
+                     (i == 0 && j == 0) ? first : 1u);
           }
         }
       }
@@ -112,9 +118,9 @@ wgrad_halo_kernel(const __grid_constant__ WgradHaloParams p, const __grid_consta
 
   const int P = 8 * p.J + 2;
   const int xrow = p.Cx * 2, zrow = p.Cz * 2;
-  const int halo_bytes = (kTH + 2) * P * xrow;
-  const int z_bytes = kTH * 8 * p.J * zrow;
-  // 1 KiB of slack after the halo tile: the junk filter column (s = 3) reads up to 3 pixel rows past its end
+  const int halo_bytes = kTH * P * xrow;                   // X: 16 rows x (8J+2) columns
+  const int z_bytes = (kTH + 2) * 8 * p.J * zrow;          // dZ: 18 rows x 8J columns
+  // slack after the X tile: the junk filter column (s = 3) reads up to 3 pixel rows past its end
   const int halo_stride = round_up_1k(halo_bytes + 4 * xrow);
   const int stage_bytes = halo_stride + round_up_1k(z_bytes);
   float* bias_scratch = reinterpret_cast<float*>(smem + p.stages * stage_bytes);
@@ -124,7 +130,7 @@ wgrad_halo_kernel(const __grid_constant__ WgradHaloParams p, const __grid_consta
   const int lane = threadIdx.x & 31;
   const int num_tiles = p.N * p.tiles_h * p.tiles_w;
   const int groups = p.Cx == 32 ? 1 : 2;          // stacked filter columns per MMA: 4 (Cx=32) or 2 (Cx=64)
-  const int n_acc = 3 * groups;
+  const int n_acc = 3 * groups;                   // accumulator g holds filter rows 2, 1, 0 side by side (3*Cz columns)
   uint32_t tmem_cols = 32;
   while (tmem_cols < static_cast<uint32_t>(n_acc * p.Cz)) tmem_cols <<= 1;
   const int my_tiles = (num_tiles > static_cast<int>(blockIdx.x))
@@ -165,8 +171,8 @@ wgrad_halo_kernel(const __grid_constant__ WgradHaloParams p, const __grid_consta
         mbar_wait(&bars->empty[stage], phase ^ 1u);
         uint8_t* sx = smem + stage * stage_bytes;
         mbar_arrive_expect_tx(&bars->full[stage], static_cast<uint32_t>(halo_bytes + z_bytes));
-        tma_load_4d(sx, &tmX, &bars->full[stage], 0, w0 - 1, h0 - 1, n);
-        tma_load_4d(sx + halo_stride, &tmZ, &bars->full[stage], 0, w0, h0, n);
+        tma_load_4d(sx, &tmX, &bars->full[stage], 0, w0 - 1, h0, n);
+        tma_load_4d(sx + halo_stride, &tmZ, &bars->full[stage], 0, w0, h0 - 1, n);
         if (++stage == p.stages) { stage = 0; phase ^= 1u; }
       }
     }
@@ -206,7 +212,7 @@ wgrad_halo_kernel(const __grid_constant__ WgradHaloParams p, const __grid_consta
       const int t = threadIdx.x - 128;
       const int chunks = p.Cz >> 3;
       const int q = t & (chunks - 1);
-      const int rows = kTH * 8 * p.J;
+      const int row_begin = 8 * p.J, row_end = (kTH + 1) * 8 * p.J;   // skip the dZ tile's halo rows
       float bsum[8];
 #pragma unroll
       for (int j = 0; j < 8; ++j) bsum[j] = 0.0f;
@@ -215,7 +221,7 @@ wgrad_halo_kernel(const __grid_constant__ WgradHaloParams p, const __grid_consta
       for (int k = 0; k < my_tiles; ++k) {
         mbar_wait(&bars->full[stage], phase);
         const uint8_t* zt = smem + stage * stage_bytes + halo_stride;
-        for (int row = t / chunks; row < rows; row += 128 / chunks) {
+        for (int row = row_begin + t / chunks; row < row_end; row += 128 / chunks) {
           const int phys = p.Cz == 64 ? (q ^ (row & 7)) : (q ^ ((row >> 1) & 3));
           const uint4 v = *reinterpret_cast<const uint4*>(zt + row * zrow + phys * 16);
           bsum[0] += bf16_lo(v.x); bsum[1] += bf16_hi(v.x); bsum[2] += bf16_lo(v.y); bsum[3] += bf16_hi(v.y);
@@ -241,8 +247,9 @@ wgrad_halo_kernel(const __grid_constant__ WgradHaloParams p, const __grid_consta
     for (int r = 0; r < 3; ++r) {
       for (int g = 0; g < groups; ++g) {
         const int s = (p.Cx == 32 ? 0 : 2 * g) + a;
+        // filter row r is B atom 2 - r of accumulator g
         const uint32_t t_row = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) +
-                               static_cast<uint32_t>((r * groups + g) * p.Cz);
+                               static_cast<uint32_t>((g * 3 + (2 - r)) * p.Cz);
         for (int c = 0; c < p.Cz; c += 16) {
           uint32_t v[16];
           if (my_tiles > 0) {
@@ -339,7 +346,7 @@ int wgrad_halo_launch(const CUtensorMap& x_map, const CUtensorMap& z_map, int N,
   p.ws = ws;
   p.with_bias = db ? 1 : 0;
   const int P = 8 * J + 2;
-  const int stage_bytes = round_up_1k((kTH + 2) * P * Cx * 2 + 4 * Cx * 2) + round_up_1k(kTH * 8 * J * Cz * 2);
+  const int stage_bytes = round_up_1k(kTH * P * Cx * 2 + 4 * Cx * 2) + round_up_1k((kTH + 2) * 8 * J * Cz * 2);
   int stages = (225 * 1024 - 1024 - kBiasScratch - static_cast<int>(sizeof(WgradHaloBarriers))) / stage_bytes;
   if (stages > kMaxStages) stages = kMaxStages;
   UB_REQUIRE(stages >= 2, "wgrad_halo: stage of %d bytes does not fit twice in shared memory", stage_bytes);
