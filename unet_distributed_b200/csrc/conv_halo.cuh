@@ -33,6 +33,7 @@ struct HaloParams {
   int acc_double;         // two accumulator sets: epilogue overlaps the next super-tile's MMAs
   int fast_epi;           // set by halo_launch: 0 generic epilogue, 1 forward, 2 dgrad, 3 dgrad split at block_n/2,
                           // 4 = 3 with destination 0 summed 2x2 onto the coarse grid
+  int rp;                 // row-pair variant (conv_halo_rp.cu): 32-row super-tiles, accumulators 2 * block_n wide
   IgemmEpilogue epi;      // d2s_cout must be 0
 };
 
@@ -41,5 +42,12 @@ bool halo_plan(HaloParams& p, int N, int H, int W, int kc, int ncols);
 
 int halo_launch(const HaloParams& p, const CUtensorMap& a0, const CUtensorMap& a1, const CUtensorMap& b,
                 cudaStream_t stream);
+
+// Row-pair variant for GEMM N = 32 / 64 (conv_halo_rp.cu): plan, which lean epilogue (0 = not covered) and launch.
+// The activation tensor map must have a box of 34 rows x (8J+2) columns.
+bool halo_rp_plan(HaloParams& p, int N, int H, int W, int kc, int ncols);
+int halo_rp_epilogue_code(const HaloParams& p);
+int halo_rp_launch(const HaloParams& p, const CUtensorMap& a0, const CUtensorMap& a1, const CUtensorMap& b,
+                   cudaStream_t stream);
 
 }  // namespace ub

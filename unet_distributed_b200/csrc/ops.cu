@@ -101,6 +101,34 @@ int pick_block_n(int ncols_per_dest) {
 // Returns true when it took the launch (status in *rc).
 bool try_halo(const IgemmParams& p, const void* src0, int C0, const void* src1, int C1, const void* w_packed,
               int ncols, int ktot, cudaStream_t s, int* rc) {
+  {   // row-pair variant first: twice the GEMM N per A-operand read on the 32/64-column layers
+    HaloParams rp;
+    std::memset(&rp, 0, sizeof(rp));
+    if (halo_rp_plan(rp, p.N, p.H, p.W, p.kc, ncols)) {
+      rp.num_src = p.num_src;
+      for (int i = 0; i < 2; ++i) {
+        rp.src_kblocks[i] = p.src_kblocks[i];
+        rp.src_ci_off[i] = p.src_ci_off[i];
+      }
+      rp.epi = p.epi;
+      rp.fast_epi = halo_rp_epilogue_code(rp);
+      if (rp.fast_epi) {
+        const Box hb = {1, 34, 8 * rp.J + 2};
+        CUtensorMap a0, a1, bm;
+        *rc = nhwc_map(&a0, src0, p.N, p.H, p.W, C0, p.kc, hb);
+        if (*rc) return true;
+        a1 = a0;
+        if (C1) {
+          *rc = nhwc_map(&a1, src1, p.N, p.H, p.W, C1, p.kc, hb);
+          if (*rc) return true;
+        }
+        *rc = weight_map(&bm, w_packed, ncols, 9, ktot, p.kc, rp.block_n);
+        if (*rc) return true;
+        *rc = halo_rp_launch(rp, a0, a1, bm, s);
+        return true;
+      }
+    }
+  }
   HaloParams hp;
   std::memset(&hp, 0, sizeof(hp));
   if (!halo_plan(hp, p.N, p.H, p.W, p.kc, ncols)) return false;
