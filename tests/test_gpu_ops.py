@@ -53,6 +53,9 @@ CONV_CASES = [
     (5, 4, 4, 128, 0, 128),        # four images per tile (64x64 inputs reach 4x4)
     (1, 15, 15, 64, 0, 128),       # ragged grid (240x240 inputs reach 15x15)
     (5, 64, 64, 32, 0, 64),        # 160 tiles > 148 SMs
+    (2, 64, 32, 32, 32, 32),       # row-pair kernel: two 32-channel sources, N = 32, four strips
+    (1, 32, 64, 64, 0, 32),        # row-pair kernel: 64-channel blocks, N = 32
+    (1, 96, 40, 32, 0, 32),        # row-pair kernel: three row tiles, width 40 -> one strip per tile
 ]
 
 
