@@ -140,11 +140,14 @@ __device__ __forceinline__ void rp_mma_role(const HaloParams& p, RpBarriers* bar
 // ------------------------------------------------------------------------------------------------ epilogue
 // Accumulator row m = 8 t + column: pixel (h0 + 2t, w0 + 8j + column); accumulator columns [0, BN) belong to that
 // pixel, [BN, 2BN) to the pixel one image row below. Items are 16-column chunks; the two warps of a TMEM lane quarter
-// take alternate chunks. SPLIT: channels [BN/2, BN) go to destination 1.
-template <int J, int BN, bool FWD, bool SPLIT>
+// take alternate chunks. SPLIT: channels [BN/2, BN) go to destination 1. POOL (with SPLIT): destination 0 is the coarse
+// tensor and receives the 2x2 block sums -- the two rows of a block are the two halves of this lane's accumulator row,
+// the two columns are lanes l and l ^ 1; the even-column lane stores.
+template <int J, int BN, bool FWD, bool SPLIT, bool POOL = false>
 __device__ __forceinline__ void rp_epilogue(const HaloParams& p, RpBarriers* bars, uint32_t tmem_base, int warp, int lane,
                                             int num_tiles) {
   static_assert(!SPLIT || (BN == 64 && !FWD), "split destinations: dgrad into two 32-channel tensors");
+  static_assert(!POOL || SPLIT, "2x2 pooling of destination 0 is a split-dgrad feature");
   constexpr int kCl = 2 * BN / 32;          // 16-column chunks per warp and strip
   constexpr int kItems = J * kCl;
   constexpr int kBiasCl = BN / 32;
@@ -174,7 +177,7 @@ __device__ __forceinline__ void rp_epilogue(const HaloParams& p, RpBarriers* bar
   for (int sl = 0; sl < kSlots; ++sl) {
     strip_b[sl] = static_cast<uint32_t>(16 * e.dst_C[sl]);                 // 8 pixels, bytes
     row_b[sl] = static_cast<uint32_t>(2 * p.W * e.dst_C[sl]);             // one image row, bytes
-    const int gc = FWD ? e.dst_C[sl] : e.aux_C[sl];
+    const int gc = (FWD || (POOL && sl == 0)) ? e.dst_C[sl] : e.aux_C[sl];
     gstrip[sl] = static_cast<uint32_t>(gc >> 1);                          // 8 pixels, gate words
     grow[sl] = static_cast<uint32_t>((p.W * gc) >> 4);                    // one image row, gate words
   }
@@ -195,6 +198,13 @@ __device__ __forceinline__ void rp_epilogue(const HaloParams& p, RpBarriers* bar
       if (!FWD && e.gate_in[sl]) gin_b[sl] = e.gate_in[sl] + ((pix0 * e.aux_C[sl] + e.aux_coff[sl]) >> 4) + half;
     }
     if (FWD && e.gate_out) gout_b = e.gate_out + ((pix0 * e.dst_C[0] + e.dst_coff[0]) >> 4) + half;
+    const bool pool_lane = (lane & 1) == 0;   // even column (every accumulator row is an even image row)
+    if (POOL) {   // destination 0 on the coarse grid
+      const size_t cpix0 = (static_cast<size_t>(n) * (p.H >> 1) + ((h0 >> 1) + th)) * (p.W >> 1) + ((w0 + twl) >> 1);
+      dst_b[0] = reinterpret_cast<char*>(e.dst[0]) + (cpix0 * e.dst_C[0] + e.dst_coff[0] + half * 16) * 2;
+      gin_b[0] = nullptr;
+      if (e.gate_in[0] && pool_lane) gin_b[0] = e.gate_in[0] + ((cpix0 * e.dst_C[0] + e.dst_coff[0]) >> 4) + half;
+    }
     uint32_t gb[kItems];
     if (!FWD) {
 #pragma unroll
@@ -204,12 +214,17 @@ __device__ __forceinline__ void rp_epilogue(const HaloParams& p, RpBarriers* bar
         const int chl = 32 * cl - par * BN;                 // first channel of the chunk pair (before + half * 16)
         const int sl = (SPLIT && chl >= BN / 2) ? 1 : 0;
         gb[k] = 0xFFFFu;
-        if (gin_b[sl]) gb[k] = __ldg(gin_b[sl] + j * gstrip[sl] + par * grow[sl] + ((chl - sl * (BN / 2)) >> 4));
+        if (POOL && sl == 0) {   // one coarse gate word per block, fetched with the lower-row item
+          if (par == 1 && gin_b[0]) gb[k] = __ldg(gin_b[0] + j * (gstrip[0] >> 1) + (chl >> 4));
+        } else if (gin_b[sl]) {
+          gb[k] = __ldg(gin_b[sl] + j * gstrip[sl] + par * grow[sl] + ((chl - sl * (BN / 2)) >> 4));
+        }
       }
     }
     mbar_wait(&bars->tmem_full[a], fparity);
     tc_fence_after();
     const uint32_t t_acc = t_lane + static_cast<uint32_t>(a * J * 2 * BN);
+    float vs[POOL ? 16 : 1];   // upper-row values of the block waiting for the lower row
 #pragma unroll
     for (int k = 0; k < kItems; ++k) {
       const int j = k / kCl, cl = k % kCl;
@@ -236,6 +251,18 @@ __device__ __forceinline__ void rp_epilogue(const HaloParams& p, RpBarriers* bar
         float v[16];
 #pragma unroll
         for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
+        if (POOL && sl == 0) {
+          if (par == 0) {
+#pragma unroll
+            for (int i = 0; i < 16; ++i) vs[POOL ? i : 0] = v[i];
+            continue;
+          }
+#pragma unroll
+          for (int i = 0; i < 16; ++i) {
+            v[i] += vs[POOL ? i : 0];
+            v[i] += __shfl_xor_sync(0xffffffffu, v[i], 1);
+          }
+        }
         if (gin_b[sl]) {
           const uint32_t b = gb[k];
           if (scaled) {
@@ -251,7 +278,11 @@ __device__ __forceinline__ void rp_epilogue(const HaloParams& p, RpBarriers* bar
       U32x8 o;
 #pragma unroll
       for (int i = 0; i < 8; ++i) o.v[i] = w[i];
-      st_global_v8(dst_b[sl] + j * strip_b[sl] + par * row_b[sl] + (chl - sl * (BN / 2)) * 2, o);
+      if (POOL && sl == 0) {   // coarse strips are 4 pixels apart
+        if (pool_lane) st_global_v8(dst_b[0] + j * (strip_b[0] >> 1) + chl * 2, o);
+      } else {
+        st_global_v8(dst_b[sl] + j * strip_b[sl] + par * row_b[sl] + (chl - sl * (BN / 2)) * 2, o);
+      }
     }
     tc_fence_before();
     __syncwarp();
@@ -377,7 +408,8 @@ conv_halo_rp_kernel(const __grid_constant__ HaloParams p, const __grid_constant_
     do {                                                                                                \
       if (p.fast_epi == 1) rp_epilogue<JJ, NN, true, false>(p, bars, tmem_base, warp, lane, num_tiles);  \
       else if (p.fast_epi == 2) rp_epilogue<JJ, NN, false, false>(p, bars, tmem_base, warp, lane, num_tiles); \
-      else rp_epilogue<JJ, 64, false, true>(p, bars, tmem_base, warp, lane, num_tiles);                  \
+      else if (p.fast_epi == 3) rp_epilogue<JJ, 64, false, true>(p, bars, tmem_base, warp, lane, num_tiles); \
+      else rp_epilogue<JJ, 64, false, true, true>(p, bars, tmem_base, warp, lane, num_tiles);            \
     } while (0)
 #define UB_RP_EPI_J(NN)                      \
     do {                                     \
@@ -439,24 +471,25 @@ bool halo_rp_plan(HaloParams& p, int N, int H, int W, int kc, int ncols) {
   return true;
 }
 
-// fast_epi code (1 forward, 2 dgrad, 3 dgrad split) if the lean row-pair epilogue covers this epilogue, else 0.
+// fast_epi code (1 forward, 2 dgrad, 3 dgrad split, 4 dgrad split + 2x2 pooling of destination 0) if the lean row-pair epilogue covers this epilogue, else 0.
 int halo_rp_epilogue_code(const HaloParams& p) {
   const IgemmEpilogue& e = p.epi;
   const bool aligned = reinterpret_cast<uintptr_t>(e.dst[0]) % 32 == 0 && reinterpret_cast<uintptr_t>(e.dst[1]) % 32 == 0 &&
                        e.dst_coff[0] % 16 == 0 && e.dst_coff[1] % 16 == 0 && e.dst_C[0] % 16 == 0 && e.dst_C[1] % 16 == 0;
-  if (!aligned || e.aux[0] || e.aux[1] || e.drop_keep < 1.0f || e.pool2_slot0 || e.d2s_cout) return 0;
+  if (!aligned || e.aux[0] || e.aux[1] || e.drop_keep < 1.0f || e.d2s_cout) return 0;
+  if (e.pool2_slot0 && !(p.block_n == 64 && e.split_col == 32 && !e.relu && !e.bias && !e.gate_out)) return 0;
   const bool gates_in = e.gate_in[0] || e.gate_in[1];
   if (e.relu && !gates_in && e.split_col >= p.block_n) return 1;
   if (!e.relu && !e.bias && !e.gate_out) {
     if (e.split_col >= p.block_n) return 2;
-    if (p.block_n == 64 && e.split_col == 32) return 3;
+    if (p.block_n == 64 && e.split_col == 32) return e.pool2_slot0 ? 4 : 3;
   }
   return 0;
 }
 
 int halo_rp_launch(const HaloParams& p, const CUtensorMap& a0, const CUtensorMap& a1, const CUtensorMap& b,
                    cudaStream_t stream) {
-  UB_REQUIRE(p.rp == 1 && p.fast_epi >= 1 && p.fast_epi <= 3, "conv_halo_rp: not a row-pair plan");
+  UB_REQUIRE(p.rp == 1 && p.fast_epi >= 1 && p.fast_epi <= 4, "conv_halo_rp: not a row-pair plan");
   const size_t smem = rp_smem_bytes(p);
   UB_REQUIRE(smem <= 227 * 1024, "conv_halo_rp: %zu bytes of shared memory requested", smem);
   static bool attr_set[64] = {false};
