@@ -60,54 +60,78 @@ def load_peaks():
 
 
 class ClockSampler:
-    """nvidia-smi clocks and throttle reasons sampled every 200 ms during the timed region."""
-    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
-         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
-         "clocks_event_reasons.sw_power_cap")
+    """SM clock and throttle reasons sampled DURING the timed region: an in-process NVML thread polling every ~4 ms
+    (the timed region of the default run is ~80 ms, too short for nvidia-smi's own loop); falls back to one
+    nvidia-smi query if NVML is not importable."""
+    REASONS = ((0x8, "hw_slowdown"), (0x40, "hw_thermal_slowdown"), (0x20, "sw_thermal_slowdown"),
+               (0x4, "sw_power_cap"))
 
     def __init__(self, gpu_index=0):
-        self.proc, self.path = None, f"/tmp/unetb200_clocks_{os.getpid()}.csv"
         self.gpu = gpu_index
+        self.samples, self.reasons, self.max_mhz = [], set(), None
+        self._stop, self._thread, self._h, self._nv = False, None, None, None
+
+    def _handle(self):
+        import pynvml as nv
+        nv.nvmlInit()
+        try:
+            import torch
+            uuid = str(torch.cuda.get_device_properties(self.gpu).uuid)
+            if not uuid.startswith("GPU-"):
+                uuid = "GPU-" + uuid
+            try:
+                h = nv.nvmlDeviceGetHandleByUUID(uuid)
+            except TypeError:
+                h = nv.nvmlDeviceGetHandleByUUID(uuid.encode())
+        except Exception:
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES", "")
+            idx = int(vis.split(",")[self.gpu]) if vis and vis.split(",")[self.gpu].isdigit() else self.gpu
+            h = nv.nvmlDeviceGetHandleByIndex(idx)
+        return nv, h
+
+    def _loop(self):
+        nv, h = self._nv, self._h
+        while not self._stop:
+            try:
+                self.samples.append(float(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)))
+                try:
+                    mask = int(nv.nvmlDeviceGetCurrentClocksEventReasons(h))
+                except Exception:
+                    mask = int(nv.nvmlDeviceGetCurrentClocksThrottleReasons(h))
+                for bit, name in self.REASONS:
+                    if mask & bit:
+                        self.reasons.add(name)
+            except Exception:
+                pass
+            time.sleep(0.004)
 
     def start(self):
         try:
-            self.f = open(self.path, "w")
-            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                                          "-lms", "200", "-i", str(self.gpu)], stdout=self.f,
-                                         stderr=subprocess.DEVNULL)
+            self._nv, self._h = self._handle()
+            self.max_mhz = float(self._nv.nvmlDeviceGetMaxClockInfo(self._h, self._nv.NVML_CLOCK_SM))
+            import threading
+            self._thread = threading.Thread(target=self._loop, daemon=True)
+            self._thread.start()
         except Exception:
-            self.proc = None
+            self._thread = None
 
     def stop(self):
         out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
-        if self.proc is None:
-            return out
-        self.proc.terminate()
-        try:
-            self.proc.wait(timeout=5)
-        except Exception:
-            self.proc.kill()
-        self.f.close()
-        sm, mx, reasons = [], [], set()
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        try:
-            for line in open(self.path):
-                parts = [x.strip() for x in line.split(",")]
-                if len(parts) < 8:
-                    continue
-                try:
-                    sm.append(float(parts[1]))
-                    mx.append(float(parts[2]))
-                except ValueError:
-                    continue
-                for nm, v in zip(names, parts[4:8]):
-                    if v.lower().startswith("active"):
-                        reasons.add(nm)
-            os.remove(self.path)
+        if self._thread is not None:
+            self._stop = True
+            self._thread.join(timeout=2)
+            if self.samples:
+                out.update(sm_mhz=statistics.median(self.samples), sm_max_mhz=self.max_mhz,
+                           reasons=sorted(self.reasons), samples=len(self.samples), source="nvml, 4 ms polling")
+                return out
+        try:   # fallback: a single nvidia-smi query right after the timed region
+            q = "clocks.sm,clocks.max.sm"
+            r = subprocess.run(["nvidia-smi", f"--query-gpu={q}", "--format=csv,noheader,nounits", "-i", str(self.gpu)],
+                               stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True, timeout=10)
+            parts = [x.strip() for x in r.stdout.strip().split(",")]
+            out.update(sm_mhz=float(parts[0]), sm_max_mhz=float(parts[1]), samples=1, source="nvidia-smi after the run")
         except Exception:
             pass
-        if sm:
-            out.update(sm_mhz=statistics.median(sm), sm_max_mhz=max(mx), reasons=sorted(reasons), samples=len(sm))
         return out
 
 
@@ -322,7 +346,7 @@ def run_b200(args):
                             "stream, every step's metrics are read back; last step's loss %.4f" % float(e2e_last[0])},
             "gpu_launches": int(launches),
             "roofline": {
-                "kernel": "conv_halo_kernel + igemm_kernel (3x3 conv / transposed conv forward + dgrad, tcgen05 "
+                "kernel": "conv_halo_rp_kernel + conv_halo_kernel + igemm_kernel (3x3 conv / transposed conv forward + dgrad, tcgen05 "
                           "implicit GEMM; every launch of the class in a step)",
                 "bound": "tensor", "achieved": achieved, "peak": peak_tf, "unit": "TFLOP/s",
                 "frac": achieved / peak_tf if peak_tf else None, "traffic": traffic,

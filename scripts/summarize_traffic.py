@@ -50,9 +50,9 @@ with open(f"profiles/{tag}_ncu_launches_step.csv", "w") as f:
         k = re.sub(r"\(.*", "", l["name"]).split("::")[-1]
         f.write(f"{i},{k},{l.get('grid','')},{l.get('gpu__time_duration.sum',0):.2f},{l.get('dram__bytes_read.sum',0):.0f},"
                 f"{l.get('dram__bytes_write.sum',0):.0f},{l.get('sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_elapsed',0):.1f}\n")
-conv = [agg[k] for k in agg if k.startswith("conv_halo_kernel") or k.startswith("igemm_kernel")]
+conv = [agg[k] for k in agg if k.startswith("conv_halo") or k.startswith("igemm_kernel")]
 n = sum(c[0] for c in conv)
 json.dump({"igemm_dram_bytes_per_launch": sum(c[2] + c[3] for c in conv) / n, "launches": n,
            "source": f"profiles/{tag}_ncu_step_traffic.txt (ncu dram__bytes_read.sum + dram__bytes_write.sum, "
-                     "conv_halo_kernel + igemm_kernel launches of one training step)"},
+                     "conv_halo_rp_kernel + conv_halo_kernel + igemm_kernel launches of one training step)"},
           open("profiles/traffic.json", "w"), indent=1)
