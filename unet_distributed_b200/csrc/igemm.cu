@@ -1,5 +1,7 @@
 #include "igemm.cuh"
 
+#include <cstdlib>
+
 #include "common.h"
 #include "ptx.cuh"
 
@@ -7,7 +9,8 @@ namespace ub {
 
 namespace {
 
-constexpr int kThreads = 192;  // warp0: TMA producer, warp1: MMA issuer + TMEM owner, warps 2..5: epilogue
+constexpr int kThreads = 320;  // warp0: TMA producer, warp1: MMA issuer + TMEM owner, warps 2..9: epilogue (two per
+                               // TMEM lane quarter, alternating column groups: layers with a short K are epilogue-bound)
 constexpr int kMaxStages = 8;
 
 struct __align__(8) IgemmBarriers {
@@ -56,7 +59,7 @@ igemm_kernel(const __grid_constant__ IgemmParams p, const __grid_constant__ CUte
     }
     for (int a = 0; a < 2; ++a) {
       mbar_init(&bars->tmem_full[a], 1);
-      mbar_init(&bars->tmem_empty[a], 4);
+      mbar_init(&bars->tmem_empty[a], 8);
     }
     mbar_fence_init();
     tma_prefetch_desc(&tmA0);
@@ -140,6 +143,7 @@ igemm_kernel(const __grid_constant__ IgemmParams p, const __grid_constant__ CUte
   } else {
     // ------------------------------------------------------------ epilogue (4 warps, one TMEM lane quarter each)
     const int quarter = warp & 3;
+    const int half = (warp - 2) >> 2;   // which of the two warps of this quarter
     const int m = quarter * 32 + lane;
     const int tw = m % p.TW;
     const int th = (m / p.TW) % p.TH;
@@ -153,6 +157,104 @@ igemm_kernel(const __grid_constant__ IgemmParams p, const __grid_constant__ CUte
       const int n = n0 + tn, h = h0 + th, w = w0 + tw;
       const bool valid = (n < p.N) && (h < p.H) && (w < p.W);
       const int col0 = nt * p.block_n;  // first GEMM column of this tile
+
+      if (p.lean) {
+        // Lean epilogue: full tiles, 32-byte aligned destinations, no dropout, no tensor masks. Everything that does
+        // not depend on the 16-column chunk is computed once per tile, two chunks are in flight per TMEM wait and a
+        // lane stores one full 32-byte sector per chunk. (ncu: the general code below spends ~300 instructions per
+        // chunk with one warp per scheduler -- ~1000 cycles per chunk; the transposed-conv layers, whose K is 64,
+        // were bound by it: 0.125 ms for the 64x64 -> 128x128 layer.)
+        int slot = 0, chb = col0;
+        if (e.d2s_cout == 0 && col0 >= e.split_col) { slot = 1; chb = col0 - e.split_col; }
+        const size_t pix = (static_cast<size_t>(n) * p.H + h) * p.W + w;
+        char* dbase = reinterpret_cast<char*>(e.dst[slot]) + (pix * e.dst_C[slot] + e.dst_coff[slot] + chb) * 2;
+        // depth-to-space: byte offsets of the four sub-pixels (a, b) from sub-pixel (0, 0) of this lane's pixel
+        char* d2s_base = nullptr;
+        size_t sub_off[3] = {0, 0, 0};   // [1]: next fine column, [2]: next fine row
+        if (e.d2s_cout > 0) {
+          const size_t fpix = (static_cast<size_t>(n) * (2 * p.H) + 2 * h) * (2 * p.W) + 2 * w;
+          d2s_base = reinterpret_cast<char*>(e.dst[0]) + (fpix * e.dst_C[0] + e.dst_coff[0]) * 2;
+          const size_t px = static_cast<size_t>(e.dst_C[0]) * 2;
+          sub_off[1] = px; sub_off[2] = px * 2 * p.W;
+        }
+        const unsigned short* gin = nullptr;
+        if (e.gate_in[slot]) gin = e.gate_in[slot] + ((pix * e.aux_C[slot] + e.aux_coff[slot] + chb) >> 4);
+        unsigned short* gout = nullptr;
+        if (e.gate_out) gout = e.gate_out + ((pix * e.dst_C[0] + e.dst_coff[0] + col0) >> 4);
+        const float scale = e.mask_scale;
+        const int d2s_shift = e.d2s_cout > 0 ? 31 - __clz(e.d2s_cout) : 0;
+        mbar_wait(&bars->tmem_full[acc], (it >> 1) & 1);
+        tc_fence_after();
+        const uint32_t t_row = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) +
+                               static_cast<uint32_t>(acc * p.block_n);
+        for (int c = half * 32; c < p.block_n; c += 64) {
+          uint32_t r[2][16];
+          uint32_t gbits[2] = {0xFFFFu, 0xFFFFu};
+          tmem_ld_32x32b_x16(t_row + static_cast<uint32_t>(c), r[0]);
+          tmem_ld_32x32b_x16(t_row + static_cast<uint32_t>(c + 16), r[1]);
+          if (gin) {
+            gbits[0] = __ldg(gin + (c >> 4));
+            gbits[1] = __ldg(gin + (c >> 4) + 1);
+          }
+          float4 bq[2][4];   // bias of both chunks, requested before the accumulators are waited for
+          if (e.bias) {
+#pragma unroll
+            for (int u = 0; u < 2; ++u) {
+              const int cc = c + 16 * u;
+              const int bcol = (e.d2s_cout > 0) ? ((col0 + cc) & (e.d2s_cout - 1)) : col0 + cc;   // Cout is a power of 2
+              const float4* bp = reinterpret_cast<const float4*>(e.bias + bcol);
+#pragma unroll
+              for (int q = 0; q < 4; ++q) bq[u][q] = __ldg(bp + q);
+            }
+          }
+          tmem_ld_wait();
+#pragma unroll
+          for (int u = 0; u < 2; ++u) {
+            const int cc = c + 16 * u;
+            float v[16];
+#pragma unroll
+            for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[u][i]);
+            if (e.bias) {
+#pragma unroll
+              for (int q = 0; q < 4; ++q) {
+                v[4 * q + 0] += bq[u][q].x; v[4 * q + 1] += bq[u][q].y; v[4 * q + 2] += bq[u][q].z; v[4 * q + 3] += bq[u][q].w;
+              }
+            }
+            if (gin) {
+#pragma unroll
+              for (int i = 0; i < 16; ++i) v[i] = ((gbits[u] >> i) & 1u) ? v[i] * scale : 0.0f;
+            }
+            U32x8 o;
+            if (e.relu) {
+#pragma unroll
+              for (int i = 0; i < 8; ++i) {
+                asm("cvt.rn.relu.bf16x2.f32 %0, %1, %2;" : "=r"(o.v[i]) : "f"(v[2 * i + 1]), "f"(v[2 * i]));
+              }
+            } else {
+#pragma unroll
+              for (int i = 0; i < 8; ++i) o.v[i] = pack_bf16x2(v[2 * i], v[2 * i + 1]);
+            }
+            if (gout) {
+              uint32_t accb = 0;
+#pragma unroll
+              for (int i = 0; i < 8; ++i) accb |= ((o.v[i] + 0x7FFF7FFFu) >> (15 - 2 * i)) & (0x00010001u << (2 * i));
+              gout[cc >> 4] = static_cast<unsigned short>((accb & 0xFFFFu) | (accb >> 15));
+            }
+            if (e.d2s_cout > 0) {
+              const int col = col0 + cc;
+              const int ab = col >> d2s_shift;
+              const size_t so = ((ab & 1) ? sub_off[1] : 0) + ((ab & 2) ? sub_off[2] : 0);
+              st_global_v8(d2s_base + so + (col & (e.d2s_cout - 1)) * 2, o);
+            } else {
+              st_global_v8(dbase + cc * 2, o);
+            }
+          }
+        }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&bars->tmem_empty[acc]);
+        continue;
+      }
 
       // Destination slot, pixel index and channel origin.
       int slot = 0, ch0 = col0;
@@ -171,22 +273,31 @@ igemm_kernel(const __grid_constant__ IgemmParams p, const __grid_constant__ CUte
         aux = reinterpret_cast<const __nv_bfloat16*>(e.aux[slot]) + pix * e.aux_C[slot] + e.aux_coff[slot] + ch0;
       }
       const size_t drop_elem0 = pix * e.dst_C[slot] + e.dst_coff[slot] + ch0;
+      // (a depth-to-space tile wider than Cout starts at ab = 0, ch0 = 0: bias index = column mod Cout)
       const int bias0 = (e.d2s_cout > 0) ? ch0 : col0;
 
       mbar_wait(&bars->tmem_full[acc], (it >> 1) & 1);
       tc_fence_after();
       const uint32_t t_row = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) +
                              static_cast<uint32_t>(acc * p.block_n);
-      for (int c = 0; c < p.block_n; c += 16) {
+      for (int c = half * 16; c < p.block_n; c += 32) {
         uint32_t r[16];
         tmem_ld_32x32b_x16(t_row + static_cast<uint32_t>(c), r);
         tmem_ld_wait();
+        if (e.d2s_cout > 0 && p.block_n > e.d2s_cout) {
+          // depth-to-space tile spanning several (a, b) sub-pixels: destination of this 16-column chunk
+          const int col = col0 + c;
+          const int ab = col / e.d2s_cout;
+          const size_t px = (static_cast<size_t>(n) * (2 * p.H) + (2 * h + (ab >> 1))) * (2 * p.W) + (2 * w + (ab & 1));
+          dst = reinterpret_cast<__nv_bfloat16*>(e.dst[0]) + px * e.dst_C[0] + e.dst_coff[0] + (col % e.d2s_cout) - c;
+        }
         if (valid) {
           float v[16];
 #pragma unroll
           for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
           if (e.bias) {
-            const float4* bp = reinterpret_cast<const float4*>(e.bias + bias0 + c);
+            const int bcol = (e.d2s_cout > 0) ? (bias0 + c) % e.d2s_cout : bias0 + c;
+            const float4* bp = reinterpret_cast<const float4*>(e.bias + bcol);
 #pragma unroll
             for (int q = 0; q < 4; ++q) {
               const float4 bq = __ldg(bp + q);
@@ -260,8 +371,9 @@ igemm_kernel(const __grid_constant__ IgemmParams p, const __grid_constant__ CUte
 
 }  // namespace
 
-int igemm_launch(const IgemmParams& p, const CUtensorMap& a0, const CUtensorMap& a1, const CUtensorMap& b,
+int igemm_launch(const IgemmParams& p_in, const CUtensorMap& a0, const CUtensorMap& a1, const CUtensorMap& b,
                  cudaStream_t stream) {
+  IgemmParams p = p_in;
   UB_REQUIRE(p.TN * p.TH * p.TW == 128, "igemm: tile box %dx%dx%d is not 128 pixels", p.TN, p.TH, p.TW);
   UB_REQUIRE(p.block_n == 32 || p.block_n == 64 || p.block_n == 128 || p.block_n == 256,
              "igemm: block_n %d unsupported", p.block_n);
@@ -279,6 +391,19 @@ int igemm_launch(const IgemmParams& p, const CUtensorMap& a0, const CUtensorMap&
   }
   const int num_tiles = p.tiles_n * p.tiles_h * p.tiles_w * p.n_tiles;
   UB_REQUIRE(num_tiles > 0, "igemm: empty problem");
+  {
+    static const bool no_lean = getenv("UNETB200_NO_LEAN_IGEMM") != nullptr;
+    const IgemmEpilogue& e = p.epi;
+    const bool full = p.N % p.TN == 0 && p.H % p.TH == 0 && p.W % p.TW == 0;
+    bool aligned = reinterpret_cast<uintptr_t>(e.dst[0]) % 32 == 0 && reinterpret_cast<uintptr_t>(e.dst[1]) % 32 == 0 &&
+                   e.dst_coff[0] % 16 == 0 && e.dst_coff[1] % 16 == 0 && e.dst_C[0] % 16 == 0 && e.dst_C[1] % 16 == 0;
+    // two destinations must meet at a tile boundary; gate bits are only written for a single plain destination
+    const bool split_ok = e.split_col >= p.n_tiles * p.block_n || e.split_col % p.block_n == 0;
+    const bool gate_ok = !e.gate_out || (e.d2s_cout == 0 && e.split_col >= p.n_tiles * p.block_n);
+    p.lean = (!no_lean && full && aligned && split_ok && gate_ok && p.block_n >= 32 && !e.aux[0] && !e.aux[1] &&
+              e.drop_keep >= 1.0f &&
+              (e.d2s_cout == 0 || (e.d2s_cout >= 32 && (e.d2s_cout & (e.d2s_cout - 1)) == 0))) ? 1 : 0;
+  }
   int grid = device_sm_count();
   if (grid > num_tiles) grid = num_tiles;
   if (profiling_enabled()) {

@@ -56,6 +56,7 @@ struct IgemmParams {
   int src_ci_off[2];                // channel offset of the source inside the packed weight row
   int kc;                           // 64 (SWIZZLE_128B) or 32 (SWIZZLE_64B)
   int stages;
+  int lean;                         // set by igemm_launch: the lean epilogue applies (see igemm.cu)
   IgemmEpilogue epi;
 };
 

@@ -459,8 +459,10 @@ int tconv2x2_fwd(const void* x, int Cin, const void* w_packed, const float* bias
                  cudaStream_t s) {
   const int kc = pick_kc(Cin, 0);
   UB_REQUIRE(kc != 0, "tconv2x2_fwd: Cin %d must be a multiple of 32", Cin);
-  const int block_n = pick_block_n(Cout);
-  UB_REQUIRE(block_n != 0, "tconv2x2_fwd: Cout %d must be a multiple of 32", Cout);
+  UB_REQUIRE(Cout % 32 == 0, "tconv2x2_fwd: Cout %d must be a multiple of 32", Cout);
+  // GEMM N = 4 * Cout (the four sub-pixels side by side): one tile may span several of them, so the input tile is
+  // loaded once and the MMAs are 128 / 256 wide even for Cout = 32 (four N = 32 tiles ran at 70 TFLOP/s)
+  const int block_n = pick_block_n(4 * Cout);
   IgemmParams p;
   std::memset(&p, 0, sizeof(p));
   const Box b = pick_box(128, H, W);
