@@ -164,7 +164,7 @@ def run_reference(args):
     if rank != 0:
         return 0
     cores = os.cpu_count() or 1
-    sample = 8
+    sample = 32   # images per step: ~0.5 s of CPU work per step, the same sample as the GPU arm's cpu_baseline
     value, ms = cpu_train_images_per_sec(args.decoder, args.size, args.channels, sample, args.steps, args.warmup, cores)
     line = {
         "impl": "reference", "metric": "train images/sec", "value": value, "unit": "images/s", "n_gpus": args.gpus,
