@@ -327,12 +327,14 @@ def run_b200(args):
                 traffic = json.load(open(tpath)).get("igemm_dram_bytes_per_launch")
             except Exception:
                 traffic = None
+        # which BASELINE.json configuration this shape is
+        cfg_index = 3 if (S, C) == (240, 4) else (4 if N == 512 else (2 if world > 1 else (1 if ups else 0)))
         line = {
             "metric": "train images/sec", "value": value, "unit": "images/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
             "config": {
-                "workload": f"UNet {S}x{S}x{C} {args.decoder} decoder (BASELINE configs[{1 if ups else 0}] shape), "
+                "workload": f"UNet {S}x{S}x{C} {args.decoder} decoder (BASELINE configs[{cfg_index}] shape), "
                             f"bs{N} per GPU, Adam, dropout 0.2, train step fwd+dice+bwd+allreduce+Adam",
                 "decoder": args.decoder, "per_gpu_batch": N, "global_batch": gb, "image": [S, S, C],
                 "parallelism": f"dp{world}", "cuda_graph": bool(not args.no_graph),
