@@ -677,6 +677,8 @@ bool halo_plan(HaloParams& p, int N, int H, int W, int kc, int ncols) {
   if (ncols % 128 == 0 && ncols >= 256 && ncols <= nsplit_max_cols && H >= nsplit_min_h) block_n = 128;
   if (block_n != 32 && block_n != 64 && block_n != 128) return false;
   int J = W >= 25 ? 4 : (W >= 9 ? 2 : 1);
+  // prefer strips that tile the width exactly (e.g. 240 = 15 x 16): full tiles take the lean epilogue
+  while (J > 1 && W % (8 * J) != 0 && W % (4 * J) == 0) J >>= 1;
   while (J > 1 && J * block_n > 512) J >>= 1;
   p.N = N; p.H = H; p.W = W;
   p.block_n = block_n;

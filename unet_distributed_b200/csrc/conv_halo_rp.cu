@@ -188,6 +188,7 @@ __device__ __forceinline__ void rp_epilogue(const HaloParams& p, RpBarriers* bar
     int n, h0, w0;
     decode_tile(p, tile, n, h0, w0);
     const size_t pix0 = (static_cast<size_t>(n) * p.H + (h0 + 2 * th)) * p.W + (w0 + twl);
+    const bool row_ok = (h0 + 2 * th) < p.H;   // H is even: both rows of the pair are inside or outside together
     char* dst_b[kSlots];
     const unsigned short* gin_b[kSlots];
     unsigned short* gout_b = nullptr;
@@ -215,8 +216,8 @@ __device__ __forceinline__ void rp_epilogue(const HaloParams& p, RpBarriers* bar
         const int sl = (SPLIT && chl >= BN / 2) ? 1 : 0;
         gb[k] = 0xFFFFu;
         if (POOL && sl == 0) {   // one coarse gate word per block, fetched with the lower-row item
-          if (par == 1 && gin_b[0]) gb[k] = __ldg(gin_b[0] + j * (gstrip[0] >> 1) + (chl >> 4));
-        } else if (gin_b[sl]) {
+          if (par == 1 && gin_b[0] && row_ok) gb[k] = __ldg(gin_b[0] + j * (gstrip[0] >> 1) + (chl >> 4));
+        } else if (gin_b[sl] && row_ok) {
           gb[k] = __ldg(gin_b[sl] + j * gstrip[sl] + par * grow[sl] + ((chl - sl * (BN / 2)) >> 4));
         }
       }
@@ -241,7 +242,7 @@ __device__ __forceinline__ void rp_epilogue(const HaloParams& p, RpBarriers* bar
         for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]) + bias_r[FWD ? chl / 32 : 0][i];
 #pragma unroll
         for (int i = 0; i < 8; ++i) w[i] = pack_bf16x2_relu(v[2 * i], v[2 * i + 1]);
-        if (gout_b) {
+        if (gout_b && row_ok) {
           uint32_t acc = 0;
 #pragma unroll
           for (int i = 0; i < 8; ++i) acc |= ((w[i] + 0x7FFF7FFFu) >> (15 - 2 * i)) & (0x00010001u << (2 * i));
@@ -279,9 +280,9 @@ __device__ __forceinline__ void rp_epilogue(const HaloParams& p, RpBarriers* bar
 #pragma unroll
       for (int i = 0; i < 8; ++i) o.v[i] = w[i];
       if (POOL && sl == 0) {   // coarse strips are 4 pixels apart
-        if (pool_lane) st_global_v8(dst_b[0] + j * (strip_b[0] >> 1) + chl * 2, o);
+        if (pool_lane && row_ok) st_global_v8(dst_b[0] + j * (strip_b[0] >> 1) + chl * 2, o);
       } else {
-        st_global_v8(dst_b[sl] + j * strip_b[sl] + par * row_b[sl] + (chl - sl * (BN / 2)) * 2, o);
+        if (row_ok) st_global_v8(dst_b[sl] + j * strip_b[sl] + par * row_b[sl] + (chl - sl * (BN / 2)) * 2, o);
       }
     }
     tc_fence_before();
@@ -446,7 +447,7 @@ bool halo_rp_plan(HaloParams& p, int N, int H, int W, int kc, int ncols) {
   static const bool disabled = getenv("UNETB200_NO_HALO") != nullptr || getenv("UNETB200_NO_RP") != nullptr;
   if (disabled) return false;
   if (ncols != 32 && ncols != 64) return false;
-  if (H % kTHR != 0 || W % 8 != 0) return false;
+  if (H < kTHR || H % 2 != 0 || W % 8 != 0) return false;   // the last row tile may be partial (rows are masked)
   int J = ncols == 32 ? 4 : 2;                 // TMEM: two sets of J accumulators of 2 * ncols columns
   if (kc == 64 && J > 2) J = 2;                // shared memory: a 34-row halo tile of 128-byte pixels
   while (J > 1 && W % (8 * J) != 0) J >>= 1;
@@ -465,7 +466,7 @@ bool halo_rp_plan(HaloParams& p, int N, int H, int W, int kc, int ncols) {
   if (stages > 4) stages = 4;
   if (stages < 2) return false;
   p.b_stages = stages;
-  p.tiles_h = H / kTHR;
+  p.tiles_h = (H + kTHR - 1) / kTHR;
   p.tiles_w = W / (8 * J);
   p.rp = 1;
   return true;
