@@ -143,11 +143,14 @@ __device__ __forceinline__ void rp_mma_role(const HaloParams& p, RpBarriers* bar
 // take alternate chunks. SPLIT: channels [BN/2, BN) go to destination 1. POOL (with SPLIT): destination 0 is the coarse
 // tensor and receives the 2x2 block sums -- the two rows of a block are the two halves of this lane's accumulator row,
 // the two columns are lanes l and l ^ 1; the even-column lane stores.
-template <int J, int BN, bool FWD, bool SPLIT, bool POOL = false>
+// FPOOL (forward): MaxPool2D fused -- the max of the block's two rows is taken between the two halves of the lane's
+// accumulator row (packed bf16x2 max), the two columns between lanes l and l ^ 1; the even-column lane stores.
+template <int J, int BN, bool FWD, bool SPLIT, bool POOL = false, bool FPOOL = false>
 __device__ __forceinline__ void rp_epilogue(const HaloParams& p, RpBarriers* bars, uint32_t tmem_base, int warp, int lane,
                                             int num_tiles) {
   static_assert(!SPLIT || (BN == 64 && !FWD), "split destinations: dgrad into two 32-channel tensors");
   static_assert(!POOL || SPLIT, "2x2 pooling of destination 0 is a split-dgrad feature");
+  static_assert(!FPOOL || FWD, "max pooling belongs to the forward epilogue");
   constexpr int kCl = 2 * BN / 32;          // 16-column chunks per warp and strip
   constexpr int kItems = J * kCl;
   constexpr int kBiasCl = BN / 32;
@@ -200,6 +203,11 @@ __device__ __forceinline__ void rp_epilogue(const HaloParams& p, RpBarriers* bar
     }
     if (FWD && e.gate_out) gout_b = e.gate_out + ((pix0 * e.dst_C[0] + e.dst_coff[0]) >> 4) + half;
     const bool pool_lane = (lane & 1) == 0;   // even column (every accumulator row is an even image row)
+    char* mp_b = nullptr;
+    if (FPOOL) {
+      const size_t cpix0 = (static_cast<size_t>(n) * (p.H >> 1) + ((h0 >> 1) + th)) * (p.W >> 1) + ((w0 + twl) >> 1);
+      mp_b = reinterpret_cast<char*>(e.maxpool_out) + (cpix0 * e.dst_C[0] + half * 16) * 2;
+    }
     if (POOL) {   // destination 0 on the coarse grid
       const size_t cpix0 = (static_cast<size_t>(n) * (p.H >> 1) + ((h0 >> 1) + th)) * (p.W >> 1) + ((w0 + twl) >> 1);
       dst_b[0] = reinterpret_cast<char*>(e.dst[0]) + (cpix0 * e.dst_C[0] + e.dst_coff[0] + half * 16) * 2;
@@ -226,6 +234,7 @@ __device__ __forceinline__ void rp_epilogue(const HaloParams& p, RpBarriers* bar
     tc_fence_after();
     const uint32_t t_acc = t_lane + static_cast<uint32_t>(a * J * 2 * BN);
     float vs[POOL ? 16 : 1];   // upper-row values of the block waiting for the lower row
+    uint32_t wsave[FPOOL ? kBiasCl : 1][8];   // forward pooling: packed upper-row outputs per channel chunk
 #pragma unroll
     for (int k = 0; k < kItems; ++k) {
       const int j = k / kCl, cl = k % kCl;
@@ -242,6 +251,26 @@ __device__ __forceinline__ void rp_epilogue(const HaloParams& p, RpBarriers* bar
         for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]) + bias_r[FWD ? chl / 32 : 0][i];
 #pragma unroll
         for (int i = 0; i < 8; ++i) w[i] = pack_bf16x2_relu(v[2 * i], v[2 * i + 1]);
+        if (FPOOL) {
+          if (par == 0) {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) wsave[FPOOL ? chl / 32 : 0][i] = w[i];
+          } else {
+            U32x8 mx;
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+              __nv_bfloat162 a2 = *reinterpret_cast<__nv_bfloat162*>(&w[i]);
+              __nv_bfloat162 b2 = *reinterpret_cast<__nv_bfloat162*>(&wsave[FPOOL ? chl / 32 : 0][i]);
+              __nv_bfloat162 m2 = __hmax2(a2, b2);
+              uint32_t mw = *reinterpret_cast<uint32_t*>(&m2);
+              const uint32_t ow = __shfl_xor_sync(0xffffffffu, mw, 1);
+              __nv_bfloat162 o2 = *reinterpret_cast<const __nv_bfloat162*>(&ow);
+              m2 = __hmax2(m2, o2);
+              mx.v[i] = *reinterpret_cast<uint32_t*>(&m2);
+            }
+            if (pool_lane && row_ok) st_global_v8(mp_b + j * (strip_b[0] >> 1) + chl * 2, mx);
+          }
+        }
         if (gout_b && row_ok) {
           uint32_t acc = 0;
 #pragma unroll
@@ -408,6 +437,7 @@ conv_halo_rp_kernel(const __grid_constant__ HaloParams p, const __grid_constant_
 #define UB_RP_EPI(JJ, NN)                                                                               \
     do {                                                                                                \
       if (p.fast_epi == 1) rp_epilogue<JJ, NN, true, false>(p, bars, tmem_base, warp, lane, num_tiles);  \
+      else if (p.fast_epi == 5) rp_epilogue<JJ, NN, true, false, false, true>(p, bars, tmem_base, warp, lane, num_tiles); \
       else if (p.fast_epi == 2) rp_epilogue<JJ, NN, false, false>(p, bars, tmem_base, warp, lane, num_tiles); \
       else if (p.fast_epi == 3) rp_epilogue<JJ, 64, false, true>(p, bars, tmem_base, warp, lane, num_tiles); \
       else rp_epilogue<JJ, 64, false, true, true>(p, bars, tmem_base, warp, lane, num_tiles);            \
@@ -472,7 +502,8 @@ bool halo_rp_plan(HaloParams& p, int N, int H, int W, int kc, int ncols) {
   return true;
 }
 
-// fast_epi code (1 forward, 2 dgrad, 3 dgrad split, 4 dgrad split + 2x2 pooling of destination 0) if the lean row-pair epilogue covers this epilogue, else 0.
+// fast_epi code (1 forward, 2 dgrad, 3 dgrad split, 4 dgrad split + 2x2 pooling of destination 0, 5 forward + fused
+// MaxPool2D) if the lean row-pair epilogue covers this epilogue, else 0.
 int halo_rp_epilogue_code(const HaloParams& p) {
   const IgemmEpilogue& e = p.epi;
   const bool aligned = reinterpret_cast<uintptr_t>(e.dst[0]) % 32 == 0 && reinterpret_cast<uintptr_t>(e.dst[1]) % 32 == 0 &&
@@ -480,7 +511,11 @@ int halo_rp_epilogue_code(const HaloParams& p) {
   if (!aligned || e.aux[0] || e.aux[1] || e.drop_keep < 1.0f || e.d2s_cout) return 0;
   if (e.pool2_slot0 && !(p.block_n == 64 && e.split_col == 32 && !e.relu && !e.bias && !e.gate_out)) return 0;
   const bool gates_in = e.gate_in[0] || e.gate_in[1];
-  if (e.relu && !gates_in && e.split_col >= p.block_n) return 1;
+  if (e.relu && !gates_in && e.split_col >= p.block_n) {
+    if (!e.maxpool_out) return 1;
+    return (reinterpret_cast<uintptr_t>(e.maxpool_out) % 32 == 0 && e.dst_coff[0] == 0) ? 5 : 0;
+  }
+  if (e.maxpool_out) return 0;
   if (!e.relu && !e.bias && !e.gate_out) {
     if (e.split_col >= p.block_n) return 2;
     if (p.block_n == 64 && e.split_col == 32) return e.pool2_slot0 ? 4 : 3;
@@ -490,7 +525,7 @@ int halo_rp_epilogue_code(const HaloParams& p) {
 
 int halo_rp_launch(const HaloParams& p, const CUtensorMap& a0, const CUtensorMap& a1, const CUtensorMap& b,
                    cudaStream_t stream) {
-  UB_REQUIRE(p.rp == 1 && p.fast_epi >= 1 && p.fast_epi <= 4, "conv_halo_rp: not a row-pair plan");
+  UB_REQUIRE(p.rp == 1 && p.fast_epi >= 1 && p.fast_epi <= 5, "conv_halo_rp: not a row-pair plan");
   const size_t smem = rp_smem_bytes(p);
   UB_REQUIRE(smem <= 227 * 1024, "conv_halo_rp: %zu bytes of shared memory requested", smem);
   static bool attr_set[64] = {false};

@@ -32,6 +32,9 @@ struct IgemmEpilogue {
   // of each 2x2 block of the gradient (ResizeNearestNeighborGrad fused into the producer); gate_in[0] then holds the
   // coarse tensor's ReLU gates
   int pool2_slot0;
+  // forward, conv_halo_rp only: also write max over each 2x2 block of the (ReLU'd) output to this coarse tensor
+  // [N, H/2, W/2, dst_C[0]] (MaxPool2D fused into the producer)
+  void* maxpool_out;
   int split_col;       // GEMM columns >= split_col go to slot 1
   const float* bias;   // fp32 per GEMM column (tconv: per column modulo d2s_cout), or null
   int relu;

@@ -129,6 +129,7 @@ bool try_halo(const IgemmParams& p, const void* src0, int C0, const void* src1, 
       }
     }
   }
+  if (p.epi.maxpool_out) return false;   // only the row-pair kernel fuses MaxPool2D (the caller reports the error)
   HaloParams hp;
   std::memset(&hp, 0, sizeof(hp));
   if (!halo_plan(hp, p.N, p.H, p.W, p.kc, ncols)) return false;
@@ -156,8 +157,17 @@ bool try_halo(const IgemmParams& p, const void* src0, int C0, const void* src1, 
 }  // namespace
 
 // ------------------------------------------------------------------------------------------------ conv3x3 forward
+bool conv3x3_fwd_maxpool_ok(int N, int H, int W, int C0, int C1, int Cout) {
+  static const bool off = getenv("UNETB200_NO_FUSED_MAXPOOL") != nullptr;
+  const int kc = pick_kc(C0, C1);
+  if (off || kc == 0 || H % 2 != 0 || W % 2 != 0) return false;
+  HaloParams rp;
+  std::memset(&rp, 0, sizeof(rp));
+  return halo_rp_plan(rp, N, H, W, kc, Cout);
+}
+
 int conv3x3_fwd(ConvSrc x0, ConvSrc x1, const void* w_packed, const float* bias, void* y, int N, int H, int W, int Cout,
-                int relu, DropoutCfg drop, cudaStream_t s, unsigned short* gate_out) {
+                int relu, DropoutCfg drop, cudaStream_t s, unsigned short* gate_out, void* maxpool_out) {
   const int C1 = x1.ptr ? x1.C : 0;
   const int kc = pick_kc(x0.C, C1);
   UB_REQUIRE(kc != 0, "conv3x3_fwd: input channels %d/%d must be multiples of 32", x0.C, C1);
@@ -188,8 +198,10 @@ int conv3x3_fwd(ConvSrc x0, ConvSrc x1, const void* w_packed, const float* bias,
   p.epi.drop_stream = drop.stream;
   p.epi.drop_seed_add = drop.seed_add;
   p.epi.gate_out = gate_out;
+  p.epi.maxpool_out = maxpool_out;
   int rc = UB_OK;
   if (try_halo(p, x0.ptr, x0.C, x1.ptr, C1, w_packed, Cout, x0.C + C1, s, &rc)) return rc;
+  UB_REQUIRE(!maxpool_out, "conv3x3_fwd: fused max pooling is not available for this shape (conv3x3_fwd_maxpool_ok)");
   CUtensorMap a0, a1, bm;
   rc = nhwc_map(&a0, x0.ptr, N, H, W, x0.C, kc, b);
   if (rc) return rc;

@@ -19,8 +19,11 @@ struct DropoutCfg {
 };
 
 // y = relu?(conv3x3_same([x0, x1]) + bias) (* dropout); w_packed = bf16 [Cout][9][C0+C1].
+// maxpool_out (optional): also write MaxPool2D(y) to this [N, H/2, W/2, Cout] tensor from the conv's epilogue; only where
+// conv3x3_fwd_maxpool_ok() says so (the row-pair kernel).
+bool conv3x3_fwd_maxpool_ok(int N, int H, int W, int C0, int C1, int Cout);
 int conv3x3_fwd(ConvSrc x0, ConvSrc x1, const void* w_packed, const float* bias, void* y, int N, int H, int W, int Cout,
-                int relu, DropoutCfg drop, cudaStream_t s, unsigned short* gate_out = nullptr);
+                int relu, DropoutCfg drop, cudaStream_t s, unsigned short* gate_out = nullptr, void* maxpool_out = nullptr);
 
 // dx_k = conv3x3_same(dz, flipped weights)[channels of source k] * (mask_k > 0 ? scale_k : 0)   (mask optional)
 // w_packed_d = bf16 [C0+C1][9][Cout] (tap-flipped).

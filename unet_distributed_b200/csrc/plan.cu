@@ -381,9 +381,11 @@ int unetb200_plan_forward(unetb200_plan* P, const float* imgs, const float* msks
       RC(conv3x3_fwd(ConvSrc{P->at(P->p[L - 1]), P->ch[L - 1]}, ConvSrc{nullptr, 0}, P->pkf(la), P->B_(la),
                      P->at(P->a[L]), N, H, W, P->ch[L], 1, d, s, P->gate(P->gt_a[L])));
     }
+    // MaxPool2D comes out of conv{L+1}b's epilogue where the row-pair kernel runs (128x128 and 64x64 levels)
+    const bool fused_pool = L < 4 && conv3x3_fwd_maxpool_ok(N, H, W, P->ch[L], 0, P->layers[lb].cout);
     RC(conv3x3_fwd(ConvSrc{P->at(P->a[L]), P->ch[L]}, ConvSrc{nullptr, 0}, P->pkf(lb), P->B_(lb), P->at(P->c[L]), N, H,
-                   W, P->layers[lb].cout, 1, no_drop, s, P->gate(P->gt_c[L])));
-    if (L < 4) RC(maxpool2x2_fwd(P->at(P->c[L]), P->at(P->p[L]), N, H, W, P->ch[L], s));
+                   W, P->layers[lb].cout, 1, no_drop, s, P->gate(P->gt_c[L]), fused_pool ? P->at(P->p[L]) : nullptr));
+    if (L < 4 && !fused_pool) RC(maxpool2x2_fwd(P->at(P->c[L]), P->at(P->p[L]), N, H, W, P->ch[L], s));
   }
   // decoder
   for (int L = 3; L >= 0; --L) {
