@@ -60,8 +60,9 @@ def load_peaks():
 
 
 class ClockSampler:
-    """SM clock and throttle reasons sampled DURING the timed region: an in-process NVML thread polling every ~4 ms
-    (the timed region of the default run is ~80 ms, too short for nvidia-smi's own loop); falls back to one
+    """SM clock and throttle reasons sampled DURING the timed region: an in-process NVML thread polling every ~15 ms
+    (the timed region of the default run is ~80 ms, too short for nvidia-smi's own loop; polling faster takes the GIL
+    from the launch loop, which costs 4 % at N > 1 where a step is four graph launches plus three NCCL calls); falls back to one
     nvidia-smi query if NVML is not importable."""
     REASONS = ((0x8, "hw_slowdown"), (0x40, "hw_thermal_slowdown"), (0x20, "sw_thermal_slowdown"),
                (0x4, "sw_power_cap"))
@@ -103,7 +104,7 @@ class ClockSampler:
                         self.reasons.add(name)
             except Exception:
                 pass
-            time.sleep(0.004)
+            time.sleep(0.015)
 
     def start(self):
         try:
@@ -122,7 +123,7 @@ class ClockSampler:
             self._thread.join(timeout=2)
             if self.samples:
                 out.update(sm_mhz=statistics.median(self.samples), sm_max_mhz=self.max_mhz,
-                           reasons=sorted(self.reasons), samples=len(self.samples), source="nvml, 4 ms polling")
+                           reasons=sorted(self.reasons), samples=len(self.samples), source="nvml, 15 ms polling")
                 return out
         try:   # fallback: a single nvidia-smi query right after the timed region
             q = "clocks.sm,clocks.max.sm"
