@@ -205,7 +205,7 @@ head32_bwd_kernel(const uint4* __restrict__ x, const float* __restrict__ w, cons
 // stay in registers across strips. Lanes l and l^4, l^8, l^16 hold the same channel group; warps, then blocks, are
 // summed in a fixed order (bit-reproducible): block -> ws[block][nout] -> rows_reduce_kernel.
 template <int CIN>
-__global__ void __launch_bounds__(128)
+__global__ void __launch_bounds__(128, 4)
 conv_first32_wgrad_kernel(const float* __restrict__ x, const uint4* __restrict__ dz, float* __restrict__ ws, int H,
                           int W, unsigned n_strips) {
   constexpr int kNout = 9 * CIN * 32 + 32;
