@@ -521,9 +521,10 @@ pack_all_kernel(const PackLayer* __restrict__ layers, int nlayers, const float* 
                 uint8_t* __restrict__ arena) {
   __shared__ float tile[32][33];
   int li = 0;
-  while (li + 1 < nlayers && layers[li + 1].tile_start <= static_cast<int>(blockIdx.x)) ++li;   // block-uniform
+  const int tile_id = static_cast<int>(blockIdx.x);
+  while (li + 1 < nlayers && layers[li + 1].tile_start <= tile_id) ++li;   // block-uniform
   const PackLayer L = layers[li];
-  const int t = static_cast<int>(blockIdx.x) - L.tile_start;
+  const int t = tile_id - L.tile_start;
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
   const float* w = params + L.src;
   __nv_bfloat16* out_f = reinterpret_cast<__nv_bfloat16*>(arena + L.dst_fwd);
@@ -860,18 +861,26 @@ int head_bwd(const void* x, const float* w, const float* y_true, const float* p,
   const int subs = C / 8;
   UB_REQUIRE(C % 8 == 0 && subs >= 1 && subs <= 32 && (subs & (subs - 1)) == 0, "head_bwd: C %d unsupported", C);
   const int nout = C * n_cl + n_cl;
+  int rows = kRedBlocks;   // partial rows in ws = blocks launched
   if (C == 32 && n_cl == 1 && P < (1ll << 31) && reinterpret_cast<uintptr_t>(x) % 32 == 0 &&
       reinterpret_cast<uintptr_t>(dx) % 32 == 0) {   // thread-per-pixel fast path
-    head32_bwd_kernel<<<kRedBlocks, kThreads, 0, s>>>(reinterpret_cast<const uint4*>(x), w, y_true, p, sums, smooth,
-                                                      grad_scale, reinterpret_cast<uint4*>(dx), ws,
-                                                      static_cast<unsigned>(P));
+    // one wave: 78 registers x 256 threads -> three resident blocks per SM (592 blocks would run as 444 + 148)
+    static int blocks_per_sm = 0;
+    if (blocks_per_sm == 0) {
+      UB_CHECK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, head32_bwd_kernel, kThreads, 0));
+      if (blocks_per_sm < 1) blocks_per_sm = 1;
+    }
+    rows = blocks_per_sm * device_sm_count();
+    if (rows > kRedBlocks) rows = kRedBlocks;
+    head32_bwd_kernel<<<rows, kThreads, 0, s>>>(reinterpret_cast<const uint4*>(x), w, y_true, p, sums, smooth,
+                                                grad_scale, reinterpret_cast<uint4*>(dx), ws, static_cast<unsigned>(P));
   } else {
     const size_t smem = (C * n_cl + (kThreads / 32) * nout) * sizeof(float);
     head_bwd_kernel<<<kRedBlocks, kThreads, smem, s>>>(reinterpret_cast<const uint4*>(x), w, y_true, p, sums, smooth,
                                                        grad_scale, reinterpret_cast<uint4*>(dx), ws, P, C, n_cl);
   }
   UB_CHECK_CUDA(cudaGetLastError());
-  rows_reduce_kernel<<<grid_for(nout, 32), 1024, 0, s>>>(ws, kRedBlocks, nout, dw, C * n_cl, db);
+  rows_reduce_kernel<<<grid_for(nout, 32), 1024, 0, s>>>(ws, rows, nout, dw, C * n_cl, db);
   UB_CHECK_CUDA(cudaGetLastError());
   return UB_OK;
 }

@@ -221,9 +221,11 @@ int unetb200_plan_create(unetb200_plan** out, int N, int H, int W, int in_channe
   P->sums = P->bump(64);
   P->metrics = P->bump(64);
   // ---- workspace: the largest any single op asks for (ops are serialised on one stream)
-  P->ws_bytes = unetb200_head_ws_bytes(pixels, 32, n_cl_out);
+  // main-stream workspace: the head and conv1a's weight gradient (the last kernel of the dgrad chain; it runs on
+  // the main stream so that it overlaps conv1b's weight gradient on the side stream)
+  P->ws_bytes = max_sz(unetb200_head_ws_bytes(pixels, 32, n_cl_out), unetb200_conv_first_wgrad_ws_bytes(in_channels, 32));
   P->ws = P->bump(P->ws_bytes);
-  size_t ws = unetb200_conv_first_wgrad_ws_bytes(in_channels, 32);
+  size_t ws = 0;
   for (int L = 0; L < 5; ++L) {
     ws = max_sz(ws, unetb200_bias_grad_ws_bytes(P->ch[L]));
     const auto& la = P->layers[P->enc_a[L]];
@@ -511,7 +513,6 @@ int unetb200_plan_backward(unetb200_plan* P, const float* imgs, const float* msk
   if (segment == 1) {
     const int L = 4;
     const int H = P->Hl(L), W = P->Wl(L);
-    const long long px = static_cast<long long>(N) * H * W;
     const int la = P->enc_a[L], lb = P->enc_b[L];
     RC(fork());
     RC(conv3x3_wgrad(P->at(P->g_c[L]), P->c4_out, ConvSrc{P->at(P->a[L]), P->ch[L]}, ConvSrc{nullptr, 0}, P->dW_(lb), wsv,
@@ -529,7 +530,6 @@ int unetb200_plan_backward(unetb200_plan* P, const float* imgs, const float* msk
 
   for (int L = 3; L >= 0; --L) {
     const int H = P->Hl(L), W = P->Wl(L);
-    const long long px = static_cast<long long>(N) * H * W;
     const int la = P->enc_a[L], lb = P->enc_b[L];
     // MaxPoolGrad + skip gradient + ReluGrad of conv{L+1}b, in place in g_c[L]
     RC(maxpool2x2_bwd(P->at(P->c[L]), P->at(P->g_p[L]), P->at(P->g_c[L]), P->at(P->g_c[L]), N, H, W, P->ch[L], s));
@@ -549,8 +549,7 @@ int unetb200_plan_backward(unetb200_plan* P, const float* imgs, const float* msk
                        DgradDst{P->at(P->g_p[L - 1]), P->ch[L - 1], nullptr, 1.0f}, DgradDst{nullptr, 0, nullptr, 1.0f},
                        N, H, W, s));
     } else {
-      RC(fork());
-      RC(conv_first_wgrad(imgs, P->at(P->g_a[0]), P->dW_(la), P->dB_(la), wss, N, H, W, P->Cin, 32, w));
+      RC(conv_first_wgrad(imgs, P->at(P->g_a[0]), P->dW_(la), P->dB_(la), ws, N, H, W, P->Cin, 32, s));
     }
   }
   RC(join());
