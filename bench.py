@@ -59,80 +59,103 @@ def load_peaks():
     return d
 
 
+_SAMPLER_SRC = r"""
+import sys, time
+import pynvml as nv
+nv.nvmlInit()
+uuid, idx = sys.argv[1], int(sys.argv[2])
+try:
+    try:
+        h = nv.nvmlDeviceGetHandleByUUID(uuid)
+    except TypeError:
+        h = nv.nvmlDeviceGetHandleByUUID(uuid.encode())
+except Exception:
+    h = nv.nvmlDeviceGetHandleByIndex(idx)
+print("max", nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM), flush=True)
+while True:
+    try:
+        try:
+            mask = int(nv.nvmlDeviceGetCurrentClocksEventReasons(h))
+        except Exception:
+            mask = int(nv.nvmlDeviceGetCurrentClocksThrottleReasons(h))
+        print(time.time(), nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM), mask, flush=True)
+    except Exception:
+        pass
+    time.sleep(0.004)
+"""
+
+
 class ClockSampler:
-    """SM clock and throttle reasons sampled DURING the timed region: an in-process NVML thread polling every ~15 ms
-    (the timed region of the default run is ~80 ms, too short for nvidia-smi's own loop; polling faster takes the GIL
-    from the launch loop, which costs 4 % at N > 1 where a step is four graph launches plus three NCCL calls); falls back to one
-    nvidia-smi query if NVML is not importable."""
+    """SM clock and throttle reasons sampled DURING the timed region by a CHILD PROCESS polling NVML every ~4 ms
+    (started before the warm-up; samples are filtered to the timed region by wall-clock time). A polling thread in
+    this process took the GIL from the launch loop and cost 8 % at N = 8, where a step is four graph launches plus
+    three NCCL calls; nvidia-smi's own loop starts too slowly for an 80 ms timed region."""
     REASONS = ((0x8, "hw_slowdown"), (0x40, "hw_thermal_slowdown"), (0x20, "sw_thermal_slowdown"),
                (0x4, "sw_power_cap"))
 
     def __init__(self, gpu_index=0):
         self.gpu = gpu_index
-        self.samples, self.reasons, self.max_mhz = [], set(), None
-        self._stop, self._thread, self._h, self._nv = False, None, None, None
+        self.proc = None
+        self.t0 = self.t1 = None
 
-    def _handle(self):
-        import pynvml as nv
-        nv.nvmlInit()
+    def start(self):
+        """Launch the child (call well before the timed region: importing NVML takes a few hundred ms)."""
         try:
             import torch
             uuid = str(torch.cuda.get_device_properties(self.gpu).uuid)
             if not uuid.startswith("GPU-"):
                 uuid = "GPU-" + uuid
-            try:
-                h = nv.nvmlDeviceGetHandleByUUID(uuid)
-            except TypeError:
-                h = nv.nvmlDeviceGetHandleByUUID(uuid.encode())
-        except Exception:
             vis = os.environ.get("CUDA_VISIBLE_DEVICES", "")
-            idx = int(vis.split(",")[self.gpu]) if vis and vis.split(",")[self.gpu].isdigit() else self.gpu
-            h = nv.nvmlDeviceGetHandleByIndex(idx)
-        return nv, h
-
-    def _loop(self):
-        nv, h = self._nv, self._h
-        while not self._stop:
-            try:
-                self.samples.append(float(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)))
-                try:
-                    mask = int(nv.nvmlDeviceGetCurrentClocksEventReasons(h))
-                except Exception:
-                    mask = int(nv.nvmlDeviceGetCurrentClocksThrottleReasons(h))
-                for bit, name in self.REASONS:
-                    if mask & bit:
-                        self.reasons.add(name)
-            except Exception:
-                pass
-            time.sleep(0.015)
-
-    def start(self):
-        try:
-            self._nv, self._h = self._handle()
-            self.max_mhz = float(self._nv.nvmlDeviceGetMaxClockInfo(self._h, self._nv.NVML_CLOCK_SM))
-            import threading
-            self._thread = threading.Thread(target=self._loop, daemon=True)
-            self._thread.start()
+            parts = vis.split(",") if vis else []
+            idx = int(parts[self.gpu]) if self.gpu < len(parts) and parts[self.gpu].isdigit() else self.gpu
+            self.proc = subprocess.Popen([sys.executable, "-c", _SAMPLER_SRC, uuid, str(idx)], stdout=subprocess.PIPE,
+                                         stderr=open(os.environ.get("UNETB200_SAMPLER_ERR", os.devnull), "w"), text=True)
         except Exception:
-            self._thread = None
+            self.proc = None
+
+    def begin(self):
+        self.t0 = time.time()
+
+    def end(self):
+        self.t1 = time.time()
 
     def stop(self):
         out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
-        if self._thread is not None:
-            self._stop = True
-            self._thread.join(timeout=2)
-            if self.samples:
-                out.update(sm_mhz=statistics.median(self.samples), sm_max_mhz=self.max_mhz,
-                           reasons=sorted(self.reasons), samples=len(self.samples), source="nvml, 15 ms polling")
-                return out
-        try:   # fallback: a single nvidia-smi query right after the timed region
-            q = "clocks.sm,clocks.max.sm"
-            r = subprocess.run(["nvidia-smi", f"--query-gpu={q}", "--format=csv,noheader,nounits", "-i", str(self.gpu)],
-                               stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True, timeout=10)
-            parts = [x.strip() for x in r.stdout.strip().split(",")]
-            out.update(sm_mhz=float(parts[0]), sm_max_mhz=float(parts[1]), samples=1, source="nvidia-smi after the run")
+        if self.proc is None:
+            return out
+        try:
+            self.proc.terminate()
+            text, _ = self.proc.communicate(timeout=5)
         except Exception:
-            pass
+            try:
+                self.proc.kill()
+            except Exception:
+                pass
+            return out
+        sm, late, reasons, mx = [], [], set(), None
+        for line in text.splitlines():
+            parts = line.split()
+            try:
+                if parts[0] == "max":
+                    mx = float(parts[1])
+                    continue
+                t, clk, mask = float(parts[0]), float(parts[1]), int(parts[2])
+            except (ValueError, IndexError):
+                continue
+            inside = self.t0 is None or self.t1 is None or (self.t0 <= t <= self.t1)
+            late.append(clk)
+            if not inside:
+                continue
+            sm.append(clk)
+            for bit, name in self.REASONS:
+                if mask & bit:
+                    reasons.add(name)
+        if sm:
+            out.update(sm_mhz=statistics.median(sm), sm_max_mhz=mx, reasons=sorted(reasons), samples=len(sm),
+                       source="nvml child process, 4 ms polling, samples inside the timed region")
+        elif late:   # the child came up too late for the timed region: report what it saw, and say so
+            out.update(sm_mhz=statistics.median(late), sm_max_mhz=mx, samples=len(late),
+                       source="nvml child process, samples OUTSIDE the timed region (child started late)")
         return out
 
 
@@ -196,6 +219,9 @@ def run_b200(args):
     if world == 1:
         torch.cuda.set_device(0)
     dev = torch.device("cuda", torch.cuda.current_device())
+    sampler = ClockSampler(torch.cuda.current_device())
+    if rank == 0:
+        sampler.start()   # child process; it needs a moment to load NVML, so it starts before the model is built
     N, S, C = args.batch, args.size, args.channels
     ups = args.decoder == "upsampling"
     tr = Trainer(N, S, S, C, 1, ups, dropout=0.2, learning_rate=0.0005,
@@ -222,16 +248,15 @@ def run_b200(args):
     for i in range(args.warmup):
         tr.train_step(*d_batches[i % nb])
     barrier()
-    sampler = ClockSampler(torch.cuda.current_device())
-    if rank == 0:
-        sampler.start()
     launches0 = L.unetb200_launch_count()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    sampler.begin()
     e0.record()
     for i in range(args.steps):
         tr.train_step(*d_batches[i % nb])
     e1.record()
     barrier()
+    sampler.end()
     launches = L.unetb200_launch_count() - launches0
     if tr.use_cuda_graph:   # replays bypass the library's counter: kernels per captured step x steps
         launches = tr.graph_launches_per_step * args.steps
