@@ -201,3 +201,40 @@ def test_pipelined_host_steps_match_synchronous(cuda_device):
     assert outs[0][2] == outs[1][2] == len(batches)
     np.testing.assert_array_equal(outs[0][0], outs[1][0])
     np.testing.assert_array_equal(outs[0][1], outs[1][1])
+
+
+def test_evaluate_and_checkpoint_resume(cuda_device, tmp_path):
+    """Trainer.evaluate forms the reference's test metrics (test_dist.py:406-424) from per-sub-batch dice sums, and a
+    state saved under TF names resumes to bit-identical training."""
+    from unet_distributed_b200 import checkpoint
+    from unet_distributed_b200.evaluate import metrics_from_sums
+    from unet_distributed_b200.trainer import Trainer
+    N, H, W = 2, 32, 32
+    weights = O.init_weights(21)
+    tr = Trainer(N, H, W, dropout=0.0, learning_rate=1e-3, weights=weights)
+    imgs, msks = synthetic_batch(12, H, W, seed=77)
+    # one sub-batch: the sums give the same metrics as the plan's own finalisation and as the oracle's forward
+    s = tr.dice_sums(imgs[:N], msks[:N])
+    got = metrics_from_sums(*s)
+    np.testing.assert_allclose(got, tr.plan.metrics.cpu().numpy(), rtol=2e-5, atol=2e-6)
+    ref = O.loss_and_grads(weights, imgs[:N], msks[:N], dropout=0.0)
+    assert abs(got[0] - ref["loss"]) < 1e-2 and abs(got[1] - ref["dice"]) < 1e-2
+    # global batch 4 = two sub-batches per test batch; 12 test slices -> batches at 0 and 4, divisor 3
+    m = tr.evaluate(imgs, msks, batch_size=4)
+    assert m["batches"] == 2 and m["divisor"] == 3
+    want = np.zeros(4)
+    for i in (0, 4):
+        sums = tr.dice_sums(imgs[i:i + 2], msks[i:i + 2]) + tr.dice_sums(imgs[i + 2:i + 4], msks[i + 2:i + 4])
+        want += np.array(metrics_from_sums(*sums)) / 3
+    np.testing.assert_allclose([m["loss"], m["dice"], m["sensitivity"], m["specificity"]], want, rtol=1e-6)
+    # checkpoint after two steps, resume in a fresh trainer, continue: identical parameters
+    for k in range(2):
+        tr.train_step_host(imgs[2 * k:2 * k + 2], msks[2 * k:2 * k + 2])
+    path = checkpoint.save_checkpoint(str(tmp_path / checkpoint.LAST_GOOD), tr.state_dict())
+    tr2 = Trainer(N, H, W, dropout=0.0, learning_rate=1e-3, weights=O.init_weights(99))
+    tr2.load_state_dict(checkpoint.load_checkpoint(path))
+    assert tr2.global_step() == 2
+    for t in (tr, tr2):
+        t.train_step_host(imgs[4:6], msks[4:6])
+    np.testing.assert_array_equal(tr.plan.params.cpu().numpy(), tr2.plan.params.cpu().numpy())
+    assert tr.global_step() == tr2.global_step() == 3

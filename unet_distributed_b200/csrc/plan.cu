@@ -314,13 +314,17 @@ int unetb200_plan_bind(unetb200_plan* P, void* arena, float* params, float* grad
 }
 
 // Arena offset of a named tensor (debugging / per-layer parity tests). Names: a1..a5, c1..c5, p1..p4, u6..u9,
-// a6..a9, c6..c9 and the same with a leading 'g' for gradients; 'preds', 'metrics'.
+// a6..a9, c6..c9 and the same with a leading 'g' for gradients; 'preds', 'metrics', 'sums'.
 int unetb200_plan_tensor(const unetb200_plan* P, const char* name, long long* offset, int* n, int* h, int* w, int* c,
                          int* elem_bytes) {
   std::string s(name);
   bool grad = false;
   if (s == "preds") {
     *offset = static_cast<long long>(P->preds); *n = P->N; *h = P->H; *w = P->W; *c = P->ncl; *elem_bytes = 4;
+    return UB_OK;
+  }
+  if (s == "sums") {   // the three dice sums of the last forward: sum(y*p), sum(y), sum(p)
+    *offset = static_cast<long long>(P->sums); *n = 1; *h = 1; *w = 1; *c = 3; *elem_bytes = 4;
     return UB_OK;
   }
   if (s == "metrics") {

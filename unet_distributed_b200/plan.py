@@ -138,7 +138,9 @@ class UNetPlan:
         raw = self.arena[off.value:off.value + count * eb.value]
         dt = torch.bfloat16 if eb.value == 2 else torch.float32
         t = raw.view(dt)
-        return t.view(4) if name == "metrics" else t.view(n.value, h.value, w.value, c.value)
+        if name in ("metrics", "sums"):
+            return t.view(count)
+        return t.view(n.value, h.value, w.value, c.value)
 
     @property
     def preds(self):
@@ -147,6 +149,11 @@ class UNetPlan:
     @property
     def metrics(self):
         return self.tensor("metrics")
+
+    @property
+    def sums(self):
+        """[sum(y*p), sum(y), sum(p)] of the last forward with labels (fp32, device)."""
+        return self.tensor("sums")
 
     # ------------------------------------------------------------------ launches (asynchronous on the current stream)
     def side_stream(self, enable):

@@ -5,16 +5,18 @@
 
 `--batch_size` is the GLOBAL batch (test_dist.py:390): every rank trains on batch_size / world_size samples of each
 batch.  The parameter server, Supervisor, TensorBoard and SavedModel export of the reference are out of scope; this
-is the loop of test_dist.py:380-398, 448-459 only."""
+is the loop of test_dist.py:380-398, 448-459 plus the chief's test pass after every epoch and at the end
+(test_dist.py:406-446, 461-490) and `last_good_model` checkpoints under TF variable names (.npz, see checkpoint.py)."""
 from __future__ import annotations
 
 import argparse
+import os
 import time
 
 import numpy as np
 import torch
 
-from . import parallel, settings_dist
+from . import checkpoint, parallel, settings_dist
 from .data import get_epoch, load_all_data
 from .synthetic import make_slices
 from .trainer import Trainer
@@ -44,6 +46,9 @@ def build_parser():
     p.add_argument("--data_path", type=str, default=None, help="directory with imgs_/msks_{train,test}.npy")
     p.add_argument("--max_steps", type=int, default=0, help="stop early after this many steps (0 = all)")
     p.add_argument("--optimizer", type=str, default="adam", choices=["adam", "sgd"])
+    p.add_argument("--checkpoint_dir", type=str, default=settings_dist.CHECKPOINT_DIRECTORY)
+    p.add_argument("--resume", type=_bool, default=False, help="start from <checkpoint_dir>/last_good_model.npz")
+    p.add_argument("--test", type=_bool, default=True, help="run the chief's test pass after each epoch and at the end")
     return p
 
 
@@ -55,14 +60,36 @@ def main(argv=None):
     if FLAGS.synthetic:
         imgs_train, msks_train = make_slices(FLAGS.synthetic, settings_dist.IMG_ROWS, settings_dist.IMG_COLS,
                                              settings_dist.IN_CHANNEL_NO)
+        n_test = max(FLAGS.synthetic // 8, 2 * FLAGS.batch_size)
+        imgs_test, msks_test = make_slices(n_test, settings_dist.IMG_ROWS, settings_dist.IMG_COLS,
+                                           settings_dist.IN_CHANNEL_NO, seed=4242)
     else:
-        imgs_train, msks_train, _, _ = load_all_data(FLAGS.data_path)
+        imgs_train, msks_train, imgs_test, msks_test = load_all_data(FLAGS.data_path)
     batch_size = FLAGS.batch_size
     start, end = parallel.shard_range(batch_size, world, rank)           # test_dist.py:390-392
     _, H, W, C = imgs_train.shape
     trainer = Trainer(end - start, H, W, C, msks_train.shape[3], FLAGS.use_upsampling,
                       learning_rate=FLAGS.learning_rate, const_learningrate=FLAGS.const_learningrate,
                       lr_fraction=FLAGS.lr_fraction, decay_steps=FLAGS.decay_steps, optimizer=FLAGS.optimizer)
+    if FLAGS.resume:
+        path = checkpoint.latest(FLAGS.checkpoint_dir)
+        if path is None:
+            raise SystemExit("--resume: no %s under %s" % (checkpoint.LAST_GOOD, FLAGS.checkpoint_dir))
+        trainer.load_state_dict(checkpoint.load_checkpoint(path))       # every rank reads the same file
+        if rank == 0:
+            print("resumed from {} at global_step {}".format(path, trainer.global_step()), flush=True)
+
+    def test_pass(epoch_no):
+        """Chief only (test_dist.py:401-446): metrics over the test set, then the last-good-model checkpoint."""
+        if rank != 0:
+            return
+        if FLAGS.test and imgs_test.shape[0] > batch_size:
+            m = trainer.evaluate(imgs_test, msks_test, batch_size)
+            print("\nEpoch {} of {}: TEST DATASET\nloss = {:.4f}\nDice = {:.4f}\nSensitivity = {:.4f}\n"
+                  "Specificity = {:.4f}".format(epoch_no, FLAGS.epochs, m["loss"], m["dice"], m["sensitivity"],
+                                                m["specificity"]), flush=True)
+        checkpoint.save_checkpoint(os.path.join(FLAGS.checkpoint_dir, checkpoint.LAST_GOOD), trainer.state_dict())
+
     epoch = get_epoch(batch_size, imgs_train, msks_train, rng=1234)       # same shuffle on every rank
     num_batches = len(epoch)
     total = num_batches * FLAGS.epochs
@@ -86,7 +113,9 @@ def main(argv=None):
             print("step {}/{} (loss={:.4f}, dice={:.4f}) {:.1f} images/sec".format(
                 step, total, loss_v, dice_v, step * batch_size / dt), flush=True)
         if batch_idx == num_batches - 1 and step < total:
+            test_pass(step // num_batches)                                           # test_dist.py:406-446
             epoch = get_epoch(batch_size, imgs_train, msks_train, rng=1234 + step)   # test_dist.py:448-452
+    test_pass(max(step // max(num_batches, 1), 1))                                   # test_dist.py:461-490
     if world > 1:
         torch.distributed.barrier()
         torch.distributed.destroy_process_group()

@@ -217,6 +217,19 @@ class Trainer:
         self.plan.forward(imgs, msks, seed=self.dropout_seed, seed_add=self.step_dev)
         return self.plan.preds, (self.plan.metrics if msks is not None else None)
 
+    def dice_sums(self, imgs_np, msks_np):
+        """Forward only on one per-device batch of HOST arrays; returns numpy [sum(y*p), sum(y), sum(p)].
+        Dropout stays on, as in the reference's test pass (model.py:40)."""
+        self._d_imgs.copy_(torch.as_tensor(np.ascontiguousarray(imgs_np, dtype=np.float32)))
+        self._d_msks.copy_(torch.as_tensor(np.ascontiguousarray(msks_np, dtype=np.float32)))
+        self.plan.forward(self._d_imgs, self._d_msks, seed=self.dropout_seed, seed_add=self.step_dev)
+        return self.plan.sums.cpu().numpy().astype(np.float64)
+
+    def evaluate(self, imgs_test, msks_test, batch_size):
+        """Test-set metrics with the reference's batching and averaging (test_dist.py:406-424); see evaluate.py."""
+        from .evaluate import evaluate
+        return evaluate(self.dice_sums, imgs_test, msks_test, batch_size, self.plan.N)
+
     def global_step(self):
         return int(self.step_dev.item())
 
