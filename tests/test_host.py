@@ -157,3 +157,29 @@ def test_synthetic_slices():
     i2, _ = synthetic.make_slices(16, 64, 64, 1, seed=816)
     assert np.array_equal(imgs, i2)
     assert os.path.isdir(ROOT)
+
+
+def test_resident_epochs_match_get_epoch():
+    """The device-resident epoch cutter draws the same batches as get_epoch for the same seed (data.py:29-54),
+    including the dropped remainder, and hands each replica its shard (test_dist.py:390-394)."""
+    import torch
+    from unet_distributed_b200.data import ResidentEpochs, get_epoch
+    from unet_distributed_b200.parallel import shard_range
+    rng = np.random.default_rng(0)
+    imgs = rng.standard_normal((37, 8, 8, 4)).astype(np.float32)
+    msks = (rng.random((37, 8, 8, 1)) > 0.5).astype(np.float32)
+    B = 8
+    ep = get_epoch(B, imgs, msks, rng=1234)
+    res = ResidentEpochs(B, imgs, msks, torch.device("cpu")).shuffle(1234)
+    assert len(res) == len(ep) == 4
+    for b in range(len(ep)):
+        x, y = res.batch(b)
+        np.testing.assert_array_equal(x.numpy(), ep[b, 0])
+        np.testing.assert_array_equal(y.numpy(), ep[b, 1])
+        for rank in range(2):
+            s, e = shard_range(B, 2, rank)
+            xs, ys = res.batch(b, s, e)
+            np.testing.assert_array_equal(xs.numpy(), ep[b, 0][s:e])
+            np.testing.assert_array_equal(ys.numpy(), ep[b, 1][s:e])
+    res.shuffle(1235)
+    assert not np.array_equal(res.batch(0)[0].numpy(), ep[0, 0])

@@ -64,3 +64,44 @@ def get_epoch(batch_size, imgs_train, msks_train, rng=None):
     if data.shape == labels.shape:
         return np.stack([data, labels], axis=1)
     return EpochOfBatches(data, labels)
+
+
+class ResidentEpochs:
+    """The training set kept on one device (8,192 BraTS slices of 128x128 are ~1 GB: a fraction of 180 GB of HBM) and
+    cut into the same epochs as get_epoch (data.py:29-54): same permutation for the same seed, same dropped
+    remainder, same batch order. `batch(i, start, end)` gathers this replica's shard of batch i
+    (test_dist.py:390-394) with one index_select per array, so the step loop never touches the host.
+
+    imgs / msks: NHWC arrays or tensors; device: torch device (a CPU device works too, which is how this is tested)."""
+
+    def __init__(self, batch_size, imgs_train, msks_train, device, dtype=None):
+        import torch
+        self._torch = torch
+        self.batch_size = int(batch_size)
+        dtype = torch.float32 if dtype is None else dtype
+        self.imgs = torch.as_tensor(np.ascontiguousarray(imgs_train)).to(device=device, dtype=dtype)
+        self.msks = torch.as_tensor(np.ascontiguousarray(msks_train)).to(device=device, dtype=dtype)
+        self.train_size = int(self.imgs.shape[0])
+        self.epoch_length = self.train_size - self.train_size % self.batch_size
+        self.num_batches = self.epoch_length // self.batch_size
+        self.perm = None
+
+    def __len__(self):
+        return self.num_batches
+
+    def shuffle(self, rng=None):
+        """New epoch: the permutation get_epoch(batch_size, imgs, msks, rng) would draw."""
+        if not isinstance(rng, np.random.Generator):
+            rng = np.random.default_rng(rng)
+        perm = rng.permutation(self.train_size)[:self.epoch_length]
+        self.perm = self._torch.as_tensor(perm, dtype=self._torch.int64).to(self.imgs.device)
+        return self
+
+    def batch(self, batch_idx, start=0, end=None):
+        """(images, masks) of samples [start, end) of batch `batch_idx` of the current epoch, on the device."""
+        if self.perm is None:
+            raise RuntimeError("ResidentEpochs.shuffle() has not been called")
+        end = self.batch_size if end is None else end
+        lo = batch_idx * self.batch_size
+        idx = self.perm[lo + start:lo + end]
+        return self.imgs.index_select(0, idx), self.msks.index_select(0, idx)

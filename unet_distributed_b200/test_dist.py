@@ -17,7 +17,7 @@ import numpy as np
 import torch
 
 from . import checkpoint, parallel, settings_dist
-from .data import get_epoch, load_all_data
+from .data import ResidentEpochs, get_epoch, load_all_data
 from .synthetic import make_slices
 from .trainer import Trainer
 
@@ -46,6 +46,8 @@ def build_parser():
     p.add_argument("--data_path", type=str, default=None, help="directory with imgs_/msks_{train,test}.npy")
     p.add_argument("--max_steps", type=int, default=0, help="stop early after this many steps (0 = all)")
     p.add_argument("--optimizer", type=str, default="adam", choices=["adam", "sgd"])
+    p.add_argument("--resident_data", type=_bool, default=False,
+                   help="keep the training set on the GPU and gather batches there (no host copies in the step loop)")
     p.add_argument("--checkpoint_dir", type=str, default=settings_dist.CHECKPOINT_DIRECTORY)
     p.add_argument("--resume", type=_bool, default=False, help="start from <checkpoint_dir>/last_good_model.npz")
     p.add_argument("--test", type=_bool, default=True, help="run the chief's test pass after each epoch and at the end")
@@ -90,8 +92,13 @@ def main(argv=None):
                                                 m["specificity"]), flush=True)
         checkpoint.save_checkpoint(os.path.join(FLAGS.checkpoint_dir, checkpoint.LAST_GOOD), trainer.state_dict())
 
-    epoch = get_epoch(batch_size, imgs_train, msks_train, rng=1234)       # same shuffle on every rank
-    num_batches = len(epoch)
+    resident = None
+    if FLAGS.resident_data:   # same epochs as get_epoch, cut on the device
+        resident = ResidentEpochs(batch_size, imgs_train, msks_train, trainer.plan.device).shuffle(1234)
+        epoch, num_batches = None, len(resident)
+    else:
+        epoch = get_epoch(batch_size, imgs_train, msks_train, rng=1234)   # same shuffle on every rank
+        num_batches = len(epoch)
     total = num_batches * FLAGS.epochs
     if FLAGS.max_steps:
         total = min(total, FLAGS.max_steps)
@@ -99,12 +106,17 @@ def main(argv=None):
     step = 0
     while step < total:
         batch_idx = step % num_batches
-        data = np.ascontiguousarray(epoch[batch_idx, 0][start:end], dtype=np.float32)
-        labels = np.ascontiguousarray(epoch[batch_idx, 1][start:end], dtype=np.float32)
-        # steps whose numbers are printed synchronise; the others are pipelined (the copy of the next batch overlaps
-        # the kernels of this one, trainer.train_step_host)
         report = (step + 1) % 10 == 0 or step + 1 == total
-        met = trainer.train_step_host(data, labels, wait=report)
+        if resident is not None:
+            d_data, d_labels = resident.batch(batch_idx, start, end)
+            met = trainer.train_step(d_data.contiguous(), d_labels.contiguous())
+            met = met.cpu().numpy() if report else None
+        else:
+            data = np.ascontiguousarray(epoch[batch_idx, 0][start:end], dtype=np.float32)
+            labels = np.ascontiguousarray(epoch[batch_idx, 1][start:end], dtype=np.float32)
+            # steps whose numbers are printed synchronise; the others are pipelined (the copy of the next batch
+            # overlaps the kernels of this one, trainer.train_step_host)
+            met = trainer.train_step_host(data, labels, wait=report)
         step += 1
         if report:
             loss_v, dice_v = float(met[0]), float(met[1])
@@ -114,7 +126,10 @@ def main(argv=None):
                 step, total, loss_v, dice_v, step * batch_size / dt), flush=True)
         if batch_idx == num_batches - 1 and step < total:
             test_pass(step // num_batches)                                           # test_dist.py:406-446
-            epoch = get_epoch(batch_size, imgs_train, msks_train, rng=1234 + step)   # test_dist.py:448-452
+            if resident is not None:
+                resident.shuffle(1234 + step)
+            else:
+                epoch = get_epoch(batch_size, imgs_train, msks_train, rng=1234 + step)   # test_dist.py:448-452
     test_pass(max(step // max(num_batches, 1), 1))                                   # test_dist.py:461-490
     if world > 1:
         torch.distributed.barrier()
