@@ -3,11 +3,14 @@
 Two oracles, two bars (all errors are ||got - ref||_F / ||ref||_F per tensor):
 
 * fp32 oracle ("the reference's precision"): forward activations, predictions within 2e-2; loss / dice / sensitivity /
-  specificity within 1e-2 absolute.  Gradients are compared too but only bounded loosely (GRAD_VS_FP32): storing
-  activations in bf16 flips a fraction of ReLU masks and 2x2 max-pool winners (near-ties), and every flip re-routes a
-  whole gradient element, so ANY bf16-storage implementation deviates from fp32 by 10-20 % on the deep layers of
-  this network.  tests/test_oracle.py::test_bf16_storage_gradient_deviation shows the oracle does exactly that to
-  itself, which is why this cannot be a 2e-2 bar.
+  specificity within 1e-2 absolute.  Free-running gradients are bounded PER TENSOR by the oracle's own bf16-storage
+  twin (the same fp32 oracle with activations and GEMM weights rounded to bf16, run on the same inputs and dropout
+  masks): err(GPU, fp32 oracle) <= TWIN_FACTOR * err(twin, fp32 oracle) + TWIN_FLOOR.  Storing activations in bf16
+  flips a fraction of ReLU masks and 2x2 max-pool winners (near-ties) and every flip re-routes a whole gradient
+  element, so ANY bf16-storage implementation deviates from fp32 by 5-20 % on the deep layers of this network -- which
+  is why this cannot be a flat 2e-2 bar -- but it must not deviate by more than the reference's own arithmetic does
+  when it is given the same storage format.  TWIN_FLOOR covers what the twin does not model: gradient tensors stored in
+  bf16 and a different accumulation order.
 * the oracle's backward evaluated AT THE GPU'S FORWARD STATE (oracle Net.forward(forced_acts=...): layer outputs,
   ReLU/dropout gates and pool routing are the ones the GPU stored; gradients flow through the oracle's fp32
   operators with the bf16-rounded GEMM weights): every activation gradient and every weight gradient within 2e-2.
@@ -26,7 +29,17 @@ from util import O, DROPOUT_SEED, act_names, plan_dropout_masks, rel_err, synthe
 pytestmark = pytest.mark.gpu
 
 TOL_BF16 = 2e-2          # north_star bf16 tolerance
-GRAD_VS_FP32 = 0.35      # sanity bound only, see the module docstring
+TWIN_FACTOR = 1.5        # free-running gradient error allowed relative to the oracle's own bf16-storage twin
+TWIN_FLOOR = 1e-2
+
+
+def _weights_with_biases(ups, in_ch, n_cl):
+    weights = O.init_weights(1234, ups, in_ch, n_cl)
+    rng = np.random.default_rng(5)
+    for k in weights:                      # non-zero biases so that the bias paths are exercised
+        if k.endswith("/bias"):
+            weights[k] = rng.uniform(-0.05, 0.05, weights[k].shape).astype(np.float32)
+    return weights
 
 
 def _run_case(cuda_device, N, H, W, in_ch, ups, dropout, n_cl=1):
@@ -34,11 +47,7 @@ def _run_case(cuda_device, N, H, W, in_ch, ups, dropout, n_cl=1):
     imgs, msks = synthetic_batch(N, H, W, in_ch)
     if n_cl > 1:
         msks = np.concatenate([msks] + [np.roll(msks, 3 * k, axis=1) for k in range(1, n_cl)], axis=3)
-    weights = O.init_weights(1234, ups, in_ch, n_cl)
-    rng = np.random.default_rng(5)
-    for k in weights:                      # non-zero biases so that the bias paths are exercised
-        if k.endswith("/bias"):
-            weights[k] = rng.uniform(-0.05, 0.05, weights[k].shape).astype(np.float32)
+    weights = _weights_with_biases(ups, in_ch, n_cl)
     plan = UNetPlan(N, H, W, in_ch, n_cl, ups, dropout)
     assert list(plan.variables) == list(weights), "variable order / names differ from the TF creation order"
     for k, (_, shape) in plan.variables.items():
@@ -50,22 +59,7 @@ def _run_case(cuda_device, N, H, W, in_ch, ups, dropout, n_cl=1):
     plan.backward(d_imgs, d_msks)
     torch.cuda.synchronize()
     masks = plan_dropout_masks(plan, DROPOUT_SEED) if dropout > 0 else None
-    ref = O.loss_and_grads(weights, imgs, msks, ups, masks, dropout, torch.float32, keep_act_grads=True)
     names = act_names(ups)
-    forced = {oname: plan.tensor(pname).float().cpu().numpy() for pname, oname in names.items()}
-    emu = O.loss_and_grads(weights, imgs, msks, ups, None, dropout, torch.float32, emulate_bf16=True,
-                           keep_act_grads=True, forced_acts=forced)
-
-    report = []          # (what, err vs fp32 oracle, err vs oracle evaluated at the GPU's forward state)
-    for pname, oname in names.items():
-        got = plan.tensor(pname).float().cpu().numpy()
-        report.append((f"act {oname}", rel_err(got, ref["acts"][oname]), rel_err(got, emu["acts"][oname])))
-    preds = plan.preds.cpu().numpy()
-    report.append(("act preds", rel_err(preds, ref["preds"]), rel_err(preds, emu["preds"])))
-    met = plan.metrics.cpu().numpy()
-    for i, key in enumerate(("loss", "dice", "sensitivity", "specificity")):
-        assert abs(met[i] - ref[key]) < 1e-2, (key, met[i], ref[key])
-
     keep_scale = 1.0 / (1.0 - dropout) if dropout > 0 else 1.0
 
     def masked(o, oname):   # the plan stores d/d(pre-activation): oracle's d/d(output) times ReLU (and dropout) mask
@@ -75,28 +69,67 @@ def _run_case(cuda_device, N, H, W, in_ch, ups, dropout, n_cl=1):
         g = g * (o["acts"][oname] > 0)
         return g * keep_scale if oname in ("conv3a", "conv4a") else g
 
-    for pname, oname in names.items():
-        got = plan.tensor("g" + pname).float().cpu().numpy()
-        report.append((f"dact {oname}", rel_err(got, masked(ref, oname)), rel_err(got, masked(emu, oname))))
+    gpu_acts = {oname: plan.tensor(pname).float().cpu().numpy() for pname, oname in names.items()}
+    gpu_dacts = {oname: plan.tensor("g" + pname).float().cpu().numpy() for pname, oname in names.items()}
+    preds = plan.preds.cpu().numpy()
+    met = plan.metrics.cpu().numpy()
     grads = plan.get_grads()
-    for k in ref["grads"]:
-        report.append((f"grad {k}", rel_err(grads[k], ref["grads"][k]), rel_err(grads[k], emu["grads"][k])))
 
+    # one oracle pass at a time (the bs128 cases hold ~3 GB of fp32 activations per pass)
+    ref = O.loss_and_grads(weights, imgs, msks, ups, masks, dropout, torch.float32, keep_act_grads=True)
+    for i, key in enumerate(("loss", "dice", "sensitivity", "specificity")):
+        assert abs(met[i] - ref[key]) < 1e-2, (key, met[i], ref[key])
+    e32 = {}
+    for oname, got in gpu_acts.items():
+        e32[f"act {oname}"] = rel_err(got, ref["acts"][oname])
+    e32["act preds"] = rel_err(preds, ref["preds"])
+    ref_dacts = {oname: masked(ref, oname) for oname in gpu_dacts}
+    for oname, got in gpu_dacts.items():
+        e32[f"dact {oname}"] = rel_err(got, ref_dacts[oname])
+    for k in ref["grads"]:
+        e32[f"grad {k}"] = rel_err(grads[k], ref["grads"][k])
+    ref_grads = ref["grads"]
+    del ref
+
+    # the oracle's bf16-storage twin, free-running on the same inputs and masks, against the fp32 oracle
+    twin = O.loss_and_grads(weights, imgs, msks, ups, masks, dropout, torch.float32, emulate_bf16=True,
+                            keep_act_grads=True)
+    etw = {}
+    for oname in gpu_dacts:
+        etw[f"dact {oname}"] = rel_err(masked(twin, oname), ref_dacts[oname])
+    for k in ref_grads:
+        etw[f"grad {k}"] = rel_err(twin["grads"][k], ref_grads[k])
+    del twin, ref_dacts
+
+    # the oracle's backward at the GPU's forward state
+    emu = O.loss_and_grads(weights, imgs, msks, ups, None, dropout, torch.float32, emulate_bf16=True,
+                           keep_act_grads=True, forced_acts=gpu_acts)
+    eb = {}
+    for oname, got in gpu_acts.items():
+        eb[f"act {oname}"] = rel_err(got, emu["acts"][oname])
+    eb["act preds"] = rel_err(preds, emu["preds"])
+    for oname, got in gpu_dacts.items():
+        eb[f"dact {oname}"] = rel_err(got, masked(emu, oname))
+    for k in ref_grads:
+        eb[f"grad {k}"] = rel_err(grads[k], emu["grads"][k])
+    del emu
+
+    report = [(name, e32[name], eb[name], etw.get(name)) for name in e32]
     out = os.environ.get("UNETB200_TEST_REPORT")
     if out:
         with open(out, "a") as f:
             f.write(f"# N{N} {H}x{W} cin{in_ch} ups={ups} dropout={dropout} ncl={n_cl}   "
-                    f"[vs fp32 oracle | vs oracle backward at the GPU's forward state]\n")
-            for name, e32, eb in report:
-                f.write(f"{name:<28s} {e32:.3e} {eb:.3e}\n")
+                    f"[vs fp32 oracle | vs oracle backward at the GPU's forward state | oracle bf16 twin vs fp32 oracle]\n")
+            for name, a, b, t in report:
+                f.write(f"{name:<28s} {a:.3e} {b:.3e} {'' if t is None else format(t, '.3e')}\n")
     bad = []
-    for name, e32, eb in report:
-        if name.startswith("act ") and not e32 < TOL_BF16:
-            bad.append(f"{name}: {e32:.3e} vs fp32 oracle")
-        if not eb < TOL_BF16:
-            bad.append(f"{name}: {eb:.3e} vs the oracle at the same forward state")
-        if not e32 < GRAD_VS_FP32:
-            bad.append(f"{name}: {e32:.3e} vs fp32 oracle (sanity bound)")
+    for name, a, b, t in report:
+        if name.startswith("act ") and not a < TOL_BF16:
+            bad.append(f"{name}: {a:.3e} vs fp32 oracle")
+        if not b < TOL_BF16:
+            bad.append(f"{name}: {b:.3e} vs the oracle at the same forward state")
+        if t is not None and not a <= TWIN_FACTOR * t + TWIN_FLOOR:
+            bad.append(f"{name}: {a:.3e} vs fp32 oracle, the oracle's own bf16 twin is at {t:.3e}")
     assert not bad, "; ".join(bad)
     return report
 
@@ -128,6 +161,43 @@ def test_four_modalities_240(cuda_device):
 
 def test_four_modalities_240_upsampling(cuda_device):
     _run_case(cuda_device, 1, 240, 240, 4, True, 0.0)
+
+
+@pytest.mark.parametrize("ups", [False, True])
+def test_benchmarked_shape_bs128(cuda_device, ups):
+    """The shape bench.py times (BASELINE configs[0] / [1]: 128x128x1, bs128 per GPU): kernel variants, split-K factors
+    and wave sizing depend on the batch, so parity is asserted at this batch too, not only at N <= 4."""
+    _run_case(cuda_device, 128, 128, 128, 1, ups, 0.2)
+
+
+def test_bs512_one_step(cuda_device):
+    """BASELINE configs[4] shape (bs512 per GPU): loss / dice against the fp32 oracle, every weight gradient against
+    the oracle's backward at the GPU's forward state (activation gradients are not pulled back: 23 GB)."""
+    from unet_distributed_b200.plan import UNetPlan
+    N, H, W, ups, dropout = 512, 128, 128, True, 0.2
+    imgs, msks = synthetic_batch(N, H, W, 1)
+    weights = _weights_with_biases(ups, 1, 1)
+    plan = UNetPlan(N, H, W, 1, 1, ups, dropout)
+    plan.set_weights(weights)
+    d_imgs, d_msks = torch.tensor(imgs, device=cuda_device), torch.tensor(msks, device=cuda_device)
+    plan.forward(d_imgs, d_msks, seed=DROPOUT_SEED)
+    plan.backward(d_imgs, d_msks)
+    torch.cuda.synchronize()
+    masks = plan_dropout_masks(plan, DROPOUT_SEED)
+    met = plan.metrics.cpu().numpy()
+    grads = plan.get_grads()
+    names = act_names(ups)
+    ref = O.loss_and_grads(weights, imgs, msks, ups, masks, dropout, torch.float32)
+    for i, key in enumerate(("loss", "dice", "sensitivity", "specificity")):
+        assert abs(met[i] - ref[key]) < 1e-2, (key, met[i], ref[key])
+    assert rel_err(plan.preds.cpu().numpy(), ref["preds"]) < TOL_BF16
+    assert rel_err(plan.tensor("c5").float().cpu().numpy(), ref["acts"]["conv5b"]) < TOL_BF16
+    del ref
+    forced = {oname: plan.tensor(pname).float().cpu().numpy() for pname, oname in names.items()}
+    emu = O.loss_and_grads(weights, imgs, msks, ups, None, dropout, torch.float32, emulate_bf16=True,
+                           forced_acts=forced)
+    bad = [f"{k}: {rel_err(grads[k], g):.3e}" for k, g in emu["grads"].items() if not rel_err(grads[k], g) < TOL_BF16]
+    assert not bad, "; ".join(bad)
 
 
 def test_deterministic_repeat(cuda_device):
