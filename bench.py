@@ -315,7 +315,7 @@ def run_b200(args):
     allreduce = None
     if world > 1:
         for _ in range(3):
-            for seg in range(3):
+            for seg in range(len(tr.reducer.buckets)):
                 tr.reducer.launch(seg)
             tr.reducer.wait()
         barrier()
@@ -323,7 +323,7 @@ def run_b200(args):
         reps = 20
         a0.record()
         for _ in range(reps):
-            for seg in range(3):
+            for seg in range(len(tr.reducer.buckets)):
                 tr.reducer.launch(seg)
             tr.reducer.wait()
         a1.record()

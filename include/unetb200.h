@@ -23,6 +23,10 @@
 extern "C" {
 #endif
 
+/* Element types named across the ABI. Activations of the tile engines are BF16 (default) or, in the fp32/tf32 precision
+ * mode, F32 computed with kind::tf32 tensor-core MMAs (the reference computes in fp32, test_dist.py:196-202). */
+enum { UNETB200_BF16 = 0, UNETB200_TF32 = 1, UNETB200_F32 = 2, UNETB200_F64 = 3 };
+
 int unetb200_version(void);
 const char* unetb200_last_error_string(void);
 
@@ -135,6 +139,13 @@ int unetb200_dropout_mask(unsigned char* keep, long long n, float keep_prob, uin
 long long unetb200_launch_count(void);
 int unetb200_profile_enable(int on);
 int unetb200_profile_collect(double* ms, double* flops, double* bytes, long long* launches);
+/* One shuffled batch, or one replica's shard of it, cut out of a training set that stays in HBM: data.py:29-54
+ * (get_epoch: shuffle, drop the remainder, reshape into batches) and the shard slice of test_dist.py:390-394.
+ * dst[r][0..row_elems) = (float) src[perm[first + r]][...] for r in [0, rows); perm is a DEVICE int64 permutation
+ * (NULL = identity). src rows are UNETB200_F32 or UNETB200_F64 (update_channels returns float64 arrays,
+ * preprocess.py:301-302, which TF casts at feed time); row_elems (= H*W*C) must be a multiple of 4. */
+int unetb200_gather_batch(const void* src, int src_dtype, long long src_rows, const long long* perm, long long first,
+                          int rows, long long row_elems, float* dst, void* stream);
 int unetb200_cast_f32_to_bf16(const float* x, void* y, long long n, void* stream);
 int unetb200_cast_bf16_to_f32(const void* x, float* y, long long n, void* stream);
 
@@ -161,12 +172,18 @@ int unetb200_plan_pack_weights(unetb200_plan* plan, void* stream);
  * Dropout stream seed = seed + *seed_add (seed_add: optional device int64, e.g. the global step). */
 int unetb200_plan_forward(unetb200_plan* plan, const float* imgs, const float* msks, uint64_t seed,
                           const long long* seed_add, void* stream);
-/* Backward in three segments (0: head + decoder, 1: conv5a/b, 2: encoder); gradients land in the bound flat buffer,
- * multiplied by grad_scale. The loss is dice_coef_loss(msks, preds) of the last forward, unless dpreds (fp32
- * [N,H,W,n_cl], an explicit dL/dpreds) is given. unetb200_plan_bucket gives the flat range complete after a segment. */
+/* Backward in unetb200_plan_num_segments() (= 5) segments, in this order: 0 head + conv9/conv8 levels, 1 conv7/conv6
+ * levels, 2 conv5a/b, 3 conv4/conv3, 4 conv2/conv1. Gradients land in the bound flat buffer, multiplied by grad_scale.
+ * The loss is dice_coef_loss(msks, preds) of the last forward, unless dpreds (fp32 [N,H,W,n_cl], an explicit
+ * dL/dpreds) is given. unetb200_plan_bucket gives the contiguous flat range that is complete after a segment (the
+ * buckets tile [0, num_params) exactly): its all-reduce (SyncReplicasOptimizer, test_dist.py:251-258) and optimizer
+ * update can start while later segments run; unetb200_plan_pack_range then refreshes the packed GEMM operands of
+ * just that range. */
+int unetb200_plan_num_segments(const unetb200_plan* plan);
 int unetb200_plan_backward(unetb200_plan* plan, const float* imgs, const float* msks, const float* dpreds,
                            float grad_scale, int segment, void* stream);
 int unetb200_plan_bucket(const unetb200_plan* plan, int segment, long long* begin, long long* end);
+int unetb200_plan_pack_range(unetb200_plan* plan, long long begin, long long end, void* stream);
 /* The weight gradients of plan_backward run on a second, plan-owned stream that is forked from and joined back into
  * the caller's stream inside every segment (so the call stays stream-ordered and capturable). enable = 0 keeps all
  * kernels on the caller's stream in program order (used when timing kernels one at a time); returns the old setting.

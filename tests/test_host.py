@@ -57,10 +57,12 @@ def test_native_planner_variable_table(ups, cin, ncl):
     assert d["num_params_padded"] >= offs[-1][0] + offs[-1][1]
     # buckets: a partition of the flat buffer, in the order backward completes them
     b = d["buckets"]
-    assert b[2][0] == 0 and b[2][1] == b[1][0] and b[1][1] == b[0][0] and b[0][1] == d["num_params_padded"]
-    assert b[1][0] == d["variables"]["conv5a/kernel"][0]
-    first_decoder = "conv6a/kernel" if ups else "transConv6/kernel"
-    assert b[0][0] == d["variables"][first_decoder][0]
+    assert len(b) == 5 and b[4][0] == 0 and b[0][1] == d["num_params_padded"]
+    assert all(b[i + 1][1] == b[i][0] for i in range(4))
+    first = {0: "conv8a/kernel" if ups else "transConv8/kernel", 1: "conv6a/kernel" if ups else "transConv6/kernel",
+             2: "conv5a/kernel", 3: "conv3a/kernel", 4: "conv1a/kernel"}
+    for i, name in first.items():
+        assert b[i][0] == d["variables"][name][0], (i, name)
     assert d["arena_bytes"] > 0
 
 

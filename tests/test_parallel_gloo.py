@@ -42,7 +42,7 @@ def _worker(rank, port, outdir):
     parallel.broadcast_flat(wflat)
     assert torch.all(wflat == 0)
     red = parallel.BucketedAllReduce(flat, d["buckets"])
-    for seg in range(3):                                      # launched in the order backward completes them
+    for seg in range(len(d["buckets"])):                      # launched in the order backward completes them
         red.launch(seg)
     red.wait()
     flat *= 1.0 / ws                                          # folded into the optimizer's grad_scale on the GPU
@@ -66,3 +66,24 @@ def test_bucketed_allreduce_reproduces_sync_replicas():
         n = int(np.prod(shape))
         a, b = got[off:off + n].reshape(shape).astype(np.float64), mean[k]
         assert np.linalg.norm(a - b) <= 1e-6 * np.linalg.norm(b) + 1e-12, k
+
+
+def test_buckets_tile_the_flat_buffer():
+    """The gradient buckets (one per backward segment) are contiguous, ordered from the end of the flat buffer to its
+    start (the order backward completes them) and tile [0, num_params) exactly, for both decoders and both inputs;
+    every variable lies inside exactly one bucket."""
+    from unet_distributed_b200.plan import describe_plan
+    for ups in (False, True):
+        for (H, C) in ((128, 1), (240, 4)):
+            d = describe_plan(2, H, H, in_channels=C, use_upsampling=ups)
+            b = d["buckets"]
+            assert len(b) == 5 and b[0][1] == d["num_params_padded"] and b[-1][0] == 0
+            for (lo, hi), (lo2, hi2) in zip(b[:-1], b[1:]):
+                assert lo < hi and hi2 == lo and lo % 4 == 0
+            for name, (off, shape) in d["variables"].items():
+                n = int(np.prod(shape))
+                assert sum(1 for lo, hi in b if lo <= off and off + n <= hi) == 1, name
+            first = {next(i for i, (lo, hi) in enumerate(b) if lo <= off < hi) for name, (off, _) in
+                     d["variables"].items() if name.startswith(("conv1", "conv2"))}
+            assert first == {4}, "the last (exposed) bucket holds conv1a..conv2b only"
+            assert (b[4][1] - b[4][0]) * 4 < 300_000

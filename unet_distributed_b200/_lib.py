@@ -19,6 +19,10 @@ class UnetB200Error(RuntimeError):
     pass
 
 
+# element-type enum of include/unetb200.h
+BF16, TF32, F32, F64 = 0, 1, 2, 3
+
+
 _SCALARS = {
     "int": ctypes.c_int,
     "float": ctypes.c_float,

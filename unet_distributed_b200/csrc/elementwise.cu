@@ -518,10 +518,10 @@ __global__ void pack_tconv_dgrad_kernel(const float* __restrict__ w, __nv_bfloat
 }
 __global__ void __launch_bounds__(256)
 pack_all_kernel(const PackLayer* __restrict__ layers, int nlayers, const float* __restrict__ params,
-                uint8_t* __restrict__ arena) {
+                uint8_t* __restrict__ arena, int tile_base) {
   __shared__ float tile[32][33];
   int li = 0;
-  const int tile_id = static_cast<int>(blockIdx.x);
+  const int tile_id = static_cast<int>(blockIdx.x) + tile_base;
   while (li + 1 < nlayers && layers[li + 1].tile_start <= tile_id) ++li;   // block-uniform
   const PackLayer L = layers[li];
   const int t = tile_id - L.tile_start;
@@ -578,6 +578,34 @@ __global__ void cast_f32_bf16_kernel(const float* __restrict__ x, __nv_bfloat16*
 __global__ void cast_bf16_f32_kernel(const __nv_bfloat16* __restrict__ x, float* __restrict__ y, long long n) {
   const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
   if (i < n) y[i] = __bfloat162float(x[i]);
+}
+
+// ------------------------------------------------------------------------------------------ batch gather (data.py:29-54)
+// dst[r][:] = float(src[perm[first + r]][:]): one shuffled batch (or one replica's shard of it) cut out of a training
+// set that stays in HBM. A thread moves four elements: one 16-byte load (fp32 rows) or two (float64 rows, the dtype
+// update_channels hands out, preprocess.py:301-302) and one 16-byte store; the row index is read once per thread.
+template <typename T>
+__global__ void gather_rows_kernel(const T* __restrict__ src, const long long* __restrict__ perm, long long first,
+                                   long long row_elems, long long quads_per_row, long long total_quads,
+                                   long long src_rows, float* __restrict__ dst) {
+  for (long long q = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; q < total_quads;
+       q += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const long long r = q / quads_per_row;
+    const long long e = (q - r * quads_per_row) * 4;
+    long long row = perm ? perm[first + r] : first + r;
+    row = row < 0 ? 0 : (row >= src_rows ? src_rows - 1 : row);   // a bad index must not read outside the set
+    const T* p = src + row * row_elems + e;
+    float4 o;
+    if constexpr (sizeof(T) == 8) {
+      const double2 a = *reinterpret_cast<const double2*>(p);
+      const double2 b = *reinterpret_cast<const double2*>(p + 2);
+      o = make_float4(static_cast<float>(a.x), static_cast<float>(a.y), static_cast<float>(b.x),
+                      static_cast<float>(b.y));
+    } else {
+      o = *reinterpret_cast<const float4*>(p);
+    }
+    *reinterpret_cast<float4*>(dst + r * row_elems + e) = o;
+  }
 }
 
 // ------------------------------------------------------------------------------------------ optimizers
@@ -946,10 +974,10 @@ int colsum_bf16_static(const void* dz, float* db, long long P, int C, cudaStream
 }
 
 int pack_all(const PackLayer* layers_dev, int nlayers, int total_tiles, const float* params, void* arena,
-             cudaStream_t s) {
+             cudaStream_t s, int tile_base) {
   if (nlayers <= 0 || total_tiles <= 0) return UB_OK;
   pack_all_kernel<<<static_cast<unsigned>(total_tiles), 256, 0, s>>>(layers_dev, nlayers, params,
-                                                                     reinterpret_cast<uint8_t*>(arena));
+                                                                     reinterpret_cast<uint8_t*>(arena), tile_base);
   UB_CHECK_CUDA(cudaGetLastError());
   return UB_OK;
 }
@@ -1022,6 +1050,30 @@ int cast_f32_to_bf16(const float* x, void* y, long long n, cudaStream_t s) {
 }
 int cast_bf16_to_f32(const void* x, float* y, long long n, cudaStream_t s) {
   cast_bf16_f32_kernel<<<grid_for(n, kThreads), kThreads, 0, s>>>(reinterpret_cast<const __nv_bfloat16*>(x), y, n);
+  UB_CHECK_CUDA(cudaGetLastError());
+  return UB_OK;
+}
+
+int gather_rows(const void* src, int src_is_f64, long long src_rows, const long long* perm, long long first, int rows,
+                long long row_elems, float* dst, cudaStream_t s) {
+  UB_REQUIRE(src && dst && rows >= 0 && row_elems > 0 && src_rows > 0, "gather_batch: null buffer or empty shape");
+  UB_REQUIRE(row_elems % 4 == 0, "gather_batch: row of %lld elements is not a multiple of 4", row_elems);
+  UB_REQUIRE(reinterpret_cast<uintptr_t>(src) % 16 == 0 && reinterpret_cast<uintptr_t>(dst) % 16 == 0,
+             "gather_batch: buffers must be 16-byte aligned");
+  UB_REQUIRE(perm || first + rows <= src_rows, "gather_batch: rows [%lld, %lld) outside the set of %lld", first,
+             first + rows, src_rows);
+  if (rows == 0) return UB_OK;
+  const long long qpr = row_elems / 4, total = qpr * rows;
+  long long blocks = (total + kThreads - 1) / kThreads;
+  const long long cap = static_cast<long long>(device_sm_count()) * 16;   // grid-stride: a few waves at most
+  if (blocks > cap) blocks = cap;
+  if (src_is_f64) {
+    gather_rows_kernel<double><<<static_cast<unsigned>(blocks), kThreads, 0, s>>>(
+        reinterpret_cast<const double*>(src), perm, first, row_elems, qpr, total, src_rows, dst);
+  } else {
+    gather_rows_kernel<float><<<static_cast<unsigned>(blocks), kThreads, 0, s>>>(
+        reinterpret_cast<const float*>(src), perm, first, row_elems, qpr, total, src_rows, dst);
+  }
   UB_CHECK_CUDA(cudaGetLastError());
   return UB_OK;
 }

@@ -66,8 +66,9 @@ struct PackLayer {
   int taps, cin, cout;  // multiples of 32 channels
   int tile_start;       // first block of this layer (layers sorted by tile_start)
 };
+// layers_dev may point into the middle of the table: tile_base is then the tile_start of its first entry.
 int pack_all(const PackLayer* layers_dev, int nlayers, int total_tiles, const float* params, void* arena,
-             cudaStream_t s);
+             cudaStream_t s, int tile_base = 0);
 
 // TF-1.4 AdamOptimizer on a flat fp32 buffer. step_ptr holds the number of updates applied so far (device int64).
 //   lr = const_lr ? lr0 : lr0 * lr_fraction^(step/decay_steps);  t = step+1
@@ -83,6 +84,11 @@ int step_increment(long long* step_ptr, cudaStream_t s);
 // keep[i] = 1/0 for the dropout stream (same Philox function as the conv epilogue); n multiple of 8.
 int dropout_mask(unsigned char* keep, long long n, float keep_prob, unsigned long long seed, unsigned int stream_id,
                  cudaStream_t s);
+
+// dst[r][0..row_elems) = float(src[perm ? perm[first + r] : first + r][...]) for r in [0, rows): one shuffled batch cut
+// out of a device-resident training set (data.py:29-54). src rows are fp32 or float64; perm is a device int64 array.
+int gather_rows(const void* src, int src_is_f64, long long src_rows, const long long* perm, long long first, int rows,
+                long long row_elems, float* dst, cudaStream_t s);
 
 int cast_f32_to_bf16(const float* x, void* y, long long n, cudaStream_t s);
 int cast_bf16_to_f32(const void* x, float* y, long long n, cudaStream_t s);

@@ -36,6 +36,7 @@ struct Layer {
 };
 
 constexpr size_t kAlign = 1024;
+constexpr int kSegments = 5;   // backward segments = gradient buckets
 constexpr size_t kNoGate = ~static_cast<size_t>(0);
 
 }  // namespace
@@ -427,14 +428,17 @@ int unetb200_plan_forward(unetb200_plan* P, const float* imgs, const float* msks
 }
 
 // Backward segments (the autodiff graph optimizer.compute_gradients builds at test_dist.py:246-248), split so the
-// caller can start the all-reduce of a gradient bucket as soon as the segment that completes it has been enqueued:
-//   segment 0: head + decoder  -> gradients of transConv6|conv6a .. Mask   (tail of the flat buffer)
-//   segment 1: conv5b, conv5a  -> the two largest tensors
-//   segment 2: encoder         -> conv1a .. conv4b
+// caller can start the all-reduce (and then the update) of a gradient bucket as soon as the segment that completes it
+// has been enqueued. Backward walks the flat buffer from its end to its start, so every bucket is one contiguous range:
+//   segment 0: head, conv9b/a, [transConv9], conv8b/a, [transConv8]   (tail of the flat buffer, 0.7 MB)
+//   segment 1: conv7b/a, [transConv7], conv6b/a, [transConv6]        (11.5 MB; 7.4 MB with UpSampling2D)
+//   segment 2: conv5b, conv5a                                          (the two largest tensors)
+//   segment 3: conv4b/a, conv3b/a
+//   segment 4: conv2b/a, conv1b/a     (0.26 MB: the only all-reduce that cannot hide behind backward work)
 int unetb200_plan_backward(unetb200_plan* P, const float* imgs, const float* msks, const float* dpreds,
                            float grad_scale, int segment, void* stream) {
   UB_REQUIRE(P->arena, "plan_backward: plan is not bound");
-  UB_REQUIRE(segment >= 0 && segment <= 2, "plan_backward: segment %d outside 0..2", segment);
+  UB_REQUIRE(segment >= 0 && segment < kSegments, "plan_backward: segment %d outside 0..%d", segment, kSegments - 1);
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
   const int N = P->N;
   float* ws = reinterpret_cast<float*>(P->at(P->ws));              // main stream: head
@@ -463,13 +467,15 @@ int unetb200_plan_backward(unetb200_plan* P, const float* imgs, const float* msk
     return UB_OK;
   };
 
-  if (segment == 0) {
+  if (segment <= 1) {
+    if (segment == 0) {
     const long long pixels = static_cast<long long>(N) * P->H * P->W;
     UB_REQUIRE(msks || dpreds, "plan_backward: need the labels or an explicit dL/dpreds");
     RC(head_bwd(P->at(P->dc[0]), P->W_(P->mask), dpreds ? dpreds : msks, reinterpret_cast<const float*>(P->at(P->preds)),
                 dpreds ? nullptr : reinterpret_cast<const float*>(P->at(P->sums)), 1.0f, grad_scale, P->at(P->g_dc[0]), P->dW_(P->mask),
                 P->dB_(P->mask), ws, pixels, 32, P->ncl, s));
-    for (int L = 0; L < 4; ++L) {
+    }
+    for (int L = 2 * segment; L < 2 * segment + 2; ++L) {
       const int H = P->Hl(L), W = P->Wl(L);
       const long long px = static_cast<long long>(N) * H * W;
       const int la = P->dec_a[L], lb = P->dec_b[L];
@@ -514,7 +520,7 @@ int unetb200_plan_backward(unetb200_plan* P, const float* imgs, const float* msk
     return UB_OK;
   }
 
-  if (segment == 1) {
+  if (segment == 2) {
     const int L = 4;
     const int H = P->Hl(L), W = P->Wl(L);
     const int la = P->enc_a[L], lb = P->enc_b[L];
@@ -532,7 +538,7 @@ int unetb200_plan_backward(unetb200_plan* P, const float* imgs, const float* msk
     return UB_OK;
   }
 
-  for (int L = 3; L >= 0; --L) {
+  for (int L = (segment == 3 ? 3 : 1); L >= (segment == 3 ? 2 : 0); --L) {
     const int H = P->Hl(L), W = P->Wl(L);
     const int la = P->enc_a[L], lb = P->enc_b[L];
     // MaxPoolGrad + skip gradient + ReluGrad of conv{L+1}b, in place in g_c[L]
@@ -568,13 +574,36 @@ int unetb200_plan_side_stream(unetb200_plan* P, int enable) {
 
 // Flat-buffer range [begin, end) (floats) whose gradients are complete once `segment` has run.
 int unetb200_plan_bucket(const unetb200_plan* P, int segment, long long* begin, long long* end) {
-  UB_REQUIRE(segment >= 0 && segment <= 2, "plan_bucket: segment %d outside 0..2", segment);
-  const long long conv5a = P->layers[P->enc_a[4]].w_off;
-  const long long after5 = P->ups ? P->layers[P->dec_a[3]].w_off : P->layers[P->tc[3]].w_off;
-  if (segment == 0) { *begin = after5; *end = P->nparams; }
-  else if (segment == 1) { *begin = conv5a; *end = after5; }
-  else { *begin = 0; *end = conv5a; }
+  UB_REQUIRE(segment >= 0 && segment < kSegments, "plan_bucket: segment %d outside 0..%d", segment, kSegments - 1);
+  // first variable of decoder level L (flat order inside a level: [transConv], conv_a, conv_b)
+  auto dec_begin = [&](int L) { return P->ups ? P->layers[P->dec_a[L]].w_off : P->layers[P->tc[L]].w_off; };
+  const long long cut[kSegments + 1] = {P->nparams, dec_begin(1), dec_begin(3), P->layers[P->enc_a[4]].w_off,
+                                        P->layers[P->enc_a[2]].w_off, 0};
+  *begin = cut[segment + 1];
+  *end = cut[segment];
   return UB_OK;
+}
+
+int unetb200_plan_num_segments(const unetb200_plan*) { return kSegments; }
+
+// Refresh the bf16 GEMM operands of the variables inside [begin, end) of the flat buffer only (the update of one
+// gradient bucket, applied while the rest of backward still runs).
+int unetb200_plan_pack_range(unetb200_plan* P, long long begin, long long end, void* stream) {
+  UB_REQUIRE(P->arena, "plan_pack_range: plan is not bound");
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  int first = -1, last = -1;   // pack_layers is in flat order
+  for (int i = 0; i < static_cast<int>(P->pack_layers.size()); ++i) {
+    const long long off = P->pack_layers[i].src;
+    if (off >= begin && off < end) {
+      if (first < 0) first = i;
+      last = i;
+    }
+  }
+  if (first < 0) return UB_OK;
+  const int tile0 = P->pack_layers[first].tile_start;
+  const int tile1 = last + 1 < static_cast<int>(P->pack_layers.size()) ? P->pack_layers[last + 1].tile_start : P->pack_tiles;
+  return pack_all(reinterpret_cast<const PackLayer*>(P->at(P->pack_table)) + first, last - first + 1, tile1 - tile0,
+                  P->params, P->arena, s, tile0);
 }
 
 }  // extern "C"

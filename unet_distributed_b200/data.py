@@ -70,17 +70,23 @@ class ResidentEpochs:
     """The training set kept on one device (8,192 BraTS slices of 128x128 are ~1 GB: a fraction of 180 GB of HBM) and
     cut into the same epochs as get_epoch (data.py:29-54): same permutation for the same seed, same dropped
     remainder, same batch order. `batch(i, start, end)` gathers this replica's shard of batch i
-    (test_dist.py:390-394) with one index_select per array, so the step loop never touches the host.
+    (test_dist.py:390-394) with one unetb200_gather_batch launch per array straight into fp32 step inputs, so the
+    step loop never touches the host.
 
-    imgs / msks: NHWC arrays or tensors; device: torch device (a CPU device works too, which is how this is tested)."""
+    imgs / msks: NHWC arrays or tensors. dtype: torch dtype of the resident copy -- float32 (default: cast once at
+    upload) or float64 (update_channels hands out float64 arrays, preprocess.py:301-302; the gather kernel then does
+    the cast TensorFlow does at feed time). On a CPU device (how the epoch logic is tested without a GPU) the gather
+    is torch.index_select; on a CUDA device it is the library's kernel and nothing else."""
 
     def __init__(self, batch_size, imgs_train, msks_train, device, dtype=None):
         import torch
         self._torch = torch
         self.batch_size = int(batch_size)
         dtype = torch.float32 if dtype is None else dtype
-        self.imgs = torch.as_tensor(np.ascontiguousarray(imgs_train)).to(device=device, dtype=dtype)
-        self.msks = torch.as_tensor(np.ascontiguousarray(msks_train)).to(device=device, dtype=dtype)
+        if dtype not in (torch.float32, torch.float64):
+            raise ValueError("ResidentEpochs: dtype must be torch.float32 or torch.float64")
+        self.imgs = torch.as_tensor(np.ascontiguousarray(imgs_train)).to(device=device, dtype=dtype).contiguous()
+        self.msks = torch.as_tensor(np.ascontiguousarray(msks_train)).to(device=device, dtype=dtype).contiguous()
         self.train_size = int(self.imgs.shape[0])
         self.epoch_length = self.train_size - self.train_size % self.batch_size
         self.num_batches = self.epoch_length // self.batch_size
@@ -97,11 +103,31 @@ class ResidentEpochs:
         self.perm = self._torch.as_tensor(perm, dtype=self._torch.int64).to(self.imgs.device)
         return self
 
-    def batch(self, batch_idx, start=0, end=None):
-        """(images, masks) of samples [start, end) of batch `batch_idx` of the current epoch, on the device."""
+    def _gather(self, src, lo, rows, out):
+        torch = self._torch
+        shape = (rows,) + tuple(src.shape[1:])
+        if out is None:
+            out = torch.empty(shape, dtype=torch.float32, device=src.device)
+        elif tuple(out.shape) != shape or out.dtype != torch.float32 or not out.is_contiguous():
+            raise ValueError(f"ResidentEpochs.batch: out must be a contiguous float32 tensor of shape {shape}")
+        if not src.is_cuda:
+            out.copy_(src.index_select(0, self.perm[lo:lo + rows]))
+            return out
+        import ctypes
+        from . import _lib
+        row_elems = int(np.prod(src.shape[1:]))
+        _lib.call("unetb200_gather_batch", ctypes.c_void_p(src.data_ptr()),
+                  _lib.F64 if src.dtype == torch.float64 else _lib.F32, ctypes.c_longlong(self.train_size),
+                  ctypes.c_void_p(self.perm.data_ptr()), ctypes.c_longlong(lo), int(rows), ctypes.c_longlong(row_elems),
+                  ctypes.c_void_p(out.data_ptr()), ctypes.c_void_p(torch.cuda.current_stream().cuda_stream))
+        return out
+
+    def batch(self, batch_idx, start=0, end=None, out=None):
+        """(images, masks) of samples [start, end) of batch `batch_idx` of the current epoch, fp32 on the device.
+        out: optional (imgs, msks) pair of preallocated fp32 tensors to fill (e.g. the trainer's input slots)."""
         if self.perm is None:
             raise RuntimeError("ResidentEpochs.shuffle() has not been called")
         end = self.batch_size if end is None else end
-        lo = batch_idx * self.batch_size
-        idx = self.perm[lo + start:lo + end]
-        return self.imgs.index_select(0, idx), self.msks.index_select(0, idx)
+        lo = batch_idx * self.batch_size + start
+        o_i, o_m = out if out is not None else (None, None)
+        return self._gather(self.imgs, lo, end - start, o_i), self._gather(self.msks, lo, end - start, o_m)

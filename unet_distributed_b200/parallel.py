@@ -23,6 +23,12 @@ def shard_range(batch_size, num_replicas, rank):
     return start, start + data_range
 
 
+def replica_seed(seed, rank):
+    """Dropout seed of replica `rank`: the reference's workers draw independent masks (every sess.run samples its own
+    RandomUniform, model.py:60,66), so the rank is folded into the Philox seed (64-bit golden-ratio stride)."""
+    return (int(seed) + int(rank) * 0x9E3779B97F4A7C15) & 0xFFFFFFFFFFFFFFFF
+
+
 def world():
     if dist.is_available() and dist.is_initialized():
         return dist.get_world_size(), dist.get_rank()
@@ -60,14 +66,18 @@ class BucketedAllReduce:
         self.group = group
         self._pending = []
 
-    def launch(self, bucket_index):
-        """Enqueue the all-reduce of one bucket behind the work already on the current stream."""
+    def launch(self, bucket_index, track=True):
+        """Enqueue the all-reduce of one bucket behind the work already on the current stream. Returns the work
+        handle (None at world size 1); with track=True it is also kept for wait()."""
         if world()[0] == 1:
-            return
+            return None
         b, e = self.buckets[bucket_index]
-        if e > b:
-            self._pending.append(dist.all_reduce(self.flat[b:e], op=dist.ReduceOp.SUM, group=self.group,
-                                                 async_op=True))
+        if e <= b:
+            return None
+        work = dist.all_reduce(self.flat[b:e], op=dist.ReduceOp.SUM, group=self.group, async_op=True)
+        if track:
+            self._pending.append(work)
+        return work
 
     def wait(self):
         """Make the current stream (or, with gloo, the host) wait for every launched bucket."""

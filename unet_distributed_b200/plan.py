@@ -21,7 +21,7 @@ def _stream():
 
 def describe_plan(N, H, W, in_channels=1, n_cl_out=1, use_upsampling=False, dropout=0.2):
     """Host-only description of a plan (no GPU needed): variable table (TF names -> (offset, shape)), padded flat
-    size, arena bytes and the three gradient buckets.  This is the native planner's own answer, not a Python copy."""
+    size, arena bytes and the gradient buckets (one per backward segment).  This is the native planner's own answer, not a Python copy."""
     L = _lib.lib()
     h = ctypes.c_void_p()
     _lib.check(L.unetb200_plan_create(ctypes.byref(h), int(N), int(H), int(W), int(in_channels), int(n_cl_out),
@@ -37,7 +37,7 @@ def describe_plan(N, H, W, in_channels=1, n_cl_out=1, use_upsampling=False, drop
             variables[name.value.decode()] = (int(off.value), tuple(shape[k] for k in range(rank.value)))
         buckets = []
         b, e = ctypes.c_longlong(), ctypes.c_longlong()
-        for seg in range(3):
+        for seg in range(L.unetb200_plan_num_segments(h)):
             _lib.check(L.unetb200_plan_bucket(h, seg, ctypes.byref(b), ctypes.byref(e)), "unetb200_plan_bucket")
             buckets.append((int(b.value), int(e.value)))
         return {"variables": variables, "num_params_padded": int(L.unetb200_plan_num_params(h)),
@@ -83,7 +83,8 @@ class UNetPlan:
         self.bind(self.params, self.grads)
         self.buckets = []
         b, e = ctypes.c_longlong(), ctypes.c_longlong()
-        for seg in range(3):
+        self.num_segments = int(L.unetb200_plan_num_segments(h))
+        for seg in range(self.num_segments):
             _lib.check(L.unetb200_plan_bucket(h, seg, ctypes.byref(b), ctypes.byref(e)), "unetb200_plan_bucket")
             self.buckets.append((int(b.value), int(e.value)))
 
@@ -160,8 +161,13 @@ class UNetPlan:
         """Run weight gradients on the plan's second stream (default) or in program order; returns the old setting."""
         return bool(_lib.lib().unetb200_plan_side_stream(self._h, 1 if enable else 0))
 
-    def pack_weights(self):
-        _lib.call("unetb200_plan_pack_weights", self._h, _stream())
+    def pack_weights(self, begin=None, end=None):
+        """Refresh the packed bf16 GEMM operands from the fp32 masters: all of them, or only the variables inside the
+        flat range [begin, end) (one gradient bucket)."""
+        if begin is None:
+            _lib.call("unetb200_plan_pack_weights", self._h, _stream())
+        else:
+            _lib.call("unetb200_plan_pack_range", self._h, ctypes.c_longlong(begin), ctypes.c_longlong(end), _stream())
 
     def forward(self, imgs, msks=None, seed=0, seed_add=None):
         """imgs fp32 [N,H,W,Cin] and msks fp32 [N,H,W,n_cl] on this device, contiguous."""
@@ -172,7 +178,7 @@ class UNetPlan:
                   _ptr(seed_add), _stream())
 
     def backward(self, imgs, msks=None, dpreds=None, grad_scale=1.0, segment=None):
-        segs = (0, 1, 2) if segment is None else (segment,)
+        segs = range(self.num_segments) if segment is None else (segment,)
         for s in segs:
             _lib.call("unetb200_plan_backward", self._h, _ptr(imgs), _ptr(msks), _ptr(dpreds),
                       ctypes.c_float(grad_scale), int(s), _stream())

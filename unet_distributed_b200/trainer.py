@@ -23,7 +23,7 @@ class Trainer:
     def __init__(self, N, H=128, W=128, in_channels=1, n_cl_out=1, use_upsampling=False, dropout=0.2,
                  learning_rate=0.0005, const_learningrate=True, lr_fraction=0.2, decay_steps=100, optimizer="adam",
                  beta1=0.9, beta2=0.999, epsilon=1e-8, weight_seed=1234, dropout_seed=816, weights=None,
-                 use_cuda_graph=False):
+                 use_cuda_graph=False, shared_dropout_masks=False):
         self.world, self.rank = parallel.world()
         self.plan = UNetPlan(N, H, W, in_channels, n_cl_out, use_upsampling, dropout)
         p = self.plan
@@ -37,12 +37,16 @@ class Trainer:
         self.optimizer = optimizer
         if optimizer not in ("adam", "sgd"):
             raise ValueError("optimizer must be 'adam' or 'sgd'")
-        self.dropout_seed = int(dropout_seed)
+        # Every replica draws its own dropout masks, as the reference's workers do (each sess.run samples anew,
+        # model.py:60,66); shared_dropout_masks=True gives all ranks the same Philox seed (parity tests).
+        self.dropout_seed = parallel.replica_seed(dropout_seed, 0 if shared_dropout_masks else self.rank)
+        self._eval_calls = 0
         p.set_weights(weights if weights is not None else initial_weights(p.variables, weight_seed))
         parallel.broadcast_flat(p.params)
         if self.world > 1:
             p.pack_weights()
         self.reducer = parallel.BucketedAllReduce(p.grads, p.buckets)
+        self._upd_stream = torch.cuda.Stream(device=dev)   # bucket updates run here, beside the rest of backward
         self.use_cuda_graph = bool(use_cuda_graph)
         self._graph = None
         self._g_imgs = self._g_msks = None
@@ -54,37 +58,42 @@ class Trainer:
         self._d_msks = torch.empty((N, H, W, n_cl_out), dtype=torch.float32, device=dev)
 
     # ------------------------------------------------------------------ one optimizer step on device-resident data
-    def _piece(self, i, imgs, msks):
-        """The step in four launch sequences; the gradient all-reduces go between them (eager NCCL calls)."""
-        p = self.plan
-        if i == 0:
-            p.forward(imgs, msks, seed=self.dropout_seed, seed_add=self.step_dev)
-            p.backward(imgs, msks, grad_scale=1.0, segment=0)
-        elif i < 3:
-            p.backward(imgs, msks, grad_scale=1.0, segment=i)
-        else:
-            self._apply_update()
-
     def _enqueue_step(self, imgs, msks):
-        for seg in range(3):
-            self._piece(seg, imgs, msks)
-            self.reducer.launch(seg)
-        self.reducer.wait()
-        self._piece(3, imgs, msks)
-
-    def _apply_update(self):
+        """The whole step as one launch sequence (eager, or captured into ONE CUDA graph at any world size):
+        forward, then per backward segment: the segment's kernels -> all-reduce of the bucket it completes (NCCL on
+        its own stream) -> optimizer update + operand re-pack of that bucket on the update stream.  Only the last,
+        smallest bucket (conv1a..conv2b, 0.26 MB) has no backward work left to hide behind."""
         p = self.plan
+        cur = torch.cuda.current_stream()
+        upd = self._upd_stream
+        p.forward(imgs, msks, seed=self.dropout_seed, seed_add=self.step_dev)
+        for seg in range(p.num_segments):
+            p.backward(imgs, msks, grad_scale=1.0, segment=seg)
+            work = self.reducer.launch(seg, track=False)      # ordered behind the segment on the current stream
+            upd.wait_stream(cur)
+            with torch.cuda.stream(upd):
+                if work is not None:
+                    work.wait()                                # the update stream waits for NCCL, `cur` does not
+                self._update_range(*p.buckets[seg])
+        with torch.cuda.stream(upd):
+            _lib.call("unetb200_step_increment", _ptr(self.step_dev), _stream())
+        cur.wait_stream(upd)
+
+    def _update_range(self, b, e):
+        """Optimizer update of the flat range [b, e) and re-pack of the GEMM operands inside it (current stream)."""
+        p = self.plan
+        if e <= b:
+            return
         scale = 1.0 / self.world            # SyncReplicasOptimizer averages the replica gradients
-        n = ctypes.c_longlong(p.num_params_padded)
+        n = ctypes.c_longlong(e - b)
         if self.optimizer == "adam":
-            _lib.call("unetb200_adam_step", _ptr(p.params), _ptr(self.m), _ptr(self.v), _ptr(p.grads), n,
-                      _ptr(self.step_dev), self.lr0, int(self.const_lr), self.lr_fraction, self.decay_steps,
-                      self.beta1, self.beta2, self.eps, scale, _stream())
+            _lib.call("unetb200_adam_step", _ptr(p.params[b:e]), _ptr(self.m[b:e]), _ptr(self.v[b:e]),
+                      _ptr(p.grads[b:e]), n, _ptr(self.step_dev), self.lr0, int(self.const_lr), self.lr_fraction,
+                      self.decay_steps, self.beta1, self.beta2, self.eps, scale, _stream())
         else:
-            _lib.call("unetb200_sgd_step", _ptr(p.params), _ptr(p.grads), n, _ptr(self.step_dev), self.lr0,
+            _lib.call("unetb200_sgd_step", _ptr(p.params[b:e]), _ptr(p.grads[b:e]), n, _ptr(self.step_dev), self.lr0,
                       int(self.const_lr), self.lr_fraction, self.decay_steps, scale, _stream())
-        _lib.call("unetb200_step_increment", _ptr(self.step_dev), _stream())
-        p.pack_weights()
+        p.pack_weights(b, e)
 
     def train_step(self, imgs, msks):
         """imgs/msks: contiguous CUDA float32 NHWC tensors for THIS replica's shard. Returns the device tensor
@@ -94,14 +103,7 @@ class Trainer:
                 self._capture(imgs, msks)
             self._g_imgs.copy_(imgs, non_blocking=True)
             self._g_msks.copy_(msks, non_blocking=True)
-            if self.world == 1:
-                self._graph.replay()
-            else:   # four graphs with the bucket all-reduces between them (NCCL stays outside the graphs)
-                for seg in range(3):
-                    self._graph[seg].replay()
-                    self.reducer.launch(seg)
-                self.reducer.wait()
-                self._graph[3].replay()
+            self._graph.replay()      # one replay per step at every world size (the all-reduces are inside)
         else:
             self._enqueue_step(imgs, msks)
         self.steps_done += 1
@@ -109,7 +111,8 @@ class Trainer:
 
     def _capture(self, imgs, msks):
         self._g_imgs, self._g_msks = imgs.clone(), msks.clone()
-        # warm-up outside capture (kernel attribute set-up, lazy module loading) on a side stream, then restore state
+        # warm-up outside capture (kernel attribute set-up, lazy module loading, NCCL channel set-up) on a side stream,
+        # then restore state
         snap = [t.clone() for t in (self.plan.params, self.m, self.v, self.step_dev)]
         s = torch.cuda.Stream()
         s.wait_stream(torch.cuda.current_stream())
@@ -121,19 +124,10 @@ class Trainer:
         self.plan.pack_weights()
         torch.cuda.synchronize()
         before = _lib.lib().unetb200_launch_count()
-        if self.world == 1:
-            self._graph = torch.cuda.CUDAGraph()
-            with torch.cuda.graph(self._graph):
-                self._enqueue_step(self._g_imgs, self._g_msks)
-        else:
-            graphs = []
-            for i in range(4):
-                g = torch.cuda.CUDAGraph()
-                # thread_local: the NCCL watchdog thread may query events while this thread captures
-                with torch.cuda.graph(g, capture_error_mode="thread_local"):
-                    self._piece(i, self._g_imgs, self._g_msks)
-                graphs.append(g)
-            self._graph = graphs
+        self._graph = torch.cuda.CUDAGraph()
+        # thread_local: the NCCL watchdog thread may query events while this thread captures
+        with torch.cuda.graph(self._graph, capture_error_mode="thread_local"):
+            self._enqueue_step(self._g_imgs, self._g_msks)
         # kernels of this library inside one replay (the library's launch counter only sees the capture)
         self.graph_launches_per_step = int(_lib.lib().unetb200_launch_count() - before)
 
@@ -214,7 +208,7 @@ class Trainer:
     # ------------------------------------------------------------------ evaluation / state
     def predict(self, imgs, msks=None):
         """Forward only (dropout stays on, as in the reference: model.py:40). Returns (preds, metrics)."""
-        self.plan.forward(imgs, msks, seed=self.dropout_seed, seed_add=self.step_dev)
+        self.plan.forward(imgs, msks, seed=self._eval_seed(), seed_add=self.step_dev)
         return self.plan.preds, (self.plan.metrics if msks is not None else None)
 
     def dice_sums(self, imgs_np, msks_np):
@@ -222,8 +216,14 @@ class Trainer:
         Dropout stays on, as in the reference's test pass (model.py:40)."""
         self._d_imgs.copy_(torch.as_tensor(np.ascontiguousarray(imgs_np, dtype=np.float32)))
         self._d_msks.copy_(torch.as_tensor(np.ascontiguousarray(msks_np, dtype=np.float32)))
-        self.plan.forward(self._d_imgs, self._d_msks, seed=self.dropout_seed, seed_add=self.step_dev)
+        self.plan.forward(self._d_imgs, self._d_msks, seed=self._eval_seed(), seed_add=self.step_dev)
         return self.plan.sums.cpu().numpy().astype(np.float64)
+
+    def _eval_seed(self):
+        """Every evaluation forward draws fresh dropout masks (the reference samples anew on each sess.run of the
+        test pass, test_dist.py:421): a per-call counter is folded into the Philox seed."""
+        self._eval_calls += 1
+        return (self.dropout_seed + 0xD1B54A32D192ED03 * self._eval_calls) & 0xFFFFFFFFFFFFFFFF
 
     def evaluate(self, imgs_test, msks_test, batch_size):
         """Test-set metrics with the reference's batching and averaging (test_dist.py:406-424); see evaluate.py."""
