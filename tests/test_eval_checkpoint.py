@@ -73,3 +73,55 @@ def test_checkpoint_round_trip_uses_tf_names(tmp_path):
     for k in state:
         np.testing.assert_array_equal(np.asarray(state[k]), back[k])
     assert not [f for f in os.listdir(os.path.dirname(path)) if f.endswith(".tmp.npz")]
+
+
+def test_latest_prefers_the_newer_of_last_good_and_autosave(tmp_path):
+    d = str(tmp_path)
+    assert checkpoint.latest(d) is None
+    checkpoint.save_checkpoint(os.path.join(d, checkpoint.LAST_GOOD), {"global_step": 10, "conv1a/bias": np.zeros(32)})
+    assert checkpoint.latest(d).endswith(checkpoint.LAST_GOOD)
+    checkpoint.save_checkpoint(os.path.join(d, checkpoint.AUTOSAVE), {"global_step": 14, "conv1a/bias": np.ones(32)})
+    assert checkpoint.latest(d).endswith(checkpoint.AUTOSAVE)
+    checkpoint.save_checkpoint(os.path.join(d, checkpoint.LAST_GOOD), {"global_step": 20, "conv1a/bias": np.zeros(32)})
+    assert checkpoint.latest(d).endswith(checkpoint.LAST_GOOD)
+
+
+def test_epoch_seed_is_a_function_of_the_global_step():
+    """A resumed run must re-draw the permutation of the epoch it stopped in: the seed depends only on
+    which epoch the restored global_step lies in."""
+    from unet_distributed_b200.test_dist import epoch_seed
+    nb = 7
+    assert [epoch_seed(s, nb) for s in (0, 3, 6)] == [1234] * 3
+    assert [epoch_seed(s, nb) for s in (7, 13)] == [1241] * 2 and epoch_seed(14, nb) == 1248
+
+
+def test_chief_summaries_write_the_references_tags(tmp_path):
+    """test_dist.py:275-298, 322-326: scalar + histogram per metric, percent_complete, three images of each kind, and
+    the *_test scalars; a disabled writer (non-chief ranks) writes nothing."""
+    from tensorboard.backend.event_processing.event_accumulator import EventAccumulator
+    from unet_distributed_b200.summaries import ChiefSummaries
+    rng = np.random.default_rng(0)
+    imgs, msks = rng.standard_normal((5, 16, 16, 4)).astype(np.float32), (rng.random((5, 16, 16, 1)) > 0.5) * 1.0
+    preds = rng.random((5, 16, 16, 1)).astype(np.float32)
+    s = ChiefSummaries(str(tmp_path / "run"), total_steps=40)
+    assert s.percent_complete(10) == 25.0
+    for step in (1, 2):
+        s.train_step(step, [2.5 / step, 0.1 * step, 0.2, 0.3], imgs, msks, preds)
+    s.test_pass(2, {"loss": 1.5, "dice": 0.4, "sensitivity": 0.5, "specificity": 0.6})
+    s.close()
+    acc = EventAccumulator(str(tmp_path / "run"), size_guidance={"images": 0, "scalars": 0, "histograms": 0})
+    acc.Reload()
+    tags = acc.Tags()
+    for t in ("loss", "dice", "sensitivity", "specificity", "percent_complete", "loss_test", "dice_test",
+              "sensitivity_test", "specificity_test"):
+        assert t in tags["scalars"], t
+    for t in ("loss", "dice", "sensitivity", "specificity"):
+        assert t in tags["histograms"], t
+    for kind in ("predictions", "ground_truth", "images"):
+        assert sorted(t for t in tags["images"] if t.startswith(kind + "/")) == [f"{kind}/image/{i}" for i in range(3)]
+    assert [e.value for e in acc.Scalars("loss")] == [2.5, 1.25]
+    assert [e.value for e in acc.Scalars("percent_complete")] == [2.5, 5.0]
+    off = ChiefSummaries(str(tmp_path / "none"), total_steps=40, enabled=False)
+    off.train_step(1, [1, 1, 1, 1], imgs, msks, preds)
+    off.close()
+    assert not os.path.exists(str(tmp_path / "none"))

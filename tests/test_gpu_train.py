@@ -11,6 +11,8 @@ implementation can stay within 1e-2 of the fp32 curve for 200 steps.  The bars h
   * 200 steps with the reference's default optimizer settings: both curves reach the same plateau (mean loss of the
     last 40 steps within 0.05, both far below the starting loss), no non-finite value anywhere;
   * the optimizer itself (Adam slots, decaying LR, global_step) and the eager API: exact against the fused path."""
+import os
+
 import numpy as np
 import pytest
 import torch
@@ -238,3 +240,39 @@ def test_evaluate_and_checkpoint_resume(cuda_device, tmp_path):
         t.train_step_host(imgs[4:6], msks[4:6])
     np.testing.assert_array_equal(tr.plan.params.cpu().numpy(), tr2.plan.params.cpu().numpy())
     assert tr.global_step() == tr2.global_step() == 3
+
+
+def test_cli_resume_finishes_the_remaining_steps_and_logs_summaries(cuda_device, tmp_path, capsys):
+    """The training driver (test_dist.py:380-398 loop) with the reference's flags: an interrupted run resumed with
+    --resume stops at num_batches * epochs total global steps (not that many MORE), re-draws the epoch permutation it
+    stopped in (identical parameters to an uninterrupted run), and the chief's TensorBoard file carries the
+    reference's tags (test_dist.py:275-298)."""
+    from tensorboard.backend.event_processing.event_accumulator import EventAccumulator
+    from unet_distributed_b200 import checkpoint, settings_dist, test_dist
+    common = ["--synthetic", "40", "--batch_size", "8", "--epochs", "2", "--learning_rate", "0.001", "--test", "0",
+              "--progress", "0", "--save_model_secs", "0"]
+    old = (settings_dist.IMG_ROWS, settings_dist.IMG_COLS)
+    settings_dist.IMG_ROWS = settings_dist.IMG_COLS = 32
+    try:
+        d_full, d_cut = str(tmp_path / "full"), str(tmp_path / "cut")
+        assert test_dist.main(common + ["--checkpoint_dir", d_full]) == 0                       # 2 epochs x 5 batches
+        assert test_dist.main(common + ["--checkpoint_dir", d_cut, "--max_steps", "7"]) == 0    # stops inside epoch 2
+        cut = checkpoint.load_checkpoint(checkpoint.latest(d_cut))
+        assert cut["global_step"] == 7
+        assert test_dist.main(common + ["--checkpoint_dir", d_cut, "--resume", "1"]) == 0
+    finally:
+        settings_dist.IMG_ROWS, settings_dist.IMG_COLS = old
+    full = checkpoint.load_checkpoint(checkpoint.latest(d_full))
+    res = checkpoint.load_checkpoint(checkpoint.latest(d_cut))
+    assert full["global_step"] == res["global_step"] == 10
+    for k in ("conv1a/kernel", "conv5b/kernel", "Mask/bias", "conv5b/kernel/Adam_1"):
+        np.testing.assert_array_equal(full[k], res[k], err_msg=k)
+    run = [os.path.join(d_full, n) for n in os.listdir(d_full) if n.startswith("unet,lr=")]
+    assert len(run) == 1
+    acc = EventAccumulator(run[0], size_guidance={"images": 0, "scalars": 0, "histograms": 0})
+    acc.Reload()
+    tags = acc.Tags()
+    assert {"loss", "dice", "sensitivity", "specificity", "percent_complete"} <= set(tags["scalars"])
+    assert [e.step for e in acc.Scalars("loss")] == list(range(1, 11))
+    assert acc.Scalars("percent_complete")[-1].value == 100.0
+    assert len([t for t in tags["images"] if t.startswith("predictions/")]) == 3

@@ -10,6 +10,7 @@ import os
 import numpy as np
 
 LAST_GOOD = "last_good_model.npz"      # test_dist.py:446,490 saves `last_good_model.cpkt` after every test pass
+AUTOSAVE = "model.autosave.npz"        # tf.train.Supervisor(save_model_secs=60) (test_dist.py:347-355)
 
 
 def save_checkpoint(path, state):
@@ -33,6 +34,15 @@ def load_checkpoint(path):
 
 
 def latest(checkpoint_dir):
-    """Path of the checkpoint to resume from (the last good model), or None."""
-    p = os.path.join(checkpoint_dir, LAST_GOOD)
-    return p if os.path.exists(p) else None
+    """Path of the checkpoint to resume from -- whichever of the last good model and the periodic autosave holds the
+    larger global_step (the Supervisor restores the most recent checkpoint of its logdir) -- or None."""
+    best, best_step = None, -1
+    for name in (LAST_GOOD, AUTOSAVE):
+        p = os.path.join(checkpoint_dir, name)
+        if not os.path.exists(p):
+            continue
+        with np.load(p) as z:
+            step = int(z["global_step"]) if "global_step" in z.files else 0
+        if step > best_step:
+            best, best_step = p, step
+    return best
