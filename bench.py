@@ -41,6 +41,8 @@ def parse_args():
     p.add_argument("--channels", type=int, default=1)
     p.add_argument("--no-graph", action="store_true", help="do not replay the step from a CUDA graph (1 GPU)")
     p.add_argument("--no-cpu-baseline", action="store_true")
+    p.add_argument("--no-tconv-block", dest="no_tconv_block", action="store_true",
+                   help="skip the side measurement of the Conv2DTranspose decoder")
     p.add_argument("--const_learningrate", type=int, default=1)
     p.add_argument("--decay_steps", type=int, default=100)
     p.add_argument("--lr_fraction", type=float, default=0.2)
@@ -159,10 +161,39 @@ class ClockSampler:
         return out
 
 
+# ---------------------------------------------------------------------------------------------------- shared
+def workload_config(args, world):
+    """The `config` object of the JSON line -- the same for the GPU arm and for --impl reference (which times the CPU
+    restatement ON the GPU arm's configuration; cuda_graph / l2 describe the GPU arm)."""
+    N, S, C = args.batch, args.size, args.channels
+    ups = args.decoder == "upsampling"
+    cfg_index = 3 if (S, C) == (240, 4) else (4 if N == 512 else (2 if world > 1 else (1 if ups else 0)))
+    return {
+        "workload": f"UNet {S}x{S}x{C} {args.decoder} decoder (BASELINE configs[{cfg_index}] shape), "
+                    f"bs{N} per GPU, Adam, dropout 0.2, train step fwd+dice+bwd+allreduce+Adam",
+        "decoder": args.decoder, "per_gpu_batch": N, "global_batch": N * world, "image": [S, S, C],
+        "parallelism": f"dp{world}", "const_learningrate": bool(args.const_learningrate),
+        "cuda_graph": bool(not args.no_graph),
+        "l2": "no explicit flush: one step touches >2.5 GB of activations and gradients (L2 is 126 MB); "
+              "input batches rotate"}
+
+
+def cpu_model_name():
+    try:
+        for line in open("/proc/cpuinfo"):
+            if line.startswith("model name"):
+                return line.split(":", 1)[1].strip()
+    except OSError:
+        pass
+    return "unknown"
+
+
 # ---------------------------------------------------------------------------------------------------- CPU arms
+CPU_WARMUP, CPU_STEPS = 2, 5      # SURVEY.md section 8(d): 2 warm-up + 5 timed steps of the bs128 workload
+
+
 def cpu_train_images_per_sec(decoder, size, channels, images_per_step, steps, warmup, threads):
     """The oracle's training step (fwd + dice loss + bwd + TF-Adam, fp32, dropout on) on the host cores."""
-    import numpy as np
     import torch
     from oracle import unet_oracle as O
     from unet_distributed_b200.synthetic import make_slices
@@ -183,23 +214,32 @@ def cpu_train_images_per_sec(decoder, size, channels, images_per_step, steps, wa
     return images_per_step * steps / t_total, t_total / steps * 1e3
 
 
+def cpu_baseline_block(args, steps, warmup):
+    """One recipe for both arms: every step is the FULL per-GPU batch of the workload (bs128 unless --batch says
+    otherwise) through the torch-CPU fp32 restatement on all host cores; only the number of timed steps differs
+    (the GPU arm times CPU_STEPS after CPU_WARMUP, --impl reference times the --steps / --warmup it is given)."""
+    cores = os.cpu_count() or 1
+    value, ms = cpu_train_images_per_sec(args.decoder, args.size, args.channels, args.batch, steps, warmup, cores)
+    return {"value": value, "unit": "images/s", "cores": cores, "kind": "port", "cpu_model": cpu_model_name(),
+            "ms_per_step": ms,
+            "sample": f"{steps} timed steps of {args.batch} images ({args.size}x{args.size}x{args.channels}, "
+                      f"{args.decoder} decoder: the full per-GPU batch of the workload) after {warmup} warm-up steps; "
+                      "torch-CPU fp32 (oneDNN) restatement of the reference's train step (oracle/unet_oracle.py), "
+                      "1 process, no parameter server / gRPC; TF 1.4 is not installable"}
+
+
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return 0
-    cores = os.cpu_count() or 1
-    sample = 32   # images per step: ~0.5 s of CPU work per step, the same sample as the GPU arm's cpu_baseline
-    value, ms = cpu_train_images_per_sec(args.decoder, args.size, args.channels, sample, args.steps, args.warmup, cores)
+    base = cpu_baseline_block(args, max(args.steps, 1), max(args.warmup, 1))
+    value, ms = base["value"], base["ms_per_step"]
     line = {
         "impl": "reference", "metric": "train images/sec", "value": value, "unit": "images/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": f"UNet {args.size}x{args.size}x{args.channels} {args.decoder} decoder, train step "
-                               f"(fwd+dice+bwd+Adam), bs{args.batch} per GPU in the GPU arm",
-                   "decoder": args.decoder, "image": [args.size, args.size, args.channels]},
-        "cpu_baseline": {"value": value, "unit": "images/s", "cores": cores, "kind": "port",
-                         "sample": f"{sample} images per step (of the bs{args.batch} workload), torch-CPU fp32 "
-                                   "restatement of the reference (oracle/unet_oracle.py); TF 1.4 is not installable"},
+        "config": workload_config(args, max(args.gpus, 1)),
+        "cpu_baseline": base,
         "e2e": {"value": value, "unit": "images/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
     emit(line)
@@ -207,23 +247,16 @@ def run_reference(args):
 
 
 # ---------------------------------------------------------------------------------------------------- GPU arm
-def run_b200(args):
+def measure_decoder(args, decoder, world, rank, dev, sampler, with_roofline):
+    """Device-resident and end-to-end timing of one decoder variant (+ the per-kernel-class roofline timing)."""
     import numpy as np
     import torch
     import torch.distributed as dist
-    from unet_distributed_b200 import _lib, parallel
+    from unet_distributed_b200 import _lib
     from unet_distributed_b200.synthetic import make_slices
     from unet_distributed_b200.trainer import Trainer
-
-    world, rank, local = parallel.init_from_env("nccl")
-    if world == 1:
-        torch.cuda.set_device(0)
-    dev = torch.device("cuda", torch.cuda.current_device())
-    sampler = ClockSampler(torch.cuda.current_device())
-    if rank == 0:
-        sampler.start()   # child process; it needs a moment to load NVML, so it starts before the model is built
     N, S, C = args.batch, args.size, args.channels
-    ups = args.decoder == "upsampling"
+    ups = decoder == "upsampling"
     tr = Trainer(N, S, S, C, 1, ups, dropout=0.2, learning_rate=0.0005,
                  const_learningrate=bool(args.const_learningrate), lr_fraction=args.lr_fraction,
                  decay_steps=args.decay_steps, use_cuda_graph=(not args.no_graph))
@@ -244,28 +277,31 @@ def run_b200(args):
             dist.barrier()
         torch.cuda.synchronize()
 
+    out = {"decoder": decoder}
     # ---- device-resident timing
     for i in range(args.warmup):
         tr.train_step(*d_batches[i % nb])
     barrier()
     launches0 = L.unetb200_launch_count()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    sampler.begin()
+    if sampler is not None:
+        sampler.begin()
     e0.record()
     for i in range(args.steps):
         tr.train_step(*d_batches[i % nb])
     e1.record()
     barrier()
-    sampler.end()
+    if sampler is not None:
+        sampler.end()
     launches = L.unetb200_launch_count() - launches0
     if tr.use_cuda_graph:   # replays bypass the library's counter: kernels per captured step x steps
         launches = tr.graph_launches_per_step * args.steps
     ms_total = torch.tensor([e0.elapsed_time(e1)], device=dev)
     if world > 1:
         dist.all_reduce(ms_total, op=dist.ReduceOp.MAX)
-    ms_step = float(ms_total.item()) / args.steps
-    clocks = sampler.stop() if rank == 0 else None
-    metrics_last = tr.plan.metrics.cpu().numpy()
+    out["ms_step"] = float(ms_total.item()) / args.steps
+    out["launches"] = int(launches)
+    out["metrics_last"] = tr.plan.metrics.cpu().numpy()
 
     # ---- end-to-end timing through the host-facing call (pinned host -> device copy and loss read-back per step)
     # software-pipelined: the pinned-host -> device copy of step k+1 is enqueued on a copy stream while step k computes;
@@ -284,38 +320,41 @@ def run_b200(args):
     ms_e2e = torch.tensor([e2.elapsed_time(e3)], device=dev)
     if world > 1:
         dist.all_reduce(ms_e2e, op=dist.ReduceOp.MAX)
-    ms_e2e_step = float(ms_e2e.item()) / args.steps
+    out["ms_e2e_step"] = float(ms_e2e.item()) / args.steps
+    out["e2e_last_loss"] = float(e2e_last[0])
+    out["h2d"], out["d2h"] = tr.h2d_bytes_per_step(), tr.d2h_bytes_per_step()
 
     # ---- per-kernel-class timing for the roofline (events around every tile-engine launch; graph replay off)
     # every rank runs these steps (they contain the gradient all-reduce); only rank 0's records are reported
-    roof = None
-    if tr.use_cuda_graph:
-        tr.use_cuda_graph = False
-    # kernels are timed one at a time: in the timed region above the weight gradients share the GPU with the dgrad
-    # chain (second stream), which would charge each kernel for the time it waits for SMs
-    tr.plan.side_stream(False)
-    for i in range(2):
-        tr.train_step(*d_batches[i % nb])
-    torch.cuda.synchronize()
-    L.unetb200_profile_enable(1)
-    psteps = 3
-    for i in range(psteps):
-        tr.train_step(*d_batches[i % nb])
-    ms = (ctypes.c_double * 3)()
-    fl = (ctypes.c_double * 3)()
-    by = (ctypes.c_double * 3)()
-    ln = (ctypes.c_longlong * 3)()
-    _lib.check(L.unetb200_profile_collect(ms, fl, by, ln), "profile_collect")
-    L.unetb200_profile_enable(0)
-    tr.plan.side_stream(True)
-    roof = {"igemm": (ms[0], fl[0], by[0], ln[0]), "wgrad": (ms[1], fl[1], by[1], ln[1]), "steps": psteps}
-    barrier()
+    if with_roofline:
+        if tr.use_cuda_graph:
+            tr.use_cuda_graph = False
+        # kernels are timed one at a time: in the timed region above the weight gradients share the GPU with the
+        # dgrad chain (second stream), which would charge each kernel for the time it waits for SMs
+        tr.plan.side_stream(False)
+        for i in range(2):
+            tr.train_step(*d_batches[i % nb])
+        torch.cuda.synchronize()
+        L.unetb200_profile_enable(1)
+        psteps = 3
+        for i in range(psteps):
+            tr.train_step(*d_batches[i % nb])
+        ms = (ctypes.c_double * 3)()
+        fl = (ctypes.c_double * 3)()
+        by = (ctypes.c_double * 3)()
+        ln = (ctypes.c_longlong * 3)()
+        _lib.check(L.unetb200_profile_collect(ms, fl, by, ln), "profile_collect")
+        L.unetb200_profile_enable(0)
+        tr.plan.side_stream(True)
+        out["roof"] = {"igemm": (ms[0], fl[0], by[0], ln[0]), "wgrad": (ms[1], fl[1], by[1], ln[1]), "steps": psteps}
+        barrier()
 
-    # ---- the gradient all-reduce alone (the three buckets back to back), for bus bandwidth against NVLink
-    allreduce = None
-    if world > 1:
+    # ---- the gradient all-reduce alone (the buckets back to back), for bus bandwidth against NVLink
+    out["allreduce"] = None
+    if world > 1 and with_roofline:
+        nbk = len(tr.reducer.buckets)
         for _ in range(3):
-            for seg in range(len(tr.reducer.buckets)):
+            for seg in range(nbk):
                 tr.reducer.launch(seg)
             tr.reducer.wait()
         barrier()
@@ -323,7 +362,7 @@ def run_b200(args):
         reps = 20
         a0.record()
         for _ in range(reps):
-            for seg in range(len(tr.reducer.buckets)):
+            for seg in range(nbk):
                 tr.reducer.launch(seg)
             tr.reducer.wait()
         a1.record()
@@ -332,16 +371,46 @@ def run_b200(args):
         dist.all_reduce(t_ar, op=dist.ReduceOp.MAX)
         nbytes = tr.reducer.bytes_per_step()
         alg = nbytes / (float(t_ar.item()) * 1e-3) / 1e9
-        allreduce = {"bytes_per_step": nbytes, "ms": float(t_ar.item()), "alg_gbs": alg,
-                     "bus_gbs": alg * 2 * (world - 1) / world, "nvlink_peak_gbs_per_direction": 900, "buckets": 3}
+        out["allreduce"] = {"bytes_per_step": nbytes, "ms_back_to_back": float(t_ar.item()), "alg_gbs": alg,
+                            "bus_gbs": alg * 2 * (world - 1) / world, "peak": 900, "unit": "GB/s",
+                            "frac": alg * 2 * (world - 1) / world / 900.0,
+                            "peak_source": "NVLink 5 nominal per direction per GPU", "buckets": nbk,
+                            "note": "latency-bound: %.1f MB per step in %d buckets; inside the step the buckets "
+                                    "overlap the backward segments that follow them" % (nbytes / 1e6, nbk)}
+    del tr
+    torch.cuda.empty_cache()
+    return out
+
+
+def run_b200(args):
+    import torch
+    import torch.distributed as dist
+    from unet_distributed_b200 import parallel
+
+    world, rank, local = parallel.init_from_env("nccl")
+    if world == 1:
+        torch.cuda.set_device(0)
+    dev = torch.device("cuda", torch.cuda.current_device())
+    sampler = ClockSampler(torch.cuda.current_device())
+    if rank == 0:
+        sampler.start()   # child process; it needs a moment to load NVML, so it starts before the model is built
+    N, S, C = args.batch, args.size, args.channels
+    main = measure_decoder(args, args.decoder, world, rank, dev, sampler, True)
+    clocks = sampler.stop() if rank == 0 else None
+    # the reference's DEFAULT decoder is Conv2DTranspose (settings_dist.py:24, USE_UPSAMPLING = False): its numbers ride
+    # along in every line whose headline workload is the UpSampling2D decoder (BASELINE configs[1])
+    other = None
+    if args.decoder == "upsampling" and not args.no_tconv_block:
+        other = measure_decoder(args, "tconv", world, rank, dev, None, False)
 
     if rank == 0:
         peaks = load_peaks()
         gb = N * world
+        ms_step, ms_e2e_step = main["ms_step"], main["ms_e2e_step"]
         value = gb / (ms_step * 1e-3)
         e2e_value = gb / (ms_e2e_step * 1e-3)
-        key = (args.decoder, S, C)
-        gflop_img = TRAIN_GFLOP_PER_IMG.get(key)
+        gflop_img = TRAIN_GFLOP_PER_IMG.get((args.decoder, S, C))
+        roof = main["roof"]
         ig_ms, ig_fl, ig_by, ig_n = roof["igemm"]
         wg_ms, wg_fl, wg_by, wg_n = roof["wgrad"]
         peak_tf = float(peaks.get("bf16_tflops_sustained", FALLBACK_PEAKS["bf16_tflops_sustained"]))
@@ -353,26 +422,18 @@ def run_b200(args):
                 traffic = json.load(open(tpath)).get("igemm_dram_bytes_per_launch")
             except Exception:
                 traffic = None
-        # which BASELINE.json configuration this shape is
-        cfg_index = 3 if (S, C) == (240, 4) else (4 if N == 512 else (2 if world > 1 else (1 if ups else 0)))
+        cfg = workload_config(args, world)
         line = {
             "metric": "train images/sec", "value": value, "unit": "images/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
-            "config": {
-                "workload": f"UNet {S}x{S}x{C} {args.decoder} decoder (BASELINE configs[{cfg_index}] shape), "
-                            f"bs{N} per GPU, Adam, dropout 0.2, train step fwd+dice+bwd+allreduce+Adam",
-                "decoder": args.decoder, "per_gpu_batch": N, "global_batch": gb, "image": [S, S, C],
-                "parallelism": f"dp{world}", "cuda_graph": bool(not args.no_graph),
-                "l2": "no explicit flush: one step touches >2.5 GB of activations and gradients (L2 is 126 MB); "
-                      "input batches rotate",
-                "const_learningrate": bool(args.const_learningrate)},
+            "config": cfg,
             "clocks": clocks,
             "e2e": {"value": e2e_value, "unit": "images/s", "ms_per_step": ms_e2e_step,
-                    "h2d_bytes_per_step": tr.h2d_bytes_per_step(), "d2h_bytes_per_step": tr.d2h_bytes_per_step(),
+                    "h2d_bytes_per_step": main["h2d"], "d2h_bytes_per_step": main["d2h"],
                     "mode": "Trainer.train_step_pinned(wait=False): H2D of step k+1 overlaps step k on a copy "
-                            "stream, every step's metrics are read back; last step's loss %.4f" % float(e2e_last[0])},
-            "gpu_launches": int(launches),
+                            "stream, every step's metrics are read back; last step's loss %.4f" % main["e2e_last_loss"]},
+            "gpu_launches": int(main["launches"]),
             "roofline": {
                 "kernel": "conv_halo_rp_kernel + conv_halo_kernel + igemm_kernel (3x3 conv / transposed conv forward + dgrad, tcgen05 "
                           "implicit GEMM; every launch of the class in a step)",
@@ -385,16 +446,24 @@ def run_b200(args):
                 "wgrad": {"achieved": (wg_fl / (wg_ms * 1e-3) / 1e12 if wg_ms > 0 else 0.0), "unit": "TFLOP/s",
                           "launches_per_step": wg_n / roof["steps"], "ms_per_step": wg_ms / roof["steps"]},
                 "whole_step": ({"achieved": value * gflop_img / 1e3 / world, "unit": "TFLOP/s per GPU",
-                                "frac": value * gflop_img / 1e3 / world / peak_tf} if gflop_img else None)},
-            "loss": float(metrics_last[0]), "dice": float(metrics_last[1]), "allreduce": allreduce,
+                                "frac": value * gflop_img / 1e3 / world / peak_tf} if gflop_img else None),
+                "collective": main["allreduce"]},
+            "loss": float(main["metrics_last"][0]), "dice": float(main["metrics_last"][1]),
         }
+        if other is not None:
+            gf = TRAIN_GFLOP_PER_IMG.get(("tconv", S, C))
+            v = gb / (other["ms_step"] * 1e-3)
+            line["tconv"] = {
+                "what": "the same run with the reference's default decoder (Conv2DTranspose, settings_dist.py:24; "
+                        "BASELINE configs[0] shape), measured in this process right after the headline workload",
+                "value": v, "unit": "images/s", "ms_per_step": other["ms_step"],
+                "whole_step_frac": (v * gf / 1e3 / world / peak_tf) if gf else None,
+                "e2e": {"value": gb / (other["ms_e2e_step"] * 1e-3), "unit": "images/s",
+                        "ms_per_step": other["ms_e2e_step"], "h2d_bytes_per_step": other["h2d"],
+                        "d2h_bytes_per_step": other["d2h"]},
+                "gpu_launches": int(other["launches"]), "loss": float(other["metrics_last"][0])}
         if world == 1 and not args.no_cpu_baseline:
-            cores = os.cpu_count() or 1
-            cpu_v, cpu_ms = cpu_train_images_per_sec(args.decoder, S, C, 32, 3, 1, cores)
-            line["cpu_baseline"] = {
-                "value": cpu_v, "unit": "images/s", "cores": cores, "kind": "port",
-                "sample": "3 timed steps of 32 images (of the bs128 workload) after 1 warm-up, torch-CPU fp32 "
-                          "restatement of the reference's train step (oracle/unet_oracle.py)"}
+            line["cpu_baseline"] = cpu_baseline_block(args, CPU_STEPS, CPU_WARMUP)
         emit(line)
     if world > 1:
         dist.barrier()
