@@ -117,6 +117,47 @@ int unetb200_head_bwd(const void* x, const float* w, const float* y_true, const 
                       float smooth, float grad_scale, void* dx, float* dw, float* db, void* ws, long long pixels,
                       int C, int n_cl, void* stream);
 
+/* ---- the fp32/tf32 precision mode: every operator above with an explicit element type ----------------------------- */
+/* The reference computes in fp32 (test_dist.py:196-202). `_dt` variants take dtype = UNETB200_BF16 (identical to the
+ * plain entry point) or UNETB200_TF32: activations, activation gradients, masks and packed weights are then fp32 words
+ * (16-byte aligned tensors, same NHWC / packed layouts), rounded to tf32 by whatever produced them; the convolutions
+ * run on the tensor cores with tcgen05 kind::tf32 MMAs and fp32 accumulation, the bandwidth kernels in fp32.
+ * Every `_dt` output tensor is itself tf32-rounded. Arguments other than dtype are those of the plain entry point. */
+int unetb200_pack_conv3x3_fwd_dt(const float* w_hwio, void* w_packed, int Cin, int Cout, int dtype, void* stream);
+int unetb200_pack_conv3x3_dgrad_dt(const float* w_hwio, void* w_packed, int Cin, int Cout, int dtype, void* stream);
+int unetb200_pack_tconv2x2_fwd_dt(const float* w, void* w_packed, int Cin, int Cout, int dtype, void* stream);
+int unetb200_pack_tconv2x2_dgrad_dt(const float* w, void* w_packed, int Cin, int Cout, int dtype, void* stream);
+int unetb200_conv3x3_fwd_dt(const void* x0, int C0, const void* x1, int C1, const void* w_packed, const float* bias,
+                            void* y, int N, int H, int W, int Cout, int relu, float drop_keep, uint64_t drop_seed,
+                            uint32_t drop_stream, int dtype, void* stream);
+int unetb200_conv3x3_dgrad_dt(const void* dz, int Cout, const void* w_packed_d, void* dx0, int C0, const void* mask0,
+                              void* dx1, int C1, const void* mask1, float scale, int N, int H, int W, int dtype,
+                              void* stream);
+int unetb200_conv3x3_wgrad_dt(const void* dz, int Cout, const void* x0, int C0, const void* x1, int C1, float* dw,
+                              void* ws, size_t ws_bytes, int N, int H, int W, int dtype, void* stream);
+int unetb200_tconv2x2_fwd_dt(const void* x, int Cin, const void* w_packed, const float* bias, void* y, int Cout, int N,
+                             int H, int W, int dtype, void* stream);
+int unetb200_tconv2x2_dgrad_dt(const void* dy, int Cout, const void* w_packed_d, void* dx, int Cin, const void* mask,
+                               float scale, int N, int H, int W, int dtype, void* stream);
+int unetb200_tconv2x2_wgrad_dt(const void* dy, int Cout, const void* x, int Cin, float* dw, void* ws, size_t ws_bytes,
+                               int N, int H, int W, int dtype, void* stream);
+int unetb200_conv_first_fwd_dt(const float* x, const float* w_hwio, const float* bias, void* y, int N, int H, int W,
+                               int Cin, int Cout, int dtype, void* stream);
+int unetb200_conv_first_wgrad_dt(const float* x, const void* dz, float* dw, float* db, void* ws, int N, int H, int W,
+                                 int Cin, int Cout, int dtype, void* stream);
+int unetb200_bias_grad_dt(const void* dz, float* db, void* ws, long long pixels, int C, int dtype, void* stream);
+int unetb200_maxpool2x2_fwd_dt(const void* x, void* y, int N, int H, int W, int C, int dtype, void* stream);
+int unetb200_maxpool2x2_bwd_dt(const void* x, const void* dpool, const void* skip_grad, void* dz, int N, int H, int W,
+                               int C, int dtype, void* stream);
+int unetb200_upsample2x2_fwd_dt(const void* x, void* y, int N, int H, int W, int C, int dtype, void* stream);
+int unetb200_upsample2x2_bwd_dt(const void* dy, const void* x, void* dx, int N, int H, int W, int C, int relu_mask,
+                                int dtype, void* stream);
+int unetb200_head_fwd_dt(const void* x, const float* w, const float* b, const float* y_true, float* p, float* sums,
+                         void* ws, long long pixels, int C, int n_cl, int dtype, void* stream);
+int unetb200_head_bwd_dt(const void* x, const float* w, const float* y_true, const float* p, const float* sums,
+                         float smooth, float grad_scale, void* dx, float* dw, float* db, void* ws, long long pixels,
+                         int C, int n_cl, int dtype, void* stream);
+
 /* ---- optimizer: tf.train.AdamOptimizer + exponential_decay (test_dist.py:228-248) ------------------------------ */
 /* step is a device int64 holding global_step (updates applied so far); the LR uses its value before the increment.
  * grad_scale multiplies g first (1/replicas: SyncReplicasOptimizer averages, test_dist.py:251-258). */
@@ -156,6 +197,14 @@ int unetb200_cast_bf16_to_f32(const void* x, float* y, long long n, void* stream
 typedef struct unetb200_plan unetb200_plan;
 int unetb200_plan_create(unetb200_plan** out, int N, int H, int W, int in_channels, int n_cl_out, int use_upsampling,
                          float dropout);
+/* Same plan in a chosen precision. dtype = UNETB200_BF16 (what unetb200_plan_create builds) or UNETB200_TF32: the
+ * fp32/tf32 mode -- activations, activation gradients and packed GEMM operands are fp32 words rounded to tf32 by
+ * their producers, every conv / transposed conv runs on the tensor cores with kind::tf32 MMAs (fp32 accumulation),
+ * and the bandwidth kernels (pooling, upsampling, head, conv1a, bias gradients) run in fp32. The reference computes in
+ * fp32 (test_dist.py:196-202); this mode is the one its 1e-3 tolerance is stated for. Arena tensors then have
+ * elem_bytes = 4 (unetb200_plan_tensor). */
+int unetb200_plan_create_dt(unetb200_plan** out, int N, int H, int W, int in_channels, int n_cl_out,
+                            int use_upsampling, float dropout, int dtype);
 void unetb200_plan_destroy(unetb200_plan* plan);
 long long unetb200_plan_num_params(const unetb200_plan* plan); /* floats in the flat buffers, padding included */
 int unetb200_plan_num_variables(const unetb200_plan* plan);

@@ -101,6 +101,16 @@ def _bf16_round(t):
     return t.to(torch.bfloat16).to(t.dtype)
 
 
+def _tf32_round(t):
+    """Nearest tf32 value (10-bit mantissa, ties away from zero -- PTX cvt.rna.tf32.f32) of an fp32/fp64 tensor."""
+    bits = t.detach().to(torch.float32).contiguous().view(torch.int32)
+    bits = (bits + 0x1000) & ~0x1FFF
+    return bits.view(torch.float32).to(t.dtype)
+
+
+_ROUNDERS = {True: _bf16_round, "bf16": _bf16_round, "tf32": _tf32_round}
+
+
 def _conv3x3(x, k_hwio, b):
     # NHWC semantics expressed in NCHW storage: kernel HWIO -> OIHW, zero pad 1 ('same')
     return F.conv2d(x, k_hwio.permute(3, 2, 0, 1), b, padding=1)
@@ -124,12 +134,13 @@ class Net:
     def _w(self, name):
         k = self.params[name + "/kernel"]
         if self.emulate_bf16 and not name.startswith(("conv1a", "Mask")):
-            k = k + (_bf16_round(k) - k).detach()              # bf16 weights, straight-through gradient
+            rnd = _ROUNDERS[self.emulate_bf16]                 # True / "bf16", or "tf32"
+            k = k + (rnd(k) - k).detach()                      # reduced-precision GEMM weights, straight-through gradient
         return k, self.params[name + "/bias"]
 
     def _act(self, t):
         if self.emulate_bf16:
-            t = t + (_bf16_round(t) - t).detach()              # activations stored in bf16
+            t = t + (_ROUNDERS[self.emulate_bf16](t) - t).detach()   # activations stored in bf16 / rounded to tf32
         return t
 
     def forward(self, imgs_nhwc, dropout_masks=None, dropout=0.2, keep_intermediates=False, forced_acts=None):

@@ -146,4 +146,107 @@ int unetb200_cast_bf16_to_f32(const void* x, float* y, long long n, void* stream
   return cast_bf16_to_f32(x, y, n, S(stream));
 }
 
+// ---- the same operators with an explicit element type (UNETB200_BF16 or UNETB200_TF32; include/unetb200.h) ----------
+#define UB_DT(dtype, what)                                                                                   \
+  UB_REQUIRE((dtype) == UNETB200_BF16 || (dtype) == UNETB200_TF32, what ": dtype %d is neither BF16 nor TF32", \
+             (dtype));                                                                                       \
+  const int dt = (dtype) == UNETB200_TF32 ? UB_DT_TF32 : UB_DT_BF16
+
+int unetb200_pack_conv3x3_fwd_dt(const float* w, void* out, int Cin, int Cout, int dtype, void* stream) {
+  UB_DT(dtype, "pack_conv3x3_fwd");
+  return pack_conv_fwd(w, out, 9, Cin, Cout, S(stream), dt);
+}
+int unetb200_pack_conv3x3_dgrad_dt(const float* w, void* out, int Cin, int Cout, int dtype, void* stream) {
+  UB_DT(dtype, "pack_conv3x3_dgrad");
+  return pack_conv_dgrad(w, out, 9, Cin, Cout, S(stream), dt);
+}
+int unetb200_pack_tconv2x2_fwd_dt(const float* w, void* out, int Cin, int Cout, int dtype, void* stream) {
+  UB_DT(dtype, "pack_tconv2x2_fwd");
+  return pack_tconv_fwd(w, out, Cin, Cout, S(stream), dt);
+}
+int unetb200_pack_tconv2x2_dgrad_dt(const float* w, void* out, int Cin, int Cout, int dtype, void* stream) {
+  UB_DT(dtype, "pack_tconv2x2_dgrad");
+  return pack_tconv_dgrad(w, out, Cin, Cout, S(stream), dt);
+}
+int unetb200_conv3x3_fwd_dt(const void* x0, int C0, const void* x1, int C1, const void* w_packed, const float* bias,
+                            void* y, int N, int H, int W, int Cout, int relu, float drop_keep, uint64_t drop_seed,
+                            uint32_t drop_stream, int dtype, void* stream) {
+  UB_DT(dtype, "conv3x3_fwd");
+  ConvSrc s0{x0, C0}, s1{x1, x1 ? C1 : 0};
+  DropoutCfg d{drop_keep <= 0.0f ? 1.0f : drop_keep, drop_seed, drop_stream, nullptr};
+  return conv3x3_fwd(s0, s1, w_packed, bias, y, N, H, W, Cout, relu, d, S(stream), nullptr, nullptr, dt);
+}
+int unetb200_conv3x3_dgrad_dt(const void* dz, int Cout, const void* w_packed_d, void* dx0, int C0, const void* mask0,
+                              void* dx1, int C1, const void* mask1, float scale, int N, int H, int W, int dtype,
+                              void* stream) {
+  UB_DT(dtype, "conv3x3_dgrad");
+  DgradDst d0{dx0, C0, mask0, scale}, d1{dx1, dx1 ? C1 : 0, mask1, scale};
+  return conv3x3_dgrad(dz, Cout, w_packed_d, d0, d1, N, H, W, S(stream), dt);
+}
+int unetb200_conv3x3_wgrad_dt(const void* dz, int Cout, const void* x0, int C0, const void* x1, int C1, float* dw,
+                              void* ws, size_t ws_bytes, int N, int H, int W, int dtype, void* stream) {
+  UB_DT(dtype, "conv3x3_wgrad");
+  ConvSrc s0{x0, C0}, s1{x1, x1 ? C1 : 0};
+  return conv3x3_wgrad(dz, Cout, s0, s1, dw, ws, ws_bytes, N, H, W, S(stream), nullptr, dt);
+}
+int unetb200_tconv2x2_fwd_dt(const void* x, int Cin, const void* w_packed, const float* bias, void* y, int Cout, int N,
+                             int H, int W, int dtype, void* stream) {
+  UB_DT(dtype, "tconv2x2_fwd");
+  return tconv2x2_fwd(x, Cin, w_packed, bias, y, Cout, N, H, W, S(stream), dt);
+}
+int unetb200_tconv2x2_dgrad_dt(const void* dy, int Cout, const void* w_packed_d, void* dx, int Cin, const void* mask,
+                               float scale, int N, int H, int W, int dtype, void* stream) {
+  UB_DT(dtype, "tconv2x2_dgrad");
+  return tconv2x2_dgrad(dy, Cout, w_packed_d, dx, Cin, mask, scale, N, H, W, S(stream), nullptr, dt);
+}
+int unetb200_tconv2x2_wgrad_dt(const void* dy, int Cout, const void* x, int Cin, float* dw, void* ws, size_t ws_bytes,
+                               int N, int H, int W, int dtype, void* stream) {
+  UB_DT(dtype, "tconv2x2_wgrad");
+  return tconv2x2_wgrad(dy, Cout, x, Cin, dw, ws, ws_bytes, N, H, W, S(stream), dt);
+}
+int unetb200_conv_first_fwd_dt(const float* x, const float* w, const float* bias, void* y, int N, int H, int W, int Cin,
+                               int Cout, int dtype, void* stream) {
+  UB_DT(dtype, "conv_first_fwd");
+  return conv_first_fwd(x, w, bias, y, N, H, W, Cin, Cout, S(stream), nullptr, dt);
+}
+int unetb200_conv_first_wgrad_dt(const float* x, const void* dz, float* dw, float* db, void* ws, int N, int H, int W,
+                                 int Cin, int Cout, int dtype, void* stream) {
+  UB_DT(dtype, "conv_first_wgrad");
+  return conv_first_wgrad(x, dz, dw, db, reinterpret_cast<float*>(ws), N, H, W, Cin, Cout, S(stream), dt);
+}
+int unetb200_bias_grad_dt(const void* dz, float* db, void* ws, long long pixels, int C, int dtype, void* stream) {
+  UB_DT(dtype, "bias_grad");
+  return colsum_act(dz, db, reinterpret_cast<float*>(ws), pixels, C, S(stream), dt);
+}
+int unetb200_maxpool2x2_fwd_dt(const void* x, void* y, int N, int H, int W, int C, int dtype, void* stream) {
+  UB_DT(dtype, "maxpool2x2_fwd");
+  return maxpool2x2_fwd(x, y, N, H, W, C, S(stream), dt);
+}
+int unetb200_maxpool2x2_bwd_dt(const void* x, const void* dpool, const void* skip_grad, void* dz, int N, int H, int W,
+                               int C, int dtype, void* stream) {
+  UB_DT(dtype, "maxpool2x2_bwd");
+  return maxpool2x2_bwd(x, dpool, skip_grad, dz, N, H, W, C, S(stream), dt);
+}
+int unetb200_upsample2x2_fwd_dt(const void* x, void* y, int N, int H, int W, int C, int dtype, void* stream) {
+  UB_DT(dtype, "upsample2x2_fwd");
+  return upsample2x2_fwd(x, y, N, H, W, C, S(stream), dt);
+}
+int unetb200_upsample2x2_bwd_dt(const void* dy, const void* x, void* dx, int N, int H, int W, int C, int relu_mask,
+                                int dtype, void* stream) {
+  UB_DT(dtype, "upsample2x2_bwd");
+  return upsample2x2_bwd(dy, x, dx, N, H, W, C, relu_mask, S(stream), dt);
+}
+int unetb200_head_fwd_dt(const void* x, const float* w, const float* b, const float* y_true, float* p, float* sums,
+                         void* ws, long long pixels, int C, int n_cl, int dtype, void* stream) {
+  UB_DT(dtype, "head_fwd");
+  return head_fwd(x, w, b, y_true, p, sums, reinterpret_cast<float*>(ws), pixels, C, n_cl, S(stream), dt);
+}
+int unetb200_head_bwd_dt(const void* x, const float* w, const float* y_true, const float* p, const float* sums,
+                         float smooth, float grad_scale, void* dx, float* dw, float* db, void* ws, long long pixels,
+                         int C, int n_cl, int dtype, void* stream) {
+  UB_DT(dtype, "head_bwd");
+  return head_bwd(x, w, y_true, p, sums, smooth, grad_scale, dx, dw, db, reinterpret_cast<float*>(ws), pixels, C, n_cl,
+                  S(stream), dt);
+}
+
 }  // extern "C"

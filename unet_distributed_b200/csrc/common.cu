@@ -5,6 +5,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <mutex>
+#include <unordered_map>
 #include <vector>
 
 namespace ub {
@@ -38,12 +39,55 @@ static EncodeTiledFn encode_fn() {
   return fn;
 }
 
-int make_tmap_bf16(CUtensorMap* out, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
-                   const uint32_t* box, int swizzle_bytes) {
+// Tensor maps are cached per (base pointer, element size, rank, dims, strides, box, swizzle): a training step encodes
+// the same ~150 maps over and over, and cuTensorMapEncodeTiled costs ~1 us each on the eager path.
+// Unified virtual addressing makes the base pointer unique across devices. The cache is bounded: when full it is cleared.
+namespace {
+struct TmapKey {
+  const void* base;
+  int rank, swizzle, elt;
+  uint64_t dims[5];
+  uint64_t strides[4];
+  uint32_t box[5];
+  bool operator==(const TmapKey& o) const { return std::memcmp(this, &o, sizeof(TmapKey)) == 0; }
+};
+struct TmapKeyHash {
+  size_t operator()(const TmapKey& k) const {
+    const unsigned char* p = reinterpret_cast<const unsigned char*>(&k);
+    uint64_t h = 1469598103934665603ull;
+    for (size_t i = 0; i < sizeof(TmapKey); ++i) h = (h ^ p[i]) * 1099511628211ull;
+    return static_cast<size_t>(h);
+  }
+};
+std::unordered_map<TmapKey, CUtensorMap, TmapKeyHash> g_tmaps;
+std::mutex g_tmaps_mu;
+std::atomic<long long> g_tmap_hits{0}, g_tmap_misses{0};
+constexpr size_t kTmapCacheMax = 8192;
+}  // namespace
+
+long long tmap_cache_hits() { return g_tmap_hits.load(); }
+long long tmap_cache_misses() { return g_tmap_misses.load(); }
+
+int make_tmap(CUtensorMap* out, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
+              const uint32_t* box, int swizzle_bytes, int elt_bytes) {
   EncodeTiledFn fn = encode_fn();
   if (!fn) {
     set_error("cuTensorMapEncodeTiled is not available (no CUDA driver?)");
     return UB_ERR_CUDA;
+  }
+  TmapKey key;
+  std::memset(&key, 0, sizeof(key));   // padding bytes too: the key is compared and hashed as raw bytes
+  key.base = base; key.rank = rank; key.swizzle = swizzle_bytes; key.elt = elt_bytes;
+  for (int i = 0; i < rank; ++i) { key.dims[i] = dims[i]; key.box[i] = box[i]; }
+  for (int i = 0; i + 1 < rank; ++i) key.strides[i] = strides_bytes[i];
+  {
+    std::lock_guard<std::mutex> lk(g_tmaps_mu);
+    auto it = g_tmaps.find(key);
+    if (it != g_tmaps.end()) {
+      *out = it->second;
+      g_tmap_hits.fetch_add(1, std::memory_order_relaxed);
+      return UB_OK;
+    }
   }
   cuuint64_t gdims[5];
   cuuint64_t gstr[4];
@@ -59,20 +103,33 @@ int make_tmap_bf16(CUtensorMap* out, const void* base, int rank, const uint64_t*
   if (swizzle_bytes == 128) sw = CU_TENSOR_MAP_SWIZZLE_128B;
   else if (swizzle_bytes == 64) sw = CU_TENSOR_MAP_SWIZZLE_64B;
   else if (swizzle_bytes == 32) sw = CU_TENSOR_MAP_SWIZZLE_32B;
-  CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, static_cast<cuuint32_t>(rank), const_cast<void*>(base), gdims,
+  // fp32 tensors hold values already rounded to tf32 by their producers: plain FLOAT32, no conversion on load
+  const CUtensorMapDataType dt = elt_bytes == 4 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
+  CUresult r = fn(out, dt, static_cast<cuuint32_t>(rank), const_cast<void*>(base), gdims,
                   gstr, bx, es, CU_TENSOR_MAP_INTERLEAVE_NONE, sw, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
-    set_error("cuTensorMapEncodeTiled failed (CUresult %d): rank=%d dims=[%llu,%llu,%llu,%llu,%llu] box=[%u,%u,%u,%u,%u] "
+    set_error("cuTensorMapEncodeTiled failed (CUresult %d): rank=%d elt=%d dims=[%llu,%llu,%llu,%llu,%llu] box=[%u,%u,%u,%u,%u] "
               "stride0=%llu sw=%d base=%p",
-              static_cast<int>(r), rank, (unsigned long long)dims[0], (unsigned long long)(rank > 1 ? dims[1] : 0),
+              static_cast<int>(r), rank, elt_bytes, (unsigned long long)dims[0], (unsigned long long)(rank > 1 ? dims[1] : 0),
               (unsigned long long)(rank > 2 ? dims[2] : 0), (unsigned long long)(rank > 3 ? dims[3] : 0),
               (unsigned long long)(rank > 4 ? dims[4] : 0), box[0], rank > 1 ? box[1] : 0, rank > 2 ? box[2] : 0,
               rank > 3 ? box[3] : 0, rank > 4 ? box[4] : 0, (unsigned long long)(rank > 1 ? strides_bytes[0] : 0),
               swizzle_bytes, base);
     return UB_ERR_CUDA;
   }
+  g_tmap_misses.fetch_add(1, std::memory_order_relaxed);
+  {
+    std::lock_guard<std::mutex> lk(g_tmaps_mu);
+    if (g_tmaps.size() >= kTmapCacheMax) g_tmaps.clear();
+    g_tmaps.emplace(key, *out);
+  }
   return UB_OK;
+}
+
+int make_tmap_bf16(CUtensorMap* out, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
+                   const uint32_t* box, int swizzle_bytes) {
+  return make_tmap(out, base, rank, dims, strides_bytes, box, swizzle_bytes, 2);
 }
 
 // ------------------------------------------------------------------------------------------------ launch accounting

@@ -50,6 +50,16 @@ void prof_end(cudaStream_t stream);
 // swizzle_bytes: 128, 64, 32 or 0. Out-of-bounds elements read as zero.
 int make_tmap_bf16(CUtensorMap* out, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
                    const uint32_t* box, int swizzle_bytes);
+// Same for elements of elt_bytes = 2 (bf16) or 4 (fp32 holding tf32-rounded values). Encoded maps are cached by
+// (base, element size, rank, dims, strides, box, swizzle); tmap_cache_hits/misses count look-ups (tests, tuning).
+int make_tmap(CUtensorMap* out, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
+              const uint32_t* box, int swizzle_bytes, int elt_bytes);
+long long tmap_cache_hits();
+long long tmap_cache_misses();
+
+// Activation / operand element types inside the library (the ABI enum UNETB200_BF16 / UNETB200_TF32 maps onto these).
+enum : int { UB_DT_BF16 = 0, UB_DT_TF32 = 1 };
+inline int dt_bytes(int dt) { return dt == UB_DT_TF32 ? 4 : 2; }
 
 int device_sm_count();
 

@@ -3,6 +3,7 @@
 #include <cstdlib>
 #include <initializer_list>
 
+#include <atomic>
 #include <mutex>
 
 #include "common.h"
@@ -27,6 +28,42 @@ __device__ __forceinline__ uint4 pack8(const float (&f)[8]) {
   return o;
 }
 
+// Eight consecutive channels of an activation tensor: 16 bytes of bf16 (uint4) or, in the fp32/tf32 mode, 32 bytes of
+// fp32 (F32x8). The generic kernels below are templates over this vector type; stores of F32x8 round to tf32 because
+// the tensors they write are read by kind::tf32 MMAs (exact only on tf32-representable values).
+struct __align__(32) F32x8 {
+  float4 lo, hi;
+};
+__device__ __forceinline__ void unpackv(const uint4& v, float (&f)[8]) { unpack8(v, f); }
+__device__ __forceinline__ void unpackv(const F32x8& v, float (&f)[8]) {
+  f[0] = v.lo.x; f[1] = v.lo.y; f[2] = v.lo.z; f[3] = v.lo.w; f[4] = v.hi.x; f[5] = v.hi.y; f[6] = v.hi.z; f[7] = v.hi.w;
+}
+__device__ __forceinline__ uint4 ldv(const uint4* p) { return __ldg(p); }
+__device__ __forceinline__ F32x8 ldv(const F32x8* p) {
+  F32x8 v;
+  v.lo = __ldg(reinterpret_cast<const float4*>(p));
+  v.hi = __ldg(reinterpret_cast<const float4*>(p) + 1);
+  return v;
+}
+template <typename V>
+__device__ __forceinline__ V zerov() {
+  V v;
+  memset(&v, 0, sizeof(V));
+  return v;
+}
+template <typename V>
+__device__ __forceinline__ void ld8(const V* p, float (&f)[8]) { unpackv(ldv(p), f); }
+// plain (coherent) load: for tensors the same kernel also writes (in-place accumulation)
+__device__ __forceinline__ void ld8_rw(const uint4* p, float (&f)[8]) { unpack8(*p, f); }
+__device__ __forceinline__ void ld8_rw(const F32x8* p, float (&f)[8]) { unpackv(*p, f); }
+__device__ __forceinline__ void st8(uint4* p, const float (&f)[8]) { *p = pack8(f); }
+__device__ __forceinline__ void st8(F32x8* p, const float (&f)[8]) {
+  F32x8 v;
+  v.lo = make_float4(round_tf32(f[0]), round_tf32(f[1]), round_tf32(f[2]), round_tf32(f[3]));
+  v.hi = make_float4(round_tf32(f[4]), round_tf32(f[5]), round_tf32(f[6]), round_tf32(f[7]));
+  *p = v;
+}
+
 inline unsigned grid_for(long long items, int threads) {
   long long b = (items + threads - 1) / threads;
   if (b < 1) b = 1;
@@ -34,8 +71,9 @@ inline unsigned grid_for(long long items, int threads) {
 }
 
 // ------------------------------------------------------------------------------------------ conv1a forward
+template <typename V>
 __global__ void conv_first_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w,
-                                      const float* __restrict__ bias, uint4* __restrict__ y, int N, int H, int W,
+                                      const float* __restrict__ bias, V* __restrict__ y, int N, int H, int W,
                                       int Cin, int Cout) {
   extern __shared__ float sw[];  // [9*Cin*Cout] weights then [Cout] bias
   const int nw = 9 * Cin * Cout;
@@ -73,13 +111,14 @@ __global__ void conv_first_fwd_kernel(const float* __restrict__ x, const float* 
     }
 #pragma unroll
     for (int j = 0; j < 8; ++j) acc[j] = fmaxf(acc[j], 0.0f);
-    y[idx] = pack8(acc);
+    st8(y + idx, acc);
   }
 }
 
 // ------------------------------------------------------------------------------------------ conv1a wgrad (+ bias grad)
 // Each thread owns one 8-channel group of dz and walks pixels with a stride; partial sums go block -> ws -> final.
-__global__ void conv_first_wgrad_kernel(const float* __restrict__ x, const uint4* __restrict__ dz,
+template <typename V>
+__global__ void conv_first_wgrad_kernel(const float* __restrict__ x, const V* __restrict__ dz,
                                         float* __restrict__ ws, int N, int H, int W, int Cin, int Cout) {
   // every warp owns one row of partial sums in shared memory, the block sums its warps in a fixed order and writes
   // one row to ws (no atomics: results are bit-reproducible); rows are summed by rows_reduce_kernel
@@ -105,7 +144,7 @@ __global__ void conv_first_wgrad_kernel(const float* __restrict__ x, const uint4
       const unsigned row = pix / W;            // n*H + h
       const int hq = static_cast<int>(row % H);
       float d[8];
-      unpack8(__ldg(dz + idx), d);
+      ld8(dz + idx, d);
       if (ci == 0) {
 #pragma unroll
         for (int j = 0; j < 8; ++j) accb[j] += d[j];
@@ -184,7 +223,8 @@ __global__ void rows_reduce_kernel(const float* __restrict__ ws, int nrows, int 
 }
 
 // ------------------------------------------------------------------------------------------ pooling
-__global__ void maxpool_fwd_kernel(const uint4* __restrict__ x, uint4* __restrict__ y, int N, int H, int W, int C) {
+template <typename V>
+__global__ void maxpool_fwd_kernel(const V* __restrict__ x, V* __restrict__ y, int N, int H, int W, int C) {
   const int groups = C / 8;
   const int Ho = H / 2, Wo = W / 2;
   const long long total = static_cast<long long>(N) * Ho * Wo * groups;
@@ -197,17 +237,17 @@ __global__ void maxpool_fwd_kernel(const uint4* __restrict__ x, uint4* __restric
   const int ho = static_cast<int>(t % Ho);
   const long long n = t / Ho;
   const long long base = ((n * H + 2 * ho) * W + 2 * wo) * groups + g;
-  const uint4 a = __ldg(x + base), b = __ldg(x + base + groups);
-  const uint4 c = __ldg(x + base + static_cast<long long>(W) * groups), d = __ldg(x + base + static_cast<long long>(W) * groups + groups);
   float fa[8], fb[8], fc[8], fd[8], o[8];
-  unpack8(a, fa); unpack8(b, fb); unpack8(c, fc); unpack8(d, fd);
+  ld8(x + base, fa); ld8(x + base + groups, fb);
+  ld8(x + base + static_cast<long long>(W) * groups, fc); ld8(x + base + static_cast<long long>(W) * groups + groups, fd);
 #pragma unroll
   for (int j = 0; j < 8; ++j) o[j] = fmaxf(fmaxf(fa[j], fb[j]), fmaxf(fc[j], fd[j]));
-  y[idx] = pack8(o);
+  st8(y + idx, o);
 }
 
-__global__ void maxpool_bwd_kernel(const uint4* __restrict__ x, const uint4* __restrict__ dp,
-                                   const uint4* skip, uint4* dz, int N, int H, int W, int C) {
+template <typename V>
+__global__ void maxpool_bwd_kernel(const V* __restrict__ x, const V* __restrict__ dp,
+                                   const V* skip, V* dz, int N, int H, int W, int C) {
   const int groups = C / 8;
   const int Ho = H / 2, Wo = W / 2;
   const long long total = static_cast<long long>(N) * Ho * Wo * groups;
@@ -225,15 +265,15 @@ __global__ void maxpool_bwd_kernel(const uint4* __restrict__ x, const uint4* __r
   float xv[4][8], gv[4][8], d[8];
 #pragma unroll
   for (int k = 0; k < 4; ++k) {
-    unpack8(__ldg(x + off[k]), xv[k]);
+    ld8(x + off[k], xv[k]);
     if (skip) {
-      unpack8(skip[off[k]], gv[k]);
+      ld8_rw(skip + off[k], gv[k]);
     } else {
 #pragma unroll
       for (int j = 0; j < 8; ++j) gv[k][j] = 0.0f;
     }
   }
-  unpack8(__ldg(dp + idx), d);
+  ld8(dp + idx, d);
 #pragma unroll
   for (int j = 0; j < 8; ++j) {
     int arg = 0;
@@ -249,11 +289,12 @@ __global__ void maxpool_bwd_kernel(const uint4* __restrict__ x, const uint4* __r
     }
   }
 #pragma unroll
-  for (int k = 0; k < 4; ++k) dz[off[k]] = pack8(gv[k]);
+  for (int k = 0; k < 4; ++k) st8(dz + off[k], gv[k]);
 }
 
 // ------------------------------------------------------------------------------------------ nearest 2x upsampling
-__global__ void upsample_fwd_kernel(const uint4* __restrict__ x, uint4* __restrict__ y, int N, int H, int W, int C) {
+template <typename V>
+__global__ void upsample_fwd_kernel(const V* __restrict__ x, V* __restrict__ y, int N, int H, int W, int C) {
   const int groups = C / 8;
   const long long total = static_cast<long long>(N) * (2 * H) * (2 * W) * groups;
   const long long idx = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
@@ -264,10 +305,11 @@ __global__ void upsample_fwd_kernel(const uint4* __restrict__ x, uint4* __restri
   t /= (2 * W);
   const int ho = static_cast<int>(t % (2 * H));
   const long long n = t / (2 * H);
-  y[idx] = __ldg(x + ((n * H + ho / 2) * W + wo / 2) * groups + g);
+  y[idx] = ldv(x + ((n * H + ho / 2) * W + wo / 2) * groups + g);
 }
 
-__global__ void upsample_bwd_kernel(const uint4* __restrict__ dy, const uint4* __restrict__ x, uint4* __restrict__ dx,
+template <typename V>
+__global__ void upsample_bwd_kernel(const V* __restrict__ dy, const V* __restrict__ x, V* __restrict__ dx,
                                     int N, int H, int W, int C, int relu_mask) {
   const int groups = C / 8;
   const long long total = static_cast<long long>(N) * H * W * groups;
@@ -281,25 +323,26 @@ __global__ void upsample_bwd_kernel(const uint4* __restrict__ dy, const uint4* _
   const long long n = t / H;
   const long long base = ((n * 2 * H + 2 * h) * (2 * W) + 2 * w) * groups + g;
   float a[8], b[8], c[8], d[8], o[8];
-  unpack8(__ldg(dy + base), a);
-  unpack8(__ldg(dy + base + groups), b);
-  unpack8(__ldg(dy + base + static_cast<long long>(2 * W) * groups), c);
-  unpack8(__ldg(dy + base + static_cast<long long>(2 * W) * groups + groups), d);
+  ld8(dy + base, a);
+  ld8(dy + base + groups, b);
+  ld8(dy + base + static_cast<long long>(2 * W) * groups, c);
+  ld8(dy + base + static_cast<long long>(2 * W) * groups + groups, d);
 #pragma unroll
   for (int j = 0; j < 8; ++j) o[j] = (a[j] + b[j]) + (c[j] + d[j]);
   if (relu_mask) {
     float xv[8];
-    unpack8(__ldg(x + idx), xv);
+    ld8(x + idx, xv);
 #pragma unroll
     for (int j = 0; j < 8; ++j) o[j] = xv[j] > 0.0f ? o[j] : 0.0f;
   }
-  dx[idx] = pack8(o);
+  st8(dx + idx, o);
 }
 
 // ------------------------------------------------------------------------------------------ head: 1x1 conv + sigmoid + dice sums
 constexpr int kMaxCl = 4;
 
-__global__ void head_fwd_kernel(const uint4* __restrict__ x, const float* __restrict__ w, const float* __restrict__ b,
+template <typename V>
+__global__ void head_fwd_kernel(const V* __restrict__ x, const float* __restrict__ w, const float* __restrict__ b,
                                 const float* __restrict__ y_true, float* __restrict__ p_out, float* __restrict__ ws,
                                 long long P, int C, int n_cl) {
   extern __shared__ float sh[];  // [C*n_cl] weights, [n_cl] bias, then 3 floats per warp
@@ -314,16 +357,16 @@ __global__ void head_fwd_kernel(const uint4* __restrict__ x, const float* __rest
   // every lane of a pixel group must stay in the loop for the shuffles: iterate on a uniform bound
   const long long iters = (total + stride - 1) / stride;
   long long idx = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
-  uint4 nxt = make_uint4(0u, 0u, 0u, 0u);
-  if (idx < total) nxt = __ldg(x + idx);
+  V nxt = zerov<V>();
+  if (idx < total) nxt = ldv(x + idx);
   for (long long itn = 0; itn < iters; ++itn, idx += stride) {
     const bool live = idx < total;
-    const uint4 cur = nxt;
-    if (idx + stride < total) nxt = __ldg(x + idx + stride);   // next iteration's load is already in flight
+    const V cur = nxt;
+    if (idx + stride < total) nxt = ldv(x + idx + stride);   // next iteration's load is already in flight
     float acc[kMaxCl] = {0.0f, 0.0f, 0.0f, 0.0f};
     if (live) {
       float f[8];
-      unpack8(cur, f);
+      unpackv(cur, f);
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
         for (int k = 0; k < n_cl; ++k) acc[k] = fmaf(f[j], sh[(sub * 8 + j) * n_cl + k], acc[k]);
@@ -365,9 +408,10 @@ __global__ void dice_finalize_kernel(const float* __restrict__ sums, float smoot
   out4[3] = (I + smooth) / (Sp + smooth);
 }
 
-__global__ void head_bwd_kernel(const uint4* __restrict__ x, const float* __restrict__ w,
+template <typename V>
+__global__ void head_bwd_kernel(const V* __restrict__ x, const float* __restrict__ w,
                                 const float* __restrict__ y_true, const float* __restrict__ p,
-                                const float* __restrict__ sums, float smooth, float grad_scale, uint4* __restrict__ dx,
+                                const float* __restrict__ sums, float smooth, float grad_scale, V* __restrict__ dx,
                                 float* __restrict__ ws, long long P, int C, int n_cl) {
   extern __shared__ float sh[];  // [C*n_cl] weights
   const int subs = C / 8;
@@ -394,7 +438,7 @@ __global__ void head_bwd_kernel(const uint4* __restrict__ x, const float* __rest
   for (long long idx = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; idx < total; idx += stride) {
     const long long pix = idx / subs;
     float f[8], o[8];
-    unpack8(__ldg(x + idx), f);
+    ld8(x + idx, f);
 #pragma unroll
     for (int j = 0; j < 8; ++j) o[j] = 0.0f;
 #pragma unroll
@@ -413,7 +457,7 @@ __global__ void head_bwd_kernel(const uint4* __restrict__ x, const float* __rest
     }
 #pragma unroll
     for (int j = 0; j < 8; ++j) o[j] = f[j] > 0.0f ? o[j] : 0.0f;
-    dx[idx] = pack8(o);
+    st8(dx + idx, o);
   }
   // reduce over lanes sharing `sub`; every warp owns one row in shared memory, the block sums its warps in a fixed
   // order and writes one row of partials to ws (no atomics)
@@ -445,7 +489,8 @@ __global__ void head_bwd_kernel(const uint4* __restrict__ x, const float* __rest
 }
 
 // ------------------------------------------------------------------------------------------ bias gradient (column sums)
-__global__ void colsum_kernel(const uint4* __restrict__ dz, float* __restrict__ ws, long long P, int C) {
+template <typename V>
+__global__ void colsum_kernel(const V* __restrict__ dz, float* __restrict__ ws, long long P, int C) {
   // one row of partial sums per block in ws; inside the block: lanes -> warps (or runs of C/8 threads) -> fixed-order sum
   extern __shared__ float red[];  // [blockDim/span][C]
   const int groups = C / 8;
@@ -458,16 +503,16 @@ __global__ void colsum_kernel(const uint4* __restrict__ dz, float* __restrict__ 
   float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
   long long idx = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
   for (; idx + 3 * stride < total; idx += 4 * stride) {   // four independent 16-byte loads in flight
-    const uint4 v0 = __ldg(dz + idx), v1 = __ldg(dz + idx + stride), v2 = __ldg(dz + idx + 2 * stride),
-                v3 = __ldg(dz + idx + 3 * stride);
+    const V v0 = ldv(dz + idx), v1 = ldv(dz + idx + stride), v2 = ldv(dz + idx + 2 * stride),
+            v3 = ldv(dz + idx + 3 * stride);
     float f0[8], f1[8], f2[8], f3[8];
-    unpack8(v0, f0); unpack8(v1, f1); unpack8(v2, f2); unpack8(v3, f3);
+    unpackv(v0, f0); unpackv(v1, f1); unpackv(v2, f2); unpackv(v3, f3);
 #pragma unroll
     for (int j = 0; j < 8; ++j) acc[j] += (f0[j] + f1[j]) + (f2[j] + f3[j]);
   }
   for (; idx < total; idx += stride) {
     float f[8];
-    unpack8(__ldg(dz + idx), f);
+    ld8(dz + idx, f);
 #pragma unroll
     for (int j = 0; j < 8; ++j) acc[j] += f[j];
   }
@@ -487,7 +532,12 @@ __global__ void colsum_kernel(const uint4* __restrict__ dz, float* __restrict__ 
 }
 
 // ------------------------------------------------------------------------------------------ weight packing
-__global__ void pack_conv_fwd_kernel(const float* __restrict__ w, __nv_bfloat16* __restrict__ out, int taps, int Cin,
+// GEMM operand element from an fp32 master: bf16, or (fp32/tf32 mode) the nearest tf32 value kept in an fp32 word
+__device__ __forceinline__ void cvt_operand(__nv_bfloat16* p, float v) { *p = __float2bfloat16(v); }
+__device__ __forceinline__ void cvt_operand(float* p, float v) { *p = round_tf32(v); }
+
+template <typename T>
+__global__ void pack_conv_fwd_kernel(const float* __restrict__ w, T* __restrict__ out, int taps, int Cin,
                                      int Cout) {
   const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
   const long long n = static_cast<long long>(taps) * Cin * Cout;
@@ -495,9 +545,10 @@ __global__ void pack_conv_fwd_kernel(const float* __restrict__ w, __nv_bfloat16*
   const int ci = static_cast<int>(i % Cin);
   const int tap = static_cast<int>((i / Cin) % taps);
   const int co = static_cast<int>(i / (static_cast<long long>(Cin) * taps));
-  out[i] = __float2bfloat16(w[(static_cast<long long>(tap) * Cin + ci) * Cout + co]);
+  cvt_operand(out + i, w[(static_cast<long long>(tap) * Cin + ci) * Cout + co]);
 }
-__global__ void pack_conv_dgrad_kernel(const float* __restrict__ w, __nv_bfloat16* __restrict__ out, int taps, int Cin,
+template <typename T>
+__global__ void pack_conv_dgrad_kernel(const float* __restrict__ w, T* __restrict__ out, int taps, int Cin,
                                        int Cout) {
   const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
   const long long n = static_cast<long long>(taps) * Cin * Cout;
@@ -505,17 +556,19 @@ __global__ void pack_conv_dgrad_kernel(const float* __restrict__ w, __nv_bfloat1
   const int co = static_cast<int>(i % Cout);
   const int tap = static_cast<int>((i / Cout) % taps);
   const int ci = static_cast<int>(i / (static_cast<long long>(Cout) * taps));
-  out[i] = __float2bfloat16(w[(static_cast<long long>(taps - 1 - tap) * Cin + ci) * Cout + co]);
+  cvt_operand(out + i, w[(static_cast<long long>(taps - 1 - tap) * Cin + ci) * Cout + co]);
 }
-__global__ void pack_tconv_dgrad_kernel(const float* __restrict__ w, __nv_bfloat16* __restrict__ out, int Cin, int Cout) {
+template <typename T>
+__global__ void pack_tconv_dgrad_kernel(const float* __restrict__ w, T* __restrict__ out, int Cin, int Cout) {
   const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
   const long long n = 4ll * Cin * Cout;
   if (i >= n) return;
   const int o = static_cast<int>(i % Cout);
   const int ab = static_cast<int>((i / Cout) % 4);
   const int c = static_cast<int>(i / (4ll * Cout));
-  out[i] = __float2bfloat16(w[(static_cast<long long>(ab) * Cout + o) * Cin + c]);
+  cvt_operand(out + i, w[(static_cast<long long>(ab) * Cout + o) * Cin + c]);
 }
+template <typename T>
 __global__ void __launch_bounds__(256)
 pack_all_kernel(const PackLayer* __restrict__ layers, int nlayers, const float* __restrict__ params,
                 uint8_t* __restrict__ arena, int tile_base) {
@@ -527,8 +580,8 @@ pack_all_kernel(const PackLayer* __restrict__ layers, int nlayers, const float* 
   const int t = tile_id - L.tile_start;
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
   const float* w = params + L.src;
-  __nv_bfloat16* out_f = reinterpret_cast<__nv_bfloat16*>(arena + L.dst_fwd);
-  __nv_bfloat16* out_d = reinterpret_cast<__nv_bfloat16*>(arena + L.dst_dgrad);
+  T* out_f = reinterpret_cast<T*>(arena + L.dst_fwd);
+  T* out_d = reinterpret_cast<T*>(arena + L.dst_dgrad);
   if (L.kind == 0) {
     // master w[tap][ci][co]; fwd out[co][tap][ci] (transposed), dgrad out[ci][T-1-tap][co] (straight)
     const int tiles_co = L.cout >> 5, tiles_ci = L.cin >> 5;
@@ -540,13 +593,13 @@ pack_all_kernel(const PackLayer* __restrict__ layers, int nlayers, const float* 
       const int ci = ci0 + ty + 8 * r;
       const float v = w[(static_cast<size_t>(tap) * L.cin + ci) * L.cout + co0 + tx];
       tile[ty + 8 * r][tx] = v;
-      out_d[(static_cast<size_t>(ci) * L.taps + (L.taps - 1 - tap)) * L.cout + co0 + tx] = __float2bfloat16(v);
+      cvt_operand(out_d + (static_cast<size_t>(ci) * L.taps + (L.taps - 1 - tap)) * L.cout + co0 + tx, v);
     }
     __syncthreads();
 #pragma unroll
     for (int r = 0; r < 4; ++r) {
       const int co = co0 + ty + 8 * r;
-      out_f[(static_cast<size_t>(co) * L.taps + tap) * L.cin + ci0 + tx] = __float2bfloat16(tile[tx][ty + 8 * r]);
+      cvt_operand(out_f + (static_cast<size_t>(co) * L.taps + tap) * L.cin + ci0 + tx, tile[tx][ty + 8 * r]);
     }
   } else {
     // master w[ab][o][c]; fwd out[ab*Cout + o][c] (straight), dgrad out[c][ab][o] (transposed)
@@ -560,13 +613,13 @@ pack_all_kernel(const PackLayer* __restrict__ layers, int nlayers, const float* 
       const size_t idx = (static_cast<size_t>(ab) * L.cout + o) * L.cin + c0 + tx;
       const float v = w[idx];
       tile[ty + 8 * r][tx] = v;
-      out_f[idx] = __float2bfloat16(v);
+      cvt_operand(out_f + idx, v);
     }
     __syncthreads();
 #pragma unroll
     for (int r = 0; r < 4; ++r) {
       const int c = c0 + ty + 8 * r;
-      out_d[(static_cast<size_t>(c) * 4 + ab) * L.cout + o0 + tx] = __float2bfloat16(tile[tx][ty + 8 * r]);
+      cvt_operand(out_d + (static_cast<size_t>(c) * 4 + ab) * L.cout + o0 + tx, tile[tx][ty + 8 * r]);
     }
   }
 }
@@ -574,6 +627,10 @@ pack_all_kernel(const PackLayer* __restrict__ layers, int nlayers, const float* 
 __global__ void cast_f32_bf16_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ y, long long n) {
   const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
   if (i < n) y[i] = __float2bfloat16(x[i]);
+}
+__global__ void round_tf32_kernel(const float* __restrict__ x, float* __restrict__ y, long long n) {
+  const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i < n) y[i] = round_tf32(x[i]);
 }
 __global__ void cast_bf16_f32_kernel(const __nv_bfloat16* __restrict__ x, float* __restrict__ y, long long n) {
   const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
@@ -704,7 +761,7 @@ int check_groups(int C, const char* what) {
 bool conv_first_fwd_writes_gates(int Cin, int Cout) { return Cout == 32 && (Cin == 1 || Cin == 4); }
 
 int conv_first_fwd(const float* x, const float* w, const float* bias, void* y, int N, int H, int W, int Cin, int Cout,
-                   cudaStream_t s, unsigned short* gate_out) {
+                   cudaStream_t s, unsigned short* gate_out, int dt) {
   UB_REQUIRE(Cin >= 1 && Cin <= 8, "conv_first_fwd: Cin %d outside 1..8", Cin);
   UB_REQUIRE(gate_out == nullptr || conv_first_fwd_writes_gates(Cin, Cout),
              "conv_first_fwd: gate bits are only written for Cout 32 and Cin 1 or 4");
@@ -714,7 +771,8 @@ int conv_first_fwd(const float* x, const float* w, const float* bias, void* y, i
   const bool y32 = reinterpret_cast<uintptr_t>(y) % 32 == 0;   // the fast path stores 32 bytes per instruction
   UB_REQUIRE(gate_out == nullptr || (y32 && W % 2 == 0),
              "conv_first_fwd: gate bits need a 32-byte aligned output tensor and an even width");
-  if (y32 && W % 2 == 0 && Cout == 32 && (Cin == 1 || Cin == 4)) {   // two-pixels-per-thread fast path (the network's conv1a)
+  UB_REQUIRE(dt == UB_DT_BF16 || gate_out == nullptr, "conv_first_fwd: gate bits are a bf16-mode feature");
+  if (dt == UB_DT_BF16 && y32 && W % 2 == 0 && Cout == 32 && (Cin == 1 || Cin == 4)) {   // two-pixels-per-thread fast path (the network's conv1a)
     const unsigned P = static_cast<unsigned>(static_cast<long long>(N) * H * W);
     unsigned blocks = grid_for(P / 2, kThreads);
     const unsigned cap = 8u * static_cast<unsigned>(device_sm_count());
@@ -733,7 +791,11 @@ int conv_first_fwd(const float* x, const float* w, const float* bias, void* y, i
   unsigned blocks = grid_for(total, kThreads);
   const unsigned cap = 8u * static_cast<unsigned>(device_sm_count());   // weights are staged once per block
   if (blocks > cap) blocks = cap;
-  conv_first_fwd_kernel<<<blocks, kThreads, smem, s>>>(x, w, bias, reinterpret_cast<uint4*>(y), N, H, W, Cin, Cout);
+  if (dt == UB_DT_TF32) {
+    conv_first_fwd_kernel<<<blocks, kThreads, smem, s>>>(x, w, bias, reinterpret_cast<F32x8*>(y), N, H, W, Cin, Cout);
+  } else {
+    conv_first_fwd_kernel<<<blocks, kThreads, smem, s>>>(x, w, bias, reinterpret_cast<uint4*>(y), N, H, W, Cin, Cout);
+  }
   UB_CHECK_CUDA(cudaGetLastError());
   return UB_OK;
 }
@@ -743,14 +805,14 @@ long long conv_first_wgrad_ws_floats(int Cin, int Cout) {
 }
 
 int conv_first_wgrad(const float* x, const void* dz, float* dw, float* db, float* ws, int N, int H, int W, int Cin,
-                     int Cout, cudaStream_t s) {
+                     int Cout, cudaStream_t s, int dt) {
   UB_REQUIRE(Cin >= 1 && Cin <= 8, "conv_first_wgrad: Cin %d outside 1..8", Cin);
   const int groups = Cout / 8;
   UB_REQUIRE(Cout % 8 == 0 && groups >= 1 && groups <= 8 && (groups & (groups - 1)) == 0,
              "conv_first_wgrad: Cout %d unsupported", Cout);
   const int nout = 9 * Cin * Cout + Cout;
   UB_REQUIRE(static_cast<long long>(N) * H * W * groups < (1ll << 31), "conv_first_wgrad: tensor too large");
-  if (Cout == 32 && (Cin == 1 || Cin == 4) && W % 8 == 0) {   // strip kernel (level0.cuh)
+  if (dt == UB_DT_BF16 && Cout == 32 && (Cin == 1 || Cin == 4) && W % 8 == 0) {   // strip kernel (level0.cuh)
     const unsigned n_strips = static_cast<unsigned>(N) * H * (W / 8);
     const uint4* dz4 = reinterpret_cast<const uint4*>(dz);
     if (Cin == 1) conv_first32_wgrad_kernel<1><<<kRedBlocks, 128, 0, s>>>(x, dz4, ws, H, W, n_strips);
@@ -762,11 +824,18 @@ int conv_first_wgrad(const float* x, const void* dz, float* dw, float* db, float
   }
   const size_t smem = static_cast<size_t>(kThreads / 32) * nout * sizeof(float);
   if (smem > 48 * 1024) {
-    UB_CHECK_CUDA(cudaFuncSetAttribute(conv_first_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    UB_CHECK_CUDA(cudaFuncSetAttribute(conv_first_wgrad_kernel<uint4>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       static_cast<int>(smem)));
+    UB_CHECK_CUDA(cudaFuncSetAttribute(conv_first_wgrad_kernel<F32x8>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        static_cast<int>(smem)));
   }
-  conv_first_wgrad_kernel<<<kRedBlocks, kThreads, smem, s>>>(x, reinterpret_cast<const uint4*>(dz), ws, N, H, W, Cin,
-                                                            Cout);
+  if (dt == UB_DT_TF32) {
+    conv_first_wgrad_kernel<<<kRedBlocks, kThreads, smem, s>>>(x, reinterpret_cast<const F32x8*>(dz), ws, N, H, W,
+                                                              Cin, Cout);
+  } else {
+    conv_first_wgrad_kernel<<<kRedBlocks, kThreads, smem, s>>>(x, reinterpret_cast<const uint4*>(dz), ws, N, H, W,
+                                                              Cin, Cout);
+  }
   UB_CHECK_CUDA(cudaGetLastError());
   rows_reduce_kernel<<<grid_for(nout, 32), 1024, 0, s>>>(ws, kRedBlocks, nout, dw, 9 * Cin * Cout, db);
   UB_CHECK_CUDA(cudaGetLastError());
@@ -785,8 +854,15 @@ static bool v8_ok(int C, long long fine_pixels, std::initializer_list<const void
   return true;
 }
 
-int maxpool2x2_fwd(const void* x, void* y, int N, int H, int W, int C, cudaStream_t s) {
+int maxpool2x2_fwd(const void* x, void* y, int N, int H, int W, int C, cudaStream_t s, int dt) {
   UB_REQUIRE(C % 8 == 0 && H % 2 == 0 && W % 2 == 0, "maxpool2x2_fwd: shape %dx%dx%d unsupported", H, W, C);
+  if (dt == UB_DT_TF32) {
+    const long long total = static_cast<long long>(N) * (H / 2) * (W / 2) * (C / 8);
+    maxpool_fwd_kernel<<<grid_for(total, kThreads), kThreads, 0, s>>>(reinterpret_cast<const F32x8*>(x),
+                                                                      reinterpret_cast<F32x8*>(y), N, H, W, C);
+    UB_CHECK_CUDA(cudaGetLastError());
+    return UB_OK;
+  }
   if (v8_ok(C, static_cast<long long>(N) * H * W, {x, y}, 1)) {
     const unsigned groups = C / 16, total16 = static_cast<unsigned>(N) * (H / 2) * (W / 2) * groups;
     maxpool_fwd_v8_kernel<<<grid_for(total16, 256), 256, 0, s>>>(reinterpret_cast<const U32x8*>(x),
@@ -802,9 +878,16 @@ int maxpool2x2_fwd(const void* x, void* y, int N, int H, int W, int C, cudaStrea
 }
 
 int maxpool2x2_bwd(const void* x, const void* dpool, const void* skip_grad, void* dz_full, int N, int H, int W, int C,
-                   cudaStream_t s) {
+                   cudaStream_t s, int dt) {
   UB_REQUIRE(C % 8 == 0 && H % 2 == 0 && W % 2 == 0, "maxpool2x2_bwd: shape %dx%dx%d unsupported", H, W, C);
   const long long total = static_cast<long long>(N) * (H / 2) * (W / 2) * (C / 8);
+  if (dt == UB_DT_TF32) {
+    maxpool_bwd_kernel<<<grid_for(total, kThreads), kThreads, 0, s>>>(
+        reinterpret_cast<const F32x8*>(x), reinterpret_cast<const F32x8*>(dpool),
+        reinterpret_cast<const F32x8*>(skip_grad), reinterpret_cast<F32x8*>(dz_full), N, H, W, C);
+    UB_CHECK_CUDA(cudaGetLastError());
+    return UB_OK;
+  }
   maxpool_bwd_kernel<<<grid_for(total, kThreads), kThreads, 0, s>>>(
       reinterpret_cast<const uint4*>(x), reinterpret_cast<const uint4*>(dpool),
       reinterpret_cast<const uint4*>(skip_grad), reinterpret_cast<uint4*>(dz_full), N, H, W, C);
@@ -812,8 +895,15 @@ int maxpool2x2_bwd(const void* x, const void* dpool, const void* skip_grad, void
   return UB_OK;
 }
 
-int upsample2x2_fwd(const void* x, void* y, int N, int H, int W, int C, cudaStream_t s) {
+int upsample2x2_fwd(const void* x, void* y, int N, int H, int W, int C, cudaStream_t s, int dt) {
   UB_REQUIRE(C % 8 == 0, "upsample2x2_fwd: C %d", C);
+  if (dt == UB_DT_TF32) {
+    const long long total = static_cast<long long>(N) * (2 * H) * (2 * W) * (C / 8);
+    upsample_fwd_kernel<<<grid_for(total, kThreads), kThreads, 0, s>>>(reinterpret_cast<const F32x8*>(x),
+                                                                       reinterpret_cast<F32x8*>(y), N, H, W, C);
+    UB_CHECK_CUDA(cudaGetLastError());
+    return UB_OK;
+  }
   if (v8_ok(C, static_cast<long long>(N) * 4 * H * W, {x, y}, 4)) {
     const unsigned groups = C / 16, total16 = static_cast<unsigned>(N) * H * W * groups;
     upsample_fwd_v8_kernel<<<grid_for(total16, 256), 256, 0, s>>>(reinterpret_cast<const U32x8*>(x),
@@ -828,8 +918,17 @@ int upsample2x2_fwd(const void* x, void* y, int N, int H, int W, int C, cudaStre
   return UB_OK;
 }
 
-int upsample2x2_bwd(const void* dy, const void* x, void* dx, int N, int H, int W, int C, int relu_mask, cudaStream_t s) {
+int upsample2x2_bwd(const void* dy, const void* x, void* dx, int N, int H, int W, int C, int relu_mask, cudaStream_t s,
+                    int dt) {
   UB_REQUIRE(C % 8 == 0, "upsample2x2_bwd: C %d", C);
+  if (dt == UB_DT_TF32) {
+    const long long total = static_cast<long long>(N) * H * W * (C / 8);
+    upsample_bwd_kernel<<<grid_for(total, kThreads), kThreads, 0, s>>>(
+        reinterpret_cast<const F32x8*>(dy), reinterpret_cast<const F32x8*>(x), reinterpret_cast<F32x8*>(dx), N, H, W, C,
+        relu_mask);
+    UB_CHECK_CUDA(cudaGetLastError());
+    return UB_OK;
+  }
   if (v8_ok(C, static_cast<long long>(N) * 4 * H * W, {dy, x, dx}, 8)) {
     const unsigned groups = C / 16, total16 = static_cast<unsigned>(N) * H * W * groups;
     upsample_bwd_v8_kernel<<<grid_for(total16, 256), 256, 0, s>>>(
@@ -853,11 +952,15 @@ long long head_ws_floats(long long, int C, int n_cl) {
 }
 
 int head_fwd(const void* x, const float* w, const float* b, const float* y_true, float* p_out, float* sums, float* ws,
-             long long P, int C, int n_cl, cudaStream_t s) {
+             long long P, int C, int n_cl, cudaStream_t s, int dt) {
   UB_REQUIRE(n_cl >= 1 && n_cl <= kMaxCl, "head_fwd: n_cl_out %d outside 1..%d", n_cl, kMaxCl);
   const int subs = C / 8;
   UB_REQUIRE(C % 8 == 0 && subs >= 1 && subs <= 32 && (subs & (subs - 1)) == 0, "head_fwd: C %d unsupported", C);
-  if (C == 32 && P < (1ll << 31) && reinterpret_cast<uintptr_t>(x) % 32 == 0) {   // thread-per-pixel fast path (the network's Mask layer)
+  if (dt == UB_DT_TF32) {
+    const size_t smem = (C * n_cl + n_cl + 3 * (kThreads / 32)) * sizeof(float);
+    head_fwd_kernel<<<kRedBlocks, kThreads, smem, s>>>(reinterpret_cast<const F32x8*>(x), w, b, y_true, p_out, ws, P, C,
+                                                       n_cl);
+  } else if (C == 32 && P < (1ll << 31) && reinterpret_cast<uintptr_t>(x) % 32 == 0) {   // thread-per-pixel fast path (the network's Mask layer)
     const uint4* xv = reinterpret_cast<const uint4*>(x);
     const unsigned Pu = static_cast<unsigned>(P);
     switch (n_cl) {
@@ -884,19 +987,29 @@ int dice_finalize(const float* sums, float smooth, float* out4, cudaStream_t s) 
 }
 
 int head_bwd(const void* x, const float* w, const float* y_true, const float* p, const float* sums, float smooth,
-             float grad_scale, void* dx, float* dw, float* db, float* ws, long long P, int C, int n_cl, cudaStream_t s) {
+             float grad_scale, void* dx, float* dw, float* db, float* ws, long long P, int C, int n_cl, cudaStream_t s,
+             int dt) {
   UB_REQUIRE(n_cl >= 1 && n_cl <= kMaxCl, "head_bwd: n_cl_out %d outside 1..%d", n_cl, kMaxCl);
   const int subs = C / 8;
   UB_REQUIRE(C % 8 == 0 && subs >= 1 && subs <= 32 && (subs & (subs - 1)) == 0, "head_bwd: C %d unsupported", C);
   const int nout = C * n_cl + n_cl;
   int rows = kRedBlocks;   // partial rows in ws = blocks launched
-  if (C == 32 && n_cl == 1 && P < (1ll << 31) && reinterpret_cast<uintptr_t>(x) % 32 == 0 &&
+  if (dt == UB_DT_TF32) {
+    const size_t smem = (C * n_cl + (kThreads / 32) * nout) * sizeof(float);
+    head_bwd_kernel<<<kRedBlocks, kThreads, smem, s>>>(reinterpret_cast<const F32x8*>(x), w, y_true, p, sums, smooth,
+                                                       grad_scale, reinterpret_cast<F32x8*>(dx), ws, P, C, n_cl);
+  } else if (C == 32 && n_cl == 1 && P < (1ll << 31) && reinterpret_cast<uintptr_t>(x) % 32 == 0 &&
       reinterpret_cast<uintptr_t>(dx) % 32 == 0) {   // thread-per-pixel fast path
     // one wave: 78 registers x 256 threads -> three resident blocks per SM (592 blocks would run as 444 + 148)
-    static int blocks_per_sm = 0;
+    static std::atomic<int> blocks_per_sm_of[64];   // per device (zero-initialised), like device_sm_count()
+    int dev = 0;
+    UB_CHECK_CUDA(cudaGetDevice(&dev));
+    UB_REQUIRE(dev >= 0 && dev < 64, "head_bwd: device index %d unsupported", dev);
+    int blocks_per_sm = blocks_per_sm_of[dev].load(std::memory_order_relaxed);
     if (blocks_per_sm == 0) {
       UB_CHECK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, head32_bwd_kernel, kThreads, 0));
       if (blocks_per_sm < 1) blocks_per_sm = 1;
+      blocks_per_sm_of[dev].store(blocks_per_sm, std::memory_order_relaxed);
     }
     rows = blocks_per_sm * device_sm_count();
     if (rows > kRedBlocks) rows = kRedBlocks;
@@ -916,10 +1029,18 @@ int head_bwd(const void* x, const float* w, const float* y_true, const float* p,
 long long colsum_ws_floats(int C) { return static_cast<long long>(kRedBlocks) * (kThreads / 32) * C; }
 
 int colsum_bf16(const void* dz, float* db, float* ws, long long P, int C, cudaStream_t s) {
-  int rc = check_groups(C, "colsum_bf16");
+  return colsum_act(dz, db, ws, P, C, s, UB_DT_BF16);
+}
+
+int colsum_act(const void* dz, float* db, float* ws, long long P, int C, cudaStream_t s, int dt) {
+  int rc = check_groups(C, "colsum");
   if (rc) return rc;
-  colsum_kernel<<<kRedBlocks, kThreads, (kThreads / 32) * C * sizeof(float), s>>>(reinterpret_cast<const uint4*>(dz),
-                                                                                 ws, P, C);
+  const size_t smem = (kThreads / 32) * C * sizeof(float);
+  if (dt == UB_DT_TF32) {
+    colsum_kernel<<<kRedBlocks, kThreads, smem, s>>>(reinterpret_cast<const F32x8*>(dz), ws, P, C);
+  } else {
+    colsum_kernel<<<kRedBlocks, kThreads, smem, s>>>(reinterpret_cast<const uint4*>(dz), ws, P, C);
+  }
   UB_CHECK_CUDA(cudaGetLastError());
   rows_reduce_kernel<<<grid_for(C, 32), 1024, 0, s>>>(ws, kRedBlocks, C, db, C, nullptr);
   UB_CHECK_CUDA(cudaGetLastError());
@@ -974,35 +1095,59 @@ int colsum_bf16_static(const void* dz, float* db, long long P, int C, cudaStream
 }
 
 int pack_all(const PackLayer* layers_dev, int nlayers, int total_tiles, const float* params, void* arena,
-             cudaStream_t s, int tile_base) {
+             cudaStream_t s, int tile_base, int dt) {
   if (nlayers <= 0 || total_tiles <= 0) return UB_OK;
-  pack_all_kernel<<<static_cast<unsigned>(total_tiles), 256, 0, s>>>(layers_dev, nlayers, params,
-                                                                     reinterpret_cast<uint8_t*>(arena), tile_base);
+  if (dt == UB_DT_TF32) {
+    pack_all_kernel<float><<<static_cast<unsigned>(total_tiles), 256, 0, s>>>(
+        layers_dev, nlayers, params, reinterpret_cast<uint8_t*>(arena), tile_base);
+  } else {
+    pack_all_kernel<__nv_bfloat16><<<static_cast<unsigned>(total_tiles), 256, 0, s>>>(
+        layers_dev, nlayers, params, reinterpret_cast<uint8_t*>(arena), tile_base);
+  }
   UB_CHECK_CUDA(cudaGetLastError());
   return UB_OK;
 }
 
-int pack_conv_fwd(const float* w, void* out, int taps, int Cin, int Cout, cudaStream_t s) {
+int pack_conv_fwd(const float* w, void* out, int taps, int Cin, int Cout, cudaStream_t s, int dt) {
   const long long n = static_cast<long long>(taps) * Cin * Cout;
-  pack_conv_fwd_kernel<<<grid_for(n, kThreads), kThreads, 0, s>>>(w, reinterpret_cast<__nv_bfloat16*>(out), taps, Cin,
-                                                                  Cout);
-  UB_CHECK_CUDA(cudaGetLastError());
-  return UB_OK;
-}
-int pack_conv_dgrad(const float* w, void* out, int taps, int Cin, int Cout, cudaStream_t s) {
-  const long long n = static_cast<long long>(taps) * Cin * Cout;
-  pack_conv_dgrad_kernel<<<grid_for(n, kThreads), kThreads, 0, s>>>(w, reinterpret_cast<__nv_bfloat16*>(out), taps, Cin,
+  if (dt == UB_DT_TF32) {
+    pack_conv_fwd_kernel<<<grid_for(n, kThreads), kThreads, 0, s>>>(w, reinterpret_cast<float*>(out), taps, Cin, Cout);
+  } else {
+    pack_conv_fwd_kernel<<<grid_for(n, kThreads), kThreads, 0, s>>>(w, reinterpret_cast<__nv_bfloat16*>(out), taps, Cin,
                                                                     Cout);
+  }
   UB_CHECK_CUDA(cudaGetLastError());
   return UB_OK;
 }
-int pack_tconv_fwd(const float* w, void* out, int Cin, int Cout, cudaStream_t s) {
+int pack_conv_dgrad(const float* w, void* out, int taps, int Cin, int Cout, cudaStream_t s, int dt) {
+  const long long n = static_cast<long long>(taps) * Cin * Cout;
+  if (dt == UB_DT_TF32) {
+    pack_conv_dgrad_kernel<<<grid_for(n, kThreads), kThreads, 0, s>>>(w, reinterpret_cast<float*>(out), taps, Cin,
+                                                                      Cout);
+  } else {
+    pack_conv_dgrad_kernel<<<grid_for(n, kThreads), kThreads, 0, s>>>(w, reinterpret_cast<__nv_bfloat16*>(out), taps,
+                                                                      Cin, Cout);
+  }
+  UB_CHECK_CUDA(cudaGetLastError());
+  return UB_OK;
+}
+int pack_tconv_fwd(const float* w, void* out, int Cin, int Cout, cudaStream_t s, int dt) {
+  if (dt == UB_DT_TF32) {
+    const long long n = 4ll * Cin * Cout;
+    round_tf32_kernel<<<grid_for(n, kThreads), kThreads, 0, s>>>(w, reinterpret_cast<float*>(out), n);
+    UB_CHECK_CUDA(cudaGetLastError());
+    return UB_OK;
+  }
   return cast_f32_to_bf16(w, out, 4ll * Cin * Cout, s);
 }
-int pack_tconv_dgrad(const float* w, void* out, int Cin, int Cout, cudaStream_t s) {
+int pack_tconv_dgrad(const float* w, void* out, int Cin, int Cout, cudaStream_t s, int dt) {
   const long long n = 4ll * Cin * Cout;
-  pack_tconv_dgrad_kernel<<<grid_for(n, kThreads), kThreads, 0, s>>>(w, reinterpret_cast<__nv_bfloat16*>(out), Cin,
-                                                                     Cout);
+  if (dt == UB_DT_TF32) {
+    pack_tconv_dgrad_kernel<<<grid_for(n, kThreads), kThreads, 0, s>>>(w, reinterpret_cast<float*>(out), Cin, Cout);
+  } else {
+    pack_tconv_dgrad_kernel<<<grid_for(n, kThreads), kThreads, 0, s>>>(w, reinterpret_cast<__nv_bfloat16*>(out), Cin,
+                                                                       Cout);
+  }
   UB_CHECK_CUDA(cudaGetLastError());
   return UB_OK;
 }

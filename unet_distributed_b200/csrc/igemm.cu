@@ -40,8 +40,9 @@ igemm_kernel(const __grid_constant__ IgemmParams p, const __grid_constant__ CUte
   const uint32_t raw_addr = smem_u32(smem_raw);
   uint8_t* smem = smem_raw + ((1024u - (raw_addr & 1023u)) & 1023u);
 
-  const int a_bytes = 128 * p.kc * 2;
-  const int b_bytes = p.block_n * p.kc * 2;
+  const int elt = p.elt == 4 ? 4 : 2;        // operand / activation element: bf16, or fp32 read as tf32
+  const int a_bytes = 128 * p.kc * elt;
+  const int b_bytes = p.block_n * p.kc * elt;
   const int stage_bytes = a_bytes + b_bytes;
   IgemmBarriers* bars = reinterpret_cast<IgemmBarriers*>(smem + p.stages * stage_bytes);
 
@@ -107,9 +108,11 @@ igemm_kernel(const __grid_constant__ IgemmParams p, const __grid_constant__ CUte
   } else if (warp == 1) {
     // ------------------------------------------------------------ MMA issuer
     // The warp walks the uniform control flow together; one elected lane issues (bare UTCHMMAs, uniform registers).
-    const uint32_t idesc = umma_idesc_bf16(128, static_cast<uint32_t>(p.block_n), 0, 0);
-    const uint32_t sw = p.kc == 64 ? UMMA_SW_128B : UMMA_SW_64B;
-    const uint32_t sbo = static_cast<uint32_t>(8 * p.kc * 2);  // 8 rows of kc bf16
+    const uint32_t idesc = elt == 4 ? umma_idesc_tf32(128, static_cast<uint32_t>(p.block_n), 0, 0)
+                                    : umma_idesc_bf16(128, static_cast<uint32_t>(p.block_n), 0, 0);
+    const int row_bytes = p.kc * elt;                          // one pixel's K block: 128 B (SWIZZLE_128B) or 64 B
+    const uint32_t sw = row_bytes == 128 ? UMMA_SW_128B : UMMA_SW_64B;
+    const uint32_t sbo = static_cast<uint32_t>(8 * row_bytes);  // 8 rows of kc elements
     const uint64_t desc_hi = umma_smem_desc(0, 0, sbo, sw);
     int stage = 0;
     uint32_t phase = 0;
@@ -127,11 +130,20 @@ igemm_kernel(const __grid_constant__ IgemmParams p, const __grid_constant__ CUte
         const uint64_t bdesc = desc_hi + ((sa + static_cast<uint32_t>(a_bytes)) >> 4);
         if (elect_one()) {
           const uint32_t acc_flag = kb ? 1u : 0u;
+          if (elt == 4) {   // kind::tf32: K = 8 fp32 words = 32 bytes per instruction, like 16 bf16
+            umma_tf32(d_tmem, adesc, bdesc, idesc, acc_flag);
+            umma_tf32(d_tmem, adesc + 2, bdesc + 2, idesc, 1u);
+            if (row_bytes == 128) {
+              umma_tf32(d_tmem, adesc + 4, bdesc + 4, idesc, 1u);
+              umma_tf32(d_tmem, adesc + 6, bdesc + 6, idesc, 1u);
+            }
+          } else {
           umma_f16(d_tmem, adesc, bdesc, idesc, acc_flag);
           umma_f16(d_tmem, adesc + 2, bdesc + 2, idesc, 1u);
           if (p.kc == 64) {
             umma_f16(d_tmem, adesc + 4, bdesc + 4, idesc, 1u);
             umma_f16(d_tmem, adesc + 6, bdesc + 6, idesc, 1u);
+          }
           }
           umma_commit(&bars->empty[stage]);
           if (kb == num_kb - 1) umma_commit(&bars->tmem_full[acc]);
@@ -267,10 +279,11 @@ igemm_kernel(const __grid_constant__ IgemmParams p, const __grid_constant__ CUte
         if (col0 >= e.split_col) { slot = 1; ch0 = col0 - e.split_col; }
         pix = (static_cast<size_t>(n) * p.H + h) * p.W + w;
       }
-      __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(e.dst[slot]) + pix * e.dst_C[slot] + e.dst_coff[slot] + ch0;
-      const __nv_bfloat16* aux = nullptr;
+      // byte pointers: elements are bf16 or (fp32/tf32 mode) fp32
+      char* dst = reinterpret_cast<char*>(e.dst[slot]) + (pix * e.dst_C[slot] + e.dst_coff[slot] + ch0) * elt;
+      const char* aux = nullptr;
       if (e.aux[slot]) {
-        aux = reinterpret_cast<const __nv_bfloat16*>(e.aux[slot]) + pix * e.aux_C[slot] + e.aux_coff[slot] + ch0;
+        aux = reinterpret_cast<const char*>(e.aux[slot]) + (pix * e.aux_C[slot] + e.aux_coff[slot] + ch0) * elt;
       }
       const size_t drop_elem0 = pix * e.dst_C[slot] + e.dst_coff[slot] + ch0;
       // (a depth-to-space tile wider than Cout starts at ab = 0, ch0 = 0: bias index = column mod Cout)
@@ -289,7 +302,8 @@ igemm_kernel(const __grid_constant__ IgemmParams p, const __grid_constant__ CUte
           const int col = col0 + c;
           const int ab = col / e.d2s_cout;
           const size_t px = (static_cast<size_t>(n) * (2 * p.H) + (2 * h + (ab >> 1))) * (2 * p.W) + (2 * w + (ab & 1));
-          dst = reinterpret_cast<__nv_bfloat16*>(e.dst[0]) + px * e.dst_C[0] + e.dst_coff[0] + (col % e.d2s_cout) - c;
+          dst = reinterpret_cast<char*>(e.dst[0]) +
+                (static_cast<long long>(px * e.dst_C[0] + e.dst_coff[0] + (col % e.d2s_cout)) - c) * elt;
         }
         if (valid) {
           float v[16];
@@ -330,8 +344,18 @@ igemm_kernel(const __grid_constant__ IgemmParams p, const __grid_constant__ CUte
 #pragma unroll
             for (int i = 0; i < 16; ++i) v[i] = ((b >> i) & 1u) ? v[i] * e.mask_scale : 0.0f;
           }
-          if (aux) {
-            const uint4* ap = reinterpret_cast<const uint4*>(aux + c);
+          if (aux && elt == 4) {
+            const float4* ap = reinterpret_cast<const float4*>(aux + c * 4);
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+              const float4 a = __ldg(ap + q);
+              v[4 * q + 0] = a.x > 0.0f ? v[4 * q + 0] * e.mask_scale : 0.0f;
+              v[4 * q + 1] = a.y > 0.0f ? v[4 * q + 1] * e.mask_scale : 0.0f;
+              v[4 * q + 2] = a.z > 0.0f ? v[4 * q + 2] * e.mask_scale : 0.0f;
+              v[4 * q + 3] = a.w > 0.0f ? v[4 * q + 3] * e.mask_scale : 0.0f;
+            }
+          } else if (aux) {
+            const uint4* ap = reinterpret_cast<const uint4*>(aux + c * 2);
 #pragma unroll
             for (int g = 0; g < 2; ++g) {
               const uint4 a = __ldg(ap + g);
@@ -343,9 +367,17 @@ igemm_kernel(const __grid_constant__ IgemmParams p, const __grid_constant__ CUte
               }
             }
           }
-          uint4* dp = reinterpret_cast<uint4*>(dst + c);
+          if (elt == 4) {   // fp32 output, rounded to tf32 for the MMAs that read it next
+            float4* dp4 = reinterpret_cast<float4*>(dst + c * 4);
 #pragma unroll
-          for (int g = 0; g < 2; ++g) {
+            for (int q = 0; q < 4; ++q) {
+              dp4[q] = make_float4(round_tf32(v[4 * q]), round_tf32(v[4 * q + 1]), round_tf32(v[4 * q + 2]),
+                                   round_tf32(v[4 * q + 3]));
+            }
+          }
+          uint4* dp = reinterpret_cast<uint4*>(dst + c * 2);
+#pragma unroll
+          for (int g = 0; g < 2 && elt == 2; ++g) {
             uint4 o;
             o.x = pack_bf16x2(v[8 * g + 0], v[8 * g + 1]);
             o.y = pack_bf16x2(v[8 * g + 2], v[8 * g + 3]);
@@ -377,9 +409,12 @@ int igemm_launch(const IgemmParams& p_in, const CUtensorMap& a0, const CUtensorM
   UB_REQUIRE(p.TN * p.TH * p.TW == 128, "igemm: tile box %dx%dx%d is not 128 pixels", p.TN, p.TH, p.TW);
   UB_REQUIRE(p.block_n == 32 || p.block_n == 64 || p.block_n == 128 || p.block_n == 256,
              "igemm: block_n %d unsupported", p.block_n);
-  UB_REQUIRE(p.kc == 32 || p.kc == 64, "igemm: kc %d unsupported", p.kc);
+  UB_REQUIRE(p.kc == 16 || p.kc == 32 || p.kc == 64, "igemm: kc %d unsupported", p.kc);
   UB_REQUIRE(p.stages >= 2 && p.stages <= kMaxStages, "igemm: stages %d out of range", p.stages);
-  const int stage_bytes = 128 * p.kc * 2 + p.block_n * p.kc * 2;
+  UB_REQUIRE(p.elt == 0 || p.elt == 2 || p.elt == 4, "igemm: element size %d", p.elt);
+  if (p.elt == 0) p.elt = 2;
+  UB_REQUIRE(p.kc * p.elt == 128 || p.kc * p.elt == 64, "igemm: K block of %d bytes (kc %d)", p.kc * p.elt, p.kc);
+  const int stage_bytes = (128 + p.block_n) * p.kc * p.elt;
   const size_t smem = static_cast<size_t>(p.stages) * stage_bytes + sizeof(IgemmBarriers) + 1024;
   UB_REQUIRE(smem <= 227 * 1024, "igemm: %zu bytes of shared memory requested", smem);
   static bool attr_set[64] = {false};
@@ -400,7 +435,7 @@ int igemm_launch(const IgemmParams& p_in, const CUtensorMap& a0, const CUtensorM
     // two destinations must meet at a tile boundary; gate bits are only written for a single plain destination
     const bool split_ok = e.split_col >= p.n_tiles * p.block_n || e.split_col % p.block_n == 0;
     const bool gate_ok = !e.gate_out || (e.d2s_cout == 0 && e.split_col >= p.n_tiles * p.block_n);
-    p.lean = (!no_lean && full && aligned && split_ok && gate_ok && p.block_n >= 32 && !e.aux[0] && !e.aux[1] &&
+    p.lean = (!no_lean && p.elt == 2 && full && aligned && split_ok && gate_ok && p.block_n >= 32 && !e.aux[0] && !e.aux[1] &&
               e.drop_keep >= 1.0f &&
               (e.d2s_cout == 0 || (e.d2s_cout >= 32 && (e.d2s_cout & (e.d2s_cout - 1)) == 0))) ? 1 : 0;
   }
@@ -412,7 +447,7 @@ int igemm_launch(const IgemmParams& p_in, const CUtensorMap& a0, const CUtensorM
                         (p.src_kblocks[0] + (p.num_src > 1 ? p.src_kblocks[1] : 0));
     const double ncols = static_cast<double>(p.n_tiles) * p.block_n;
     prof_begin(UB_KIND_IGEMM, 2.0 * pixels * kdim * ncols,
-               2.0 * pixels * (kdim / (p.taps_r * p.taps_s) + ncols), stream);
+               static_cast<double>(p.elt) * pixels * (kdim / (p.taps_r * p.taps_s) + ncols), stream);
   }
   igemm_kernel<<<grid, kThreads, smem, stream>>>(p, a0, a1, b);
   UB_CHECK_CUDA(cudaGetLastError());
@@ -420,8 +455,8 @@ int igemm_launch(const IgemmParams& p_in, const CUtensorMap& a0, const CUtensorM
   return UB_OK;
 }
 
-int igemm_pick_stages(int block_n, int kc) {
-  const int stage_bytes = 128 * kc * 2 + block_n * kc * 2;
+int igemm_pick_stages(int block_n, int kc, int elt) {
+  const int stage_bytes = (128 + block_n) * kc * elt;
   int s = (200 * 1024) / stage_bytes;
   if (s > kMaxStages) s = kMaxStages;
   if (s < 2) s = 2;

@@ -57,7 +57,8 @@ struct IgemmParams {
   int num_src;
   int src_kblocks[2];               // channel blocks per source
   int src_ci_off[2];                // channel offset of the source inside the packed weight row
-  int kc;                           // 64 (SWIZZLE_128B) or 32 (SWIZZLE_64B)
+  int kc;                           // K block in elements: 128 B (SWIZZLE_128B) or 64 B (SWIZZLE_64B) of elt-byte elements
+  int elt;                          // element bytes of A, B and the outputs: 2 = bf16 (0 means 2), 4 = fp32 as tf32
   int stages;
   int lean;                         // set by igemm_launch: the lean epilogue applies (see igemm.cu)
   IgemmEpilogue epi;
@@ -67,7 +68,7 @@ struct IgemmParams {
 int igemm_launch(const IgemmParams& p, const CUtensorMap& a0, const CUtensorMap& a1, const CUtensorMap& b,
                  cudaStream_t stream);
 
-int igemm_pick_stages(int block_n, int kc);
+int igemm_pick_stages(int block_n, int kc, int elt = 2);
 
 // Philox-based keep decision shared by the conv epilogue and the stand-alone mask generator.
 __host__ __device__ inline void philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t k0,

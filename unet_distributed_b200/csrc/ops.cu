@@ -12,7 +12,6 @@
 
 namespace ub {
 
-int igemm_pick_stages(int block_n, int kc);
 
 namespace {
 
@@ -46,39 +45,43 @@ Box pick_box(int pixels, int H, int W, bool image_aligned = false) {
 
 int cdiv(int a, int b) { return (a + b - 1) / b; }
 
-int pick_kc(int C0, int C1) {
+int pick_kc(int C0, int C1, int elt = 2) {
+  if (elt == 4) return (C0 % 32 == 0 && (C1 == 0 || C1 % 32 == 0)) ? 32 : 0;   // 32 fp32 = one 128-byte swizzle row
   if (C0 % 64 == 0 && (C1 == 0 || C1 % 64 == 0)) return 64;
   if (C0 % 32 == 0 && (C1 == 0 || C1 % 32 == 0)) return 32;
   return 0;
 }
 
-int nhwc_map(CUtensorMap* m, const void* p, int N, int H, int W, int C, int box_c, Box b) {
+int nhwc_map(CUtensorMap* m, const void* p, int N, int H, int W, int C, int box_c, Box b, int elt = 2) {
+  const uint64_t e = static_cast<uint64_t>(elt);
   const uint64_t dims[4] = {static_cast<uint64_t>(C), static_cast<uint64_t>(W), static_cast<uint64_t>(H),
                             static_cast<uint64_t>(N)};
-  const uint64_t str[3] = {static_cast<uint64_t>(C) * 2, static_cast<uint64_t>(W) * C * 2,
-                           static_cast<uint64_t>(H) * W * C * 2};
+  const uint64_t str[3] = {static_cast<uint64_t>(C) * e, static_cast<uint64_t>(W) * C * e,
+                           static_cast<uint64_t>(H) * W * C * e};
   const uint32_t box[4] = {static_cast<uint32_t>(box_c), static_cast<uint32_t>(b.TW), static_cast<uint32_t>(b.TH),
                            static_cast<uint32_t>(b.TN)};
-  return make_tmap_bf16(m, p, 4, dims, str, box, box_c * 2);
+  return make_tmap(m, p, 4, dims, str, box, box_c * elt, elt);
 }
 
 // 5-D view of the fine tensor y[N, 2H, 2W, C] as (c, b, j, a, n*H+i) with y[n, 2i+a, 2j+b, c]; (H, W) = coarse grid.
-int fine_view_map(CUtensorMap* m, const void* p, int N, int H, int W, int C, int box_c, Box b) {
+int fine_view_map(CUtensorMap* m, const void* p, int N, int H, int W, int C, int box_c, Box b, int elt = 2) {
+  const uint64_t e = static_cast<uint64_t>(elt);
   const uint64_t dims[5] = {static_cast<uint64_t>(C), 2, static_cast<uint64_t>(W), 2,
                             static_cast<uint64_t>(N) * H};
-  const uint64_t str[4] = {static_cast<uint64_t>(C) * 2, static_cast<uint64_t>(2) * C * 2,
-                           static_cast<uint64_t>(2) * W * C * 2, static_cast<uint64_t>(4) * W * C * 2};
+  const uint64_t str[4] = {static_cast<uint64_t>(C) * e, static_cast<uint64_t>(2) * C * e,
+                           static_cast<uint64_t>(2) * W * C * e, static_cast<uint64_t>(4) * W * C * e};
   const uint32_t box[5] = {static_cast<uint32_t>(box_c), 1, static_cast<uint32_t>(b.TW), 1,
                            static_cast<uint32_t>(b.TN * b.TH)};
-  return make_tmap_bf16(m, p, 5, dims, str, box, box_c * 2);
+  return make_tmap(m, p, 5, dims, str, box, box_c * elt, elt);
 }
 
 // Packed weights [ncols][taps][ktot] bf16.
-int weight_map(CUtensorMap* m, const void* p, int ncols, int taps, int ktot, int kc, int block_n) {
+int weight_map(CUtensorMap* m, const void* p, int ncols, int taps, int ktot, int kc, int block_n, int elt = 2) {
+  const uint64_t e = static_cast<uint64_t>(elt);
   const uint64_t dims[3] = {static_cast<uint64_t>(ktot), static_cast<uint64_t>(taps), static_cast<uint64_t>(ncols)};
-  const uint64_t str[2] = {static_cast<uint64_t>(ktot) * 2, static_cast<uint64_t>(taps) * ktot * 2};
+  const uint64_t str[2] = {static_cast<uint64_t>(ktot) * e, static_cast<uint64_t>(taps) * ktot * e};
   const uint32_t box[3] = {static_cast<uint32_t>(kc), 1, static_cast<uint32_t>(block_n)};
-  return make_tmap_bf16(m, p, 3, dims, str, box, kc * 2);
+  return make_tmap(m, p, 3, dims, str, box, kc * elt, elt);
 }
 
 void fill_grid(IgemmParams& p, int N, int H, int W, Box b) {
@@ -167,9 +170,10 @@ bool conv3x3_fwd_maxpool_ok(int N, int H, int W, int C0, int C1, int Cout) {
 }
 
 int conv3x3_fwd(ConvSrc x0, ConvSrc x1, const void* w_packed, const float* bias, void* y, int N, int H, int W, int Cout,
-                int relu, DropoutCfg drop, cudaStream_t s, unsigned short* gate_out, void* maxpool_out) {
+                int relu, DropoutCfg drop, cudaStream_t s, unsigned short* gate_out, void* maxpool_out, int dt) {
   const int C1 = x1.ptr ? x1.C : 0;
-  const int kc = pick_kc(x0.C, C1);
+  const int elt = dt_bytes(dt);
+  const int kc = pick_kc(x0.C, C1, elt);
   UB_REQUIRE(kc != 0, "conv3x3_fwd: input channels %d/%d must be multiples of 32", x0.C, C1);
   const int block_n = pick_block_n(Cout);
   UB_REQUIRE(block_n != 0, "conv3x3_fwd: Cout %d must be a multiple of 32", Cout);
@@ -187,7 +191,8 @@ int conv3x3_fwd(ConvSrc x0, ConvSrc x1, const void* w_packed, const float* bias,
   p.src_ci_off[0] = 0;
   p.src_ci_off[1] = x0.C;
   p.kc = kc;
-  p.stages = igemm_pick_stages(block_n, kc);
+  p.elt = elt;
+  p.stages = igemm_pick_stages(block_n, kc, elt);
   p.epi.dst[0] = y; p.epi.dst_C[0] = Cout; p.epi.dst_coff[0] = 0;
   p.epi.split_col = INT_MAX;
   p.epi.bias = bias;
@@ -200,17 +205,18 @@ int conv3x3_fwd(ConvSrc x0, ConvSrc x1, const void* w_packed, const float* bias,
   p.epi.gate_out = gate_out;
   p.epi.maxpool_out = maxpool_out;
   int rc = UB_OK;
-  if (try_halo(p, x0.ptr, x0.C, x1.ptr, C1, w_packed, Cout, x0.C + C1, s, &rc)) return rc;
+  // the halo kernels are bf16 engines; the fp32/tf32 mode runs every conv on the generic implicit-GEMM kernel
+  if (elt == 2 && try_halo(p, x0.ptr, x0.C, x1.ptr, C1, w_packed, Cout, x0.C + C1, s, &rc)) return rc;
   UB_REQUIRE(!maxpool_out, "conv3x3_fwd: fused max pooling is not available for this shape (conv3x3_fwd_maxpool_ok)");
   CUtensorMap a0, a1, bm;
-  rc = nhwc_map(&a0, x0.ptr, N, H, W, x0.C, kc, b);
+  rc = nhwc_map(&a0, x0.ptr, N, H, W, x0.C, kc, b, elt);
   if (rc) return rc;
   a1 = a0;
   if (C1) {
-    rc = nhwc_map(&a1, x1.ptr, N, H, W, C1, kc, b);
+    rc = nhwc_map(&a1, x1.ptr, N, H, W, C1, kc, b, elt);
     if (rc) return rc;
   }
-  rc = weight_map(&bm, w_packed, Cout, 9, x0.C + C1, kc, block_n);
+  rc = weight_map(&bm, w_packed, Cout, 9, x0.C + C1, kc, block_n, elt);
   if (rc) return rc;
   return igemm_launch(p, a0, a1, bm, s);
 }
@@ -228,9 +234,10 @@ bool conv3x3_dgrad_pool2_ok(int N, int H, int W, int Cout, int C0, int C1) {
 }
 
 int conv3x3_dgrad(const void* dz, int Cout, const void* w_packed_d, DgradDst d0, DgradDst d1, int N, int H, int W,
-                  cudaStream_t s) {
+                  cudaStream_t s, int dt) {
   const int C1 = d1.ptr ? d1.C : 0;
-  const int kc = pick_kc(Cout, 0);
+  const int elt = dt_bytes(dt);
+  const int kc = pick_kc(Cout, 0, elt);
   UB_REQUIRE(kc != 0, "conv3x3_dgrad: Cout %d must be a multiple of 32", Cout);
   int block_n = pick_block_n(d0.C);
   if (C1) {
@@ -249,7 +256,8 @@ int conv3x3_dgrad(const void* dz, int Cout, const void* w_packed_d, DgradDst d0,
   p.num_src = 1;
   p.src_kblocks[0] = Cout / kc;
   p.kc = kc;
-  p.stages = igemm_pick_stages(block_n, kc);
+  p.elt = elt;
+  p.stages = igemm_pick_stages(block_n, kc, elt);
   p.epi.dst[0] = d0.ptr; p.epi.dst_C[0] = d0.C; p.epi.aux[0] = d0.gate ? nullptr : d0.mask; p.epi.aux_C[0] = d0.C;
   p.epi.dst[1] = d1.ptr; p.epi.dst_C[1] = C1; p.epi.aux[1] = d1.gate ? nullptr : d1.mask; p.epi.aux_C[1] = C1;
   p.epi.gate_in[0] = d0.gate;
@@ -262,12 +270,12 @@ int conv3x3_dgrad(const void* dz, int Cout, const void* w_packed_d, DgradDst d0,
   if (!(d0.mask || d0.gate) && (d1.mask || d1.gate)) p.epi.mask_scale = d1.scale;
   p.epi.drop_keep = 1.0f;
   int rc = UB_OK;
-  if (try_halo(p, dz, Cout, nullptr, 0, w_packed_d, d0.C + C1, Cout, s, &rc)) return rc;
+  if (elt == 2 && try_halo(p, dz, Cout, nullptr, 0, w_packed_d, d0.C + C1, Cout, s, &rc)) return rc;
   UB_REQUIRE(!d0.pool2, "conv3x3_dgrad: fused 2x2 pooling is not available for this shape (conv3x3_dgrad_pool2_ok)");
   CUtensorMap a0, bm;
-  rc = nhwc_map(&a0, dz, N, H, W, Cout, kc, b);
+  rc = nhwc_map(&a0, dz, N, H, W, Cout, kc, b, elt);
   if (rc) return rc;
-  rc = weight_map(&bm, w_packed_d, d0.C + C1, 9, Cout, kc, block_n);
+  rc = weight_map(&bm, w_packed_d, d0.C + C1, 9, Cout, kc, block_n, elt);
   if (rc) return rc;
   return igemm_launch(p, a0, a0, bm, s);
 }
@@ -280,9 +288,11 @@ struct WgradPlan {
   long long nweights;
 };
 
-int plan_wgrad(WgradPlan& wp, int N, int H, int W, int taps_r, int taps_s, int pad, int z_C, int C0, int C1) {
+int plan_wgrad(WgradPlan& wp, int N, int H, int W, int taps_r, int taps_s, int pad, int z_C, int C0, int C1,
+               int elt = 2) {
   WgradParams& p = wp.p;
   std::memset(&p, 0, sizeof(p));
+  p.elt = elt;
   const Box b = pick_box(64, H, W, taps_r == 2);
   p.N = N; p.H = H; p.W = W;
   p.TN = b.TN; p.TH = b.TH; p.TW = b.TW;
@@ -292,7 +302,7 @@ int plan_wgrad(WgradPlan& wp, int N, int H, int W, int taps_r, int taps_s, int p
   p.taps_r = taps_r; p.taps_s = taps_s; p.pad = pad;
   UB_REQUIRE(z_C % 32 == 0, "wgrad: gradient channels %d must be a multiple of 32", z_C);
   p.z_C = z_C;
-  p.z_atom = (z_C % 64 == 0) ? 64 : 32;
+  p.z_atom = (elt == 2 && z_C % 64 == 0) ? 64 : 32;   // atom = one swizzle row: <= 128 bytes of channels
   p.m_tiles = cdiv(z_C, 128);
   p.num_src = C1 ? 2 : 1;
   const int Cs[2] = {C0, C1};
@@ -301,7 +311,7 @@ int plan_wgrad(WgradPlan& wp, int N, int H, int W, int taps_r, int taps_s, int p
   for (int s = 0; s < p.num_src; ++s) {
     UB_REQUIRE(Cs[s] % 32 == 0, "wgrad: input channels %d must be a multiple of 32", Cs[s]);
     p.x_C[s] = Cs[s];
-    p.x_atom[s] = (Cs[s] % 64 == 0) ? 64 : 32;
+    p.x_atom[s] = (elt == 2 && Cs[s] % 64 == 0) ? 64 : 32;
     p.x_block_n[s] = Cs[s] >= 128 ? 128 : Cs[s];
     UB_REQUIRE(Cs[s] % p.x_block_n[s] == 0, "wgrad: input channels %d not tileable", Cs[s]);
     p.x_ntiles[s] = Cs[s] / p.x_block_n[s];
@@ -318,7 +328,7 @@ int plan_wgrad(WgradPlan& wp, int N, int H, int W, int taps_r, int taps_s, int p
   if (splits < 1) splits = 1;
   const int per = cdiv(total_pb, splits);
   p.splits = cdiv(total_pb, per);
-  p.stages = 6;
+  p.stages = elt == 4 ? 3 : 6;
   wp.nweights = static_cast<long long>(taps_r) * taps_s * (C0 + C1) * z_C;
   return UB_OK;
 }
@@ -354,17 +364,18 @@ size_t conv3x3_wgrad_ws_bytes(int N, int H, int W, int Cin_total, int Cout, bool
 
 // Bias gradient for the wgrad paths that do not produce it themselves.
 static int bias_grad_after(const void* dz, int Cout, float* db, void* ws, size_t ws_bytes, int N, int H, int W,
-                           cudaStream_t s) {
+                           cudaStream_t s, int dt = UB_DT_BF16) {
   const size_t need = static_cast<size_t>(colsum_ws_floats(Cout)) * sizeof(float);
   UB_REQUIRE(ws != nullptr && ws_bytes >= need, "conv3x3_wgrad: workspace of %zu bytes needed for the bias gradient, %zu given",
              need, ws_bytes);
-  return colsum_bf16(dz, db, reinterpret_cast<float*>(ws), static_cast<long long>(N) * H * W, Cout, s);
+  return colsum_act(dz, db, reinterpret_cast<float*>(ws), static_cast<long long>(N) * H * W, Cout, s, dt);
 }
 
 int conv3x3_wgrad(const void* dz, int Cout, ConvSrc x0, ConvSrc x1, float* dw, void* ws, size_t ws_bytes, int N, int H,
-                  int W, cudaStream_t s, float* db) {
+                  int W, cudaStream_t s, float* db, int dt) {
   const int C1 = x1.ptr ? x1.C : 0;
-  if (wgrad_halo_supported(H, W, x0.C, Cout) && (!C1 || wgrad_halo_supported(H, W, C1, Cout))) {
+  const int elt = dt_bytes(dt);   // the halo / row engines are bf16 only; fp32/tf32 goes to the generic per-tap kernel
+  if (elt == 2 && wgrad_halo_supported(H, W, x0.C, Cout) && (!C1 || wgrad_halo_supported(H, W, C1, Cout))) {
     const ConvSrc srcs[2] = {x0, x1};
     int off = 0;
     for (int i = 0; i < (C1 ? 2 : 1); ++i) {
@@ -385,7 +396,7 @@ int conv3x3_wgrad(const void* dz, int Cout, ConvSrc x0, ConvSrc x1, float* dw, v
     }
     return UB_OK;
   }
-  if (wgrad_row_supported(H, W, Cout, x0.C, C1)) {
+  if (elt == 2 && wgrad_row_supported(H, W, Cout, x0.C, C1)) {
     WgradRowParams rp;
     std::memset(&rp, 0, sizeof(rp));
     int rc = wgrad_row_plan(rp, N, H, W, Cout, x0.C, C1);
@@ -428,7 +439,7 @@ int conv3x3_wgrad(const void* dz, int Cout, ConvSrc x0, ConvSrc x1, float* dw, v
     return UB_OK;
   }
   WgradPlan wp;
-  int rc = plan_wgrad(wp, N, H, W, 3, 3, 1, Cout, x0.C, C1);
+  int rc = plan_wgrad(wp, N, H, W, 3, 3, 1, Cout, x0.C, C1, elt);
   if (rc) return rc;
   WgradParams& p = wp.p;
   p.z_mode = 0;
@@ -448,13 +459,13 @@ int conv3x3_wgrad(const void* dz, int Cout, ConvSrc x0, ConvSrc x1, float* dw, v
   }
   const Box b = {p.TN, p.TH, p.TW};
   CUtensorMap zm, xm0, xm1;
-  rc = nhwc_map(&zm, dz, N, H, W, Cout, p.z_atom, b);
+  rc = nhwc_map(&zm, dz, N, H, W, Cout, p.z_atom, b, elt);
   if (rc) return rc;
-  rc = nhwc_map(&xm0, x0.ptr, N, H, W, x0.C, p.x_atom[0], b);
+  rc = nhwc_map(&xm0, x0.ptr, N, H, W, x0.C, p.x_atom[0], b, elt);
   if (rc) return rc;
   xm1 = xm0;
   if (C1) {
-    rc = nhwc_map(&xm1, x1.ptr, N, H, W, C1, p.x_atom[1], b);
+    rc = nhwc_map(&xm1, x1.ptr, N, H, W, C1, p.x_atom[1], b, elt);
     if (rc) return rc;
   }
   rc = wgrad_launch(p, zm, xm0, xm1, s);
@@ -463,13 +474,14 @@ int conv3x3_wgrad(const void* dz, int Cout, ConvSrc x0, ConvSrc x1, float* dw, v
     rc = splitk_reduce_launch(p.out, wp.nweights, p.splits, dw, wp.nweights, s);
     if (rc) return rc;
   }
-  return db ? bias_grad_after(dz, Cout, db, ws, ws_bytes, N, H, W, s) : UB_OK;
+  return db ? bias_grad_after(dz, Cout, db, ws, ws_bytes, N, H, W, s, dt) : UB_OK;
 }
 
 // ------------------------------------------------------------------------------------------------ transposed conv
 int tconv2x2_fwd(const void* x, int Cin, const void* w_packed, const float* bias, void* y, int Cout, int N, int H, int W,
-                 cudaStream_t s) {
-  const int kc = pick_kc(Cin, 0);
+                 cudaStream_t s, int dt) {
+  const int elt = dt_bytes(dt);
+  const int kc = pick_kc(Cin, 0, elt);
   UB_REQUIRE(kc != 0, "tconv2x2_fwd: Cin %d must be a multiple of 32", Cin);
   UB_REQUIRE(Cout % 32 == 0, "tconv2x2_fwd: Cout %d must be a multiple of 32", Cout);
   // GEMM N = 4 * Cout (the four sub-pixels side by side): one tile may span several of them, so the input tile is
@@ -486,7 +498,8 @@ int tconv2x2_fwd(const void* x, int Cin, const void* w_packed, const float* bias
   p.num_src = 1;
   p.src_kblocks[0] = Cin / kc;
   p.kc = kc;
-  p.stages = igemm_pick_stages(block_n, kc);
+  p.elt = elt;
+  p.stages = igemm_pick_stages(block_n, kc, elt);
   p.epi.dst[0] = y; p.epi.dst_C[0] = Cout;
   p.epi.split_col = INT_MAX;
   p.epi.bias = bias;
@@ -494,16 +507,17 @@ int tconv2x2_fwd(const void* x, int Cin, const void* w_packed, const float* bias
   p.epi.d2s_cout = Cout;
   p.epi.drop_keep = 1.0f;
   CUtensorMap a0, bm;
-  int rc = nhwc_map(&a0, x, N, H, W, Cin, kc, b);
+  int rc = nhwc_map(&a0, x, N, H, W, Cin, kc, b, elt);
   if (rc) return rc;
-  rc = weight_map(&bm, w_packed, 4 * Cout, 1, Cin, kc, block_n);
+  rc = weight_map(&bm, w_packed, 4 * Cout, 1, Cin, kc, block_n, elt);
   if (rc) return rc;
   return igemm_launch(p, a0, a0, bm, s);
 }
 
 int tconv2x2_dgrad(const void* dy, int Cout, const void* w_packed_d, void* dx, int Cin, const void* mask, float scale,
-                   int N, int H, int W, cudaStream_t s, const unsigned short* gate) {
-  const int kc = pick_kc(Cout, 0);
+                   int N, int H, int W, cudaStream_t s, const unsigned short* gate, int dt) {
+  const int elt = dt_bytes(dt);
+  const int kc = pick_kc(Cout, 0, elt);
   UB_REQUIRE(kc != 0, "tconv2x2_dgrad: Cout %d must be a multiple of 32", Cout);
   const int block_n = pick_block_n(Cin);
   UB_REQUIRE(block_n != 0, "tconv2x2_dgrad: Cin %d must be a multiple of 32", Cin);
@@ -519,16 +533,17 @@ int tconv2x2_dgrad(const void* dy, int Cout, const void* w_packed_d, void* dx, i
   p.num_src = 1;
   p.src_kblocks[0] = Cout / kc;
   p.kc = kc;
-  p.stages = igemm_pick_stages(block_n, kc);
+  p.elt = elt;
+  p.stages = igemm_pick_stages(block_n, kc, elt);
   p.epi.dst[0] = dx; p.epi.dst_C[0] = Cin; p.epi.aux[0] = gate ? nullptr : mask; p.epi.aux_C[0] = Cin;
   p.epi.gate_in[0] = gate;
   p.epi.split_col = INT_MAX;
   p.epi.mask_scale = scale;
   p.epi.drop_keep = 1.0f;
   CUtensorMap a0, bm;
-  int rc = fine_view_map(&a0, dy, N, H, W, Cout, kc, b);
+  int rc = fine_view_map(&a0, dy, N, H, W, Cout, kc, b, elt);
   if (rc) return rc;
-  rc = weight_map(&bm, w_packed_d, Cin, 4, Cout, kc, block_n);
+  rc = weight_map(&bm, w_packed_d, Cin, 4, Cout, kc, block_n, elt);
   if (rc) return rc;
   return igemm_launch(p, a0, a0, bm, s);
 }
@@ -541,9 +556,10 @@ size_t tconv2x2_wgrad_ws_bytes(int N, int H, int W, int Cin, int Cout) {
 }
 
 int tconv2x2_wgrad(const void* dy, int Cout, const void* x, int Cin, float* dw, void* ws, size_t ws_bytes, int N, int H,
-                   int W, cudaStream_t s) {
+                   int W, cudaStream_t s, int dt) {
+  const int elt = dt_bytes(dt);
   WgradPlan wp;
-  int rc = plan_wgrad(wp, N, H, W, 2, 2, 0, Cout, Cin, 0);
+  int rc = plan_wgrad(wp, N, H, W, 2, 2, 0, Cout, Cin, 0, elt);
   if (rc) return rc;
   WgradParams& p = wp.p;
   UB_REQUIRE(p.TN == 1 || p.TH == H, "tconv2x2_wgrad: %dx%d grid needs an image-aligned block", H, W);
@@ -563,9 +579,9 @@ int tconv2x2_wgrad(const void* dy, int Cout, const void* x, int Cin, float* dw, 
   }
   const Box b = {p.TN, p.TH, p.TW};
   CUtensorMap zm, xm;
-  rc = fine_view_map(&zm, dy, N, H, W, Cout, p.z_atom, b);
+  rc = fine_view_map(&zm, dy, N, H, W, Cout, p.z_atom, b, elt);
   if (rc) return rc;
-  rc = nhwc_map(&xm, x, N, H, W, Cin, p.x_atom[0], b);
+  rc = nhwc_map(&xm, x, N, H, W, Cin, p.x_atom[0], b, elt);
   if (rc) return rc;
   rc = wgrad_launch(p, zm, xm, xm, s);
   if (rc) return rc;

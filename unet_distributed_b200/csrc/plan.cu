@@ -43,6 +43,8 @@ constexpr size_t kNoGate = ~static_cast<size_t>(0);
 
 struct unetb200_plan {
   int N, H, W, Cin, ncl, ups;
+  int dt = UB_DT_BF16;   // element type of activations, gradients and packed operands (UB_DT_TF32: fp32 words)
+  int elt = 2;
   float dropout;
   std::vector<Var> vars;
   std::vector<Layer> layers;
@@ -85,7 +87,8 @@ struct unetb200_plan {
   }
   int Hl(int L) const { return H >> L; }
   int Wl(int L) const { return W >> L; }
-  size_t act_bytes(int L, int C) const { return static_cast<size_t>(N) * Hl(L) * Wl(L) * C * 2; }
+  size_t act_bytes(int L, int C) const { return static_cast<size_t>(N) * Hl(L) * Wl(L) * C * elt; }
+  size_t gate_bytes(int L, int C) const { return static_cast<size_t>(N) * Hl(L) * Wl(L) * C / 8; }   // one bit each
   void* at(size_t off) const { return arena + off; }
   unsigned short* gate(size_t off) const {
     return off == kNoGate ? nullptr : reinterpret_cast<unsigned short*>(arena + off);
@@ -139,7 +142,13 @@ extern "C" {
 
 int unetb200_plan_create(unetb200_plan** out, int N, int H, int W, int in_channels, int n_cl_out, int use_upsampling,
                          float dropout) {
+  return unetb200_plan_create_dt(out, N, H, W, in_channels, n_cl_out, use_upsampling, dropout, UNETB200_BF16);
+}
+
+int unetb200_plan_create_dt(unetb200_plan** out, int N, int H, int W, int in_channels, int n_cl_out,
+                            int use_upsampling, float dropout, int dtype) {
   UB_REQUIRE(out != nullptr, "plan_create: null output");
+  UB_REQUIRE(dtype == UNETB200_BF16 || dtype == UNETB200_TF32, "plan_create: dtype %d is neither BF16 nor TF32", dtype);
   UB_REQUIRE(N >= 1 && H >= 16 && W >= 16 && H % 16 == 0 && W % 16 == 0,
              "plan_create: image %dx%d must be a multiple of 16 (four 2x2 poolings), batch %d >= 1", H, W, N);
   UB_REQUIRE(in_channels >= 1 && in_channels <= 8, "plan_create: in_channels %d outside 1..8", in_channels);
@@ -148,6 +157,8 @@ int unetb200_plan_create(unetb200_plan** out, int N, int H, int W, int in_channe
   unetb200_plan* P = new unetb200_plan();
   P->N = N; P->H = H; P->W = W; P->Cin = in_channels; P->ncl = n_cl_out; P->ups = use_upsampling ? 1 : 0;
   P->dropout = dropout;
+  P->dt = dtype == UNETB200_TF32 ? UB_DT_TF32 : UB_DT_BF16;
+  P->elt = dt_bytes(P->dt);
   for (int L = 0; L < 5; ++L) P->ch[L] = 32 << L;
   const int up = P->ups;
   // ---- variables in creation order (model.py:51-120)
@@ -174,7 +185,7 @@ int unetb200_plan_create(unetb200_plan** out, int N, int H, int W, int in_channe
   // ---- arena: packed weights
   for (auto& l : P->layers) {
     if (l.kind == 2 || l.cin < 32) continue;  // Mask and conv1a run from the fp32 master
-    const size_t bytes = static_cast<size_t>(l.kind == 0 ? 9 : 4) * l.cin * l.cout * 2;
+    const size_t bytes = static_cast<size_t>(l.kind == 0 ? 9 : 4) * l.cin * l.cout * P->elt;
     l.pk_fwd = P->bump(bytes);
     l.pk_dgrad = P->bump(bytes);
   }
@@ -198,23 +209,24 @@ int unetb200_plan_create(unetb200_plan** out, int N, int H, int W, int in_channe
   }
   // ---- arena: ReLU gate bits (1/16 of the activation they describe)
   for (int L = 0; L < 5; ++L) {
-    const bool a_gates = L > 0 || conv_first_fwd_writes_gates(in_channels, 32);
-    P->gt_a[L] = a_gates ? P->bump(P->act_bytes(L, P->ch[L]) / 16) : kNoGate;
+    const bool a_gates = L > 0 || (P->dt == UB_DT_BF16 && conv_first_fwd_writes_gates(in_channels, 32));
+    P->gt_a[L] = a_gates ? P->bump(P->gate_bytes(L, P->ch[L])) : kNoGate;
     const bool c_gates = L < 4 || !up;   // c[4] is masked by the transposed-conv dgrad only
-    P->gt_c[L] = c_gates ? P->bump(P->act_bytes(L, L == 4 ? P->c4_out : P->ch[L]) / 16) : kNoGate;
+    P->gt_c[L] = c_gates ? P->bump(P->gate_bytes(L, L == 4 ? P->c4_out : P->ch[L])) : kNoGate;
   }
   for (int L = 0; L < 4; ++L) {
-    P->gt_da[L] = P->bump(P->act_bytes(L, P->ch[L]) / 16);
-    P->gt_dc[L] = (!up && L > 0) ? P->bump(P->act_bytes(L, P->dc_out[L]) / 16) : kNoGate;
+    P->gt_da[L] = P->bump(P->gate_bytes(L, P->ch[L]));
+    P->gt_dc[L] = (!up && L > 0) ? P->bump(P->gate_bytes(L, P->dc_out[L])) : kNoGate;
   }
   for (int L = 0; L < 4; ++L) {
     // the coarse tensor below level L is c[4] (L == 3) or dc[L+1]; its gates are needed where the pooling is fused
-    P->pool_fused[L] = up && conv3x3_dgrad_pool2_ok(N, P->Hl(L), P->Wl(L), P->ch[L], P->ch[L], P->ch[L]);
+    P->pool_fused[L] = up && P->dt == UB_DT_BF16 &&
+                       conv3x3_dgrad_pool2_ok(N, P->Hl(L), P->Wl(L), P->ch[L], P->ch[L], P->ch[L]);
     if (!P->pool_fused[L]) continue;
     if (L == 3) {
-      if (P->gt_c[4] == kNoGate) P->gt_c[4] = P->bump(P->act_bytes(4, P->c4_out) / 16);
+      if (P->gt_c[4] == kNoGate) P->gt_c[4] = P->bump(P->gate_bytes(4, P->c4_out));
     } else if (P->gt_dc[L + 1] == kNoGate) {
-      P->gt_dc[L + 1] = P->bump(P->act_bytes(L + 1, P->dc_out[L + 1]) / 16);
+      P->gt_dc[L + 1] = P->bump(P->gate_bytes(L + 1, P->dc_out[L + 1]));
     }
   }
   const long long pixels = static_cast<long long>(N) * H * W;
@@ -350,7 +362,7 @@ int unetb200_plan_tensor(const unetb200_plan* P, const char* name, long long* of
     else if (s[0] == 'u') { off = grad ? P->g_u[L] : P->u[L]; C = P->ch[L]; }
     else { UB_REQUIRE(false, "plan_tensor: unknown tensor '%s'", name); }
   }
-  *offset = static_cast<long long>(off); *n = P->N; *h = P->Hl(L); *w = P->Wl(L); *c = C; *elem_bytes = 2;
+  *offset = static_cast<long long>(off); *n = P->N; *h = P->Hl(L); *w = P->Wl(L); *c = C; *elem_bytes = P->elt;
   return UB_OK;
 }
 
@@ -365,7 +377,7 @@ int unetb200_plan_pack_weights(unetb200_plan* P, void* stream) {
   UB_REQUIRE(P->arena, "plan_pack_weights: plan is not bound");
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
   return pack_all(reinterpret_cast<const PackLayer*>(P->at(P->pack_table)), static_cast<int>(P->pack_layers.size()),
-                  P->pack_tiles, P->params, P->arena, s);
+                  P->pack_tiles, P->params, P->arena, s, 0, P->dt);
 }
 
 // Forward pass (model.py:45-120) + dice metrics (model.py:4-21,133-143) when msks != NULL.
@@ -375,24 +387,25 @@ int unetb200_plan_forward(unetb200_plan* P, const float* imgs, const float* msks
   UB_REQUIRE(P->arena, "plan_forward: plan is not bound");
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
   const int N = P->N;
+  const int dt = P->dt;
   const DropoutCfg no_drop{1.0f, 0, 0, nullptr};
   // encoder
   for (int L = 0; L < 5; ++L) {
     const int H = P->Hl(L), W = P->Wl(L);
     const int la = P->enc_a[L], lb = P->enc_b[L];
     if (L == 0) {
-      RC(conv_first_fwd(imgs, P->W_(la), P->B_(la), P->at(P->a[0]), N, H, W, P->Cin, 32, s, P->gate(P->gt_a[0])));
+      RC(conv_first_fwd(imgs, P->W_(la), P->B_(la), P->at(P->a[0]), N, H, W, P->Cin, 32, s, P->gate(P->gt_a[0]), dt));
     } else {
       DropoutCfg d = no_drop;
       if ((L == 2 || L == 3) && P->dropout > 0.0f) d = DropoutCfg{1.0f - P->dropout, seed, static_cast<unsigned>(L), seed_add};
       RC(conv3x3_fwd(ConvSrc{P->at(P->p[L - 1]), P->ch[L - 1]}, ConvSrc{nullptr, 0}, P->pkf(la), P->B_(la),
-                     P->at(P->a[L]), N, H, W, P->ch[L], 1, d, s, P->gate(P->gt_a[L])));
+                     P->at(P->a[L]), N, H, W, P->ch[L], 1, d, s, P->gate(P->gt_a[L]), nullptr, dt));
     }
     // MaxPool2D comes out of conv{L+1}b's epilogue where the row-pair kernel runs (128x128 and 64x64 levels)
-    const bool fused_pool = L < 4 && conv3x3_fwd_maxpool_ok(N, H, W, P->ch[L], 0, P->layers[lb].cout);
+    const bool fused_pool = L < 4 && dt == UB_DT_BF16 && conv3x3_fwd_maxpool_ok(N, H, W, P->ch[L], 0, P->layers[lb].cout);
     RC(conv3x3_fwd(ConvSrc{P->at(P->a[L]), P->ch[L]}, ConvSrc{nullptr, 0}, P->pkf(lb), P->B_(lb), P->at(P->c[L]), N, H,
-                   W, P->layers[lb].cout, 1, no_drop, s, P->gate(P->gt_c[L]), fused_pool ? P->at(P->p[L]) : nullptr));
-    if (L < 4 && !fused_pool) RC(maxpool2x2_fwd(P->at(P->c[L]), P->at(P->p[L]), N, H, W, P->ch[L], s));
+                   W, P->layers[lb].cout, 1, no_drop, s, P->gate(P->gt_c[L]), fused_pool ? P->at(P->p[L]) : nullptr, dt));
+    if (L < 4 && !fused_pool) RC(maxpool2x2_fwd(P->at(P->c[L]), P->at(P->p[L]), N, H, W, P->ch[L], s, dt));
   }
   // decoder
   for (int L = 3; L >= 0; --L) {
@@ -400,16 +413,16 @@ int unetb200_plan_forward(unetb200_plan* P, const float* imgs, const float* msks
     const size_t below = (L == 3) ? P->c[4] : P->dc[L + 1];
     const int below_C = (L == 3) ? P->c4_out : P->dc_out[L + 1];
     if (P->ups) {
-      RC(upsample2x2_fwd(P->at(below), P->at(P->u[L]), N, H / 2, W / 2, below_C, s));
+      RC(upsample2x2_fwd(P->at(below), P->at(P->u[L]), N, H / 2, W / 2, below_C, s, dt));
     } else {
       const int lt = P->tc[L];
-      RC(tconv2x2_fwd(P->at(below), below_C, P->pkf(lt), P->B_(lt), P->at(P->u[L]), P->ch[L], N, H / 2, W / 2, s));
+      RC(tconv2x2_fwd(P->at(below), below_C, P->pkf(lt), P->B_(lt), P->at(P->u[L]), P->ch[L], N, H / 2, W / 2, s, dt));
     }
     const int la = P->dec_a[L], lb = P->dec_b[L];
     RC(conv3x3_fwd(ConvSrc{P->at(P->u[L]), P->ch[L]}, ConvSrc{P->at(P->c[L]), P->ch[L]}, P->pkf(la), P->B_(la),
-                   P->at(P->da[L]), N, H, W, P->ch[L], 1, no_drop, s, P->gate(P->gt_da[L])));
+                   P->at(P->da[L]), N, H, W, P->ch[L], 1, no_drop, s, P->gate(P->gt_da[L]), nullptr, dt));
     RC(conv3x3_fwd(ConvSrc{P->at(P->da[L]), P->ch[L]}, ConvSrc{nullptr, 0}, P->pkf(lb), P->B_(lb), P->at(P->dc[L]), N, H,
-                   W, P->dc_out[L], 1, no_drop, s, P->gate(P->gt_dc[L])));
+                   W, P->dc_out[L], 1, no_drop, s, P->gate(P->gt_dc[L]), nullptr, dt));
   }
   // head
   const long long pixels = static_cast<long long>(N) * P->H * P->W;
@@ -417,12 +430,12 @@ int unetb200_plan_forward(unetb200_plan* P, const float* imgs, const float* msks
   float* sums = reinterpret_cast<float*>(P->at(P->sums));
   if (msks) {
     RC(head_fwd(P->at(P->dc[0]), P->W_(P->mask), P->B_(P->mask), msks, preds, sums,
-                reinterpret_cast<float*>(P->at(P->ws)), pixels, 32, P->ncl, s));
+                reinterpret_cast<float*>(P->at(P->ws)), pixels, 32, P->ncl, s, dt));
     RC(dice_finalize(sums, 1.0f, reinterpret_cast<float*>(P->at(P->metrics)), s));
   } else {
     // inference: no labels, the dice sums degenerate to {0, 0, sum p}
     RC(head_fwd(P->at(P->dc[0]), P->W_(P->mask), P->B_(P->mask), nullptr, preds, sums,
-                reinterpret_cast<float*>(P->at(P->ws)), pixels, 32, P->ncl, s));
+                reinterpret_cast<float*>(P->at(P->ws)), pixels, 32, P->ncl, s, dt));
   }
   return UB_OK;
 }
@@ -441,6 +454,7 @@ int unetb200_plan_backward(unetb200_plan* P, const float* imgs, const float* msk
   UB_REQUIRE(segment >= 0 && segment < kSegments, "plan_backward: segment %d outside 0..%d", segment, kSegments - 1);
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
   const int N = P->N;
+  const int dt = P->dt;
   float* ws = reinterpret_cast<float*>(P->at(P->ws));              // main stream: head
   float* wss = reinterpret_cast<float*>(P->at(P->ws_side));         // weight-gradient stream
   void* wsv = P->at(P->ws_side);
@@ -473,7 +487,7 @@ int unetb200_plan_backward(unetb200_plan* P, const float* imgs, const float* msk
     UB_REQUIRE(msks || dpreds, "plan_backward: need the labels or an explicit dL/dpreds");
     RC(head_bwd(P->at(P->dc[0]), P->W_(P->mask), dpreds ? dpreds : msks, reinterpret_cast<const float*>(P->at(P->preds)),
                 dpreds ? nullptr : reinterpret_cast<const float*>(P->at(P->sums)), 1.0f, grad_scale, P->at(P->g_dc[0]), P->dW_(P->mask),
-                P->dB_(P->mask), ws, pixels, 32, P->ncl, s));
+                P->dB_(P->mask), ws, pixels, 32, P->ncl, s, dt));
     }
     for (int L = 2 * segment; L < 2 * segment + 2; ++L) {
       const int H = P->Hl(L), W = P->Wl(L);
@@ -483,16 +497,16 @@ int unetb200_plan_backward(unetb200_plan* P, const float* imgs, const float* msk
       RC(fork());
       RC(fork());
     RC(conv3x3_wgrad(P->at(P->g_dc[L]), P->dc_out[L], ConvSrc{P->at(P->da[L]), P->ch[L]}, ConvSrc{nullptr, 0},
-                       P->dW_(lb), wsv, wsb, N, H, W, w, P->dB_(lb)));
+                       P->dW_(lb), wsv, wsb, N, H, W, w, P->dB_(lb), dt));
       RC(conv3x3_dgrad(P->at(P->g_dc[L]), P->dc_out[L], P->pkd(lb),
                        DgradDst{P->at(P->g_da[L]), P->ch[L], P->at(P->da[L]), 1.0f, P->gate(P->gt_da[L])},
                        DgradDst{nullptr, 0, nullptr, 1.0f},
-                       N, H, W, s));
+                       N, H, W, s, dt));
       // conv{9-L}a over [u, skip]
       RC(fork());
       RC(fork());
     RC(conv3x3_wgrad(P->at(P->g_da[L]), P->ch[L], ConvSrc{P->at(P->u[L]), P->ch[L]}, ConvSrc{P->at(P->c[L]), P->ch[L]},
-                       P->dW_(la), wsv, wsb, N, H, W, w, P->dB_(la)));
+                       P->dW_(la), wsv, wsb, N, H, W, w, P->dB_(la), dt));
       // up path
       const size_t below = (L == 3) ? P->c[4] : P->dc[L + 1];
       const size_t g_below = (L == 3) ? P->g_c[4] : P->g_dc[L + 1];
@@ -502,18 +516,18 @@ int unetb200_plan_backward(unetb200_plan* P, const float* imgs, const float* msk
         d_up = DgradDst{P->at(g_below), P->ch[L], nullptr, 1.0f, P->gate(L == 3 ? P->gt_c[4] : P->gt_dc[L + 1]), 1};
       }
       RC(conv3x3_dgrad(P->at(P->g_da[L]), P->ch[L], P->pkd(la), d_up,
-                       DgradDst{P->at(P->g_c[L]), P->ch[L], P->at(P->c[L]), 1.0f, P->gate(P->gt_c[L])}, N, H, W, s));
+                       DgradDst{P->at(P->g_c[L]), P->ch[L], P->at(P->c[L]), 1.0f, P->gate(P->gt_c[L])}, N, H, W, s, dt));
       if (P->pool_fused[L]) {
         // g_below is complete
       } else if (P->ups) {
-        RC(upsample2x2_bwd(P->at(P->g_u[L]), P->at(below), P->at(g_below), N, H / 2, W / 2, below_C, 1, s));
+        RC(upsample2x2_bwd(P->at(P->g_u[L]), P->at(below), P->at(g_below), N, H / 2, W / 2, below_C, 1, s, dt));
       } else {
         const int lt = P->tc[L];
         RC(fork());
-        RC(tconv2x2_wgrad(P->at(P->g_u[L]), P->ch[L], P->at(below), below_C, P->dW_(lt), wsv, wsb, N, H / 2, W / 2, w));
-        RC(colsum_bf16(P->at(P->g_u[L]), P->dB_(lt), wss, px, P->ch[L], w));
+        RC(tconv2x2_wgrad(P->at(P->g_u[L]), P->ch[L], P->at(below), below_C, P->dW_(lt), wsv, wsb, N, H / 2, W / 2, w, dt));
+        RC(colsum_act(P->at(P->g_u[L]), P->dB_(lt), wss, px, P->ch[L], w, dt));
         RC(tconv2x2_dgrad(P->at(P->g_u[L]), P->ch[L], P->pkd(lt), P->at(g_below), below_C, P->at(below), 1.0f, N, H / 2,
-                          W / 2, s, P->gate(L == 3 ? P->gt_c[4] : P->gt_dc[L + 1])));
+                          W / 2, s, P->gate(L == 3 ? P->gt_c[4] : P->gt_dc[L + 1]), dt));
       }
     }
     RC(join());
@@ -526,14 +540,14 @@ int unetb200_plan_backward(unetb200_plan* P, const float* imgs, const float* msk
     const int la = P->enc_a[L], lb = P->enc_b[L];
     RC(fork());
     RC(conv3x3_wgrad(P->at(P->g_c[L]), P->c4_out, ConvSrc{P->at(P->a[L]), P->ch[L]}, ConvSrc{nullptr, 0}, P->dW_(lb), wsv,
-                     wsb, N, H, W, w, P->dB_(lb)));
+                     wsb, N, H, W, w, P->dB_(lb), dt));
     RC(conv3x3_dgrad(P->at(P->g_c[L]), P->c4_out, P->pkd(lb), DgradDst{P->at(P->g_a[L]), P->ch[L], P->at(P->a[L]), 1.0f, P->gate(P->gt_a[L])},
-                     DgradDst{nullptr, 0, nullptr, 1.0f}, N, H, W, s));
+                     DgradDst{nullptr, 0, nullptr, 1.0f}, N, H, W, s, dt));
     RC(fork());
     RC(conv3x3_wgrad(P->at(P->g_a[L]), P->ch[L], ConvSrc{P->at(P->p[L - 1]), P->ch[L - 1]}, ConvSrc{nullptr, 0},
-                     P->dW_(la), wsv, wsb, N, H, W, w, P->dB_(la)));
+                     P->dW_(la), wsv, wsb, N, H, W, w, P->dB_(la), dt));
     RC(conv3x3_dgrad(P->at(P->g_a[L]), P->ch[L], P->pkd(la), DgradDst{P->at(P->g_p[L - 1]), P->ch[L - 1], nullptr, 1.0f},
-                     DgradDst{nullptr, 0, nullptr, 1.0f}, N, H, W, s));
+                     DgradDst{nullptr, 0, nullptr, 1.0f}, N, H, W, s, dt));
     RC(join());
     return UB_OK;
   }
@@ -542,24 +556,24 @@ int unetb200_plan_backward(unetb200_plan* P, const float* imgs, const float* msk
     const int H = P->Hl(L), W = P->Wl(L);
     const int la = P->enc_a[L], lb = P->enc_b[L];
     // MaxPoolGrad + skip gradient + ReluGrad of conv{L+1}b, in place in g_c[L]
-    RC(maxpool2x2_bwd(P->at(P->c[L]), P->at(P->g_p[L]), P->at(P->g_c[L]), P->at(P->g_c[L]), N, H, W, P->ch[L], s));
+    RC(maxpool2x2_bwd(P->at(P->c[L]), P->at(P->g_p[L]), P->at(P->g_c[L]), P->at(P->g_c[L]), N, H, W, P->ch[L], s, dt));
     RC(fork());
     RC(conv3x3_wgrad(P->at(P->g_c[L]), P->ch[L], ConvSrc{P->at(P->a[L]), P->ch[L]}, ConvSrc{nullptr, 0}, P->dW_(lb), wsv,
-                     wsb, N, H, W, w, P->dB_(lb)));
+                     wsb, N, H, W, w, P->dB_(lb), dt));
     const bool dropped = (L == 2 || L == 3) && P->dropout > 0.0f;
     RC(conv3x3_dgrad(P->at(P->g_c[L]), P->ch[L], P->pkd(lb),
                      DgradDst{P->at(P->g_a[L]), P->ch[L], P->at(P->a[L]), dropped ? inv_keep : 1.0f, P->gate(P->gt_a[L])},
-                     DgradDst{nullptr, 0, nullptr, 1.0f}, N, H, W, s));
+                     DgradDst{nullptr, 0, nullptr, 1.0f}, N, H, W, s, dt));
     if (L > 0) {
       RC(fork());
       RC(fork());
     RC(conv3x3_wgrad(P->at(P->g_a[L]), P->ch[L], ConvSrc{P->at(P->p[L - 1]), P->ch[L - 1]}, ConvSrc{nullptr, 0},
-                       P->dW_(la), wsv, wsb, N, H, W, w, P->dB_(la)));
+                       P->dW_(la), wsv, wsb, N, H, W, w, P->dB_(la), dt));
       RC(conv3x3_dgrad(P->at(P->g_a[L]), P->ch[L], P->pkd(la),
                        DgradDst{P->at(P->g_p[L - 1]), P->ch[L - 1], nullptr, 1.0f}, DgradDst{nullptr, 0, nullptr, 1.0f},
-                       N, H, W, s));
+                       N, H, W, s, dt));
     } else {
-      RC(conv_first_wgrad(imgs, P->at(P->g_a[0]), P->dW_(la), P->dB_(la), ws, N, H, W, P->Cin, 32, s));
+      RC(conv_first_wgrad(imgs, P->at(P->g_a[0]), P->dW_(la), P->dB_(la), ws, N, H, W, P->Cin, 32, s, dt));
     }
   }
   RC(join());
@@ -603,7 +617,7 @@ int unetb200_plan_pack_range(unetb200_plan* P, long long begin, long long end, v
   const int tile0 = P->pack_layers[first].tile_start;
   const int tile1 = last + 1 < static_cast<int>(P->pack_layers.size()) ? P->pack_layers[last + 1].tile_start : P->pack_tiles;
   return pack_all(reinterpret_cast<const PackLayer*>(P->at(P->pack_table)) + first, last - first + 1, tile1 - tile0,
-                  P->params, P->arena, s, tile0);
+                  P->params, P->arena, s, tile0, P->dt);
 }
 
 }  // extern "C"

@@ -10,8 +10,8 @@ namespace {
 constexpr int kThreads = 192;
 constexpr int kMaxStages = 6;
 constexpr int kKP = 64;                    // pixels per K block
-constexpr int kOperandBytes = 16 * 1024;   // smem reserved per operand per stage (128 channels x 64 pixels bf16)
-constexpr int kStageBytes = 2 * kOperandBytes;
+// smem reserved per operand per stage: 128 channels x 64 pixels of elt-byte elements (16 KB bf16, 32 KB fp32/tf32)
+__host__ __device__ constexpr int operand_bytes(int elt) { return 128 * kKP * elt; }
 
 struct __align__(8) WgradBarriers {
   uint64_t full[kMaxStages];
@@ -26,6 +26,9 @@ wgrad_kernel(const __grid_constant__ WgradParams p, const __grid_constant__ CUte
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw_addr = smem_u32(smem_raw);
   uint8_t* smem = smem_raw + ((1024u - (raw_addr & 1023u)) & 1023u);
+  const int elt = p.elt == 4 ? 4 : 2;
+  const int kOperandBytes = operand_bytes(elt);
+  const int kStageBytes = 2 * kOperandBytes;
   WgradBarriers* bars = reinterpret_cast<WgradBarriers*>(smem + p.stages * kStageBytes);
 
   const int warp = threadIdx.x >> 5;
@@ -58,8 +61,8 @@ wgrad_kernel(const __grid_constant__ WgradParams p, const __grid_constant__ CUte
   int m_atoms = (p.z_C - m0 + p.z_atom - 1) / p.z_atom;
   if (m_atoms > 128 / p.z_atom) m_atoms = 128 / p.z_atom;
   const int n_atoms = block_n / x_atom;
-  const uint32_t z_atom_bytes = static_cast<uint32_t>(kKP * p.z_atom * 2);
-  const uint32_t x_atom_bytes = static_cast<uint32_t>(kKP * x_atom * 2);
+  const uint32_t z_atom_bytes = static_cast<uint32_t>(kKP * p.z_atom * elt);
+  const uint32_t x_atom_bytes = static_cast<uint32_t>(kKP * x_atom * elt);
   const uint32_t tmem_cols = block_n < 32 ? 32u : static_cast<uint32_t>(block_n);
 
   if (threadIdx.x == 0) {
@@ -117,13 +120,15 @@ wgrad_kernel(const __grid_constant__ WgradParams p, const __grid_constant__ CUte
   } else if (warp == 1) {
     if (nkb > 0) {
       // warp-uniform control flow, one elected lane issues
-      const uint32_t idesc = umma_idesc_bf16(128, static_cast<uint32_t>(block_n), 1, 1);
-      const uint32_t z_sw = p.z_atom == 64 ? UMMA_SW_128B : UMMA_SW_64B;
-      const uint32_t x_sw = x_atom == 64 ? UMMA_SW_128B : UMMA_SW_64B;
-      const uint32_t z_sbo = static_cast<uint32_t>(8 * p.z_atom * 2);
-      const uint32_t x_sbo = static_cast<uint32_t>(8 * x_atom * 2);
-      const uint32_t z_kstep = static_cast<uint32_t>(16 * p.z_atom * 2) >> 4;  // 16 pixels, in 16-byte units
-      const uint32_t x_kstep = static_cast<uint32_t>(16 * x_atom * 2) >> 4;
+      const uint32_t idesc = elt == 4 ? umma_idesc_tf32(128, static_cast<uint32_t>(block_n), 1, 1)
+                                      : umma_idesc_bf16(128, static_cast<uint32_t>(block_n), 1, 1);
+      const int kmma = 32 / elt;   // pixels (GEMM K) per instruction: 16 bf16 or 8 tf32
+      const uint32_t z_sw = p.z_atom * elt == 128 ? UMMA_SW_128B : UMMA_SW_64B;
+      const uint32_t x_sw = x_atom * elt == 128 ? UMMA_SW_128B : UMMA_SW_64B;
+      const uint32_t z_sbo = static_cast<uint32_t>(8 * p.z_atom * elt);
+      const uint32_t x_sbo = static_cast<uint32_t>(8 * x_atom * elt);
+      const uint32_t z_kstep = static_cast<uint32_t>(kmma * p.z_atom * elt) >> 4;  // kmma pixels, in 16-byte units
+      const uint32_t x_kstep = static_cast<uint32_t>(kmma * x_atom * elt) >> 4;
       const uint64_t a_hi = umma_smem_desc(0, z_atom_bytes, z_sbo, z_sw);
       const uint64_t b_hi = umma_smem_desc(0, x_atom_bytes, x_sbo, x_sw);
       int stage = 0;
@@ -135,10 +140,18 @@ wgrad_kernel(const __grid_constant__ WgradParams p, const __grid_constant__ CUte
         const uint64_t adesc = a_hi + (sa >> 4);
         const uint64_t bdesc = b_hi + ((sa + kOperandBytes) >> 4);
         if (elect_one()) {
+          if (elt == 4) {
+#pragma unroll
+            for (int k = 0; k < kKP / 8; ++k) {
+              umma_tf32(tmem_base, adesc + static_cast<uint64_t>(k * z_kstep),
+                        bdesc + static_cast<uint64_t>(k * x_kstep), idesc, (kb | k) ? 1u : 0u);
+            }
+          } else {
 #pragma unroll
           for (int k = 0; k < kKP / 16; ++k) {
             umma_f16(tmem_base, adesc + static_cast<uint64_t>(k * z_kstep), bdesc + static_cast<uint64_t>(k * x_kstep),
                      idesc, (kb | k) ? 1u : 0u);
+          }
           }
           umma_commit(&bars->empty[stage]);
           if (kb == nkb - 1) umma_commit(&bars->tmem_full);
@@ -208,15 +221,17 @@ int wgrad_launch(const WgradParams& p, const CUtensorMap& z, const CUtensorMap& 
                  cudaStream_t stream) {
   UB_REQUIRE(p.TN * p.TH * p.TW == kKP, "wgrad: pixel box %dx%dx%d is not %d pixels", p.TN, p.TH, p.TW, kKP);
   UB_REQUIRE(p.stages >= 2 && p.stages <= kMaxStages, "wgrad: stages %d out of range", p.stages);
-  UB_REQUIRE(p.z_atom == 64 || p.z_atom == 32, "wgrad: z_atom %d", p.z_atom);
+  const int elt = p.elt == 4 ? 4 : 2;
+  UB_REQUIRE(p.z_atom * elt == 128 || p.z_atom * elt == 64, "wgrad: z_atom %d x %d bytes", p.z_atom, elt);
   for (int s = 0; s < p.num_src; ++s) {
-    UB_REQUIRE(p.x_atom[s] == 64 || p.x_atom[s] == 32, "wgrad: x_atom %d", p.x_atom[s]);
+    UB_REQUIRE(p.x_atom[s] * elt == 128 || p.x_atom[s] * elt == 64, "wgrad: x_atom %d x %d bytes", p.x_atom[s], elt);
     UB_REQUIRE(p.x_block_n[s] >= 32 && p.x_block_n[s] <= 128 && p.x_block_n[s] % 16 == 0, "wgrad: block_n %d",
                p.x_block_n[s]);
   }
   const int total_pb = p.blocks_n * p.blocks_h * p.blocks_w;
   UB_REQUIRE(p.splits >= 1 && p.splits <= total_pb, "wgrad: splits %d vs %d pixel blocks", p.splits, total_pb);
-  const size_t smem = static_cast<size_t>(p.stages) * kStageBytes + sizeof(WgradBarriers) + 1024;
+  const size_t smem = static_cast<size_t>(p.stages) * 2 * operand_bytes(elt) + sizeof(WgradBarriers) + 1024;
+  UB_REQUIRE(smem <= 227 * 1024, "wgrad: %zu bytes of shared memory requested", smem);
   static bool attr_set[64] = {false};
   int dev = 0;
   UB_CHECK_CUDA(cudaGetDevice(&dev));
@@ -230,7 +245,8 @@ int wgrad_launch(const WgradParams& p, const CUtensorMap& z, const CUtensorMap& 
   if (profiling_enabled()) {
     const double pixels = static_cast<double>(p.N) * p.H * p.W;
     const double cin = static_cast<double>(p.x_C[0]) + (p.num_src > 1 ? p.x_C[1] : 0);
-    prof_begin(UB_KIND_WGRAD, 2.0 * pixels * p.taps_r * p.taps_s * cin * p.z_C, 2.0 * pixels * (cin + p.z_C), stream);
+    prof_begin(UB_KIND_WGRAD, 2.0 * pixels * p.taps_r * p.taps_s * cin * p.z_C,
+               static_cast<double>(elt) * pixels * (cin + p.z_C), stream);
   }
   wgrad_kernel<<<static_cast<unsigned>(grid), kThreads, smem, stream>>>(p, z, x0, x1);
   UB_CHECK_CUDA(cudaGetLastError());

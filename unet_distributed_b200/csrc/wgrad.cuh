@@ -29,6 +29,7 @@ struct WgradParams {
   int x_ntiles[2];
   int x_col_off[2];         // column offset of the source in the output (channel offset in the concat)
   int stages;
+  int elt;                  // element bytes of dZ and X: 2 = bf16 (0 means 2), 4 = fp32 read as tf32 (atoms of 32 channels)
   float* out;
   long long out_split_stride, out_tap_stride, out_m_stride, out_n_stride;
 };

@@ -19,13 +19,24 @@ def _stream():
     return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
 
 
-def describe_plan(N, H, W, in_channels=1, n_cl_out=1, use_upsampling=False, dropout=0.2):
+PRECISIONS = {"bf16": _lib.BF16, "tf32": _lib.TF32, "fp32": _lib.TF32}   # "fp32" = the fp32/tf32 mode
+
+
+def _dtype_code(precision):
+    try:
+        return PRECISIONS[str(precision).lower()]
+    except KeyError:
+        raise ValueError(f"precision must be one of {sorted(PRECISIONS)}, got {precision!r}") from None
+
+
+def describe_plan(N, H, W, in_channels=1, n_cl_out=1, use_upsampling=False, dropout=0.2, precision="bf16"):
     """Host-only description of a plan (no GPU needed): variable table (TF names -> (offset, shape)), padded flat
     size, arena bytes and the gradient buckets (one per backward segment).  This is the native planner's own answer, not a Python copy."""
     L = _lib.lib()
     h = ctypes.c_void_p()
-    _lib.check(L.unetb200_plan_create(ctypes.byref(h), int(N), int(H), int(W), int(in_channels), int(n_cl_out),
-                                      int(bool(use_upsampling)), float(dropout)), "unetb200_plan_create")
+    _lib.check(L.unetb200_plan_create_dt(ctypes.byref(h), int(N), int(H), int(W), int(in_channels), int(n_cl_out),
+                                         int(bool(use_upsampling)), float(dropout), _dtype_code(precision)),
+               "unetb200_plan_create_dt")
     try:
         variables = OrderedDict()
         name = ctypes.create_string_buffer(64)
@@ -48,19 +59,26 @@ def describe_plan(N, H, W, in_channels=1, n_cl_out=1, use_upsampling=False, drop
 
 
 class UNetPlan:
-    """One UNet instance for a fixed (N, H, W, in_channels) input shape on the current CUDA device."""
+    """One UNet instance for a fixed (N, H, W, in_channels) input shape on the current CUDA device.
 
-    def __init__(self, N, H, W, in_channels=1, n_cl_out=1, use_upsampling=False, dropout=0.2, device=None):
+    precision: "bf16" (default: bf16 activations and GEMM operands, fp32 accumulation) or "tf32" / "fp32" (the
+    reference's precision class, test_dist.py:196-202: fp32 activations rounded to tf32, kind::tf32 tensor-core MMAs,
+    fp32 accumulation and fp32 bandwidth kernels; arena tensors are then float32)."""
+
+    def __init__(self, N, H, W, in_channels=1, n_cl_out=1, use_upsampling=False, dropout=0.2, device=None,
+                 precision="bf16"):
         if not torch.cuda.is_available():
             raise _lib.UnetB200Error("UNetPlan needs a CUDA device (sm_100a); there is no CPU path")
         self.device = torch.device(device if device is not None else f"cuda:{torch.cuda.current_device()}")
         self.N, self.H, self.W = int(N), int(H), int(W)
         self.in_channels, self.n_cl_out = int(in_channels), int(n_cl_out)
         self.use_upsampling, self.dropout = bool(use_upsampling), float(dropout)
+        self.precision = "tf32" if _dtype_code(precision) == _lib.TF32 else "bf16"
         L = _lib.lib()
         h = ctypes.c_void_p()
-        _lib.check(L.unetb200_plan_create(ctypes.byref(h), self.N, self.H, self.W, self.in_channels, self.n_cl_out,
-                                          int(self.use_upsampling), self.dropout), "unetb200_plan_create")
+        _lib.check(L.unetb200_plan_create_dt(ctypes.byref(h), self.N, self.H, self.W, self.in_channels, self.n_cl_out,
+                                             int(self.use_upsampling), self.dropout, _dtype_code(precision)),
+                   "unetb200_plan_create_dt")
         self._h = h
         self.num_params_padded = int(L.unetb200_plan_num_params(h))
         self.variables = OrderedDict()

@@ -49,6 +49,8 @@ def build_parser():
     p.add_argument("--data_path", type=str, default=None, help="directory with imgs_/msks_{train,test}.npy")
     p.add_argument("--max_steps", type=int, default=0, help="stop early after this many steps (0 = all)")
     p.add_argument("--optimizer", type=str, default="adam", choices=["adam", "sgd"])
+    p.add_argument("--precision", type=str, default="bf16", choices=["bf16", "tf32", "fp32"],
+                   help="bf16 (default) or the fp32/tf32 mode: fp32 activations, tf32 tensor-core MMAs")
     p.add_argument("--resident_data", type=_bool, default=False,
                    help="keep the training set on the GPU and gather batches there (no host copies in the step loop)")
     p.add_argument("--checkpoint_dir", type=str, default=settings_dist.CHECKPOINT_DIRECTORY)
@@ -94,7 +96,8 @@ def main(argv=None):
     _, H, W, C = imgs_train.shape
     trainer = Trainer(end - start, H, W, C, msks_train.shape[3], FLAGS.use_upsampling,
                       learning_rate=FLAGS.learning_rate, const_learningrate=FLAGS.const_learningrate,
-                      lr_fraction=FLAGS.lr_fraction, decay_steps=FLAGS.decay_steps, optimizer=FLAGS.optimizer)
+                      lr_fraction=FLAGS.lr_fraction, decay_steps=FLAGS.decay_steps, optimizer=FLAGS.optimizer,
+                      precision=FLAGS.precision)
     if FLAGS.resume:
         path = checkpoint.latest(FLAGS.checkpoint_dir)
         if path is None:

@@ -18,14 +18,14 @@ class Trainer:
 
     Flags follow test_dist.py:64-85 / settings_dist.py:17-22: learning_rate, const_learningrate, lr_fraction,
     decay_steps, use_upsampling.  `optimizer` may be "adam" (the reference, test_dist.py:246) or "sgd" (the
-    commented alternative, test_dist.py:239-244)."""
+    commented alternative, test_dist.py:239-244).  `precision`: "bf16" or "tf32" / "fp32" (see UNetPlan)."""
 
     def __init__(self, N, H=128, W=128, in_channels=1, n_cl_out=1, use_upsampling=False, dropout=0.2,
                  learning_rate=0.0005, const_learningrate=True, lr_fraction=0.2, decay_steps=100, optimizer="adam",
                  beta1=0.9, beta2=0.999, epsilon=1e-8, weight_seed=1234, dropout_seed=816, weights=None,
-                 use_cuda_graph=False, shared_dropout_masks=False):
+                 use_cuda_graph=False, shared_dropout_masks=False, precision="bf16"):
         self.world, self.rank = parallel.world()
-        self.plan = UNetPlan(N, H, W, in_channels, n_cl_out, use_upsampling, dropout)
+        self.plan = UNetPlan(N, H, W, in_channels, n_cl_out, use_upsampling, dropout, precision=precision)
         p = self.plan
         dev = p.device
         self.m = torch.zeros_like(p.params)
