@@ -772,6 +772,19 @@ int conv_first_fwd(const float* x, const float* w, const float* bias, void* y, i
   UB_REQUIRE(gate_out == nullptr || (y32 && W % 2 == 0),
              "conv_first_fwd: gate bits need a 32-byte aligned output tensor and an even width");
   UB_REQUIRE(dt == UB_DT_BF16 || gate_out == nullptr, "conv_first_fwd: gate bits are a bf16-mode feature");
+  static const bool no_strip = getenv("UNETB200_NO_CONV1A_STRIP") != nullptr;
+  if (dt == UB_DT_BF16 && !no_strip && Cin == 1 && Cout == 32 && W % 4 == 0 &&
+      reinterpret_cast<uintptr_t>(y) % 16 == 0 && reinterpret_cast<uintptr_t>(w) % 16 == 0) {
+    // register-weight strip kernel (level0.cuh): one resident wave of 128-thread blocks, grid-stride over strips
+    const unsigned n_strips = static_cast<unsigned>(static_cast<long long>(N) * H * (W / 4));
+    unsigned blocks = grid_for(static_cast<long long>(n_strips) * 4, 128);
+    const unsigned cap = 12u * static_cast<unsigned>(device_sm_count());
+    if (blocks > cap) blocks = cap;
+    conv_first32_cin1_fwd_kernel<<<blocks, 128, 0, s>>>(x, w, bias, reinterpret_cast<uint4*>(y),
+                                                        reinterpret_cast<unsigned int*>(gate_out), H, W, n_strips);
+    UB_CHECK_CUDA(cudaGetLastError());
+    return UB_OK;
+  }
   if (dt == UB_DT_BF16 && y32 && W % 2 == 0 && Cout == 32 && (Cin == 1 || Cin == 4)) {   // two-pixels-per-thread fast path (the network's conv1a)
     const unsigned P = static_cast<unsigned>(static_cast<long long>(N) * H * W);
     unsigned blocks = grid_for(P / 2, kThreads);

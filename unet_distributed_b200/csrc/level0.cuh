@@ -92,6 +92,83 @@ conv_first32_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w
   }
 }
 
+// ---------------------------------------------------------------------------------------------- conv1a forward, Cin = 1, Cout = 32
+// The two-pixels-per-thread kernel above reads every weight vector from shared memory (72 LDS.128 per pixel pair) and
+// ran at 1.4 TB/s, a fifth of the HBM rate this layer is bound by (ncu, r01: 66 us for a 134 MB write). Here the
+// weights live in REGISTERS: a thread owns 8 of the 32 output channels (72 weights + 8 biases, loaded once) and walks
+// strips of 4 consecutive pixels of an image row; the 3 x 6 input window of a strip is loaded once (the four threads
+// of a strip share it through L1) and feeds 288 FMAs. The four threads of a pixel store its 64 bytes as four adjacent
+// 16-byte pieces, and build the pixel's 32 ReLU gate bits with two shuffles.
+__global__ void __launch_bounds__(128, 3)
+conv_first32_cin1_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ bias,
+                             uint4* __restrict__ y, unsigned int* __restrict__ gate, int H, int W, unsigned n_strips) {
+  const int g = threadIdx.x & 3;
+  float wr[9][8], br[8];
+#pragma unroll
+  for (int t = 0; t < 9; ++t) {
+    const float4 a = __ldg(reinterpret_cast<const float4*>(w + t * 32 + g * 8));
+    const float4 b = __ldg(reinterpret_cast<const float4*>(w + t * 32 + g * 8 + 4));
+    wr[t][0] = a.x; wr[t][1] = a.y; wr[t][2] = a.z; wr[t][3] = a.w;
+    wr[t][4] = b.x; wr[t][5] = b.y; wr[t][6] = b.z; wr[t][7] = b.w;
+  }
+#pragma unroll
+  for (int j = 0; j < 8; ++j) br[j] = bias ? __ldg(bias + g * 8 + j) : 0.0f;
+  const unsigned strips_w = static_cast<unsigned>(W) >> 2;
+  const unsigned step = (gridDim.x * blockDim.x) >> 2;
+  // warp-uniform trip count (the gate-bit shuffles need every lane): lanes past the end compute on strip 0, store nothing
+  const unsigned warp_first = ((blockIdx.x * blockDim.x + threadIdx.x) & ~31u) >> 2;
+  for (unsigned base = warp_first; base < n_strips; base += step) {
+    const unsigned mine = base + ((threadIdx.x & 31u) >> 2);
+    const bool live = mine < n_strips;
+    const unsigned sidx = live ? mine : 0u;
+    const unsigned row = sidx / strips_w;                        // n*H + h
+    const int w0 = static_cast<int>(sidx - row * strips_w) * 4;
+    const int hq = static_cast<int>(row % static_cast<unsigned>(H));
+    float xr[3][6];
+#pragma unroll
+    for (int r = 0; r < 3; ++r) {
+      const int hh = hq + r - 1;
+      const bool row_in = hh >= 0 && hh < H;
+      const float* xp = x + static_cast<size_t>(row + r - 1) * W + w0 - 1;
+#pragma unroll
+      for (int c = 0; c < 6; ++c) {
+        const int ww = w0 - 1 + c;
+        xr[r][c] = (row_in && ww >= 0 && ww < W) ? __ldg(xp + c) : 0.0f;
+      }
+    }
+    const size_t pix0 = static_cast<size_t>(row) * W + w0;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      float acc[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) acc[j] = br[j];
+#pragma unroll
+      for (int r = 0; r < 3; ++r) {
+#pragma unroll
+        for (int sx = 0; sx < 3; ++sx) {
+          const float xv = xr[r][k + sx];
+#pragma unroll
+          for (int j = 0; j < 8; ++j) acc[j] = fmaf(xv, wr[r * 3 + sx][j], acc[j]);
+        }
+      }
+      if (gate) {   // 32 gate bits per pixel: this thread's 8 at bit 8g, merged over the pixel's four threads
+        unsigned int bits = 0;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) bits |= (acc[j] > 0.f ? 1u : 0u) << (8 * g + j);
+        bits |= __shfl_xor_sync(0xffffffffu, bits, 1);
+        bits |= __shfl_xor_sync(0xffffffffu, bits, 2);
+        if (g == 0 && live) gate[pix0 + k] = bits;
+      }
+      uint4 o;
+      o.x = pack_bf16x2(fmaxf(acc[0], 0.f), fmaxf(acc[1], 0.f));
+      o.y = pack_bf16x2(fmaxf(acc[2], 0.f), fmaxf(acc[3], 0.f));
+      o.z = pack_bf16x2(fmaxf(acc[4], 0.f), fmaxf(acc[5], 0.f));
+      o.w = pack_bf16x2(fmaxf(acc[6], 0.f), fmaxf(acc[7], 0.f));
+      if (live) y[(pix0 + k) * 4 + g] = o;
+    }
+  }
+}
+
 // ---------------------------------------------------------------------------------------------- head forward, C = 32
 template <int NCL>
 __global__ void __launch_bounds__(256)

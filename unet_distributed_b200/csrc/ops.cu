@@ -304,6 +304,9 @@ int plan_wgrad(WgradPlan& wp, int N, int H, int W, int taps_r, int taps_s, int p
   p.z_C = z_C;
   p.z_atom = (elt == 2 && z_C % 64 == 0) ? 64 : 32;   // atom = one swizzle row: <= 128 bytes of channels
   p.m_tiles = cdiv(z_C, 128);
+  static const bool no_tap_in_m = getenv("UNETB200_NO_TAP_IN_M") != nullptr;
+  p.tap_in_m = (taps_r == 2 && !no_tap_in_m) ? 1 : 0;   // transposed conv: taps stacked along GEMM M
+  if (p.tap_in_m) p.m_tiles = cdiv(taps_r * taps_s * z_C, 128);
   p.num_src = C1 ? 2 : 1;
   const int Cs[2] = {C0, C1};
   int off = 0;
@@ -320,7 +323,7 @@ int plan_wgrad(WgradPlan& wp, int N, int H, int W, int taps_r, int taps_s, int p
     total_nt += p.x_ntiles[s];
   }
   const int total_pb = p.blocks_n * p.blocks_h * p.blocks_w;
-  const int base = taps_r * taps_s * p.m_tiles * total_nt;
+  const int base = (p.tap_in_m ? 1 : taps_r * taps_s) * p.m_tiles * total_nt;
   static const int waves = getenv("UNETB200_WGRAD_WAVES") ? atoi(getenv("UNETB200_WGRAD_WAVES")) : 1;
   int splits = waves == 1 ? device_sm_count() / base : cdiv(waves * device_sm_count(), base);
   const int max_splits = total_pb / 8 > 1 ? total_pb / 8 : 1;

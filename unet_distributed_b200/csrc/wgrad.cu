@@ -41,9 +41,13 @@ wgrad_kernel(const __grid_constant__ WgradParams p, const __grid_constant__ CUte
   bid /= total_nt;
   const int mt = bid % p.m_tiles;
   bid /= p.m_tiles;
-  const int ntaps = p.taps_r * p.taps_s;
+  // tap_in_m (transposed conv): the four taps are stacked along GEMM M (row = tap * z_C + channel), so one CTA reads
+  // the X tile once for all of them and the MMAs use all 128 rows even when z_C is 32
+  const int ntaps = p.tap_in_m ? 1 : p.taps_r * p.taps_s;
   const int tap = bid % ntaps;
   const int split = bid / ntaps;
+  const int m_total = p.tap_in_m ? p.taps_r * p.taps_s * p.z_C : p.z_C;
+  const int atoms_per_tap = p.z_C / p.z_atom;
   const int src = (ntg >= p.x_ntiles[0]) ? 1 : 0;
   const int nt = src ? ntg - p.x_ntiles[0] : ntg;
   const int block_n = p.x_block_n[src];
@@ -58,7 +62,7 @@ wgrad_kernel(const __grid_constant__ WgradParams p, const __grid_constant__ CUte
   const int pb_end = (pb_begin + per_split < total_pb) ? pb_begin + per_split : total_pb;
   const int nkb = pb_end > pb_begin ? pb_end - pb_begin : 0;
 
-  int m_atoms = (p.z_C - m0 + p.z_atom - 1) / p.z_atom;
+  int m_atoms = (m_total - m0 + p.z_atom - 1) / p.z_atom;
   if (m_atoms > 128 / p.z_atom) m_atoms = 128 / p.z_atom;
   const int n_atoms = block_n / x_atom;
   const uint32_t z_atom_bytes = static_cast<uint32_t>(kKP * p.z_atom * elt);
@@ -104,6 +108,11 @@ wgrad_kernel(const __grid_constant__ WgradParams p, const __grid_constant__ CUte
         for (int a = 0; a < m_atoms; ++a) {
           if (p.z_mode == 0) {
             tma_load_4d(sa + a * z_atom_bytes, &tmZ, &bars->full[stage], m0 + a * p.z_atom, w0, h0, n0);
+          } else if (p.tap_in_m) {
+            const int ga = m0 / p.z_atom + a;            // atom index over all taps
+            const int atap = ga / atoms_per_tap;
+            tma_load_5d(sa + a * z_atom_bytes, &tmZ, &bars->full[stage], (ga % atoms_per_tap) * p.z_atom,
+                        atap % p.taps_s, w0, atap / p.taps_s, n0 * p.H + h0);
           } else {
             tma_load_5d(sa + a * z_atom_bytes, &tmZ, &bars->full[stage], m0 + a * p.z_atom, ts, w0, tr,
                         n0 * p.H + h0);
@@ -163,9 +172,11 @@ wgrad_kernel(const __grid_constant__ WgradParams p, const __grid_constant__ CUte
   } else {
     const int quarter = warp & 3;
     const int row = quarter * 32 + lane;
-    const int co = m0 + row;
-    const bool valid = co < p.z_C;
-    float* out = p.out + split * p.out_split_stride + tap * p.out_tap_stride + co * p.out_m_stride +
+    const int mrow = m0 + row;
+    const bool valid = mrow < m_total;
+    const int otap = p.tap_in_m ? mrow / p.z_C : tap;
+    const int co = p.tap_in_m ? mrow % p.z_C : mrow;
+    float* out = p.out + split * p.out_split_stride + otap * p.out_tap_stride + co * p.out_m_stride +
                  static_cast<long long>(p.x_col_off[src] + c0) * p.out_n_stride;
     if (nkb > 0) {
       mbar_wait(&bars->tmem_full, 0);
@@ -240,7 +251,7 @@ int wgrad_launch(const WgradParams& p, const CUtensorMap& z, const CUtensorMap& 
     attr_set[dev] = true;
   }
   const int total_nt = p.x_ntiles[0] + (p.num_src > 1 ? p.x_ntiles[1] : 0);
-  const long long grid = static_cast<long long>(p.splits) * p.taps_r * p.taps_s * p.m_tiles * total_nt;
+  const long long grid = static_cast<long long>(p.splits) * (p.tap_in_m ? 1 : p.taps_r * p.taps_s) * p.m_tiles * total_nt;
   UB_REQUIRE(grid > 0 && grid < (1ll << 30), "wgrad: grid %lld", grid);
   if (profiling_enabled()) {
     const double pixels = static_cast<double>(p.N) * p.H * p.W;

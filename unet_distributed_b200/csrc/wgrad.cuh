@@ -21,7 +21,8 @@ struct WgradParams {
   int x_shift;              // 1: X box is shifted by the tap (conv); 0: not shifted (tconv)
   int z_C;                  // channels of dZ (GEMM M extent)
   int z_atom;               // 64 (SWIZZLE_128B) or 32 (SWIZZLE_64B)
-  int m_tiles;              // ceil(z_C / 128)
+  int m_tiles;              // ceil(z_C / 128), or ceil(taps * z_C / 128) with tap_in_m
+  int tap_in_m;             // z_mode 1 only: stack the taps along GEMM M (row = tap * z_C + channel), one CTA for all taps
   int num_src;              // X sources (concat inputs)
   int x_C[2];               // channels per source
   int x_atom[2];            // 64 or 32

@@ -79,6 +79,15 @@ class BucketedAllReduce:
             self._pending.append(work)
         return work
 
+    def reduce_now(self, bucket_index):
+        """All-reduce of one bucket ordered on the CURRENT stream: work already enqueued on it comes first, work
+        enqueued on it afterwards sees the reduced values (NCCL runs on its own stream in between)."""
+        if world()[0] == 1:
+            return
+        b, e = self.buckets[bucket_index]
+        if e > b:
+            dist.all_reduce(self.flat[b:e], op=dist.ReduceOp.SUM, group=self.group)
+
     def wait(self):
         """Make the current stream (or, with gloo, the host) wait for every launched bucket."""
         for w in self._pending:

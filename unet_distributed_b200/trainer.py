@@ -4,6 +4,7 @@ No host synchronisation happens inside a step; loss / dice stay on the device un
 from __future__ import annotations
 
 import ctypes
+import os
 
 import numpy as np
 import torch
@@ -67,13 +68,23 @@ class Trainer:
         cur = torch.cuda.current_stream()
         upd = self._upd_stream
         p.forward(imgs, msks, seed=self.dropout_seed, seed_add=self.step_dev)
+        mode = os.environ.get("UNETB200_NCCL_MODE", "upd_sync")
         for seg in range(p.num_segments):
             p.backward(imgs, msks, grad_scale=1.0, segment=seg)
-            work = self.reducer.launch(seg, track=False)      # ordered behind the segment on the current stream
+            if mode == "cur":        # debugging: everything in program order on the current stream (no overlap)
+                self.reducer.launch(seg, track=True)
+                self.reducer.wait()
+                self._update_range(*p.buckets[seg])
+                continue
+            work = self.reducer.launch(seg, track=False) if mode == "upd_async" else None
             upd.wait_stream(cur)
             with torch.cuda.stream(upd):
-                if work is not None:
-                    work.wait()                                # the update stream waits for NCCL, `cur` does not
+                # the all-reduce is ordered behind the segment through the update stream; `cur` does not wait for it
+                if mode == "upd_async":
+                    if work is not None:
+                        work.wait()
+                else:
+                    self.reducer.reduce_now(seg)
                 self._update_range(*p.buckets[seg])
         with torch.cuda.stream(upd):
             _lib.call("unetb200_step_increment", _ptr(self.step_dev), _stream())
