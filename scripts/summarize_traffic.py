@@ -23,7 +23,8 @@ for r in rows[hi + 1:]:
         v *= {"ns": 1e-3, "us": 1.0, "ms": 1e3, "s": 1e6}.get(unit, 1.0)   # -> us
     d[r[mi]] = v
 L = list(launch.values())
-adam = [i for i, l in enumerate(L) if "adam_kernel" in l["name"] or "sgd_kernel" in l["name"]]
+# a step ends with step_increment_kernel (once per step; Adam runs once per gradient bucket)
+adam = [i for i, l in enumerate(L) if "step_increment_kernel" in l["name"]]
 step = L[adam[-2] + 1: adam[-1] + 1]
 agg = collections.OrderedDict()
 for l in step:

@@ -95,7 +95,7 @@ def test_conv3x3_tf32(cuda_device, N, H, W, C0, C1, Co):
     yr = F.relu(z).permute(0, 2, 3, 1).detach().numpy()
     assert _is_tf32(y), "activation outputs of the tf32 mode are rounded to tf32"
     assert rel_err(y.cpu().numpy(), yr) < TOL_TF32
-    assert rel_err(y.cpu().numpy(), _tf32(yr)) < 2e-5       # nothing but the final rounding separates the two
+    assert rel_err(y.cpu().numpy(), _tf32(yr)) < 1e-4       # only the final rounding (and its ties) separates the two
     z.backward(torch.tensor(dz, dtype=torch.float64).permute(0, 3, 1, 2))
     d_dz = torch.tensor(dz, device=dev)
     dx0 = torch.empty_like(d_x0)

@@ -179,3 +179,21 @@ def test_bf16_storage_gradient_deviation():
     flips = ma != mb
     assert flips.mean() < 5e-3                                     # ... a tiny fraction of gates flips ...
     assert (d[flips] ** 2).sum() > 0.9 * (d ** 2).sum()            # ... and carries nearly all of the deviation
+
+
+def test_curve_fixtures_are_the_oracles():
+    """tests/golden/curve_*.npz (the 200-step fp32 / bf16-twin curves the GPU curve test compares against) re-derived
+    for their first steps from the live oracle: a stale or hand-edited file cannot pass.  Also the premise the GPU test
+    rests on: the twin stays within 1e-2 of the fp32 oracle over all 200 steps at the stored learning rate."""
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("make_curves", os.path.join(GOLDEN, "make_curves.py"))
+    mc = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mc)
+    for name, ups in (("tconv", False), ("ups", True)):
+        z = np.load(os.path.join(GOLDEN, f"curve_{name}.npz"))
+        assert float(z["lr"]) == mc.LR[name] and tuple(z["shape"]) == (mc.N, mc.H, mc.W, mc.STEPS, mc.NBATCH)
+        assert z["ref"].shape == (200, 2) and np.abs(z["twin"] - z["ref"]).max() < 1e-2
+        live = mc.run(ups, mc.LR[name], False, steps=3)
+        np.testing.assert_allclose(live, z["ref"][:3], rtol=0, atol=2e-5)
+        live_twin = mc.run(ups, mc.LR[name], True, steps=2)
+        np.testing.assert_allclose(live_twin, z["twin"][:2], rtol=0, atol=2e-5)

@@ -103,6 +103,7 @@ int make_tmap(CUtensorMap* out, const void* base, int rank, const uint64_t* dims
   if (swizzle_bytes == 128) sw = CU_TENSOR_MAP_SWIZZLE_128B;
   else if (swizzle_bytes == 64) sw = CU_TENSOR_MAP_SWIZZLE_64B;
   else if (swizzle_bytes == 32) sw = CU_TENSOR_MAP_SWIZZLE_32B;
+  else if (swizzle_bytes == UB_SWIZZLE_128B_ATOM32) sw = CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B;
   // fp32 tensors hold values already rounded to tf32 by their producers: plain FLOAT32, no conversion on load
   const CUtensorMapDataType dt = elt_bytes == 4 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
   CUresult r = fn(out, dt, static_cast<cuuint32_t>(rank), const_cast<void*>(base), gdims,

@@ -59,6 +59,9 @@ long long tmap_cache_misses();
 
 // Activation / operand element types inside the library (the ABI enum UNETB200_BF16 / UNETB200_TF32 maps onto these).
 enum : int { UB_DT_BF16 = 0, UB_DT_TF32 = 1 };
+// swizzle_bytes value for make_tmap: 128-byte span swizzled in 32-byte chunks (CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B),
+// the only shared-memory layout tcgen05 accepts for MN-major tf32 operands (UMMA layout type SWIZZLE_128B_BASE32B)
+enum : int { UB_SWIZZLE_128B_ATOM32 = 1032 };
 inline int dt_bytes(int dt) { return dt == UB_DT_TF32 ? 4 : 2; }
 
 int device_sm_count();

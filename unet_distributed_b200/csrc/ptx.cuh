@@ -153,7 +153,7 @@ __device__ __forceinline__ void tmem_ld_32x32b_x16(uint32_t taddr, uint32_t (&v)
 // ---------------------------------------------------------------- UMMA descriptors
 // Shared-memory matrix descriptor (64-bit). Fields per the sm_100 layout:
 //   [0,14) start>>4, [16,30) LBO>>4, [32,46) SBO>>4, [46,48) version=1, [49,52) base offset, [61,64) swizzle mode.
-enum : uint32_t { UMMA_SW_NONE = 0, UMMA_SW_128B = 2, UMMA_SW_64B = 4, UMMA_SW_32B = 6 };
+enum : uint32_t { UMMA_SW_NONE = 0, UMMA_SW_128B_BASE32B = 1, UMMA_SW_128B = 2, UMMA_SW_64B = 4, UMMA_SW_32B = 6 };
 
 __host__ __device__ __forceinline__ uint64_t umma_smem_desc(uint32_t smem_addr, uint32_t lbo_bytes,
                                                             uint32_t sbo_bytes, uint32_t swizzle,

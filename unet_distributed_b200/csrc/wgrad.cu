@@ -132,10 +132,14 @@ wgrad_kernel(const __grid_constant__ WgradParams p, const __grid_constant__ CUte
       const uint32_t idesc = elt == 4 ? umma_idesc_tf32(128, static_cast<uint32_t>(block_n), 1, 1)
                                       : umma_idesc_bf16(128, static_cast<uint32_t>(block_n), 1, 1);
       const int kmma = 32 / elt;   // pixels (GEMM K) per instruction: 16 bf16 or 8 tf32
-      const uint32_t z_sw = p.z_atom * elt == 128 ? UMMA_SW_128B : UMMA_SW_64B;
-      const uint32_t x_sw = x_atom * elt == 128 ? UMMA_SW_128B : UMMA_SW_64B;
-      const uint32_t z_sbo = static_cast<uint32_t>(8 * p.z_atom * elt);
-      const uint32_t x_sbo = static_cast<uint32_t>(8 * x_atom * elt);
+      // MN-major tf32 operands exist in one layout only: 128-byte rows swizzled in 32-byte chunks with a period of
+      // FOUR pixel rows (SWIZZLE_128B_BASE32B; the tensor maps use CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B), so the
+      // stride between K groups is 4 rows; bf16 uses the ordinary 128 B / 64 B swizzles with 8-row groups
+      const uint32_t z_sw = elt == 4 ? UMMA_SW_128B_BASE32B : (p.z_atom * elt == 128 ? UMMA_SW_128B : UMMA_SW_64B);
+      const uint32_t x_sw = elt == 4 ? UMMA_SW_128B_BASE32B : (x_atom * elt == 128 ? UMMA_SW_128B : UMMA_SW_64B);
+      const int krows = elt == 4 ? 4 : 8;
+      const uint32_t z_sbo = static_cast<uint32_t>(krows * p.z_atom * elt);
+      const uint32_t x_sbo = static_cast<uint32_t>(krows * x_atom * elt);
       const uint32_t z_kstep = static_cast<uint32_t>(kmma * p.z_atom * elt) >> 4;  // kmma pixels, in 16-byte units
       const uint32_t x_kstep = static_cast<uint32_t>(kmma * x_atom * elt) >> 4;
       const uint64_t a_hi = umma_smem_desc(0, z_atom_bytes, z_sbo, z_sw);
@@ -233,9 +237,10 @@ int wgrad_launch(const WgradParams& p, const CUtensorMap& z, const CUtensorMap& 
   UB_REQUIRE(p.TN * p.TH * p.TW == kKP, "wgrad: pixel box %dx%dx%d is not %d pixels", p.TN, p.TH, p.TW, kKP);
   UB_REQUIRE(p.stages >= 2 && p.stages <= kMaxStages, "wgrad: stages %d out of range", p.stages);
   const int elt = p.elt == 4 ? 4 : 2;
-  UB_REQUIRE(p.z_atom * elt == 128 || p.z_atom * elt == 64, "wgrad: z_atom %d x %d bytes", p.z_atom, elt);
+  UB_REQUIRE(p.z_atom * elt == 128 || (elt == 2 && p.z_atom == 32), "wgrad: z_atom %d x %d bytes", p.z_atom, elt);
   for (int s = 0; s < p.num_src; ++s) {
-    UB_REQUIRE(p.x_atom[s] * elt == 128 || p.x_atom[s] * elt == 64, "wgrad: x_atom %d x %d bytes", p.x_atom[s], elt);
+    UB_REQUIRE(p.x_atom[s] * elt == 128 || (elt == 2 && p.x_atom[s] == 32), "wgrad: x_atom %d x %d bytes", p.x_atom[s],
+               elt);
     UB_REQUIRE(p.x_block_n[s] >= 32 && p.x_block_n[s] <= 128 && p.x_block_n[s] % 16 == 0, "wgrad: block_n %d",
                p.x_block_n[s]);
   }
