@@ -377,6 +377,7 @@ def measure_decoder(args, decoder, world, rank, dev, sampler, with_roofline):
                             "peak_source": "NVLink 5 nominal per direction per GPU", "buckets": nbk,
                             "note": "latency-bound: %.1f MB per step in %d buckets; inside the step the buckets "
                                     "overlap the backward segments that follow them" % (nbytes / 1e6, nbk)}
+    tr.close()     # the captured step holds NCCL kernels: it has to go before the process group is destroyed
     del tr
     torch.cuda.empty_cache()
     return out

@@ -178,6 +178,9 @@ int unetb200_dropout_mask(unsigned char* keep, long long n, float keep_prob, uin
  * profile_collect synchronises and returns, per kind {0 igemm (conv/tconv fwd+dgrad), 1 wgrad, 2 other}, the summed
  * milliseconds, algorithmic FLOPs, minimum HBM bytes and launch count (arrays of 3), then clears the records. */
 long long unetb200_launch_count(void);
+/* Encoded TMA descriptors are cached by (base pointer, element size, dims, strides, box, swizzle), so the eager
+ * per-operator path does not re-encode ~150 tensor maps per step; hits / misses of that cache since load. */
+int unetb200_tmap_cache_stats(long long* hits, long long* misses);
 int unetb200_profile_enable(int on);
 int unetb200_profile_collect(double* ms, double* flops, double* bytes, long long* launches);
 /* One shuffled batch, or one replica's shard of it, cut out of a training set that stays in HBM: data.py:29-54

@@ -1,5 +1,5 @@
 """2-rank check that a whole training step (NCCL all-reduces included) captures into ONE CUDA graph and replays.
-torchrun --nproc-per-node 2 scripts/debug_graph_nccl.py ; UNETB200_NCCL_MODE = upd_sync | upd_async | cur."""
+torchrun --nproc-per-node 2 scripts/debug_graph_nccl.py"""
 import faulthandler
 import os
 import sys
@@ -28,7 +28,7 @@ def log(msg):
 tr = Trainer(N, S, S, dropout=0.2, use_cuda_graph=True)
 imgs, msks = make_slices(N, S, S, 1, seed=5 + rank)
 d_i, d_m = torch.tensor(imgs, device=dev), torch.tensor(msks, device=dev)
-log("trainer built, mode " + os.environ.get("UNETB200_NCCL_MODE", "upd_sync"))
+log("trainer built")
 tr._capture(d_i, d_m)
 torch.cuda.synchronize()
 log(f"captured: {tr.graph_launches_per_step} launches")
@@ -48,6 +48,7 @@ log(f"20 replays: {e0.elapsed_time(e1) / 20:.3f} ms/step")
 p = tr.plan.params.clone()
 torch.distributed.all_reduce(p, op=torch.distributed.ReduceOp.MAX)
 log(f"replicas identical: {bool(torch.equal(p, tr.plan.params))}")
+tr.close()
 torch.distributed.barrier()
 torch.distributed.destroy_process_group()
 faulthandler.cancel_dump_traceback_later()

@@ -57,6 +57,7 @@ def _worker(rank, port, outdir, ups, graph):
     np.save(os.path.join(outdir, f"grads{rank}.npy"), tr.plan.grads.cpu().numpy())
     np.save(os.path.join(outdir, f"mets{rank}.npy"), torch.stack(mets).cpu().numpy())
     assert tr.global_step() == STEPS
+    tr.close()                     # graphs that captured NCCL kernels must go before the process group does
     torch.distributed.barrier()
     torch.distributed.destroy_process_group()
 

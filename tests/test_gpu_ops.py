@@ -303,3 +303,28 @@ def test_errors_are_reported_not_swallowed(cuda_device):
     assert rc < 0 and "multiples of 32" in L.last_error()
     with pytest.raises(L.UnetB200Error):
         L.call("unetb200_maxpool2x2_fwd", _p(x), _p(y), 1, 15, 16, 24, None)
+
+
+def test_tensor_maps_are_cached(cuda_device):
+    """CUtensorMaps are cached by (pointer, dims, box) -- the second identical call encodes none."""
+    L = _lib()
+    rng = np.random.default_rng(1)
+    N, H, W, C, Co = 1, 16, 16, 64, 64
+    d_x = _bf(_rand((N, H, W, C), rng, True), cuda_device)
+    d_w = torch.tensor(_rand((3, 3, C, Co), rng, scale=0.05), device=cuda_device)
+    pk = _pack("unetb200_pack_conv3x3_fwd", d_w, C, Co)
+    y = torch.empty((N, H, W, Co), dtype=torch.bfloat16, device=cuda_device)
+    h, m = ctypes.c_longlong(), ctypes.c_longlong()
+
+    def run():
+        L.call("unetb200_conv3x3_fwd", _p(d_x), C, None, 0, _p(pk), None, _p(y), N, H, W, Co, 1, ctypes.c_float(1.0),
+               ctypes.c_uint64(0), ctypes.c_uint32(0), None)
+        L.call("unetb200_tmap_cache_stats", ctypes.byref(h), ctypes.byref(m))
+        return h.value, m.value
+
+    h0, m0 = run()
+    y0 = y.clone()
+    h1, m1 = run()
+    assert m1 == m0 and h1 >= h0 + 2, (h0, m0, h1, m1)
+    assert torch.equal(y, y0)
+    torch.cuda.synchronize()

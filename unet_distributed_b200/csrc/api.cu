@@ -133,6 +133,11 @@ int unetb200_dropout_mask(unsigned char* keep, long long n, float keep_prob, uin
                           void* stream) {
   return dropout_mask(keep, n, keep_prob, seed, stream_id, S(stream));
 }
+int unetb200_tmap_cache_stats(long long* hits, long long* misses) {
+  if (hits) *hits = tmap_cache_hits();
+  if (misses) *misses = tmap_cache_misses();
+  return UB_OK;
+}
 int unetb200_gather_batch(const void* src, int src_dtype, long long src_rows, const long long* perm, long long first,
                           int rows, long long row_elems, float* dst, void* stream) {
   UB_REQUIRE(src_dtype == UNETB200_F32 || src_dtype == UNETB200_F64, "gather_batch: src_dtype %d is neither F32 nor F64",

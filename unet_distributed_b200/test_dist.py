@@ -191,6 +191,7 @@ def main(argv=None):
               flush=True)
     test_pass(max(step // max(num_batches, 1), 1))                                   # test_dist.py:461-490
     summaries.close()
+    trainer.close()
     if world > 1:
         torch.distributed.barrier()
         torch.distributed.destroy_process_group()

@@ -4,7 +4,6 @@ No host synchronisation happens inside a step; loss / dice stay on the device un
 from __future__ import annotations
 
 import ctypes
-import os
 
 import numpy as np
 import torch
@@ -68,23 +67,12 @@ class Trainer:
         cur = torch.cuda.current_stream()
         upd = self._upd_stream
         p.forward(imgs, msks, seed=self.dropout_seed, seed_add=self.step_dev)
-        mode = os.environ.get("UNETB200_NCCL_MODE", "upd_sync")
         for seg in range(p.num_segments):
             p.backward(imgs, msks, grad_scale=1.0, segment=seg)
-            if mode == "cur":        # debugging: everything in program order on the current stream (no overlap)
-                self.reducer.launch(seg, track=True)
-                self.reducer.wait()
-                self._update_range(*p.buckets[seg])
-                continue
-            work = self.reducer.launch(seg, track=False) if mode == "upd_async" else None
             upd.wait_stream(cur)
             with torch.cuda.stream(upd):
                 # the all-reduce is ordered behind the segment through the update stream; `cur` does not wait for it
-                if mode == "upd_async":
-                    if work is not None:
-                        work.wait()
-                else:
-                    self.reducer.reduce_now(seg)
+                self.reducer.reduce_now(seg)
                 self._update_range(*p.buckets[seg])
         with torch.cuda.stream(upd):
             _lib.call("unetb200_step_increment", _ptr(self.step_dev), _stream())
@@ -119,6 +107,12 @@ class Trainer:
             self._enqueue_step(imgs, msks)
         self.steps_done += 1
         return self.plan.metrics
+
+    def close(self):
+        """Release the captured step. A CUDA graph that holds NCCL kernels keeps the communicator busy:
+        torch.distributed.destroy_process_group() blocks until every such graph is gone, so call this first."""
+        self._graph = None
+        torch.cuda.synchronize(self.plan.device)
 
     def _capture(self, imgs, msks):
         self._g_imgs, self._g_msks = imgs.clone(), msks.clone()
