@@ -15,6 +15,9 @@ import torch
 import torch.distributed as dist
 
 
+NCCL_MAX_CTAS = 0   # 0 = NCCL's default; UNETB200_NCCL_MAX_CTAS overrides (A/B: profiles/r02_nccl_max_ctas.txt)
+
+
 def shard_range(batch_size, num_replicas, rank):
     """Slice of the global batch that replica `rank` trains on -- test_dist.py:390-392
     (data_range = int(batch_size / len(worker_hosts)); start = data_range * task_index)."""
@@ -49,6 +52,14 @@ def init_from_env(backend=None):
         torch.cuda.set_device(local)
     if not dist.is_initialized():
         kw = {"device_id": torch.device("cuda", local)} if backend == "nccl" else {}
+        max_ctas = int(os.environ.get("UNETB200_NCCL_MAX_CTAS", str(NCCL_MAX_CTAS)))
+        if backend == "nccl" and max_ctas > 0:
+            # The gradient buckets are latency-bound (0.3-14 MB) and run beside persistent one-CTA-per-SM conv kernels:
+            # every SM NCCL occupies delays one of those CTAs by a whole tile loop, so NCCL gets few CTAs.
+            opts = dist.ProcessGroupNCCL.Options()
+            opts.config.max_ctas = max_ctas
+            opts.config.min_ctas = 1
+            kw["pg_options"] = opts
         # a mismatched collective should fail in minutes, not after the 10-minute default
         dist.init_process_group(backend=backend, rank=rank, world_size=ws,
                                 timeout=datetime.timedelta(seconds=int(os.environ.get("UNETB200_DIST_TIMEOUT", "180"))),
