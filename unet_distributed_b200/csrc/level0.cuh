@@ -148,22 +148,25 @@ conv_first32_cin1_fwd_kernel(const float* __restrict__ x, const float* __restric
         for (int sx = 0; sx < 3; ++sx) {
           const float xv = xr[r][k + sx];
 #pragma unroll
-          for (int j = 0; j < 8; ++j) acc[j] = fmaf(xv, wr[r * 3 + sx][j], acc[j]);
+          for (int j = 0; j < 8; j += 2) fma2(acc[j], acc[j + 1], xv, wr[r * 3 + sx][j], wr[r * 3 + sx][j + 1]);
         }
       }
-      if (gate) {   // 32 gate bits per pixel: this thread's 8 at bit 8g, merged over the pixel's four threads
-        unsigned int bits = 0;
+      uint4 o;   // ReLU inside the conversion (ncu r02: the kernel is issue-bound, every instruction counts)
+      o.x = pack_bf16x2_relu_rn(acc[0], acc[1]);
+      o.y = pack_bf16x2_relu_rn(acc[2], acc[3]);
+      o.z = pack_bf16x2_relu_rn(acc[4], acc[5]);
+      o.w = pack_bf16x2_relu_rn(acc[6], acc[7]);
+      if (gate) {   // 32 gate bits per pixel: this thread's 8 at bit 8g, merged over the pixel's four threads.
+        // A bf16 half is non-zero iff adding 0x7fff carries into its sign bit (outputs are >= 0 after the ReLU).
+        const unsigned int ow[4] = {o.x, o.y, o.z, o.w};
+        unsigned int acc2 = 0;
 #pragma unroll
-        for (int j = 0; j < 8; ++j) bits |= (acc[j] > 0.f ? 1u : 0u) << (8 * g + j);
+        for (int i = 0; i < 4; ++i) acc2 |= ((ow[i] + 0x7FFF7FFFu) >> (15 - 2 * i)) & (0x00010001u << (2 * i));
+        unsigned int bits = ((acc2 & 0xFFu) | ((acc2 >> 15) & 0xFFu)) << (8 * g);
         bits |= __shfl_xor_sync(0xffffffffu, bits, 1);
         bits |= __shfl_xor_sync(0xffffffffu, bits, 2);
         if (g == 0 && live) gate[pix0 + k] = bits;
       }
-      uint4 o;
-      o.x = pack_bf16x2(fmaxf(acc[0], 0.f), fmaxf(acc[1], 0.f));
-      o.y = pack_bf16x2(fmaxf(acc[2], 0.f), fmaxf(acc[3], 0.f));
-      o.z = pack_bf16x2(fmaxf(acc[4], 0.f), fmaxf(acc[5], 0.f));
-      o.w = pack_bf16x2(fmaxf(acc[6], 0.f), fmaxf(acc[7], 0.f));
       if (live) y[(pix0 + k) * 4 + g] = o;
     }
   }
@@ -335,7 +338,7 @@ conv_first32_wgrad_kernel(const float* __restrict__ x, const uint4* __restrict__
           for (int sx = 0; sx < 3; ++sx) {
             const float xv = xr[r][k + sx];
 #pragma unroll
-            for (int j = 0; j < 8; ++j) acc[r * 3 + sx][j] = fmaf(xv, d[j], acc[r * 3 + sx][j]);
+            for (int j = 0; j < 8; j += 2) fma2(acc[r * 3 + sx][j], acc[r * 3 + sx][j + 1], xv, d[j], d[j + 1]);
           }
         }
       }

@@ -93,6 +93,15 @@ void fill_grid(IgemmParams& p, int N, int H, int W, Box b) {
   p.tiles_w = cdiv(W, b.TW);
 }
 
+// Fewer tiles than half the SMs (the 8x8 level at bs128: 64 pixel tiles): halve a 256-wide N tile so that twice as
+// many SMs work (ncu r02: conv5b forward / dgrad ran on 64 of 148 SMs at 25 % tensor-pipe activity).
+int widen_grid(int block_n, int m_tiles, int ncols) {
+  static const bool off = getenv("UNETB200_NO_WIDEN_GRID") != nullptr;
+  if (off) return block_n;
+  while (block_n > 128 && m_tiles * (ncols / block_n) * 2 <= device_sm_count()) block_n >>= 1;
+  return block_n;
+}
+
 int pick_block_n(int ncols_per_dest) {
   if (ncols_per_dest % 256 == 0) return 256;
   if (ncols_per_dest % 128 == 0) return 128;
@@ -182,6 +191,7 @@ int conv3x3_fwd(ConvSrc x0, ConvSrc x1, const void* w_packed, const float* bias,
   std::memset(&p, 0, sizeof(p));
   const Box b = pick_box(128, H, W);
   fill_grid(p, N, H, W, b);
+  const int block_n_igemm = widen_grid(block_n, p.tiles_n * p.tiles_h * p.tiles_w, Cout);
   p.n_tiles = Cout / block_n;
   p.block_n = block_n;
   p.a_mode = IG_A_SHIFT4D;
@@ -209,6 +219,12 @@ int conv3x3_fwd(ConvSrc x0, ConvSrc x1, const void* w_packed, const float* bias,
   // the halo kernels are bf16 engines; the fp32/tf32 mode runs every conv on the generic implicit-GEMM kernel
   if (elt == 2 && try_halo(p, x0.ptr, x0.C, x1.ptr, C1, w_packed, Cout, x0.C + C1, s, &rc)) return rc;
   UB_REQUIRE(!maxpool_out, "conv3x3_fwd: fused max pooling is not available for this shape (conv3x3_fwd_maxpool_ok)");
+  if (block_n_igemm != block_n) {
+    p.block_n = block_n_igemm;
+    p.n_tiles = Cout / block_n_igemm;
+    p.stages = igemm_pick_stages(block_n_igemm, kc, elt);
+  }
+  const int bn = p.block_n;
   CUtensorMap a0, a1, bm;
   rc = nhwc_map(&a0, x0.ptr, N, H, W, x0.C, kc, b, elt);
   if (rc) return rc;
@@ -217,7 +233,7 @@ int conv3x3_fwd(ConvSrc x0, ConvSrc x1, const void* w_packed, const float* bias,
     rc = nhwc_map(&a1, x1.ptr, N, H, W, C1, kc, b, elt);
     if (rc) return rc;
   }
-  rc = weight_map(&bm, w_packed, Cout, 9, x0.C + C1, kc, block_n, elt);
+  rc = weight_map(&bm, w_packed, Cout, 9, x0.C + C1, kc, bn, elt);
   if (rc) return rc;
   return igemm_launch(p, a0, a1, bm, s);
 }
@@ -273,6 +289,15 @@ int conv3x3_dgrad(const void* dz, int Cout, const void* w_packed_d, DgradDst d0,
   int rc = UB_OK;
   if (elt == 2 && try_halo(p, dz, Cout, nullptr, 0, w_packed_d, d0.C + C1, Cout, s, &rc)) return rc;
   UB_REQUIRE(!d0.pool2, "conv3x3_dgrad: fused 2x2 pooling is not available for this shape (conv3x3_dgrad_pool2_ok)");
+  {
+    const int bn2 = widen_grid(block_n, p.tiles_n * p.tiles_h * p.tiles_w, d0.C + C1);
+    if (bn2 != block_n && (!C1 || d0.C % bn2 == 0)) {
+      block_n = bn2;
+      p.block_n = bn2;
+      p.n_tiles = (d0.C + C1) / bn2;
+      p.stages = igemm_pick_stages(bn2, kc, elt);
+    }
+  }
   CUtensorMap a0, bm;
   rc = nhwc_map(&a0, dz, N, H, W, Cout, kc, b, elt);
   if (rc) return rc;

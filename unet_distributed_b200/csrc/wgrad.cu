@@ -300,7 +300,9 @@ int wgrad_launch(const WgradParams& p, const CUtensorMap& z, const CUtensorMap& 
 int splitk_reduce_launch(const float* ws, long long split_stride, int splits, float* out, long long n,
                          cudaStream_t stream, float* out_b, long long n_a) {
   if (n <= 0) return UB_OK;
-  const int R = splits >= 8 ? 8 : (splits >= 4 ? 4 : (splits >= 2 ? 2 : 1));
+  // at least four splits per lane (four loads in flight): with few splits one thread per column is fastest
+  // (ncu r02: R = 4 on 4..7 splits ran at 1 TB/s, twice as long as the one-thread loop it replaced)
+  const int R = splits >= 32 ? 8 : (splits >= 16 ? 4 : (splits >= 8 ? 2 : 1));
   const long long blocks = (n + 256 / R - 1) / (256 / R);
   const unsigned g = static_cast<unsigned>(blocks);
   switch (R) {
