@@ -243,11 +243,17 @@ __device__ __forceinline__ void halo_epilogue(const HaloParams& p, HaloBarriers*
       const size_t off = (static_cast<size_t>(8 * j) * e.dst_C[sl] + ch) * 2;   // bytes from dst_b[sl]
       if (DROP) {
         const size_t elem0 = (pix0 + 8 * j) * e.dst_C[sl] + e.dst_coff[sl] + ch;
+        if (e.drop_bits) {
+          const uint32_t bits = __ldg(e.drop_bits + (elem0 >> 4));
+#pragma unroll
+          for (int i = 0; i < 16; ++i) v[i] = ((bits >> i) & 1u) ? v[i] * inv_keep : 0.0f;
+        } else {
 #pragma unroll
         for (int g = 0; g < 2; ++g) {
           const uint32_t bits = dropout_keep_bits8(seed, e.drop_stream, elem0 / 8 + g, e.drop_keep);
 #pragma unroll
           for (int i = 0; i < 8; ++i) v[8 * g + i] = ((bits >> i) & 1u) ? v[8 * g + i] * inv_keep : 0.0f;
+        }
         }
       }
       if (BIAS_RELU) {
@@ -433,11 +439,17 @@ __device__ __forceinline__ void halo_epilogue_fast(const HaloParams& p, HaloBarr
         }
         if (DROP) {   // (dropout of a negative value stays negative or zero: the ReLU in the conversion still applies)
           const size_t elem0 = (pix0 + 8 * j) * e.dst_C[0] + e.dst_coff[0] + half * 16 + 32 * cl;
+          if (e.drop_bits) {   // precomputed keep bits: one 2-byte load per item
+            const uint32_t bits = __ldg(e.drop_bits + (elem0 >> 4));
+#pragma unroll
+            for (int i = 0; i < 16; ++i) v[i] = ((bits >> i) & 1u) ? v[i] * inv_keep : 0.0f;
+          } else {
 #pragma unroll
           for (int g = 0; g < 2; ++g) {
             const uint32_t bits = dropout_keep_bits8(seed, e.drop_stream, elem0 / 8 + g, e.drop_keep);
 #pragma unroll
             for (int i = 0; i < 8; ++i) v[8 * g + i] = ((bits >> i) & 1u) ? v[8 * g + i] * inv_keep : 0.0f;
+          }
           }
         }
 #pragma unroll

@@ -743,6 +743,19 @@ __global__ void dropout_mask_kernel(unsigned char* __restrict__ keep, long long 
   for (int i = 0; i < 8; ++i) keep[g * 8 + i] = (bits >> i) & 1u;
 }
 
+// Keep bits of a whole dropout layer: bits[g] (uint16) = keep decisions of elements 16g .. 16g+15, from the same Philox
+// stream and element numbering as the conv epilogue's in-line generator and dropout_mask_kernel.
+__global__ void dropout_bits16_kernel(unsigned short* __restrict__ bits, long long ngroups16, float keep_prob,
+                                      unsigned long long seed, const long long* __restrict__ seed_add,
+                                      unsigned int stream_id) {
+  const long long g = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (g >= ngroups16) return;
+  const unsigned long long sd = seed + (seed_add ? static_cast<unsigned long long>(__ldg(seed_add)) : 0ull);
+  const uint32_t lo = dropout_keep_bits8(sd, stream_id, static_cast<unsigned long long>(2 * g), keep_prob);
+  const uint32_t hi = dropout_keep_bits8(sd, stream_id, static_cast<unsigned long long>(2 * g + 1), keep_prob);
+  bits[g] = static_cast<unsigned short>(lo | (hi << 8));
+}
+
 #include "level0.cuh"
 #include "pool.cuh"
 
@@ -1197,6 +1210,15 @@ int dropout_mask(unsigned char* keep, long long n, float keep_prob, unsigned lon
   UB_REQUIRE(n % 8 == 0, "dropout_mask: n %lld must be a multiple of 8", n);
   const long long ng = n / 8;
   dropout_mask_kernel<<<grid_for(ng, kThreads), kThreads, 0, s>>>(keep, ng, keep_prob, seed, stream_id);
+  UB_CHECK_CUDA(cudaGetLastError());
+  return UB_OK;
+}
+
+int dropout_keep_bits16(unsigned short* bits, long long n, float keep_prob, unsigned long long seed,
+                        const long long* seed_add, unsigned int stream_id, cudaStream_t s) {
+  UB_REQUIRE(n % 16 == 0, "dropout_keep_bits16: n %lld must be a multiple of 16", n);
+  const long long ng = n / 16;
+  dropout_bits16_kernel<<<grid_for(ng, kThreads), kThreads, 0, s>>>(bits, ng, keep_prob, seed, seed_add, stream_id);
   UB_CHECK_CUDA(cudaGetLastError());
   return UB_OK;
 }

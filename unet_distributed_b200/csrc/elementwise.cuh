@@ -95,6 +95,11 @@ int dropout_mask(unsigned char* keep, long long n, float keep_prob, unsigned lon
 int gather_rows(const void* src, int src_is_f64, long long src_rows, const long long* perm, long long first, int rows,
                 long long row_elems, float* dst, cudaStream_t s);
 
+// bits[g] (uint16) = keep decisions of elements 16g .. 16g+15 of a dropout layer's output (n elements, multiple of
+// 16): Philox stream (seed + *seed_add, stream_id), the numbering dropout_mask and the conv epilogues use.
+int dropout_keep_bits16(unsigned short* bits, long long n, float keep_prob, unsigned long long seed,
+                        const long long* seed_add, unsigned int stream_id, cudaStream_t s);
+
 int cast_f32_to_bf16(const float* x, void* y, long long n, cudaStream_t s);
 int cast_bf16_to_f32(const void* x, float* y, long long n, cudaStream_t s);
 

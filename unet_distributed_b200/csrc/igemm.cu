@@ -194,6 +194,9 @@ igemm_kernel(const __grid_constant__ IgemmParams p, const __grid_constant__ CUte
         unsigned short* gout = nullptr;
         if (e.gate_out) gout = e.gate_out + ((pix * e.dst_C[0] + e.dst_coff[0] + col0) >> 4);
         const float scale = e.mask_scale;
+        const unsigned short* dbits = nullptr;   // precomputed dropout keep bits (forward, single plain destination)
+        if (e.drop_keep < 1.0f) dbits = e.drop_bits + ((pix * e.dst_C[0] + e.dst_coff[0] + col0) >> 4);
+        const float inv_keep = e.drop_keep < 1.0f ? 1.0f / e.drop_keep : 1.0f;
         const int d2s_shift = e.d2s_cout > 0 ? 31 - __clz(e.d2s_cout) : 0;
         mbar_wait(&bars->tmem_full[acc], (it >> 1) & 1);
         tc_fence_after();
@@ -235,6 +238,11 @@ igemm_kernel(const __grid_constant__ IgemmParams p, const __grid_constant__ CUte
             if (gin) {
 #pragma unroll
               for (int i = 0; i < 16; ++i) v[i] = ((gbits[u] >> i) & 1u) ? v[i] * scale : 0.0f;
+            }
+            if (dbits) {
+              const uint32_t kb = __ldg(dbits + (cc >> 4));
+#pragma unroll
+              for (int i = 0; i < 16; ++i) v[i] = ((kb >> i) & 1u) ? v[i] * inv_keep : 0.0f;
             }
             U32x8 o;
             if (e.relu) {
@@ -326,8 +334,13 @@ igemm_kernel(const __grid_constant__ IgemmParams p, const __grid_constant__ CUte
             const float inv = 1.0f / e.drop_keep;
             const unsigned long long seed =
                 e.drop_seed + (e.drop_seed_add ? static_cast<unsigned long long>(__ldg(e.drop_seed_add)) : 0ull);
+            if (e.drop_bits) {
+              const uint32_t bits = __ldg(e.drop_bits + ((drop_elem0 + c) >> 4));
 #pragma unroll
-            for (int g = 0; g < 2; ++g) {
+              for (int i = 0; i < 16; ++i) v[i] = ((bits >> i) & 1u) ? v[i] * inv : 0.0f;
+            }
+#pragma unroll
+            for (int g = 0; g < 2 && !e.drop_bits; ++g) {
               const uint32_t bits = dropout_keep_bits8(seed, e.drop_stream, (drop_elem0 + c) / 8 + g, e.drop_keep);
 #pragma unroll
               for (int i = 0; i < 8; ++i) v[8 * g + i] = ((bits >> i) & 1u) ? v[8 * g + i] * inv : 0.0f;
@@ -436,7 +449,7 @@ int igemm_launch(const IgemmParams& p_in, const CUtensorMap& a0, const CUtensorM
     const bool split_ok = e.split_col >= p.n_tiles * p.block_n || e.split_col % p.block_n == 0;
     const bool gate_ok = !e.gate_out || (e.d2s_cout == 0 && e.split_col >= p.n_tiles * p.block_n);
     p.lean = (!no_lean && p.elt == 2 && full && aligned && split_ok && gate_ok && p.block_n >= 32 && !e.aux[0] && !e.aux[1] &&
-              e.drop_keep >= 1.0f &&
+              (e.drop_keep >= 1.0f || (e.drop_bits && e.d2s_cout == 0 && e.split_col >= p.n_tiles * p.block_n)) &&
               (e.d2s_cout == 0 || (e.d2s_cout >= 32 && (e.d2s_cout & (e.d2s_cout - 1)) == 0))) ? 1 : 0;
   }
   int grid = device_sm_count();

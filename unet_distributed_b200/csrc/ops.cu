@@ -213,6 +213,7 @@ int conv3x3_fwd(ConvSrc x0, ConvSrc x1, const void* w_packed, const float* bias,
   p.epi.drop_seed = drop.seed;
   p.epi.drop_stream = drop.stream;
   p.epi.drop_seed_add = drop.seed_add;
+  p.epi.drop_bits = drop.keep < 1.0f ? drop.bits : nullptr;
   p.epi.gate_out = gate_out;
   p.epi.maxpool_out = maxpool_out;
   int rc = UB_OK;

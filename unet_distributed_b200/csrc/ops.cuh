@@ -19,6 +19,9 @@ struct DropoutCfg {
   unsigned long long seed;
   unsigned int stream;
   const long long* seed_add;  // optional device counter added to seed
+  // optional: keep bits of this layer's output precomputed with dropout_keep_bits16 (same seed / stream / numbering);
+  // the conv epilogue then loads them instead of running Philox (elementwise.cuh)
+  const unsigned short* bits = nullptr;
 };
 
 // y = relu?(conv3x3_same([x0, x1]) + bias) (* dropout); w_packed = bf16 [Cout][9][C0+C1].

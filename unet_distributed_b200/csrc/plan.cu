@@ -59,6 +59,7 @@ struct unetb200_plan {
   // where nothing consumes them (the consumer then reads the activation tensor itself)
   size_t gt_a[5], gt_c[5], gt_da[4], gt_dc[4];
   size_t preds, sums, metrics, ws, ws_side;
+  size_t drop_bits[5];   // keep bits of the dropout layers (conv3a, conv4a: levels 2, 3), generated once per forward
   std::vector<PackLayer> pack_layers;
   int pack_tiles = 0;
   size_t pack_table = 0;
@@ -229,6 +230,9 @@ int unetb200_plan_create_dt(unetb200_plan** out, int N, int H, int W, int in_cha
       P->gt_dc[L + 1] = P->bump(P->gate_bytes(L + 1, P->dc_out[L + 1]));
     }
   }
+  for (int L = 0; L < 5; ++L) {
+    P->drop_bits[L] = ((L == 2 || L == 3) && dropout > 0.0f) ? P->bump(P->gate_bytes(L, P->ch[L])) : kNoGate;
+  }
   const long long pixels = static_cast<long long>(N) * H * W;
   P->preds = P->bump(static_cast<size_t>(pixels) * n_cl_out * 4);
   P->sums = P->bump(64);
@@ -389,6 +393,14 @@ int unetb200_plan_forward(unetb200_plan* P, const float* imgs, const float* msks
   const int N = P->N;
   const int dt = P->dt;
   const DropoutCfg no_drop{1.0f, 0, 0, nullptr};
+  // dropout keep bits of conv3a / conv4a for this forward: two small kernels up front instead of Philox in the conv
+  // epilogues (where it made conv3a's epilogue slower than its MMAs)
+  static const bool inline_philox = getenv("UNETB200_INLINE_PHILOX") != nullptr;
+  for (int L = 2; L <= 3 && !inline_philox; ++L) {
+    if (P->drop_bits[L] == kNoGate) continue;
+    RC(dropout_keep_bits16(P->gate(P->drop_bits[L]), static_cast<long long>(N) * P->Hl(L) * P->Wl(L) * P->ch[L],
+                           1.0f - P->dropout, seed, seed_add, static_cast<unsigned>(L), s));
+  }
   // encoder
   for (int L = 0; L < 5; ++L) {
     const int H = P->Hl(L), W = P->Wl(L);
@@ -397,7 +409,10 @@ int unetb200_plan_forward(unetb200_plan* P, const float* imgs, const float* msks
       RC(conv_first_fwd(imgs, P->W_(la), P->B_(la), P->at(P->a[0]), N, H, W, P->Cin, 32, s, P->gate(P->gt_a[0]), dt));
     } else {
       DropoutCfg d = no_drop;
-      if ((L == 2 || L == 3) && P->dropout > 0.0f) d = DropoutCfg{1.0f - P->dropout, seed, static_cast<unsigned>(L), seed_add};
+      if ((L == 2 || L == 3) && P->dropout > 0.0f) {
+        d = DropoutCfg{1.0f - P->dropout, seed, static_cast<unsigned>(L), seed_add,
+                       inline_philox ? nullptr : P->gate(P->drop_bits[L])};
+      }
       RC(conv3x3_fwd(ConvSrc{P->at(P->p[L - 1]), P->ch[L - 1]}, ConvSrc{nullptr, 0}, P->pkf(la), P->B_(la),
                      P->at(P->a[L]), N, H, W, P->ch[L], 1, d, s, P->gate(P->gt_a[L]), nullptr, dt));
     }
