@@ -215,6 +215,12 @@ int unetb200_plan_variable(const unetb200_plan* plan, int i, char* name, int nam
                            int* shape4);
 size_t unetb200_plan_arena_bytes(const unetb200_plan* plan);
 int unetb200_plan_bind(unetb200_plan* plan, void* arena, float* params, float* grads);
+/* The arena's sub-buffers (activations, gradients, gate bits, packed operands, workspaces) as [offset, offset + bytes)
+ * in allocation order; nothing outside them is ever written. With UNETB200_ARENA_GUARD=<bytes> in the environment at
+ * plan creation that many unused bytes follow every sub-buffer: the tests fill the arena with a pattern and check that
+ * a training step leaves every byte outside the regions untouched (compute-sanitizer is closed on the GPU pool). */
+int unetb200_plan_num_regions(const unetb200_plan* plan);
+int unetb200_plan_region(const unetb200_plan* plan, int i, long long* offset, long long* bytes);
 /* Arena offset and shape of an activation ("a1".."a9", "c1".."c9", "p1".."p4", "u6".."u9"), its gradient ("g"+name),
  * "preds" (fp32) or "metrics" (fp32 {loss, dice, sensitivity, specificity}). */
 int unetb200_plan_tensor(const unetb200_plan* plan, const char* name, long long* offset, int* n, int* h, int* w,

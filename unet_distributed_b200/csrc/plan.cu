@@ -4,6 +4,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <string>
+#include <utility>
 #include <vector>
 
 #include "../../include/unetb200.h"
@@ -81,9 +82,14 @@ struct unetb200_plan {
   float* params = nullptr;
   float* grads = nullptr;
 
+  // every sub-buffer of the arena, in allocation order (unetb200_plan_region); `guard` bytes are left unused after each
+  // one when UNETB200_ARENA_GUARD is set at plan creation (out-of-bounds write detection in the tests)
+  std::vector<std::pair<size_t, size_t>> regions;
+  size_t guard = 0;
   size_t bump(size_t bytes) {
     size_t off = arena_bytes;
-    arena_bytes += (bytes + kAlign - 1) / kAlign * kAlign;
+    arena_bytes += (bytes + kAlign - 1) / kAlign * kAlign + guard;
+    regions.emplace_back(off, bytes);
     return off;
   }
   int Hl(int L) const { return H >> L; }
@@ -158,6 +164,12 @@ int unetb200_plan_create_dt(unetb200_plan** out, int N, int H, int W, int in_cha
   unetb200_plan* P = new unetb200_plan();
   P->N = N; P->H = H; P->W = W; P->Cin = in_channels; P->ncl = n_cl_out; P->ups = use_upsampling ? 1 : 0;
   P->dropout = dropout;
+  if (const char* g = getenv("UNETB200_ARENA_GUARD")) {
+    const long long gb = atoll(g);
+    UB_REQUIRE(gb >= 0 && gb % static_cast<long long>(kAlign) == 0 && gb <= (1ll << 24),
+               "plan_create: UNETB200_ARENA_GUARD %lld must be a multiple of %zu (at most 16 MiB)", gb, kAlign);
+    P->guard = static_cast<size_t>(gb);
+  }
   P->dt = dtype == UNETB200_TF32 ? UB_DT_TF32 : UB_DT_BF16;
   P->elt = dt_bytes(P->dt);
   for (int L = 0; L < 5; ++L) P->ch[L] = 32 << L;
@@ -308,6 +320,14 @@ int unetb200_plan_variable(const unetb200_plan* P, int i, char* name, int name_c
 }
 
 size_t unetb200_plan_arena_bytes(const unetb200_plan* P) { return P->arena_bytes; }
+
+int unetb200_plan_num_regions(const unetb200_plan* P) { return static_cast<int>(P->regions.size()); }
+int unetb200_plan_region(const unetb200_plan* P, int i, long long* offset, long long* bytes) {
+  UB_REQUIRE(i >= 0 && i < static_cast<int>(P->regions.size()), "plan_region: index %d out of range", i);
+  *offset = static_cast<long long>(P->regions[i].first);
+  *bytes = static_cast<long long>(P->regions[i].second);
+  return UB_OK;
+}
 
 int unetb200_plan_bind(unetb200_plan* P, void* arena, float* params, float* grads) {
   UB_REQUIRE(arena && params && grads, "plan_bind: null buffer");
