@@ -177,6 +177,11 @@ int unetb200_dropout_mask(unsigned char* keep, long long n, float keep_prob, uin
  * in this process. With profiling enabled every tile-engine launch is bracketed by CUDA events on its stream;
  * profile_collect synchronises and returns, per kind {0 igemm (conv/tconv fwd+dgrad), 1 wgrad, 2 other}, the summed
  * milliseconds, algorithmic FLOPs, minimum HBM bytes and launch count (arrays of 3), then clears the records. */
+/* Size every grid launched from now on (host-side state, read at launch time, so also at graph capture) for the
+ * device's SM count minus n: SMs left free for kernels that run beside this library's persistent one-CTA-per-SM
+ * kernels -- the NCCL all-reduces of the gradient buckets (test_dist.py:251-258) during backward. Returns the
+ * previous reservation; 0 (default) uses every SM. No reference counterpart. */
+int unetb200_set_reserved_sms(int n);
 long long unetb200_launch_count(void);
 /* Encoded TMA descriptors are cached by (base pointer, element size, dims, strides, box, swizzle), so the eager
  * per-operator path does not re-encode ~150 tensor maps per step; hits / misses of that cache since load. */

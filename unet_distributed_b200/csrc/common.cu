@@ -209,6 +209,15 @@ int unetb200_profile_collect(double* ms, double* flops, double* bytes, long long
 }
 }  // extern "C"
 
+namespace {
+std::atomic<int> g_reserved_sms{0};
+}
+
+int set_reserved_sms(int n) {
+  if (n < 0) n = 0;
+  return g_reserved_sms.exchange(n);
+}
+
 int device_sm_count() {
   static int cached[64] = {0};
   int dev = 0;
@@ -218,7 +227,10 @@ int device_sm_count() {
     if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
     cached[dev] = n;
   }
-  return cached[dev];
+  const int usable = cached[dev] - g_reserved_sms.load(std::memory_order_relaxed);
+  return usable > 8 ? usable : 8;
 }
+
+extern "C" int unetb200_set_reserved_sms(int n) { return set_reserved_sms(n); }
 
 }  // namespace ub

@@ -64,6 +64,10 @@ enum : int { UB_DT_BF16 = 0, UB_DT_TF32 = 1 };
 enum : int { UB_SWIZZLE_128B_ATOM32 = 1032 };
 inline int dt_bytes(int dt) { return dt == UB_DT_TF32 ? 4 : 2; }
 
+// SMs this library sizes its persistent grids and split-K factors for: the device's SM count minus the reservation
+// (unetb200_set_reserved_sms). A kernel of one CTA per SM that finds k SMs taken by a concurrent NCCL kernel runs its
+// last k CTAs as a second wave and takes twice as long; leaving those SMs out of the grid costs k/148 instead.
 int device_sm_count();
+int set_reserved_sms(int n);   // returns the previous reservation
 
 }  // namespace ub

@@ -16,6 +16,7 @@ import torch.distributed as dist
 
 
 NCCL_MAX_CTAS = 0   # 0 = NCCL's default; UNETB200_NCCL_MAX_CTAS overrides (A/B: profiles/r02_nccl_max_ctas.txt)
+RESERVED_SMS = 0    # SMs the backward kernels leave to concurrent all-reduces; UNETB200_RESERVE_SMS overrides
 
 
 def shard_range(batch_size, num_replicas, rank):

@@ -4,6 +4,7 @@ No host synchronisation happens inside a step; loss / dice stay on the device un
 from __future__ import annotations
 
 import ctypes
+import os
 
 import numpy as np
 import torch
@@ -47,6 +48,8 @@ class Trainer:
             p.pack_weights()
         self.reducer = parallel.BucketedAllReduce(p.grads, p.buckets)
         self._upd_stream = torch.cuda.Stream(device=dev)   # bucket updates run here, beside the rest of backward
+        # SMs left to the NCCL kernels that run beside backward segments 1..4 (see unetb200_set_reserved_sms)
+        self.reserved_sms = int(os.environ.get("UNETB200_RESERVE_SMS", str(parallel.RESERVED_SMS)))
         self.use_cuda_graph = bool(use_cuda_graph)
         self._graph = None
         self._g_imgs = self._g_msks = None
@@ -67,13 +70,17 @@ class Trainer:
         cur = torch.cuda.current_stream()
         upd = self._upd_stream
         p.forward(imgs, msks, seed=self.dropout_seed, seed_add=self.step_dev)
+        lib = _lib.lib()
         for seg in range(p.num_segments):
+            # from the second segment on, an all-reduce runs beside the backward kernels: leave it its SMs
+            lib.unetb200_set_reserved_sms(self.reserved_sms if (self.world > 1 and seg > 0) else 0)
             p.backward(imgs, msks, grad_scale=1.0, segment=seg)
             upd.wait_stream(cur)
             with torch.cuda.stream(upd):
                 # the all-reduce is ordered behind the segment through the update stream; `cur` does not wait for it
                 self.reducer.reduce_now(seg)
                 self._update_range(*p.buckets[seg])
+        lib.unetb200_set_reserved_sms(0)
         with torch.cuda.stream(upd):
             _lib.call("unetb200_step_increment", _ptr(self.step_dev), _stream())
         cur.wait_stream(upd)
