@@ -15,8 +15,11 @@ import torch
 import torch.distributed as dist
 
 
-NCCL_MAX_CTAS = 0   # 0 = NCCL's default; UNETB200_NCCL_MAX_CTAS overrides (A/B: profiles/r02_nccl_max_ctas.txt)
-RESERVED_SMS = 0    # SMs the backward kernels leave to concurrent all-reduces; UNETB200_RESERVE_SMS overrides
+# NCCL may use 8 CTAs and the backward kernels that run beside an all-reduce leave 8 SMs out of their grids
+# (profiles/r02_reserved_sms.txt, r02_nccl_max_ctas.txt); UNETB200_NCCL_MAX_CTAS / UNETB200_RESERVE_SMS override
+# (0 = NCCL's default / no reservation)
+NCCL_MAX_CTAS = 8
+RESERVED_SMS = 8
 
 
 def shard_range(batch_size, num_replicas, rank):
