@@ -35,9 +35,9 @@ def _batches(steps=STEPS):
     return [synthetic_batch(WORLD * N, H, W, seed=300 + i) for i in range(steps)]
 
 
-def _worker(rank, port, outdir, ups, graph):
+def _worker(rank, port, outdir, ups, graph, reserve):
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(WORLD),
-                      LOCAL_RANK=str(rank))
+                      LOCAL_RANK=str(rank), UNETB200_RESERVE_SMS=str(reserve))
     from unet_distributed_b200 import parallel
     from unet_distributed_b200.trainer import Trainer
     ws, rk, local = parallel.init_from_env("nccl")
@@ -99,12 +99,15 @@ def _single_gpu_reference(ups, device, steps=STEPS):
         (torch.stack(mets).cpu().numpy() if mets else None), shard_state
 
 
-@pytest.mark.parametrize("ups,graph", [(False, False), (False, True), (True, True)])
-def test_two_rank_step_equals_mean_of_shard_gradients(cuda_device, ups, graph):
+# reserve = SMs the backward kernels leave to NCCL (unetb200_set_reserved_sms). With a reservation the split-K factors of
+# the weight-gradient kernels differ from the single-GPU reference's, i.e. partial sums are added in another (still
+# fixed) order: bit-equality is required without it, 1e-5 with the default reservation.
+@pytest.mark.parametrize("ups,graph,reserve", [(False, False, 0), (False, True, 0), (True, True, 0), (False, True, 8)])
+def test_two_rank_step_equals_mean_of_shard_gradients(cuda_device, ups, graph, reserve):
     if torch.cuda.device_count() < WORLD:
         pytest.skip("needs two GPUs (gpurun --gpus 2)")
     with tempfile.TemporaryDirectory() as td:
-        mp.spawn(_worker, args=(_free_port(), td, ups, graph), nprocs=WORLD, join=True)
+        mp.spawn(_worker, args=(_free_port(), td, ups, graph, reserve), nprocs=WORLD, join=True)
         params = [np.load(os.path.join(td, f"params{r}.npy")) for r in range(WORLD)]
         grads = [np.load(os.path.join(td, f"grads{r}.npy")) for r in range(WORLD)]
         mets = [np.load(os.path.join(td, f"mets{r}.npy")) for r in range(WORLD)]
@@ -113,20 +116,26 @@ def test_two_rank_step_equals_mean_of_shard_gradients(cuda_device, ups, graph):
     np.testing.assert_array_equal(grads[0], grads[1])
     plan, want_sum, want_mets, shard_state = _single_gpu_reference(ups, cuda_device)
     for r in range(WORLD):   # each replica reported the dice loss of ITS shard
-        np.testing.assert_array_equal(mets[r], want_mets[:, r])
+        if reserve == 0:
+            np.testing.assert_array_equal(mets[r], want_mets[:, r])
+        else:
+            np.testing.assert_allclose(mets[r], want_mets[:, r], rtol=1e-4, atol=1e-5)
     # all-reduced sum == sum of the shard gradients (variables only: the padding between them is never written)
     for k, (off, shape) in plan.variables.items():
         n = int(np.prod(shape))
-        np.testing.assert_array_equal(grads[0][off:off + n], want_sum[off:off + n], err_msg=k)
+        if reserve == 0:
+            np.testing.assert_array_equal(grads[0][off:off + n], want_sum[off:off + n], err_msg=k)
+        else:
+            assert rel_err(grads[0][off:off + n], want_sum[off:off + n]) < 1e-4, k
     want_params = plan.params.cpu().numpy()
     bit_equal = np.array_equal(params[0], want_params)
     err = rel_err(params[0], want_params)
     out = os.environ.get("UNETB200_TEST_REPORT")
     if out:
         with open(out, "a") as f:
-            f.write(f"# 2-rank NCCL step vs single-GPU mean-of-shard-gradients, ups={ups} graph={graph}: parameters "
-                    f"bit-equal={bit_equal} rel_err={err:.3e} after {STEPS} steps\n")
-    assert err <= 1e-6 and bit_equal
+            f.write(f"# 2-rank NCCL step vs single-GPU mean-of-shard-gradients, ups={ups} graph={graph} "
+                    f"reserved_sms={reserve}: parameters bit-equal={bit_equal} rel_err={err:.3e} after {STEPS} steps\n")
+    assert err <= 1e-5 and (bit_equal or reserve > 0)
 
     # and the averaged gradient is the oracle's SyncReplicasOptimizer gradient (mean over replicas of the gradient of
     # each replica's own shard loss), at the bf16 bar: oracle backward evaluated at each shard's GPU forward state
