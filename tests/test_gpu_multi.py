@@ -101,7 +101,7 @@ def _single_gpu_reference(ups, device, steps=STEPS):
 
 # reserve = SMs the backward kernels leave to NCCL (unetb200_set_reserved_sms). With a reservation the split-K factors of
 # the weight-gradient kernels differ from the single-GPU reference's, i.e. partial sums are added in another (still
-# fixed) order: bit-equality is required without it, 1e-5 with the default reservation.
+# fixed) order: bit-equality is required without it, 1e-4 (parameter vector, relative) with the default reservation.
 @pytest.mark.parametrize("ups,graph,reserve", [(False, False, 0), (False, True, 0), (True, True, 0), (False, True, 8)])
 def test_two_rank_step_equals_mean_of_shard_gradients(cuda_device, ups, graph, reserve):
     if torch.cuda.device_count() < WORLD:
@@ -135,7 +135,7 @@ def test_two_rank_step_equals_mean_of_shard_gradients(cuda_device, ups, graph, r
         with open(out, "a") as f:
             f.write(f"# 2-rank NCCL step vs single-GPU mean-of-shard-gradients, ups={ups} graph={graph} "
                     f"reserved_sms={reserve}: parameters bit-equal={bit_equal} rel_err={err:.3e} after {STEPS} steps\n")
-    assert err <= 1e-5 and (bit_equal or reserve > 0)
+    assert err <= (1e-4 if reserve else 1e-6) and (bit_equal or reserve > 0)
 
     # and the averaged gradient is the oracle's SyncReplicasOptimizer gradient (mean over replicas of the gradient of
     # each replica's own shard loss), at the bf16 bar: oracle backward evaluated at each shard's GPU forward state
