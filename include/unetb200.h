@@ -252,6 +252,12 @@ int unetb200_plan_pack_range(unetb200_plan* plan, long long begin, long long end
  * kernels on the caller's stream in program order (used when timing kernels one at a time); returns the old setting.
  * No reference counterpart: TensorFlow's executor schedules independent ops concurrently on its own. */
 int unetb200_plan_side_stream(unetb200_plan* plan, int enable);
+/* By default every plan_backward segment ends with the caller's stream waiting for the segment's weight gradients.
+ * With defer_join enabled it does not: the dgrad chain of the next segment starts without waiting, and whoever
+ * consumes the gradients calls unetb200_plan_join(plan, stream) to make ITS stream (e.g. the one that all-reduces and
+ * updates a bucket) wait for all weight gradients enqueued so far. defer_join returns the previous setting. */
+int unetb200_plan_defer_join(unetb200_plan* plan, int enable);
+int unetb200_plan_join(unetb200_plan* plan, void* stream);
 
 #ifdef __cplusplus
 }

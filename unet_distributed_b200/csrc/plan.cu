@@ -73,6 +73,10 @@ struct unetb200_plan {
   cudaEvent_t ev[40];
   int n_ev = 0, ev_next = 0;
   bool use_side = true;
+  // deferred join: plan_backward does not make the caller's stream wait for the weight gradients at the end of a
+  // segment; whoever consumes the gradients calls unetb200_plan_join(plan, stream) on ITS stream (the trainer's
+  // update stream), so the dgrad chain never stalls on the side stream between segments
+  bool defer_join = false;
   int ch[5];
   int c4_out;      // channels of c[4] (conv5b)
   int dc_out[4];   // channels of dc[L] (conv{9-L}b)
@@ -413,13 +417,33 @@ int unetb200_plan_forward(unetb200_plan* P, const float* imgs, const float* msks
   const int N = P->N;
   const int dt = P->dt;
   const DropoutCfg no_drop{1.0f, 0, 0, nullptr};
-  // dropout keep bits of conv3a / conv4a for this forward: two small kernels up front instead of Philox in the conv
-  // epilogues (where it made conv3a's epilogue slower than its MMAs)
+  // dropout keep bits of conv3a / conv4a for this forward: two small kernels instead of Philox in the conv epilogues
+  // (where it made conv3a's epilogue slower than its MMAs). They run on the plan's second stream beside conv1a..conv2b
+  // (12 us each, Philox-bound); the main stream waits for them right before conv3a.
   static const bool inline_philox = getenv("UNETB200_INLINE_PHILOX") != nullptr;
-  for (int L = 2; L <= 3 && !inline_philox; ++L) {
-    if (P->drop_bits[L] == kNoGate) continue;
-    RC(dropout_keep_bits16(P->gate(P->drop_bits[L]), static_cast<long long>(N) * P->Hl(L) * P->Wl(L) * P->ch[L],
-                           1.0f - P->dropout, seed, seed_add, static_cast<unsigned>(L), s));
+  const bool bits_on_side = P->use_side && P->side != nullptr;
+  cudaEvent_t bits_done = nullptr;
+  bool any_bits = false;
+  for (int L = 2; L <= 3 && !inline_philox; ++L) any_bits = any_bits || P->drop_bits[L] != kNoGate;
+  if (any_bits) {
+    cudaStream_t bs = s;
+    if (bits_on_side) {
+      cudaEvent_t e = P->ev[P->ev_next];
+      P->ev_next = (P->ev_next + 1) % P->n_ev;
+      UB_CHECK_CUDA(cudaEventRecord(e, s));
+      UB_CHECK_CUDA(cudaStreamWaitEvent(P->side, e, 0));   // after whatever last read the bits (previous backward)
+      bs = P->side;
+    }
+    for (int L = 2; L <= 3; ++L) {
+      if (P->drop_bits[L] == kNoGate) continue;
+      RC(dropout_keep_bits16(P->gate(P->drop_bits[L]), static_cast<long long>(N) * P->Hl(L) * P->Wl(L) * P->ch[L],
+                             1.0f - P->dropout, seed, seed_add, static_cast<unsigned>(L), bs));
+    }
+    if (bits_on_side) {
+      bits_done = P->ev[P->ev_next];
+      P->ev_next = (P->ev_next + 1) % P->n_ev;
+      UB_CHECK_CUDA(cudaEventRecord(bits_done, P->side));
+    }
   }
   // encoder
   for (int L = 0; L < 5; ++L) {
@@ -429,6 +453,7 @@ int unetb200_plan_forward(unetb200_plan* P, const float* imgs, const float* msks
       RC(conv_first_fwd(imgs, P->W_(la), P->B_(la), P->at(P->a[0]), N, H, W, P->Cin, 32, s, P->gate(P->gt_a[0]), dt));
     } else {
       DropoutCfg d = no_drop;
+      if (L == 2 && bits_done) UB_CHECK_CUDA(cudaStreamWaitEvent(s, bits_done, 0));   // both layers' bits are ready
       if ((L == 2 || L == 3) && P->dropout > 0.0f) {
         d = DropoutCfg{1.0f - P->dropout, seed, static_cast<unsigned>(L), seed_add,
                        inline_philox ? nullptr : P->gate(P->drop_bits[L])};
@@ -508,7 +533,7 @@ int unetb200_plan_backward(unetb200_plan* P, const float* imgs, const float* msk
   };
   // join: the main stream waits for all weight gradients enqueued so far (end of every segment)
   auto join = [&]() -> int {
-    if (!side_on) return UB_OK;
+    if (!side_on || P->defer_join) return UB_OK;
     cudaEvent_t e = P->ev[P->ev_next];
     P->ev_next = (P->ev_next + 1) % P->n_ev;
     UB_CHECK_CUDA(cudaEventRecord(e, w));
@@ -613,6 +638,22 @@ int unetb200_plan_backward(unetb200_plan* P, const float* imgs, const float* msk
   }
   RC(join());
   return UB_OK;
+}
+
+// Make `stream` wait for every weight gradient enqueued so far (see defer_join).
+int unetb200_plan_join(unetb200_plan* P, void* stream) {
+  if (!(P->use_side && P->side != nullptr)) return UB_OK;
+  cudaEvent_t e = P->ev[P->ev_next];
+  P->ev_next = (P->ev_next + 1) % P->n_ev;
+  UB_CHECK_CUDA(cudaEventRecord(e, P->side));
+  UB_CHECK_CUDA(cudaStreamWaitEvent(reinterpret_cast<cudaStream_t>(stream), e, 0));
+  return UB_OK;
+}
+
+int unetb200_plan_defer_join(unetb200_plan* P, int enable) {
+  const int old = P->defer_join ? 1 : 0;
+  P->defer_join = enable != 0;
+  return old;
 }
 
 int unetb200_plan_side_stream(unetb200_plan* P, int enable) {

@@ -179,6 +179,15 @@ class UNetPlan:
         """Run weight gradients on the plan's second stream (default) or in program order; returns the old setting."""
         return bool(_lib.lib().unetb200_plan_side_stream(self._h, 1 if enable else 0))
 
+    def defer_join(self, enable):
+        """Segments of backward() stop ending with a wait for their weight gradients; call join() on the stream that
+        consumes the gradients instead (see unetb200_plan_defer_join). Returns the old setting."""
+        return bool(_lib.lib().unetb200_plan_defer_join(self._h, 1 if enable else 0))
+
+    def join(self):
+        """Make the CURRENT stream wait for every weight gradient enqueued so far."""
+        _lib.call("unetb200_plan_join", self._h, _stream())
+
     def pack_weights(self, begin=None, end=None):
         """Refresh the packed bf16 GEMM operands from the fp32 masters: all of them, or only the variables inside the
         flat range [begin, end) (one gradient bucket)."""

@@ -71,16 +71,20 @@ class Trainer:
         upd = self._upd_stream
         p.forward(imgs, msks, seed=self.dropout_seed, seed_add=self.step_dev)
         lib = _lib.lib()
+        # the dgrad chain does not wait for the weight gradients between segments: the update stream does
+        old_defer = p.defer_join(True)
         for seg in range(p.num_segments):
             # from the second segment on, an all-reduce runs beside the backward kernels: leave it its SMs
             lib.unetb200_set_reserved_sms(self.reserved_sms if (self.world > 1 and seg > 0) else 0)
             p.backward(imgs, msks, grad_scale=1.0, segment=seg)
             upd.wait_stream(cur)
             with torch.cuda.stream(upd):
+                p.join()                                       # ... and behind the segment's weight gradients
                 # the all-reduce is ordered behind the segment through the update stream; `cur` does not wait for it
                 self.reducer.reduce_now(seg)
                 self._update_range(*p.buckets[seg])
         lib.unetb200_set_reserved_sms(0)
+        p.defer_join(old_defer)
         with torch.cuda.stream(upd):
             _lib.call("unetb200_step_increment", _ptr(self.step_dev), _stream())
         cur.wait_stream(upd)
