@@ -84,8 +84,8 @@ __device__ __forceinline__ int sched_consume(TileSched* s, SchedCursor& c, int* 
   return t;
 }
 
-// Host: a zeroed {next, done} counter pair on the current device for one launch (nullptr when dynamic scheduling is
-// switched off with UNETB200_STATIC_TILES=1). Slots come round-robin from a static device array; a kernel re-arms its
+// Host: a zeroed {next, done} counter pair on the current device for one launch, or nullptr = static walk (the default;
+// UNETB200_DYNAMIC_TILES=1 turns the scheduler on). Slots come round-robin from a static device array; a kernel re-arms its
 // slot when it finishes, and far fewer kernels are ever in flight than there are slots.
 int* sched_counter_slot();
 
