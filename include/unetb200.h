@@ -6,7 +6,8 @@
  * allocates or frees caller memory.
  *
  * Conventions
- *   - all pointers are DEVICE pointers unless the name ends in _host; activations are NHWC bf16 (16-byte aligned),
+ *   - all pointers are DEVICE pointers unless the name ends in _host; activations are NHWC bf16 (16-byte aligned) --
+ *     or, through the `_dt` entry points with UNETB200_TF32, NHWC fp32 holding tf32-rounded values --
  *     master weights / gradients / optimizer state are fp32 in the TensorFlow variable layouts
  *     (Conv2D kernel [kh][kw][Cin][Cout]; Conv2DTranspose kernel [kh][kw][Cout][Cin]);
  *   - `stream` is a cudaStream_t passed as void*; every call is asynchronous on it and never synchronises;
