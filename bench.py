@@ -46,6 +46,9 @@ def parse_args():
     p.add_argument("--const_learningrate", type=int, default=1)
     p.add_argument("--decay_steps", type=int, default=100)
     p.add_argument("--lr_fraction", type=float, default=0.2)
+    p.add_argument("--precision", type=str, default="bf16", choices=["bf16", "tf32"],
+                   help="bf16 (the headline) or the fp32/tf32 mode; for tf32 the tensor peak is a cuBLAS tf32 GEMM "
+                        "measured in this process (MEASURED_PEAKS.json has no tf32 number)")
     return p.parse_args()
 
 
@@ -172,7 +175,7 @@ def workload_config(args, world):
         "workload": f"UNet {S}x{S}x{C} {args.decoder} decoder (BASELINE configs[{cfg_index}] shape), "
                     f"bs{N} per GPU, Adam, dropout 0.2, train step fwd+dice+bwd+allreduce+Adam",
         "decoder": args.decoder, "per_gpu_batch": N, "global_batch": N * world, "image": [S, S, C],
-        "parallelism": f"dp{world}", "const_learningrate": bool(args.const_learningrate),
+        "parallelism": f"dp{world}", "const_learningrate": bool(args.const_learningrate), "precision": args.precision,
         "cuda_graph": bool(not args.no_graph),
         "l2": "no explicit flush: one step touches >2.5 GB of activations and gradients (L2 is 126 MB); "
               "input batches rotate"}
@@ -259,7 +262,7 @@ def measure_decoder(args, decoder, world, rank, dev, sampler, with_roofline):
     ups = decoder == "upsampling"
     tr = Trainer(N, S, S, C, 1, ups, dropout=0.2, learning_rate=0.0005,
                  const_learningrate=bool(args.const_learningrate), lr_fraction=args.lr_fraction,
-                 decay_steps=args.decay_steps, use_cuda_graph=(not args.no_graph))
+                 decay_steps=args.decay_steps, use_cuda_graph=(not args.no_graph), precision=args.precision)
     # synthetic batches: a few distinct ones per rank, rotated (inputs are far smaller than the per-step working set)
     nb = 4
     base_imgs, base_msks = make_slices(min(N, 64), S, S, C, seed=816 + rank)
@@ -383,6 +386,29 @@ def measure_decoder(args, decoder, world, rank, dev, sampler, with_roofline):
     return out
 
 
+def measure_tf32_gemm_tflops(dev):
+    """Denominator for the fp32/tf32 mode: torch.matmul (cuBLAS) on fp32 8192^3 with tf32 allowed, best of 10."""
+    import torch
+    old = torch.backends.cuda.matmul.allow_tf32
+    torch.backends.cuda.matmul.allow_tf32 = True
+    try:
+        a = torch.randn(8192, 8192, device=dev)
+        b = torch.randn(8192, 8192, device=dev)
+        for _ in range(3):
+            a @ b
+        best = float("inf")
+        for _ in range(10):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            a @ b
+            e1.record()
+            torch.cuda.synchronize()
+            best = min(best, e0.elapsed_time(e1))
+        return 2.0 * 8192 ** 3 / (best * 1e-3) / 1e12
+    finally:
+        torch.backends.cuda.matmul.allow_tf32 = old
+
+
 def run_b200(args):
     import torch
     import torch.distributed as dist
@@ -415,6 +441,10 @@ def run_b200(args):
         ig_ms, ig_fl, ig_by, ig_n = roof["igemm"]
         wg_ms, wg_fl, wg_by, wg_n = roof["wgrad"]
         peak_tf = float(peaks.get("bf16_tflops_sustained", FALLBACK_PEAKS["bf16_tflops_sustained"]))
+        peak_src = "bf16_tflops_sustained, " + peaks["_source"]
+        if args.precision == "tf32":
+            peak_tf = measure_tf32_gemm_tflops(dev)
+            peak_src = "cuBLAS tf32 GEMM 8192^3 measured in this process (best of 10), no MEASURED_PEAKS.json entry"
         achieved = ig_fl / (ig_ms * 1e-3) / 1e12 if ig_ms > 0 else 0.0
         traffic = None
         tpath = os.path.join(ROOT, "profiles", "traffic.json")
@@ -427,7 +457,7 @@ def run_b200(args):
         line = {
             "metric": "train images/sec", "value": value, "unit": "images/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
-            "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+            "vs_baseline": None, "dtype": args.precision, "data": "synthetic",
             "config": cfg,
             "clocks": clocks,
             "e2e": {"value": e2e_value, "unit": "images/s", "ms_per_step": ms_e2e_step,
@@ -440,7 +470,7 @@ def run_b200(args):
                           "implicit GEMM; every launch of the class in a step)",
                 "bound": "tensor", "achieved": achieved, "peak": peak_tf, "unit": "TFLOP/s",
                 "frac": achieved / peak_tf if peak_tf else None, "traffic": traffic,
-                "peak_source": "bf16_tflops_sustained, " + peaks["_source"],
+                "peak_source": peak_src,
                 "launches_per_step": ig_n / roof["steps"], "ms_per_step": ig_ms / roof["steps"],
                 "alg_gbs": (ig_by / (ig_ms * 1e-3) / 1e9 if ig_ms > 0 else 0.0),
                 "hbm_peak_gbs": float(peaks.get("hbm_gbs", FALLBACK_PEAKS.get("hbm_gbs", 0.0))),
