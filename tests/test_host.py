@@ -185,3 +185,41 @@ def test_resident_epochs_match_get_epoch():
             np.testing.assert_array_equal(ys.numpy(), ep[b, 1][s:e])
     res.shuffle(1235)
     assert not np.array_equal(res.batch(0)[0].numpy(), ep[0, 0])
+
+
+def test_bench_reference_arm_line(tmp_path):
+    """bench.py --impl reference (the CPU restatement timed on the host cores) prints ONE JSON line with the contract's
+    keys, and its `config` is the GPU arm's config for the same arguments (same_config in the driver's comparison)."""
+    import json
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    out = subprocess.run([sys.executable, os.path.join(root, "bench.py"), "--impl", "reference", "--steps", "1",
+                          "--warmup", "1", "--batch", "2", "--size", "32"], capture_output=True, text=True, timeout=300)
+    assert out.returncode == 0, out.stderr[-2000:]
+    lines = [ln for ln in out.stdout.splitlines() if ln.strip()]
+    assert len(lines) == 1
+    d = json.loads(lines[0])
+    for k in ("impl", "metric", "value", "unit", "n_gpus", "steps", "warmup", "ms_per_step", "higher_is_better",
+              "scaling", "vs_baseline", "dtype", "data", "config", "cpu_baseline", "e2e"):
+        assert k in d, k
+    assert d["impl"] == "reference" and d["higher_is_better"] is True and d["vs_baseline"] is None
+    assert d["cpu_baseline"]["kind"] == "port" and d["cpu_baseline"]["cores"] >= 1 and "cpu_model" in d["cpu_baseline"]
+    assert d["e2e"]["h2d_bytes_per_step"] == 0 and d["e2e"]["value"] == d["value"] > 0
+    sys.path.insert(0, root)
+    import argparse
+    import bench
+    ns = argparse.Namespace(batch=2, size=32, channels=1, decoder="upsampling", const_learningrate=1, no_graph=False,
+                            precision="bf16")
+    assert d["config"] == bench.workload_config(ns, 1)
+
+
+def test_tf32_rounding_of_the_oracle_twin():
+    """oracle._tf32_round = PTX cvt.rna.tf32.f32: nearest value with a 10-bit mantissa, ties away from zero."""
+    import torch
+    x = torch.tensor([1.0, 1.0 + 2.0 ** -11, 1.0 + 2.0 ** -11 - 2.0 ** -20, -(1.0 + 3 * 2.0 ** -11), 3.0e-5, 65504.0])
+    r = O._tf32_round(x)
+    want = torch.tensor([1.0, 1.0 + 2.0 ** -10, 1.0, -(1.0 + 2.0 ** -9)])
+    assert torch.equal(r[:4], want) and float(r[5]) == 65504.0
+    assert bool(((r.view(torch.int32) & 0x1FFF) == 0).all())
+    assert float(((r - x).abs() / x.abs()).max()) <= 2.0 ** -11 + 1e-9
