@@ -63,6 +63,7 @@ def init_from_env(backend=None):
             opts = dist.ProcessGroupNCCL.Options()
             opts.config.max_ctas = max_ctas
             opts.config.min_ctas = 1
+            opts._timeout = datetime.timedelta(seconds=int(os.environ.get("UNETB200_DIST_TIMEOUT", "180")))
             kw["pg_options"] = opts
         # a mismatched collective should fail in minutes, not after the 10-minute default
         dist.init_process_group(backend=backend, rank=rank, world_size=ws,
