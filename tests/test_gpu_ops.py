@@ -346,8 +346,8 @@ from unet_distributed_b200.plan import UNetPlan
 torch.cuda.set_device(0)
 out = {}
 for ups in (False, True):
-    imgs, msks = synthetic_batch(6, 128, 128)
-    plan = UNetPlan(6, 128, 128, 1, 1, ups, 0.2)
+    imgs, msks = synthetic_batch(12, 128, 128)          # 192 row-pair tiles at the 128x128 level: more than 148 SMs
+    plan = UNetPlan(12, 128, 128, 1, 1, ups, 0.2)
     plan.set_weights(O.init_weights(3, ups))
     d_i, d_m = torch.tensor(imgs, device="cuda"), torch.tensor(msks, device="cuda")
     plan.grads.zero_()
