@@ -7,6 +7,8 @@
 #include <utility>
 #include <vector>
 
+#include <nvtx3/nvToolsExt.h>
+
 #include "../../include/unetb200.h"
 #include "common.h"
 #include "elementwise.cuh"
@@ -39,6 +41,13 @@ struct Layer {
 constexpr size_t kAlign = 1024;
 constexpr int kSegments = 5;   // backward segments = gradient buckets
 constexpr size_t kNoGate = ~static_cast<size_t>(0);
+
+// NVTX range over one host-side launch sequence (forward, a backward segment): shows up in ncu / Nsight timelines,
+// costs nothing without a tool attached (header-only NVTX v3).
+struct NvtxRange {
+  explicit NvtxRange(const char* name) { nvtxRangePushA(name); }
+  ~NvtxRange() { nvtxRangePop(); }
+};
 
 }  // namespace
 
@@ -413,6 +422,7 @@ int unetb200_plan_pack_weights(unetb200_plan* P, void* stream) {
 int unetb200_plan_forward(unetb200_plan* P, const float* imgs, const float* msks, uint64_t seed,
                           const long long* seed_add, void* stream) {
   UB_REQUIRE(P->arena, "plan_forward: plan is not bound");
+  NvtxRange nvtx_range("unetb200.plan_forward");
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
   const int N = P->N;
   const int dt = P->dt;
@@ -512,6 +522,12 @@ int unetb200_plan_backward(unetb200_plan* P, const float* imgs, const float* msk
                            float grad_scale, int segment, void* stream) {
   UB_REQUIRE(P->arena, "plan_backward: plan is not bound");
   UB_REQUIRE(segment >= 0 && segment < kSegments, "plan_backward: segment %d outside 0..%d", segment, kSegments - 1);
+  static const char* const kSegNames[kSegments] = {"unetb200.plan_backward.seg0_head_conv9_conv8",
+                                                   "unetb200.plan_backward.seg1_conv7_conv6",
+                                                   "unetb200.plan_backward.seg2_conv5",
+                                                   "unetb200.plan_backward.seg3_conv4_conv3",
+                                                   "unetb200.plan_backward.seg4_conv2_conv1"};
+  NvtxRange nvtx_range(kSegNames[segment]);
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
   const int N = P->N;
   const int dt = P->dt;
