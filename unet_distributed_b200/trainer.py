@@ -47,7 +47,10 @@ class Trainer:
         if self.world > 1:
             p.pack_weights()
         self.reducer = parallel.BucketedAllReduce(p.grads, p.buckets)
-        self._upd_stream = torch.cuda.Stream(device=dev)   # bucket updates run here, beside the rest of backward
+        # bucket updates (all-reduce wait, Adam, re-pack) run here, beside the rest of backward, at high priority: they
+        # are short and the next step's forward waits for the last of them (UNETB200_UPD_PRIORITY=same turns it off)
+        self._upd_stream = torch.cuda.Stream(device=dev,
+                                             priority=0 if os.environ.get("UNETB200_UPD_PRIORITY") == "same" else -1)
         # SMs left to the NCCL kernels that run beside backward segments 1..4 (see unetb200_set_reserved_sms)
         self.reserved_sms = int(os.environ.get("UNETB200_RESERVE_SMS", str(parallel.RESERVED_SMS)))
         self.use_cuda_graph = bool(use_cuda_graph)
