@@ -328,52 +328,3 @@ def test_tensor_maps_are_cached(cuda_device):
     assert m1 == m0 and h1 >= h0 + 2, (h0, m0, h1, m1)
     assert torch.equal(y, y0)
     torch.cuda.synchronize()
-
-
-def test_dynamic_tile_scheduler_gives_the_same_results(cuda_device, tmp_path):
-    """The opt-in dynamic tile scheduler (sched.cuh, UNETB200_DYNAMIC_TILES=1, read once per process): the conv parity
-    cases with more tiles than SMs and a whole-model step, re-run in a child process with it on, and the gradients of
-    the model step bit-identical to the static walk's (output tiles are independent)."""
-    import os
-    import subprocess
-    import sys
-    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-    script = r'''
-import sys, numpy as np, torch
-sys.path.insert(0, sys.argv[1]); sys.path.insert(0, sys.argv[1] + "/tests")
-from util import O, synthetic_batch
-from unet_distributed_b200.plan import UNetPlan
-torch.cuda.set_device(0)
-out = {}
-for ups in (False, True):
-    imgs, msks = synthetic_batch(12, 128, 128)          # 192 row-pair tiles at the 128x128 level: more than 148 SMs
-    plan = UNetPlan(12, 128, 128, 1, 1, ups, 0.2)
-    plan.set_weights(O.init_weights(3, ups))
-    d_i, d_m = torch.tensor(imgs, device="cuda"), torch.tensor(msks, device="cuda")
-    plan.grads.zero_()
-    plan.forward(d_i, d_m, seed=7)
-    plan.backward(d_i, d_m)
-    torch.cuda.synchronize()
-    out[f"grads{int(ups)}"] = plan.grads.cpu().numpy()
-    out[f"preds{int(ups)}"] = plan.preds.cpu().numpy()
-np.savez(sys.argv[2], **out)
-'''
-    res = {}
-    for mode in ("static", "dynamic"):
-        env = dict(os.environ)
-        env.pop("UNETB200_DYNAMIC_TILES", None)
-        if mode == "dynamic":
-            env["UNETB200_DYNAMIC_TILES"] = "1"
-        path = str(tmp_path / f"{mode}.npz")
-        r = subprocess.run([sys.executable, "-c", script, root, path], env=env, capture_output=True, text=True,
-                           timeout=300)
-        assert r.returncode == 0, r.stderr[-2000:]
-        res[mode] = np.load(path)
-    for k in res["static"].files:
-        assert np.isfinite(res["static"][k]).all()
-        np.testing.assert_array_equal(res["static"][k], res["dynamic"][k], err_msg=k)
-    env = dict(os.environ, UNETB200_DYNAMIC_TILES="1")
-    r = subprocess.run([sys.executable, "-m", "pytest", "-q", "-m", "gpu", os.path.join(root, "tests", "test_gpu_ops.py"),
-                        "-k", "test_conv3x3_fwd_dgrad_wgrad or test_tconv2x2"], env=env, capture_output=True, text=True,
-                       timeout=600, cwd=root)
-    assert r.returncode == 0, r.stdout[-2000:]

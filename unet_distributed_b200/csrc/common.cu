@@ -1,5 +1,4 @@
 #include "common.h"
-#include "sched.cuh"
 
 #include <atomic>
 #include <cstdarg>
@@ -212,32 +211,6 @@ int unetb200_profile_collect(double* ms, double* flops, double* bytes, long long
 
 namespace {
 std::atomic<int> g_reserved_sms{0};
-constexpr int kSchedSlots = 512;
-__device__ int g_sched_counters[2 * kSchedSlots];   // zero-initialised; every kernel re-arms its pair when it ends
-std::atomic<unsigned> g_sched_next{0};
-int* g_sched_base[64] = {nullptr};
-std::mutex g_sched_mu;
-}
-
-int* sched_counter_slot() {
-  // Opt-in (UNETB200_DYNAMIC_TILES=1). Measured on one GPU (r02, same box): 2.611 ms/step dynamic vs 2.600 static --
-  // the draw costs ~1.3 % of the conv kernels' own time and the late-CTA delays it removes are small there.
-  static const bool on = getenv("UNETB200_DYNAMIC_TILES") != nullptr;
-  if (!on) return nullptr;
-  int dev = 0;
-  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return nullptr;
-  int* base = g_sched_base[dev];
-  if (!base) {   // first use on this device (never inside a stream capture: the trainer warms up before capturing)
-    std::lock_guard<std::mutex> lk(g_sched_mu);
-    if (!g_sched_base[dev]) {
-      void* p = nullptr;
-      if (cudaGetSymbolAddress(&p, g_sched_counters) != cudaSuccess) return nullptr;
-      g_sched_base[dev] = static_cast<int*>(p);
-    }
-    base = g_sched_base[dev];
-  }
-  const unsigned slot = g_sched_next.fetch_add(1, std::memory_order_relaxed) % kSchedSlots;
-  return base + 2 * slot;
 }
 
 int set_reserved_sms(int n) {

@@ -4,7 +4,6 @@
 
 #include "common.h"
 #include "ptx.cuh"
-#include "sched.cuh"
 
 namespace ub {
 
@@ -23,7 +22,6 @@ struct __align__(8) HaloBarriers {
   uint64_t b_empty[kMaxBStages];
   uint64_t tmem_full[2];
   uint64_t tmem_empty[2];
-  TileSched sched;   // dynamic tile scheduler ring (sched.cuh)
   uint32_t tmem_base;
 };
 
@@ -82,10 +80,7 @@ __device__ __forceinline__ void halo_mma_role(const HaloParams& p, HaloBarriers*
   uint32_t hphase = 0, bphase = 0;
   unsigned long long t_e = 0, t_h = 0, t_b = 0;
   const long long t_mma0 = clock64();
-  SchedCursor sc;
-  const int sched_lane = static_cast<int>(threadIdx.x & 31);
-  for (int tile = sched_consume(&bars->sched, sc, p.tile_ctr, num_tiles, true, sched_lane); tile >= 0;
-       tile = sched_consume(&bars->sched, sc, p.tile_ctr, num_tiles, true, sched_lane), ++it) {
+  for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
     const int a = p.acc_double ? (it & 1) : 0;
     const uint32_t eparity = p.acc_double ? (((it >> 1) & 1) ^ 1u) : ((it & 1) ^ 1u);
     timed_wait(&bars->tmem_empty[a], eparity, p.timing != 0, t_e);
@@ -159,10 +154,7 @@ __device__ __forceinline__ void halo_epilogue(const HaloParams& p, HaloBarriers*
   int it = 0;
   unsigned long long t_wait = 0;
   const long long t_begin = clock64();
-  SchedCursor sc;
-  const int sched_lane = static_cast<int>(threadIdx.x & 31);
-  for (int tile = sched_consume(&bars->sched, sc, p.tile_ctr, num_tiles, true, sched_lane); tile >= 0;
-       tile = sched_consume(&bars->sched, sc, p.tile_ctr, num_tiles, true, sched_lane), ++it) {
+  for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
     const int a = p.acc_double ? (it & 1) : 0;
     const uint32_t fparity = p.acc_double ? ((it >> 1) & 1) : (it & 1);
     int n, h0, w0, nt;
@@ -369,10 +361,7 @@ __device__ __forceinline__ void halo_epilogue_fast(const HaloParams& p, HaloBarr
   int it = 0;
   unsigned long long t_wait = 0;
   const long long t_begin = clock64();
-  SchedCursor sc;
-  const int sched_lane = static_cast<int>(threadIdx.x & 31);
-  for (int tile = sched_consume(&bars->sched, sc, p.tile_ctr, num_tiles, true, sched_lane); tile >= 0;
-       tile = sched_consume(&bars->sched, sc, p.tile_ctr, num_tiles, true, sched_lane), ++it) {
+  for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
     const int a = p.acc_double ? (it & 1) : 0;
     const uint32_t fparity = p.acc_double ? ((it >> 1) & 1) : (it & 1);
     int n, h0, w0, nt;
@@ -551,7 +540,6 @@ conv_halo_kernel(const __grid_constant__ HaloParams p, const __grid_constant__ C
       mbar_init(&bars->tmem_full[a], 1);
       mbar_init(&bars->tmem_empty[a], 8);
     }
-    sched_init(&bars->sched, 1 + 1 + 8);   // consumers: MMA warp, weight producer, eight epilogue warps
     mbar_fence_init();
     tma_prefetch_desc(&tmA0);
     if (p.num_src > 1) tma_prefetch_desc(&tmA1);
@@ -572,9 +560,7 @@ conv_halo_kernel(const __grid_constant__ HaloParams p, const __grid_constant__ C
       int hs = 0;
       uint32_t hphase = 0;
       unsigned long long t_prod = 0;
-      SchedCursor sc;
-      for (int tile = sched_produce(&bars->sched, sc, p.tile_ctr, num_tiles); tile >= 0;
-           tile = sched_produce(&bars->sched, sc, p.tile_ctr, num_tiles)) {
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
         int n, h0, w0, nt;
         decode_tile(p, tile, n, h0, w0, nt);
         for (int src = 0; src < p.num_src; ++src) {
@@ -597,9 +583,7 @@ conv_halo_kernel(const __grid_constant__ HaloParams p, const __grid_constant__ C
     if (lane == 0) {
       int bs = 0;
       uint32_t bphase = 0;
-      SchedCursor sc;
-      for (int tile = sched_consume(&bars->sched, sc, p.tile_ctr, num_tiles, false, 0); tile >= 0;
-           tile = sched_consume(&bars->sched, sc, p.tile_ctr, num_tiles, false, 0)) {
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
         const int nt = tile % p.n_tiles;
         for (int src = 0; src < p.num_src; ++src) {
           for (int cb = 0; cb < p.src_kblocks[src]; ++cb) {
@@ -778,7 +762,6 @@ int halo_launch(const HaloParams& p_in, const CUtensorMap& a0, const CUtensorMap
   }
   int grid = device_sm_count();
   if (grid > num_tiles) grid = num_tiles;
-  p.tile_ctr = num_tiles > grid ? sched_counter_slot() : nullptr;
   if (profiling_enabled()) {
     const double pixels = static_cast<double>(p.N) * p.H * p.W;
     const double kdim = 9.0 * p.kc * (p.src_kblocks[0] + (p.num_src > 1 ? p.src_kblocks[1] : 0));

@@ -30,7 +30,6 @@ struct HaloParams {
   int b_stages;
   int h_stages;           // halo ring depth (2..4)
   int timing;             // debug: accumulate per-role wait cycles (UNETB200_HALO_TIMING)
-  int* tile_ctr;          // set by the launchers: dynamic tile scheduler counters (sched.cuh), null = static walk
   int acc_double;         // two accumulator sets: epilogue overlaps the next super-tile's MMAs
   int fast_epi;           // set by halo_launch: 0 generic epilogue, 1 forward, 2 dgrad, 3 dgrad split at block_n/2,
                           // 4 = 3 with destination 0 summed 2x2 onto the coarse grid

@@ -22,7 +22,6 @@
 
 #include "common.h"
 #include "ptx.cuh"
-#include "sched.cuh"
 
 namespace ub {
 
@@ -40,7 +39,6 @@ struct __align__(8) RpBarriers {
   uint64_t b_empty[4];
   uint64_t tmem_full[2];
   uint64_t tmem_empty[2];
-  TileSched sched;   // dynamic tile scheduler ring (sched.cuh)
   uint32_t tmem_base;
 };
 
@@ -87,10 +85,7 @@ __device__ __forceinline__ void rp_mma_role(const HaloParams& p, RpBarriers* bar
   const int total_kb = p.src_kblocks[0] + (p.num_src > 1 ? p.src_kblocks[1] : 0);
   int hs = 0, bs = 0, it = 0;
   uint32_t hphase = 0, bphase = 0;
-  SchedCursor sc;
-  const int sched_lane = static_cast<int>(threadIdx.x & 31);
-  for (int tile = sched_consume(&bars->sched, sc, p.tile_ctr, num_tiles, true, sched_lane); tile >= 0;
-       tile = sched_consume(&bars->sched, sc, p.tile_ctr, num_tiles, true, sched_lane), ++it) {
+  for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
     const int a = p.acc_double ? (it & 1) : 0;
     const uint32_t eparity = p.acc_double ? (((it >> 1) & 1) ^ 1u) : ((it & 1) ^ 1u);
     mbar_wait(&bars->tmem_empty[a], eparity);
@@ -190,10 +185,7 @@ __device__ __forceinline__ void rp_epilogue(const HaloParams& p, RpBarriers* bar
     grow[sl] = static_cast<uint32_t>((p.W * gc) >> 4);                    // one image row, gate words
   }
   int it = 0;
-  SchedCursor sc;
-  const int sched_lane = static_cast<int>(threadIdx.x & 31);
-  for (int tile = sched_consume(&bars->sched, sc, p.tile_ctr, num_tiles, true, sched_lane); tile >= 0;
-       tile = sched_consume(&bars->sched, sc, p.tile_ctr, num_tiles, true, sched_lane), ++it) {
+  for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
     const int a = p.acc_double ? (it & 1) : 0;
     const uint32_t fparity = p.acc_double ? ((it >> 1) & 1) : (it & 1);
     int n, h0, w0;
@@ -365,7 +357,6 @@ conv_halo_rp_kernel(const __grid_constant__ HaloParams p, const __grid_constant_
       mbar_init(&bars->tmem_full[a], 1);
       mbar_init(&bars->tmem_empty[a], 8);
     }
-    sched_init(&bars->sched, 1 + 1 + 8);   // consumers: MMA warp, weight producer, eight epilogue warps
     mbar_fence_init();
     tma_prefetch_desc(&tmA0);
     if (p.num_src > 1) tma_prefetch_desc(&tmA1);
@@ -385,9 +376,7 @@ conv_halo_rp_kernel(const __grid_constant__ HaloParams p, const __grid_constant_
     if (lane == 0) {
       int hs = 0;
       uint32_t hphase = 0;
-      SchedCursor sc;
-      for (int tile = sched_produce(&bars->sched, sc, p.tile_ctr, num_tiles); tile >= 0;
-           tile = sched_produce(&bars->sched, sc, p.tile_ctr, num_tiles)) {
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
         int n, h0, w0;
         decode_tile(p, tile, n, h0, w0);
         for (int src = 0; src < p.num_src; ++src) {
@@ -407,9 +396,7 @@ conv_halo_rp_kernel(const __grid_constant__ HaloParams p, const __grid_constant_
       int bs = 0;
       uint32_t bphase = 0;
       const int sgroups = 9 / p.tpb;
-      SchedCursor sc;
-      for (int tile = sched_consume(&bars->sched, sc, p.tile_ctr, num_tiles, false, 0); tile >= 0;
-           tile = sched_consume(&bars->sched, sc, p.tile_ctr, num_tiles, false, 0)) {
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
         for (int src = 0; src < p.num_src; ++src) {
           for (int cb = 0; cb < p.src_kblocks[src]; ++cb) {
             for (int sg = 0; sg < sgroups; ++sg) {
@@ -536,9 +523,8 @@ int halo_rp_epilogue_code(const HaloParams& p) {
   return 0;
 }
 
-int halo_rp_launch(const HaloParams& p_in, const CUtensorMap& a0, const CUtensorMap& a1, const CUtensorMap& b,
+int halo_rp_launch(const HaloParams& p, const CUtensorMap& a0, const CUtensorMap& a1, const CUtensorMap& b,
                    cudaStream_t stream) {
-  HaloParams p = p_in;
   UB_REQUIRE(p.rp == 1 && p.fast_epi >= 1 && p.fast_epi <= 5, "conv_halo_rp: not a row-pair plan");
   const size_t smem = rp_smem_bytes(p);
   UB_REQUIRE(smem <= 227 * 1024, "conv_halo_rp: %zu bytes of shared memory requested", smem);
@@ -553,7 +539,6 @@ int halo_rp_launch(const HaloParams& p_in, const CUtensorMap& a0, const CUtensor
   UB_REQUIRE(num_tiles > 0, "conv_halo_rp: empty problem");
   int grid = device_sm_count();
   if (grid > num_tiles) grid = num_tiles;
-  p.tile_ctr = num_tiles > grid ? sched_counter_slot() : nullptr;
   if (profiling_enabled()) {
     const double pixels = static_cast<double>(p.N) * p.H * p.W;
     const double kdim = 9.0 * p.kc * (p.src_kblocks[0] + (p.num_src > 1 ? p.src_kblocks[1] : 0));

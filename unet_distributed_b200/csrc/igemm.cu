@@ -4,7 +4,6 @@
 
 #include "common.h"
 #include "ptx.cuh"
-#include "sched.cuh"
 
 namespace ub {
 
@@ -19,7 +18,6 @@ struct __align__(8) IgemmBarriers {
   uint64_t empty[kMaxStages];
   uint64_t tmem_full[2];
   uint64_t tmem_empty[2];
-  TileSched sched;
   uint32_t tmem_base;
 };
 
@@ -64,7 +62,6 @@ igemm_kernel(const __grid_constant__ IgemmParams p, const __grid_constant__ CUte
       mbar_init(&bars->tmem_full[a], 1);
       mbar_init(&bars->tmem_empty[a], 8);
     }
-    sched_init(&bars->sched, 1 + 8);   // consumers: the MMA warp and the eight epilogue warps
     mbar_fence_init();
     tma_prefetch_desc(&tmA0);
     if (p.num_src > 1) tma_prefetch_desc(&tmA1);
@@ -84,9 +81,7 @@ igemm_kernel(const __grid_constant__ IgemmParams p, const __grid_constant__ CUte
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
-      SchedCursor sc;
-      for (int tile = sched_produce(&bars->sched, sc, p.tile_ctr, num_tiles); tile >= 0;
-           tile = sched_produce(&bars->sched, sc, p.tile_ctr, num_tiles)) {
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
         int n0, h0, w0, nt;
         decode_tile(p, tile, n0, h0, w0, nt);
         for (int tap = 0; tap < p.taps_r * p.taps_s; ++tap) {
@@ -122,9 +117,7 @@ igemm_kernel(const __grid_constant__ IgemmParams p, const __grid_constant__ CUte
     int stage = 0;
     uint32_t phase = 0;
     int it = 0;
-    SchedCursor sc;
-    for (int tile = sched_consume(&bars->sched, sc, p.tile_ctr, num_tiles, true, lane); tile >= 0;
-         tile = sched_consume(&bars->sched, sc, p.tile_ctr, num_tiles, true, lane), ++it) {
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
       const int acc = it & 1;
       mbar_wait(&bars->tmem_empty[acc], (((it >> 1) & 1) ^ 1u));
       tc_fence_after();
@@ -169,9 +162,7 @@ igemm_kernel(const __grid_constant__ IgemmParams p, const __grid_constant__ CUte
     const int tn = m / (p.TW * p.TH);
     const IgemmEpilogue& e = p.epi;
     int it = 0;
-    SchedCursor sc;
-    for (int tile = sched_consume(&bars->sched, sc, p.tile_ctr, num_tiles, true, lane); tile >= 0;
-         tile = sched_consume(&bars->sched, sc, p.tile_ctr, num_tiles, true, lane), ++it) {
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
       const int acc = it & 1;
       int n0, h0, w0, nt;
       decode_tile(p, tile, n0, h0, w0, nt);
@@ -463,7 +454,6 @@ int igemm_launch(const IgemmParams& p_in, const CUtensorMap& a0, const CUtensorM
   }
   int grid = device_sm_count();
   if (grid > num_tiles) grid = num_tiles;
-  p.tile_ctr = num_tiles > grid ? sched_counter_slot() : nullptr;   // one tile per CTA needs no scheduler
   if (profiling_enabled()) {
     const double pixels = static_cast<double>(p.N) * p.H * p.W;
     const double kdim = static_cast<double>(p.taps_r) * p.taps_s * p.kc *

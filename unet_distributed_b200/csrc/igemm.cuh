@@ -66,7 +66,6 @@ struct IgemmParams {
   int elt;                          // element bytes of A, B and the outputs: 2 = bf16 (0 means 2), 4 = fp32 as tf32
   int stages;
   int lean;                         // set by igemm_launch: the lean epilogue applies (see igemm.cu)
-  int* tile_ctr;                    // set by igemm_launch: dynamic tile scheduler counters (sched.cuh), or null
   IgemmEpilogue epi;
 };
 
