@@ -335,6 +335,7 @@ def measure_decoder(args, decoder, world, rank, dev, sampler, with_roofline):
         # kernels are timed one at a time: in the timed region above the weight gradients share the GPU with the
         # dgrad chain (second stream), which would charge each kernel for the time it waits for SMs
         tr.plan.side_stream(False)
+        tr.serial_update = True        # ... and so would the bucket updates (Adam, re-pack) of the update stream
         for i in range(2):
             tr.train_step(*d_batches[i % nb])
         torch.cuda.synchronize()
@@ -349,6 +350,7 @@ def measure_decoder(args, decoder, world, rank, dev, sampler, with_roofline):
         _lib.check(L.unetb200_profile_collect(ms, fl, by, ln), "profile_collect")
         L.unetb200_profile_enable(0)
         tr.plan.side_stream(True)
+        tr.serial_update = False
         out["roof"] = {"igemm": (ms[0], fl[0], by[0], ln[0]), "wgrad": (ms[1], fl[1], by[1], ln[1]), "steps": psteps}
         barrier()
 

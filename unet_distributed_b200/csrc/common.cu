@@ -213,6 +213,26 @@ namespace {
 std::atomic<int> g_reserved_sms{0};
 }
 
+namespace {
+// UNETB200_PDL=all: every converted launch; =fwd: only inside a PdlScope (the plan's forward pass, where no second
+// stream competes for the SMs a draining kernel frees); unset / anything else: never.  Off by default -- measured on one
+// B200 inside the captured step (profiles/r02_pdl.txt): 2.534 ms off, 2.560 ms fwd, 2.56-2.61 ms all.  With `all` the
+// next dgrad kernel takes the SMs a draining kernel frees before the weight-gradient stream can use them.
+int pdl_mode() {
+  static const int mode = [] {
+    const char* e = getenv("UNETB200_PDL");
+    if (!e) return 0;
+    return strcmp(e, "all") == 0 ? 2 : (strcmp(e, "fwd") == 0 ? 1 : 0);
+  }();
+  return mode;
+}
+thread_local int t_pdl_scope = 0;
+}  // namespace
+
+bool pdl_enabled() { return pdl_mode() == 2 || (pdl_mode() == 1 && t_pdl_scope > 0); }
+PdlScope::PdlScope() { ++t_pdl_scope; }
+PdlScope::~PdlScope() { --t_pdl_scope; }
+
 int set_reserved_sms(int n) {
   if (n < 0) n = 0;
   return g_reserved_sms.exchange(n);

@@ -70,4 +70,30 @@ inline int dt_bytes(int dt) { return dt == UB_DT_TF32 ? 4 : 2; }
 int device_sm_count();
 int set_reserved_sms(int n);   // returns the previous reservation
 
+// Programmatic dependent launch (UNETB200_PDL=all|fwd|off, see common.cu): the kernel may become resident while the previous
+// kernel of the stream drains, runs its prologue (barriers, TMEM allocation, tensor-map prefetch) and then blocks in
+// griddepcontrol.wait (pdl_wait() in ptx.cuh) until that kernel has completed and its writes are visible.  ONLY for
+// kernels in which every thread executes pdl_wait() before its first global-memory access.  Stream capture keeps the
+// edge as a programmatic dependency; an event record or a cross-stream wait between two launches makes it a full one.
+bool pdl_enabled();
+struct PdlScope {   // launches of this thread inside the scope use the attribute when UNETB200_PDL=fwd
+  PdlScope();
+  ~PdlScope();
+};
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
+                              Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+
 }  // namespace ub

@@ -505,6 +505,7 @@ __device__ __forceinline__ void halo_epilogue_fast(const HaloParams& p, HaloBarr
 __global__ void __launch_bounds__(kThreads, 1)
 conv_halo_kernel(const __grid_constant__ HaloParams p, const __grid_constant__ CUtensorMap tmA0,
                  const __grid_constant__ CUtensorMap tmA1, const __grid_constant__ CUtensorMap tmB) {
+  pdl_trigger();     // the next kernel of the stream may take SMs as this grid's CTAs leave them
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw_addr = smem_u32(smem_raw);
   uint8_t* smem = smem_raw + ((1024u - (raw_addr & 1023u)) & 1023u);
@@ -552,6 +553,7 @@ conv_halo_kernel(const __grid_constant__ HaloParams p, const __grid_constant__ C
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
+  pdl_wait();        // everything above overlapped the previous kernel's tail; its results are visible from here
   const uint32_t tmem_base = bars->tmem_base;
 
   if (warp == 0) {
@@ -774,7 +776,7 @@ int halo_launch(const HaloParams& p_in, const CUtensorMap& a0, const CUtensorMap
     pt.timing = 1;
     unsigned long long z[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     cudaMemcpyToSymbol(g_halo_timing, z, sizeof(z));
-    conv_halo_kernel<<<grid, kThreads, smem, stream>>>(pt, a0, a1, b);
+    UB_CHECK_CUDA(launch_pdl(conv_halo_kernel, dim3(grid), dim3(kThreads), smem, stream, pt, a0, a1, b));
     cudaStreamSynchronize(stream);
     cudaMemcpyFromSymbol(z, g_halo_timing, sizeof(z));
     const double c = static_cast<double>(z[7] ? z[7] : 1);
@@ -784,7 +786,7 @@ int halo_launch(const HaloParams& p_in, const CUtensorMap& a0, const CUtensorMap
             z[4] / c, z[6] / c);
     return UB_OK;
   }
-  conv_halo_kernel<<<grid, kThreads, smem, stream>>>(p, a0, a1, b);
+  UB_CHECK_CUDA(launch_pdl(conv_halo_kernel, dim3(grid), dim3(kThreads), smem, stream, p, a0, a1, b));
   UB_CHECK_CUDA(cudaGetLastError());
   prof_end(stream);
   return UB_OK;

@@ -323,6 +323,7 @@ __device__ __forceinline__ void rp_epilogue(const HaloParams& p, RpBarriers* bar
 __global__ void __launch_bounds__(kThreads, 1)
 conv_halo_rp_kernel(const __grid_constant__ HaloParams p, const __grid_constant__ CUtensorMap tmA0,
                     const __grid_constant__ CUtensorMap tmA1, const __grid_constant__ CUtensorMap tmB) {
+  pdl_trigger();     // the next kernel of the stream may take SMs as this grid's CTAs leave them
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw_addr = smem_u32(smem_raw);
   uint8_t* smem = smem_raw + ((1024u - (raw_addr & 1023u)) & 1023u);
@@ -369,6 +370,7 @@ conv_halo_rp_kernel(const __grid_constant__ HaloParams p, const __grid_constant_
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
+  pdl_wait();        // everything above overlapped the previous kernel's tail; its results are visible from here
   const uint32_t tmem_base = bars->tmem_base;
 
   if (warp == 0) {
@@ -544,7 +546,7 @@ int halo_rp_launch(const HaloParams& p, const CUtensorMap& a0, const CUtensorMap
     const double kdim = 9.0 * p.kc * (p.src_kblocks[0] + (p.num_src > 1 ? p.src_kblocks[1] : 0));
     prof_begin(UB_KIND_IGEMM, 2.0 * pixels * kdim * p.block_n, 2.0 * pixels * (kdim / 9.0 + p.block_n), stream);
   }
-  conv_halo_rp_kernel<<<grid, kThreads, smem, stream>>>(p, a0, a1, b);
+  UB_CHECK_CUDA(launch_pdl(conv_halo_rp_kernel, dim3(grid), dim3(kThreads), smem, stream, p, a0, a1, b));
   UB_CHECK_CUDA(cudaGetLastError());
   prof_end(stream);
   return UB_OK;

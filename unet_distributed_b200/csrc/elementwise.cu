@@ -195,6 +195,8 @@ __global__ void conv_first_wgrad_kernel(const float* __restrict__ x, const V* __
 // 8-way sum); first n_a outputs go to out_a, the rest to out_b. Launch with 256 threads = 32 columns x 8 lanes.
 __global__ void rows_reduce_kernel(const float* __restrict__ ws, int nrows, int n, float* __restrict__ out_a, int n_a,
                                    float* __restrict__ out_b) {
+  pdl_trigger();
+  pdl_wait();
   __shared__ float part[32][32];
   const int lanes = blockDim.x >> 5;   // row lanes per column (any block of 32*k threads, k <= 32)
   const int c = threadIdx.x & 31, p = threadIdx.x >> 5;
@@ -248,6 +250,8 @@ __global__ void maxpool_fwd_kernel(const V* __restrict__ x, V* __restrict__ y, i
 template <typename V>
 __global__ void maxpool_bwd_kernel(const V* __restrict__ x, const V* __restrict__ dp,
                                    const V* skip, V* dz, int N, int H, int W, int C) {
+  pdl_trigger();
+  pdl_wait();
   const int groups = C / 8;
   const int Ho = H / 2, Wo = W / 2;
   const long long total = static_cast<long long>(N) * Ho * Wo * groups;
@@ -401,6 +405,8 @@ __global__ void head_fwd_kernel(const V* __restrict__ x, const float* __restrict
 }
 
 __global__ void dice_finalize_kernel(const float* __restrict__ sums, float smooth, float* __restrict__ out4) {
+  pdl_trigger();
+  pdl_wait();
   const float I = sums[0], Sy = sums[1], Sp = sums[2];
   out4[0] = -logf(2.0f * I + smooth) + logf(Sy + Sp + smooth);
   out4[1] = (2.0f * I + smooth) / (Sy + Sp + smooth);
@@ -793,8 +799,8 @@ int conv_first_fwd(const float* x, const float* w, const float* bias, void* y, i
     unsigned blocks = grid_for(static_cast<long long>(n_strips) * 4, 128);
     const unsigned cap = 12u * static_cast<unsigned>(device_sm_count());
     if (blocks > cap) blocks = cap;
-    conv_first32_cin1_fwd_kernel<<<blocks, 128, 0, s>>>(x, w, bias, reinterpret_cast<uint4*>(y),
-                                                        reinterpret_cast<unsigned int*>(gate_out), H, W, n_strips);
+    UB_CHECK_CUDA(launch_pdl(conv_first32_cin1_fwd_kernel, dim3(blocks), dim3(128), 0, s, x, w, bias, reinterpret_cast<uint4*>(y),
+                                                        reinterpret_cast<unsigned int*>(gate_out), H, W, n_strips));
     UB_CHECK_CUDA(cudaGetLastError());
     return UB_OK;
   }
@@ -891,8 +897,8 @@ int maxpool2x2_fwd(const void* x, void* y, int N, int H, int W, int C, cudaStrea
   }
   if (v8_ok(C, static_cast<long long>(N) * H * W, {x, y}, 1)) {
     const unsigned groups = C / 16, total16 = static_cast<unsigned>(N) * (H / 2) * (W / 2) * groups;
-    maxpool_fwd_v8_kernel<<<grid_for(total16, 256), 256, 0, s>>>(reinterpret_cast<const U32x8*>(x),
-                                                                 reinterpret_cast<U32x8*>(y), total16, groups, W / 2, H / 2);
+    UB_CHECK_CUDA(launch_pdl(maxpool_fwd_v8_kernel, dim3(grid_for(total16, 256)), dim3(256), 0, s, reinterpret_cast<const U32x8*>(x),
+                                                                 reinterpret_cast<U32x8*>(y), total16, groups, W / 2, H / 2));
     UB_CHECK_CUDA(cudaGetLastError());
     return UB_OK;
   }
@@ -914,9 +920,9 @@ int maxpool2x2_bwd(const void* x, const void* dpool, const void* skip_grad, void
     UB_CHECK_CUDA(cudaGetLastError());
     return UB_OK;
   }
-  maxpool_bwd_kernel<<<grid_for(total, kThreads), kThreads, 0, s>>>(
-      reinterpret_cast<const uint4*>(x), reinterpret_cast<const uint4*>(dpool),
-      reinterpret_cast<const uint4*>(skip_grad), reinterpret_cast<uint4*>(dz_full), N, H, W, C);
+  UB_CHECK_CUDA(launch_pdl(maxpool_bwd_kernel<uint4>, dim3(grid_for(total, kThreads)), dim3(kThreads), 0, s,
+                           reinterpret_cast<const uint4*>(x), reinterpret_cast<const uint4*>(dpool),
+                           reinterpret_cast<const uint4*>(skip_grad), reinterpret_cast<uint4*>(dz_full), N, H, W, C));
   UB_CHECK_CUDA(cudaGetLastError());
   return UB_OK;
 }
@@ -932,8 +938,8 @@ int upsample2x2_fwd(const void* x, void* y, int N, int H, int W, int C, cudaStre
   }
   if (v8_ok(C, static_cast<long long>(N) * 4 * H * W, {x, y}, 4)) {
     const unsigned groups = C / 16, total16 = static_cast<unsigned>(N) * H * W * groups;
-    upsample_fwd_v8_kernel<<<grid_for(total16, 256), 256, 0, s>>>(reinterpret_cast<const U32x8*>(x),
-                                                                  reinterpret_cast<U32x8*>(y), total16, groups, W, H);
+    UB_CHECK_CUDA(launch_pdl(upsample_fwd_v8_kernel, dim3(grid_for(total16, 256)), dim3(256), 0, s, reinterpret_cast<const U32x8*>(x),
+                                                                  reinterpret_cast<U32x8*>(y), total16, groups, W, H));
     UB_CHECK_CUDA(cudaGetLastError());
     return UB_OK;
   }
@@ -957,9 +963,9 @@ int upsample2x2_bwd(const void* dy, const void* x, void* dx, int N, int H, int W
   }
   if (v8_ok(C, static_cast<long long>(N) * 4 * H * W, {dy, x, dx}, 8)) {
     const unsigned groups = C / 16, total16 = static_cast<unsigned>(N) * H * W * groups;
-    upsample_bwd_v8_kernel<<<grid_for(total16, 256), 256, 0, s>>>(
+    UB_CHECK_CUDA(launch_pdl(upsample_bwd_v8_kernel, dim3(grid_for(total16, 256)), dim3(256), 0, s, 
         reinterpret_cast<const U32x8*>(dy), reinterpret_cast<const U32x8*>(x), reinterpret_cast<U32x8*>(dx), total16,
-        groups, W, H, relu_mask);
+        groups, W, H, relu_mask));
     UB_CHECK_CUDA(cudaGetLastError());
     return UB_OK;
   }
@@ -990,10 +996,10 @@ int head_fwd(const void* x, const float* w, const float* b, const float* y_true,
     const uint4* xv = reinterpret_cast<const uint4*>(x);
     const unsigned Pu = static_cast<unsigned>(P);
     switch (n_cl) {
-      case 1: head32_fwd_kernel<1><<<kRedBlocks, kThreads, 0, s>>>(xv, w, b, y_true, p_out, ws, Pu); break;
-      case 2: head32_fwd_kernel<2><<<kRedBlocks, kThreads, 0, s>>>(xv, w, b, y_true, p_out, ws, Pu); break;
-      case 3: head32_fwd_kernel<3><<<kRedBlocks, kThreads, 0, s>>>(xv, w, b, y_true, p_out, ws, Pu); break;
-      default: head32_fwd_kernel<4><<<kRedBlocks, kThreads, 0, s>>>(xv, w, b, y_true, p_out, ws, Pu); break;
+      case 1: UB_CHECK_CUDA(launch_pdl(head32_fwd_kernel<1>, dim3(kRedBlocks), dim3(kThreads), 0, s, xv, w, b, y_true, p_out, ws, Pu)); break;
+      case 2: UB_CHECK_CUDA(launch_pdl(head32_fwd_kernel<2>, dim3(kRedBlocks), dim3(kThreads), 0, s, xv, w, b, y_true, p_out, ws, Pu)); break;
+      case 3: UB_CHECK_CUDA(launch_pdl(head32_fwd_kernel<3>, dim3(kRedBlocks), dim3(kThreads), 0, s, xv, w, b, y_true, p_out, ws, Pu)); break;
+      default: UB_CHECK_CUDA(launch_pdl(head32_fwd_kernel<4>, dim3(kRedBlocks), dim3(kThreads), 0, s, xv, w, b, y_true, p_out, ws, Pu)); break;
     }
   } else {
     const size_t smem = (C * n_cl + n_cl + 3 * (kThreads / 32)) * sizeof(float);
@@ -1001,13 +1007,13 @@ int head_fwd(const void* x, const float* w, const float* b, const float* y_true,
                                                        n_cl);
   }
   UB_CHECK_CUDA(cudaGetLastError());
-  rows_reduce_kernel<<<1, 1024, 0, s>>>(ws, kRedBlocks, 3, sums, 3, nullptr);
+  UB_CHECK_CUDA(launch_pdl(rows_reduce_kernel, dim3(1), dim3(1024), 0, s, ws, kRedBlocks, 3, sums, 3, nullptr));
   UB_CHECK_CUDA(cudaGetLastError());
   return UB_OK;
 }
 
 int dice_finalize(const float* sums, float smooth, float* out4, cudaStream_t s) {
-  dice_finalize_kernel<<<1, 1, 0, s>>>(sums, smooth, out4);
+  UB_CHECK_CUDA(launch_pdl(dice_finalize_kernel, dim3(1), dim3(1), 0, s, sums, smooth, out4));
   UB_CHECK_CUDA(cudaGetLastError());
   return UB_OK;
 }
@@ -1039,15 +1045,15 @@ int head_bwd(const void* x, const float* w, const float* y_true, const float* p,
     }
     rows = blocks_per_sm * device_sm_count();
     if (rows > kRedBlocks) rows = kRedBlocks;
-    head32_bwd_kernel<<<rows, kThreads, 0, s>>>(reinterpret_cast<const uint4*>(x), w, y_true, p, sums, smooth,
-                                                grad_scale, reinterpret_cast<uint4*>(dx), ws, static_cast<unsigned>(P));
+    UB_CHECK_CUDA(launch_pdl(head32_bwd_kernel, dim3(rows), dim3(kThreads), 0, s, reinterpret_cast<const uint4*>(x), w, y_true, p, sums, smooth,
+                                                grad_scale, reinterpret_cast<uint4*>(dx), ws, static_cast<unsigned>(P)));
   } else {
     const size_t smem = (C * n_cl + (kThreads / 32) * nout) * sizeof(float);
     head_bwd_kernel<<<kRedBlocks, kThreads, smem, s>>>(reinterpret_cast<const uint4*>(x), w, y_true, p, sums, smooth,
                                                        grad_scale, reinterpret_cast<uint4*>(dx), ws, P, C, n_cl);
   }
   UB_CHECK_CUDA(cudaGetLastError());
-  rows_reduce_kernel<<<grid_for(nout, 32), 1024, 0, s>>>(ws, rows, nout, dw, C * n_cl, db);
+  UB_CHECK_CUDA(launch_pdl(rows_reduce_kernel, dim3(grid_for(nout, 32)), dim3(1024), 0, s, ws, rows, nout, dw, C * n_cl, db));
   UB_CHECK_CUDA(cudaGetLastError());
   return UB_OK;
 }

@@ -36,6 +36,7 @@ __device__ __forceinline__ void decode_tile(const IgemmParams& p, int tile, int&
 __global__ void __launch_bounds__(kThreads, 1)
 igemm_kernel(const __grid_constant__ IgemmParams p, const __grid_constant__ CUtensorMap tmA0,
              const __grid_constant__ CUtensorMap tmA1, const __grid_constant__ CUtensorMap tmB) {
+  pdl_trigger();     // the next kernel of the stream may take SMs as this grid's CTAs leave them
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw_addr = smem_u32(smem_raw);
   uint8_t* smem = smem_raw + ((1024u - (raw_addr & 1023u)) & 1023u);
@@ -74,6 +75,7 @@ igemm_kernel(const __grid_constant__ IgemmParams p, const __grid_constant__ CUte
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
+  pdl_wait();        // everything above overlapped the previous kernel's tail; its results are visible from here
   const uint32_t tmem_base = bars->tmem_base;
 
   if (warp == 0) {
@@ -462,7 +464,7 @@ int igemm_launch(const IgemmParams& p_in, const CUtensorMap& a0, const CUtensorM
     prof_begin(UB_KIND_IGEMM, 2.0 * pixels * kdim * ncols,
                static_cast<double>(p.elt) * pixels * (kdim / (p.taps_r * p.taps_s) + ncols), stream);
   }
-  igemm_kernel<<<grid, kThreads, smem, stream>>>(p, a0, a1, b);
+  UB_CHECK_CUDA(launch_pdl(igemm_kernel, dim3(grid), dim3(kThreads), smem, stream, p, a0, a1, b));
   UB_CHECK_CUDA(cudaGetLastError());
   prof_end(stream);
   return UB_OK;

@@ -102,6 +102,8 @@ conv_first32_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w
 __global__ void __launch_bounds__(128, 3)
 conv_first32_cin1_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ bias,
                              uint4* __restrict__ y, unsigned int* __restrict__ gate, int H, int W, unsigned n_strips) {
+  pdl_trigger();
+  pdl_wait();
   const int g = threadIdx.x & 3;
   float wr[9][8], br[8];
 #pragma unroll
@@ -177,6 +179,8 @@ template <int NCL>
 __global__ void __launch_bounds__(256)
 head32_fwd_kernel(const uint4* __restrict__ x, const float* __restrict__ w, const float* __restrict__ b,
                   const float* __restrict__ y_true, float* __restrict__ p_out, float* __restrict__ ws, unsigned P) {
+  pdl_trigger();
+  pdl_wait();
   __shared__ float sw[32 * NCL + NCL];
   __shared__ float wred[8 * 3];
   for (int i = threadIdx.x; i < 32 * NCL; i += blockDim.x) sw[i] = w[i];
@@ -224,6 +228,8 @@ __global__ void __launch_bounds__(256)
 head32_bwd_kernel(const uint4* __restrict__ x, const float* __restrict__ w, const float* __restrict__ y_true,
                   const float* __restrict__ p, const float* __restrict__ sums, float smooth, float grad_scale,
                   uint4* __restrict__ dx, float* __restrict__ ws, unsigned P) {
+  pdl_trigger();
+  pdl_wait();
   __shared__ float sw[32];
   __shared__ float red[8][33];
   if (threadIdx.x < 32) sw[threadIdx.x] = w[threadIdx.x];

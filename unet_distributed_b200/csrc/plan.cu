@@ -430,6 +430,7 @@ int unetb200_plan_forward(unetb200_plan* P, const float* imgs, const float* msks
                           const long long* seed_add, void* stream) {
   UB_REQUIRE(P->arena, "plan_forward: plan is not bound");
   NvtxRange nvtx_range("unetb200.plan_forward");
+  PdlScope pdl_scope;
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
   const int N = P->N;
   const int dt = P->dt;

@@ -29,6 +29,8 @@ __device__ __forceinline__ Quad quad_of(unsigned idx, unsigned groups, unsigned 
 __global__ void __launch_bounds__(256)
 maxpool_fwd_v8_kernel(const U32x8* __restrict__ x, U32x8* __restrict__ y, unsigned total, unsigned groups, unsigned Wc,
                       unsigned Hc) {
+  pdl_trigger();
+  pdl_wait();
   const unsigned idx = blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= total) return;
   const Quad q = quad_of(idx, groups, Wc, Hc);
@@ -46,6 +48,8 @@ maxpool_fwd_v8_kernel(const U32x8* __restrict__ x, U32x8* __restrict__ y, unsign
 __global__ void __launch_bounds__(256)
 upsample_fwd_v8_kernel(const U32x8* __restrict__ x, U32x8* __restrict__ y, unsigned total, unsigned groups, unsigned Wc,
                        unsigned Hc) {
+  pdl_trigger();
+  pdl_wait();
   const unsigned idx = blockIdx.x * blockDim.x + threadIdx.x;   // coarse element
   if (idx >= total) return;
   const Quad q = quad_of(idx, groups, Wc, Hc);
@@ -59,6 +63,8 @@ upsample_fwd_v8_kernel(const U32x8* __restrict__ x, U32x8* __restrict__ y, unsig
 __global__ void __launch_bounds__(256)
 upsample_bwd_v8_kernel(const U32x8* __restrict__ dy, const U32x8* __restrict__ x, U32x8* __restrict__ dx,
                        unsigned total, unsigned groups, unsigned Wc, unsigned Hc, int relu_mask) {
+  pdl_trigger();
+  pdl_wait();
   const unsigned idx = blockIdx.x * blockDim.x + threadIdx.x;   // coarse element
   if (idx >= total) return;
   const Quad q = quad_of(idx, groups, Wc, Hc);

@@ -60,6 +60,13 @@ __device__ __forceinline__ void fence_proxy_async_smem() {
   asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
 }
 
+// ---------------------------------------------------------------- programmatic dependent launch
+// pdl_trigger(): once every CTA of this grid has executed it (or exited), the next kernel of the stream may start
+// launching into SMs as they free up.  pdl_wait(): blocks until the preceding kernel has completed and flushed; a
+// no-op in a kernel launched without the attribute (ub::launch_pdl).
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
 // ---------------------------------------------------------------- TMA loads (tile mode, 1 CTA)
 __device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* m) {
   asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(m)) : "memory");

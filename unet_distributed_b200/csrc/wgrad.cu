@@ -23,6 +23,7 @@ struct __align__(8) WgradBarriers {
 __global__ void __launch_bounds__(kThreads, 1)
 wgrad_kernel(const __grid_constant__ WgradParams p, const __grid_constant__ CUtensorMap tmZ,
              const __grid_constant__ CUtensorMap tmX0, const __grid_constant__ CUtensorMap tmX1) {
+  pdl_trigger();     // the next kernel of the stream may take SMs as this grid's CTAs leave them
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw_addr = smem_u32(smem_raw);
   uint8_t* smem = smem_raw + ((1024u - (raw_addr & 1023u)) & 1023u);
@@ -86,6 +87,7 @@ wgrad_kernel(const __grid_constant__ WgradParams p, const __grid_constant__ CUte
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
+  pdl_wait();        // everything above overlapped the previous kernel's tail; its results are visible from here
   const uint32_t tmem_base = bars->tmem_base;
 
   if (warp == 0) {
@@ -302,7 +304,7 @@ int wgrad_launch(const WgradParams& p, const CUtensorMap& z, const CUtensorMap& 
     prof_begin(UB_KIND_WGRAD, 2.0 * pixels * p.taps_r * p.taps_s * cin * p.z_C,
                static_cast<double>(elt) * pixels * (cin + p.z_C), stream);
   }
-  wgrad_kernel<<<static_cast<unsigned>(grid), kThreads, smem, stream>>>(p, z, x0, x1);
+  UB_CHECK_CUDA(launch_pdl(wgrad_kernel, dim3(static_cast<unsigned>(grid)), dim3(kThreads), smem, stream, p, z, x0, x1));
   UB_CHECK_CUDA(cudaGetLastError());
   prof_end(stream);
   return UB_OK;

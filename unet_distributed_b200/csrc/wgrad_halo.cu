@@ -112,6 +112,7 @@ __device__ __forceinline__ void wgrad_halo_mma_role(WgradHaloBarriers* bars, uin
 __global__ void __launch_bounds__(kThreads, 1)
 wgrad_halo_kernel(const __grid_constant__ WgradHaloParams p, const __grid_constant__ CUtensorMap tmX,
                   const __grid_constant__ CUtensorMap tmZ) {
+  pdl_trigger();     // the next kernel of the stream may take SMs as this grid's CTAs leave them
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw_addr = smem_u32(smem_raw);
   uint8_t* smem = smem_raw + ((1024u - (raw_addr & 1023u)) & 1023u);
@@ -155,6 +156,7 @@ wgrad_halo_kernel(const __grid_constant__ WgradHaloParams p, const __grid_consta
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
+  pdl_wait();        // everything above overlapped the previous kernel's tail; its results are visible from here
   const uint32_t tmem_base = bars->tmem_base;
 
   if (warp == 0) {
@@ -365,7 +367,7 @@ int wgrad_halo_launch(const CUtensorMap& x_map, const CUtensorMap& z_map, int N,
     const double pixels = static_cast<double>(N) * H * W;
     prof_begin(UB_KIND_WGRAD, 2.0 * pixels * 9 * Cx * Cz, 2.0 * pixels * (Cx + Cz), stream);
   }
-  wgrad_halo_kernel<<<grid, kThreads, smem, stream>>>(p, x_map, z_map);
+  UB_CHECK_CUDA(launch_pdl(wgrad_halo_kernel, dim3(grid), dim3(kThreads), smem, stream, p, x_map, z_map));
   UB_CHECK_CUDA(cudaGetLastError());
   prof_end(stream);
   const int n = 9 * Cx * Cz + (db ? Cz : 0);

@@ -34,6 +34,7 @@ struct __align__(8) RowBarriers {
 __global__ void __launch_bounds__(kThreads, 1)
 wgrad_row_kernel(const __grid_constant__ WgradRowParams p, const __grid_constant__ CUtensorMap tmZ,
                  const __grid_constant__ CUtensorMap tmX0, const __grid_constant__ CUtensorMap tmX1) {
+  pdl_trigger();     // the next kernel of the stream may take SMs as this grid's CTAs leave them
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw_addr = smem_u32(smem_raw);
   uint8_t* smem = smem_raw + ((1024u - (raw_addr & 1023u)) & 1023u);
@@ -86,6 +87,7 @@ wgrad_row_kernel(const __grid_constant__ WgradRowParams p, const __grid_constant
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
+  pdl_wait();        // everything above overlapped the previous kernel's tail; its results are visible from here
   const uint32_t tmem_base = bars->tmem_base;
 
   if (warp == 0) {
@@ -284,7 +286,7 @@ int wgrad_row_launch(const WgradRowParams& p, const CUtensorMap& z, const CUtens
                        (p.num_src > 1 ? static_cast<double>(p.x_ntiles[1]) * p.x_block_n[1] : 0.0);
     prof_begin(UB_KIND_WGRAD, 2.0 * pixels * 9 * cin * p.z_C, 2.0 * pixels * (cin + p.z_C), stream);
   }
-  wgrad_row_kernel<<<static_cast<unsigned>(grid), kThreads, smem, stream>>>(p, z, x0, x1);
+  UB_CHECK_CUDA(launch_pdl(wgrad_row_kernel, dim3(static_cast<unsigned>(grid)), dim3(kThreads), smem, stream, p, z, x0, x1));
   UB_CHECK_CUDA(cudaGetLastError());
   prof_end(stream);
   return UB_OK;

@@ -54,6 +54,9 @@ class Trainer:
         # SMs left to the NCCL kernels that run beside backward segments 1..4 (see unetb200_set_reserved_sms)
         self.reserved_sms = int(os.environ.get("UNETB200_RESERVE_SMS", str(parallel.RESERVED_SMS)))
         self.use_cuda_graph = bool(use_cuda_graph)
+        # True: the caller's stream waits for every bucket update before the next segment (bench.py's per-kernel timing,
+        # where a kernel must not share the GPU with another stream's work); eager steps only
+        self.serial_update = False
         self._graph = None
         self._g_imgs = self._g_msks = None
         self.steps_done = 0
@@ -86,6 +89,8 @@ class Trainer:
                 # the all-reduce is ordered behind the segment through the update stream; `cur` does not wait for it
                 self.reducer.reduce_now(seg)
                 self._update_range(*p.buckets[seg])
+            if self.serial_update:
+                cur.wait_stream(upd)
         lib.unetb200_set_reserved_sms(0)
         p.defer_join(old_defer)
         with torch.cuda.stream(upd):
