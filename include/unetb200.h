@@ -142,6 +142,10 @@ int unetb200_tconv2x2_dgrad_dt(const void* dy, int Cout, const void* w_packed_d,
                                float scale, int N, int H, int W, int dtype, void* stream);
 int unetb200_tconv2x2_wgrad_dt(const void* dy, int Cout, const void* x, int Cin, float* dw, void* ws, size_t ws_bytes,
                                int N, int H, int W, int dtype, void* stream);
+/* Weight AND bias gradient of Conv2DTranspose in one pass over dy (db may be NULL); same workspace size as
+ * unetb200_tconv2x2_wgrad_ws_bytes. TensorFlow computes the two with separate ops (Conv2DBackpropFilter, BiasAddGrad). */
+int unetb200_tconv2x2_wgrad_bias_dt(const void* dy, int Cout, const void* x, int Cin, float* dw, float* db, void* ws,
+                                    size_t ws_bytes, int N, int H, int W, int dtype, void* stream);
 int unetb200_conv_first_fwd_dt(const float* x, const float* w_hwio, const float* bias, void* y, int N, int H, int W,
                                int Cin, int Cout, int dtype, void* stream);
 int unetb200_conv_first_wgrad_dt(const float* x, const void* dz, float* dw, float* db, void* ws, int N, int H, int W,

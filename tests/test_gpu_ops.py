@@ -178,6 +178,18 @@ def test_tconv2x2(cuda_device, N, H, W, Ci, Co):
     dw = torch.empty((2, 2, Co, Ci), dtype=torch.float32, device=dev)
     L.call("unetb200_tconv2x2_wgrad", _p(d_dy), Co, _p(d_x), Ci, _p(dw), _p(ws), ctypes.c_size_t(nws), N, H, W, None)
     assert rel_err(dw.cpu().numpy(), wt.grad.numpy()) < 2e-3
+    # weight and bias gradient from one pass over dy: same dW bit for bit, db = column sums of the bf16 dy
+    dw2 = torch.empty_like(dw)
+    db = torch.full((Co,), float("nan"), dtype=torch.float32, device=dev)
+    L.call("unetb200_tconv2x2_wgrad_bias_dt", _p(d_dy), Co, _p(d_x), Ci, _p(dw2), _p(db), _p(ws), ctypes.c_size_t(nws),
+           N, H, W, L.BF16, None)
+    assert torch.equal(dw2, dw)
+    db_ref = d_dy.float().cpu().numpy().astype(np.float64).reshape(-1, Co).sum(axis=0)
+    assert rel_err(db.cpu().numpy(), db_ref) < 1e-5
+    db_again = torch.empty_like(db)
+    L.call("unetb200_tconv2x2_wgrad_bias_dt", _p(d_dy), Co, _p(d_x), Ci, _p(dw2), _p(db_again), _p(ws),
+           ctypes.c_size_t(nws), N, H, W, L.BF16, None)
+    assert torch.equal(db_again, db)                                    # fixed summation order
 
 
 @pytest.mark.parametrize("N,H,W,C", [(2, 16, 16, 32), (1, 8, 8, 512), (3, 30, 30, 128)])

@@ -209,6 +209,11 @@ int unetb200_tconv2x2_wgrad_dt(const void* dy, int Cout, const void* x, int Cin,
   UB_DT(dtype, "tconv2x2_wgrad");
   return tconv2x2_wgrad(dy, Cout, x, Cin, dw, ws, ws_bytes, N, H, W, S(stream), dt);
 }
+int unetb200_tconv2x2_wgrad_bias_dt(const void* dy, int Cout, const void* x, int Cin, float* dw, float* db, void* ws,
+                                    size_t ws_bytes, int N, int H, int W, int dtype, void* stream) {
+  UB_DT(dtype, "tconv2x2_wgrad_bias");
+  return tconv2x2_wgrad(dy, Cout, x, Cin, dw, ws, ws_bytes, N, H, W, S(stream), dt, db);
+}
 int unetb200_conv_first_fwd_dt(const float* x, const float* w, const float* bias, void* y, int N, int H, int W, int Cin,
                                int Cout, int dtype, void* stream) {
   UB_DT(dtype, "conv_first_fwd");

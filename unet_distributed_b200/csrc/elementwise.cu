@@ -1058,6 +1058,13 @@ int head_bwd(const void* x, const float* w, const float* y_true, const float* p,
   return UB_OK;
 }
 
+int rows_sum(const float* ws, int nrows, int n, float* out, cudaStream_t s) {
+  if (n <= 0) return UB_OK;
+  rows_reduce_kernel<<<grid_for(n, 32), 1024, 0, s>>>(ws, nrows, n, out, n, nullptr);
+  UB_CHECK_CUDA(cudaGetLastError());
+  return UB_OK;
+}
+
 long long colsum_ws_floats(int C) { return static_cast<long long>(kRedBlocks) * (kThreads / 32) * C; }
 
 int colsum_bf16(const void* dz, float* db, float* ws, long long P, int C, cudaStream_t s) {

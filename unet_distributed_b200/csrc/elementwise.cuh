@@ -42,6 +42,8 @@ int head_bwd(const void* x, const float* w, const float* y_true, const float* p,
              float grad_scale, void* dx_bf16, float* dw, float* db, float* ws, long long P, int C, int n_cl,
              cudaStream_t s, int dt = 0);
 
+// out[i] = sum over r < nrows of ws[r * n + i], rows added in a fixed order (partial sums a kernel left per CTA).
+int rows_sum(const float* ws, int nrows, int n, float* out, cudaStream_t s);
 // db[c] = sum over pixels of dz[pixel][c] (bf16 in, fp32 out); ws needs colsum_ws_floats(C) floats.
 long long colsum_ws_floats(int C);
 int colsum_bf16(const void* dz, float* db, float* ws, long long P, int C, cudaStream_t s);

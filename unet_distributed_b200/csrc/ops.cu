@@ -584,12 +584,16 @@ int tconv2x2_dgrad(const void* dy, int Cout, const void* w_packed_d, void* dx, i
 size_t tconv2x2_wgrad_ws_bytes(int N, int H, int W, int Cin, int Cout) {
   WgradPlan wp;
   if (plan_wgrad(wp, N, H, W, 2, 2, 0, Cout, Cin, 0) != UB_OK) return 0;
-  if (wp.p.splits <= 1) return 0;  // a single pixel range writes the gradient directly
-  return static_cast<size_t>(wp.p.splits) * wp.nweights * sizeof(float);
+  // split-K partials of the weights (a single pixel range writes the gradient directly), then the bias partials of
+  // every (split, tap); the tf32 path sums the bias with colsum_act in the same workspace afterwards
+  const size_t wpart = wp.p.splits > 1 ? static_cast<size_t>(wp.p.splits) * wp.nweights * sizeof(float) : 0;
+  const size_t bpart = static_cast<size_t>(wp.p.splits) * 4 * Cout * sizeof(float);
+  const size_t colsum = static_cast<size_t>(colsum_ws_floats(Cout)) * sizeof(float);
+  return wpart + bpart > colsum ? wpart + bpart : colsum;
 }
 
 int tconv2x2_wgrad(const void* dy, int Cout, const void* x, int Cin, float* dw, void* ws, size_t ws_bytes, int N, int H,
-                   int W, cudaStream_t s, int dt) {
+                   int W, cudaStream_t s, int dt, float* db) {
   const int elt = dt_bytes(dt);
   WgradPlan wp;
   int rc = plan_wgrad(wp, N, H, W, 2, 2, 0, Cout, Cin, 0, elt);
@@ -602,14 +606,15 @@ int tconv2x2_wgrad(const void* dy, int Cout, const void* x, int Cin, float* dw, 
   p.out_m_stride = Cin;
   p.out_n_stride = 1;
   p.out_split_stride = wp.nweights;
-  if (p.splits > 1) {
-    UB_REQUIRE(ws != nullptr && ws_bytes >= static_cast<size_t>(p.splits) * wp.nweights * sizeof(float),
-               "tconv2x2_wgrad: workspace of %zu bytes needed, %zu given",
-               static_cast<size_t>(p.splits) * wp.nweights * sizeof(float), ws_bytes);
-    p.out = reinterpret_cast<float*>(ws);
-  } else {
-    p.out = dw;
-  }
+  const size_t wpart = p.splits > 1 ? static_cast<size_t>(p.splits) * wp.nweights * sizeof(float) : 0;
+  const bool fused_bias = db != nullptr && elt == 2;
+  const size_t bpart = fused_bias ? static_cast<size_t>(p.splits) * 4 * Cout * sizeof(float) : 0;
+  UB_REQUIRE(wpart + bpart == 0 || (ws != nullptr && ws_bytes >= wpart + bpart),
+             "tconv2x2_wgrad: workspace of %zu bytes needed, %zu given", wpart + bpart, ws_bytes);
+  p.out = p.splits > 1 ? reinterpret_cast<float*>(ws) : dw;
+  // the bias gradient rides along: the CTAs of the first input-channel tile sum the dY tiles they stage
+  float* bias_part = fused_bias ? reinterpret_cast<float*>(static_cast<char*>(ws) + wpart) : nullptr;
+  p.bias_out = bias_part;
   const Box b = {p.TN, p.TH, p.TW};
   CUtensorMap zm, xm;
   const int mn_sw = elt == 4 ? UB_SWIZZLE_128B_ATOM32 : 0;
@@ -619,7 +624,16 @@ int tconv2x2_wgrad(const void* dy, int Cout, const void* x, int Cin, float* dw, 
   if (rc) return rc;
   rc = wgrad_launch(p, zm, xm, xm, s);
   if (rc) return rc;
-  if (p.splits > 1) return splitk_reduce_launch(p.out, wp.nweights, p.splits, dw, wp.nweights, s);
+  if (p.splits > 1) {
+    rc = splitk_reduce_launch(p.out, wp.nweights, p.splits, dw, wp.nweights, s);
+    if (rc) return rc;
+  }
+  if (fused_bias) return rows_sum(bias_part, p.splits * 4, Cout, db, s);
+  if (db) {   // tf32: a separate pass over dY
+    const size_t need = static_cast<size_t>(colsum_ws_floats(Cout)) * sizeof(float);
+    UB_REQUIRE(ws != nullptr && ws_bytes >= need, "tconv2x2_wgrad: workspace of %zu bytes needed for the bias gradient", need);
+    return colsum_act(dy, db, reinterpret_cast<float*>(ws), static_cast<long long>(N) * 4 * H * W, Cout, s, dt);
+  }
   return UB_OK;
 }
 

@@ -63,7 +63,8 @@ int tconv2x2_dgrad(const void* dy, int Cout, const void* w_packed_d, void* dx, i
                    int N, int H, int W, cudaStream_t s, const unsigned short* gate = nullptr, int dt = 0);
 // dw fp32 [2][2][Cout][Cin].
 size_t tconv2x2_wgrad_ws_bytes(int N, int H, int W, int Cin, int Cout);
+// db (optional): also the bias gradient, summed from the dY tiles the kernel stages (bf16) or by a second pass (tf32).
 int tconv2x2_wgrad(const void* dy, int Cout, const void* x, int Cin, float* dw, void* ws, size_t ws_bytes, int N, int H,
-                   int W, cudaStream_t s, int dt = 0);
+                   int W, cudaStream_t s, int dt = 0, float* db = nullptr);
 
 }  // namespace ub

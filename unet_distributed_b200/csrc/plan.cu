@@ -608,8 +608,11 @@ int unetb200_plan_backward(unetb200_plan* P, const float* imgs, const float* msk
       } else {
         const int lt = P->tc[L];
         RC(fork());
-        RC(tconv2x2_wgrad(P->at(P->g_u[L]), P->ch[L], P->at(below), below_C, P->dW_(lt), wsv, wsb, N, H / 2, W / 2, w, dt));
-        RC(colsum_act(P->at(P->g_u[L]), P->dB_(lt), wss, px, P->ch[L], w, dt));
+        // the bias gradient (column sums of dY) comes out of the same kernel: it stages every dY tile anyway
+        static const bool separate_bias = getenv("UNETB200_TCONV_SEPARATE_BIAS") != nullptr;
+        RC(tconv2x2_wgrad(P->at(P->g_u[L]), P->ch[L], P->at(below), below_C, P->dW_(lt), wsv, wsb, N, H / 2, W / 2, w, dt,
+                          separate_bias ? nullptr : P->dB_(lt)));
+        if (separate_bias) RC(colsum_act(P->at(P->g_u[L]), P->dB_(lt), wss, px, P->ch[L], w, dt));
         RC(tconv2x2_dgrad(P->at(P->g_u[L]), P->ch[L], P->pkd(lt), P->at(g_below), below_C, P->at(below), 1.0f, N, H / 2,
                           W / 2, s, P->gate(L == 3 ? P->gt_c[4] : P->gt_dc[L + 1]), dt));
       }

@@ -30,7 +30,8 @@ wgrad_kernel(const __grid_constant__ WgradParams p, const __grid_constant__ CUte
   const int elt = p.elt == 4 ? 4 : 2;
   const int kOperandBytes = operand_bytes(elt);
   const int kStageBytes = 2 * kOperandBytes;
-  WgradBarriers* bars = reinterpret_cast<WgradBarriers*>(smem + p.stages * kStageBytes);
+  float* bias_scratch = reinterpret_cast<float*>(smem + p.stages * kStageBytes);
+  WgradBarriers* bars = reinterpret_cast<WgradBarriers*>(smem + p.stages * kStageBytes + kWgradBiasScratch);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -69,11 +70,13 @@ wgrad_kernel(const __grid_constant__ WgradParams p, const __grid_constant__ CUte
   const uint32_t z_atom_bytes = static_cast<uint32_t>(kKP * p.z_atom * elt);
   const uint32_t x_atom_bytes = static_cast<uint32_t>(kKP * x_atom * elt);
   const uint32_t tmem_cols = block_n < 32 ? 32u : static_cast<uint32_t>(block_n);
+  // the CTAs of the first X tile together read every dZ element once: they also sum it over pixels (bias gradient)
+  const bool do_bias = p.bias_out != nullptr && ntg == 0;
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < p.stages; ++s) {
       mbar_init(&bars->full[s], 1);
-      mbar_init(&bars->empty[s], 1);
+      mbar_init(&bars->empty[s], do_bias ? 5 : 1);   // MMA commit (+ the four column-summing warps)
     }
     mbar_init(&bars->tmem_full, 1);
     mbar_fence_init();
@@ -176,6 +179,51 @@ wgrad_kernel(const __grid_constant__ WgradParams p, const __grid_constant__ CUte
       }
     }
   } else {
+    if (do_bias) {
+      // While the tensor core works on a stage, warps 2..5 sum its dZ tile over the 64 pixels. The tile is m_atoms atoms
+      // of 64 pixel rows x z_atom channels (128-byte rows: 16-byte chunk ^= pixel & 7; 64-byte rows: chunk ^=
+      // (pixel >> 1) & 3). Thread t: 16-byte chunk t % 16 of the tile's channels, pixels t / 16 + 8k.
+      const int t = threadIdx.x - 64;
+      const int cpa = p.z_atom >> 3;                 // 16-byte chunks per atom row: 8 or 4
+      const int q = t & 15, rg = t >> 4;
+      const int atom = q / cpa, cq = q % cpa;
+      const int rowb = p.z_atom * 2;
+      float bsum[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) bsum[j] = 0.0f;
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int kb = 0; kb < nkb; ++kb) {
+        mbar_wait(&bars->full[stage], phase);
+        if (atom < m_atoms) {
+          const uint8_t* zt = smem + stage * kStageBytes + atom * z_atom_bytes;
+#pragma unroll
+          for (int k = 0; k < 8; ++k) {
+            const int px = rg + 8 * k;
+            const int sw = cpa == 8 ? (px & 7) : ((px >> 1) & 3);
+            const uint4 v = *reinterpret_cast<const uint4*>(zt + px * rowb + ((cq ^ sw) << 4));
+            bsum[0] += bf16_lo(v.x); bsum[1] += bf16_hi(v.x); bsum[2] += bf16_lo(v.y); bsum[3] += bf16_hi(v.y);
+            bsum[4] += bf16_lo(v.z); bsum[5] += bf16_hi(v.z); bsum[6] += bf16_lo(v.w); bsum[7] += bf16_hi(v.w);
+          }
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&bars->empty[stage]);
+        if (++stage == p.stages) { stage = 0; phase ^= 1u; }
+      }
+#pragma unroll
+      for (int j = 0; j < 8; ++j) bias_scratch[t * 8 + j] = bsum[j];
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+      // GEMM row c of the tile = chunk c / 8, element c % 8; its eight pixel-group threads in a fixed order
+      const int c = t;
+      if (m0 + c < m_total) {
+        float acc = 0.0f;
+#pragma unroll
+        for (int g = 0; g < 8; ++g) acc += bias_scratch[((c >> 3) + 16 * g) * 8 + (c & 7)];
+        const int btap = p.tap_in_m ? (m0 + c) / p.z_C : tap;
+        const int bco = p.tap_in_m ? (m0 + c) % p.z_C : m0 + c;
+        p.bias_out[(static_cast<long long>(split) * p.taps_r * p.taps_s + btap) * p.z_C + bco] = acc;
+      }
+    }
     const int quarter = warp & 3;
     const int row = quarter * 32 + lane;
     const int mrow = m0 + row;
@@ -286,7 +334,8 @@ int wgrad_launch(const WgradParams& p, const CUtensorMap& z, const CUtensorMap& 
   }
   const int total_pb = p.blocks_n * p.blocks_h * p.blocks_w;
   UB_REQUIRE(p.splits >= 1 && p.splits <= total_pb, "wgrad: splits %d vs %d pixel blocks", p.splits, total_pb);
-  const size_t smem = static_cast<size_t>(p.stages) * 2 * operand_bytes(elt) + sizeof(WgradBarriers) + 1024;
+  UB_REQUIRE(!p.bias_out || elt == 2, "wgrad: the fused bias gradient is a bf16 feature");
+  const size_t smem = static_cast<size_t>(p.stages) * 2 * operand_bytes(elt) + kWgradBiasScratch + sizeof(WgradBarriers) + 1024;
   UB_REQUIRE(smem <= 227 * 1024, "wgrad: %zu bytes of shared memory requested", smem);
   static bool attr_set[64] = {false};
   int dev = 0;

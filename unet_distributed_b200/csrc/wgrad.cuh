@@ -33,7 +33,11 @@ struct WgradParams {
   int elt;                  // element bytes of dZ and X: 2 = bf16 (0 means 2), 4 = fp32 read as tf32 (atoms of 32 channels)
   float* out;
   long long out_split_stride, out_tap_stride, out_m_stride, out_n_stride;
+  // optional (bf16 only): bias_out[(split * taps + tap) * z_C + co] = sum of dZ[.., co] over the pixels this (split, tap)
+  // walks -- the CTAs of the first X tile sum their dZ tiles in shared memory while the tensor core works on them
+  float* bias_out;
 };
+constexpr int kWgradBiasScratch = 128 * 8 * 4;   // bytes of shared memory for the column sums (128 threads x 8 floats)
 
 int wgrad_launch(const WgradParams& p, const CUtensorMap& z, const CUtensorMap& x0, const CUtensorMap& x1,
                  cudaStream_t stream);
