@@ -97,6 +97,8 @@ igemm_kernel(const __grid_constant__ IgemmParams p, const __grid_constant__ CUte
               mbar_arrive_expect_tx(&bars->full[stage], static_cast<uint32_t>(stage_bytes));
               if (p.a_mode == IG_A_SHIFT4D) {
                 tma_load_4d(sa, tmA, &bars->full[stage], cb * p.kc, w0 + ts - p.pad, h0 + tr - p.pad, n0);
+              } else if (p.a_mode == IG_A_TCONV_PAIR) {
+                tma_load_4d(sa, tmA, &bars->full[stage], cb * p.kc, w0, tr, n0 * p.H + h0);
               } else {
                 tma_load_5d(sa, tmA, &bars->full[stage], cb * p.kc, ts, w0, tr, n0 * p.H + h0);
               }

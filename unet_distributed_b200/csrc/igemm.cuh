@@ -13,7 +13,7 @@
 
 namespace ub {
 
-enum : int { IG_A_SHIFT4D = 0, IG_A_TCONV5D = 1 };
+enum : int { IG_A_SHIFT4D = 0, IG_A_TCONV5D = 1, IG_A_TCONV_PAIR = 2 };   // PAIR: fine_pair_map (ops.cu), taps_s = 1
 
 struct IgemmEpilogue {
   // Up to two destinations (concat dgrad writes the `up` half and the `skip` half to different tensors).

@@ -76,6 +76,20 @@ int fine_view_map(CUtensorMap* m, const void* p, int N, int H, int W, int C, int
   return make_tmap(m, p, 5, dims, str, box, swizzle ? swizzle : box_c * elt, elt);
 }
 
+// The same fine tensor with both column taps of a coarse pixel in one row: [N*H][a][W][2*C] -- the fine pixels (2j, 2j+1)
+// are adjacent in memory, so a coarse pixel's (b, channel) pair is 2*C contiguous elements. For C = 32 (bf16) that is one
+// 128-byte swizzle row. (A 5-D box [C, 2, ...] does NOT give this: with the inner box narrower than the swizzle span the
+// rows land 128 bytes apart in shared memory.) Coordinates: (0, j, a, n*H + h).
+int fine_pair_map(CUtensorMap* m, const void* p, int N, int H, int W, int C, Box b, int elt = 2) {
+  const uint64_t e = static_cast<uint64_t>(elt);
+  const uint64_t dims[4] = {static_cast<uint64_t>(2 * C), static_cast<uint64_t>(W), 2, static_cast<uint64_t>(N) * H};
+  const uint64_t str[3] = {static_cast<uint64_t>(2) * C * e, static_cast<uint64_t>(2) * W * C * e,
+                           static_cast<uint64_t>(4) * W * C * e};
+  const uint32_t box[4] = {static_cast<uint32_t>(2 * C), static_cast<uint32_t>(b.TW), 1,
+                           static_cast<uint32_t>(b.TN * b.TH)};
+  return make_tmap(m, p, 4, dims, str, box, 2 * C * static_cast<int>(e), elt);
+}
+
 // Packed weights [ncols][taps][ktot] bf16.
 int weight_map(CUtensorMap* m, const void* p, int ncols, int taps, int ktot, int kc, int block_n, int elt = 2) {
   const uint64_t e = static_cast<uint64_t>(elt);
@@ -336,6 +350,11 @@ int plan_wgrad(WgradPlan& wp, int N, int H, int W, int taps_r, int taps_s, int p
   // and the X tile is read once (0.118 -> 0.091 ms); wider layers already fill M per tap and were slower stacked
   p.tap_in_m = (taps_r == 2 && taps_r * taps_s * z_C <= 128 && !no_tap_in_m) ? 1 : 0;
   if (p.tap_in_m) p.m_tiles = cdiv(taps_r * taps_s * z_C, 128);
+  // ... and with 32 channels the two column taps of a filter row are one 128-byte row in memory: one TMA box of 128-byte
+  // rows per filter row instead of two boxes of 64-byte pieces at a 128-byte stride
+  static const bool no_z_pair = getenv("UNETB200_NO_Z_PAIR") != nullptr;
+  p.z_pair = (p.tap_in_m && elt == 2 && z_C == 32 && taps_s == 2 && !no_z_pair) ? 1 : 0;
+  if (p.z_pair) p.z_atom = 64;
   p.num_src = C1 ? 2 : 1;
   const int Cs[2] = {C0, C1};
   int off = 0;
@@ -550,10 +569,15 @@ int tconv2x2_fwd(const void* x, int Cin, const void* w_packed, const float* bias
 int tconv2x2_dgrad(const void* dy, int Cout, const void* w_packed_d, void* dx, int Cin, const void* mask, float scale,
                    int N, int H, int W, cudaStream_t s, const unsigned short* gate, int dt) {
   const int elt = dt_bytes(dt);
-  const int kc = pick_kc(Cout, 0, elt);
+  int kc = pick_kc(Cout, 0, elt);
   UB_REQUIRE(kc != 0, "tconv2x2_dgrad: Cout %d must be a multiple of 32", Cout);
   const int block_n = pick_block_n(Cin);
   UB_REQUIRE(block_n != 0, "tconv2x2_dgrad: Cin %d must be a multiple of 32", Cin);
+  // 32 output channels (transConv9): the two column taps of a filter row are adjacent in dY (2 x 64 B) and adjacent in
+  // the packed weights' K order (tap * Cout + co), so one 128-byte K block per filter row replaces two 64-byte ones
+  static const bool no_pair = getenv("UNETB200_NO_Z_PAIR") != nullptr;
+  const bool pair = elt == 2 && Cout == 32 && !no_pair;
+  if (pair) kc = 64;
   IgemmParams p;
   std::memset(&p, 0, sizeof(p));
   const Box b = pick_box(128, H, W, true);
@@ -562,9 +586,9 @@ int tconv2x2_dgrad(const void* dy, int Cout, const void* w_packed_d, void* dx, i
   p.n_tiles = Cin / block_n;
   p.block_n = block_n;
   p.a_mode = IG_A_TCONV5D;
-  p.taps_r = 2; p.taps_s = 2; p.pad = 0;
+  p.taps_r = 2; p.taps_s = pair ? 1 : 2; p.pad = 0;
   p.num_src = 1;
-  p.src_kblocks[0] = Cout / kc;
+  p.src_kblocks[0] = pair ? 1 : Cout / kc;
   p.kc = kc;
   p.elt = elt;
   p.stages = igemm_pick_stages(block_n, kc, elt);
@@ -574,9 +598,11 @@ int tconv2x2_dgrad(const void* dy, int Cout, const void* w_packed_d, void* dx, i
   p.epi.mask_scale = scale;
   p.epi.drop_keep = 1.0f;
   CUtensorMap a0, bm;
-  int rc = fine_view_map(&a0, dy, N, H, W, Cout, kc, b, elt);
+  if (pair) p.a_mode = IG_A_TCONV_PAIR;
+  int rc = pair ? fine_pair_map(&a0, dy, N, H, W, Cout, b, elt) : fine_view_map(&a0, dy, N, H, W, Cout, kc, b, elt);
   if (rc) return rc;
-  rc = weight_map(&bm, w_packed_d, Cin, 4, Cout, kc, block_n, elt);
+  rc = pair ? weight_map(&bm, w_packed_d, Cin, 2, 2 * Cout, kc, block_n, elt)
+            : weight_map(&bm, w_packed_d, Cin, 4, Cout, kc, block_n, elt);
   if (rc) return rc;
   return igemm_launch(p, a0, a0, bm, s);
 }
@@ -618,7 +644,8 @@ int tconv2x2_wgrad(const void* dy, int Cout, const void* x, int Cin, float* dw, 
   const Box b = {p.TN, p.TH, p.TW};
   CUtensorMap zm, xm;
   const int mn_sw = elt == 4 ? UB_SWIZZLE_128B_ATOM32 : 0;
-  rc = fine_view_map(&zm, dy, N, H, W, Cout, p.z_atom, b, elt, mn_sw);
+  if (p.z_pair) rc = fine_pair_map(&zm, dy, N, H, W, Cout, b, elt);
+  else rc = fine_view_map(&zm, dy, N, H, W, Cout, p.z_atom, b, elt, mn_sw);
   if (rc) return rc;
   rc = nhwc_map(&xm, x, N, H, W, Cin, p.x_atom[0], b, elt, mn_sw);
   if (rc) return rc;

@@ -49,7 +49,7 @@ wgrad_kernel(const __grid_constant__ WgradParams p, const __grid_constant__ CUte
   const int tap = bid % ntaps;
   const int split = bid / ntaps;
   const int m_total = p.tap_in_m ? p.taps_r * p.taps_s * p.z_C : p.z_C;
-  const int atoms_per_tap = p.z_C / p.z_atom;
+  const int atoms_per_tap = p.z_pair ? 1 : p.z_C / p.z_atom;
   const int src = (ntg >= p.x_ntiles[0]) ? 1 : 0;
   const int nt = src ? ntg - p.x_ntiles[0] : ntg;
   const int block_n = p.x_block_n[src];
@@ -113,6 +113,9 @@ wgrad_kernel(const __grid_constant__ WgradParams p, const __grid_constant__ CUte
         for (int a = 0; a < m_atoms; ++a) {
           if (p.z_mode == 0) {
             tma_load_4d(sa + a * z_atom_bytes, &tmZ, &bars->full[stage], m0 + a * p.z_atom, w0, h0, n0);
+          } else if (p.z_pair) {
+            // atom = filter row m0 / 64 + a of the pair view (ops.cu fine_pair_map): 128-byte rows of (column tap, channel)
+            tma_load_4d(sa + a * z_atom_bytes, &tmZ, &bars->full[stage], 0, w0, m0 / p.z_atom + a, n0 * p.H + h0);
           } else if (p.tap_in_m) {
             const int ga = m0 / p.z_atom + a;            // atom index over all taps
             const int atap = ga / atoms_per_tap;

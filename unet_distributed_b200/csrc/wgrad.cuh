@@ -23,6 +23,8 @@ struct WgradParams {
   int z_atom;               // 64 (SWIZZLE_128B) or 32 (SWIZZLE_64B)
   int m_tiles;              // ceil(z_C / 128), or ceil(taps * z_C / 128) with tap_in_m
   int tap_in_m;             // z_mode 1 only: stack the taps along GEMM M (row = tap * z_C + channel), one CTA for all taps
+  int z_pair;               // tap_in_m with z_C = 32 (bf16): one TMA box takes BOTH column taps of a filter row -- the two
+                            // fine pixels are adjacent in memory, 2 x 64 B = one 128-byte swizzle row = a 64-wide M atom
   int num_src;              // X sources (concat inputs)
   int x_C[2];               // channels per source
   int x_atom[2];            // 64 or 32
