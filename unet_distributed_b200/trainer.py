@@ -113,16 +113,21 @@ class Trainer:
                       int(self.const_lr), self.lr_fraction, self.decay_steps, scale, _stream())
         p.pack_weights(b, e)
 
-    def train_step(self, imgs, msks):
+    def train_step(self, imgs, msks, _after=None):
         """imgs/msks: contiguous CUDA float32 NHWC tensors for THIS replica's shard. Returns the device tensor
-        [loss, dice, sensitivity, specificity] of this step (no synchronisation)."""
+        [loss, dice, sensitivity, specificity] of this step (no synchronisation). `_after` (internal): a CUDA event the
+        step's kernels wait for -- the read-back of the previous step's metrics, which this step overwrites."""
         if self.use_cuda_graph:
             if self._graph is None:
                 self._capture(imgs, msks)
             self._g_imgs.copy_(imgs, non_blocking=True)
             self._g_msks.copy_(msks, non_blocking=True)
+            if _after is not None:
+                torch.cuda.current_stream().wait_event(_after)
             self._graph.replay()      # one replay per step at every world size (the all-reduces are inside)
         else:
+            if _after is not None:
+                torch.cuda.current_stream().wait_event(_after)
             self._enqueue_step(imgs, msks)
         self.steps_done += 1
         return self.plan.metrics
@@ -161,11 +166,15 @@ class Trainer:
         if self._slots is None:
             dev = self.plan.device
             self._copy_stream = torch.cuda.Stream(device=dev)
+            # the 16-byte read-back of a step's metrics runs on its own stream: a copy-engine operation in the compute
+            # stream would sit between two graph launches (UNETB200_D2H_INLINE=1 puts it back there)
+            self._d2h_stream = None if os.environ.get("UNETB200_D2H_INLINE") else torch.cuda.Stream(device=dev)
             self._slots = []
             for _ in range(2):
                 self._slots.append({
                     "imgs": torch.empty_like(self._d_imgs), "msks": torch.empty_like(self._d_msks),
                     "ready": torch.cuda.Event(), "free": torch.cuda.Event(), "done": torch.cuda.Event(),
+                    "met_ready": torch.cuda.Event(),
                     "h_metrics": torch.empty(4, dtype=torch.float32).pin_memory(),
                     "h_imgs": None, "h_msks": None})
             self._k = 0
@@ -201,11 +210,22 @@ class Trainer:
             slot["msks"].copy_(h_msks, non_blocking=True)
             slot["ready"].record(self._copy_stream)
         cur.wait_event(slot["ready"])
-        met = self.train_step(slot["imgs"], slot["msks"])
-        slot["free"].record(cur)
-        slot["h_metrics"].copy_(met, non_blocking=True)
-        slot["done"].record(cur)
-        prev, self._pending = self._pending, slot
+        prev = self._pending
+        if self._d2h_stream is None:
+            met = self.train_step(slot["imgs"], slot["msks"])
+            slot["free"].record(cur)
+            slot["h_metrics"].copy_(met, non_blocking=True)
+            slot["done"].record(cur)
+        else:
+            # plan.metrics is one buffer: this step may only overwrite it once the previous read-back has finished
+            met = self.train_step(slot["imgs"], slot["msks"], _after=prev["done"] if prev is not None else None)
+            slot["free"].record(cur)
+            slot["met_ready"].record(cur)
+            with torch.cuda.stream(self._d2h_stream):
+                self._d2h_stream.wait_event(slot["met_ready"])
+                slot["h_metrics"].copy_(met, non_blocking=True)
+                slot["done"].record(self._d2h_stream)
+        self._pending = slot
         if wait:
             self._pending = None
             slot["done"].synchronize()
