@@ -223,3 +223,25 @@ def test_tf32_rounding_of_the_oracle_twin():
     assert torch.equal(r[:4], want) and float(r[5]) == 65504.0
     assert bool(((r.view(torch.int32) & 0x1FFF) == 0).all())
     assert float(((r - x).abs() / x.abs()).max()) <= 2.0 ** -11 + 1e-9
+
+
+def test_readme_lists_exactly_the_switches_the_sources_read():
+    """Every UNETB200_* environment variable the library, the Python layer, bench.py or the tests read is described in
+    README.md, and README.md describes none that no longer exists (a switch removed from the kernels has to leave the
+    table too)."""
+    import glob
+    import re
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    documented = set(re.findall(r"UNETB200_[A-Z0-9_]+", open(os.path.join(root, "README.md")).read()))
+    files = [f for f in glob.glob(os.path.join(root, "unet_distributed_b200", "**", "*"), recursive=True)
+             if f.endswith((".cu", ".cuh", ".h", ".py"))]
+    files += [os.path.join(root, "bench.py"), os.path.join(root, "__graft_entry__.py")]
+    files += [f for f in glob.glob(os.path.join(root, "tests", "*.py")) if not f.endswith("test_host.py")]
+    read = set()
+    pat = re.compile(r'getenv\("(UNETB200_[A-Z0-9_]+)"\)|environ(?:\.get)?[\(\[]"(UNETB200_[A-Z0-9_]+)"')
+    for f in files:
+        for a, b in pat.findall(open(f, errors="ignore").read()):
+            read.add(a or b)
+    assert read, "no switches found: the pattern is broken"
+    assert documented - read == set(), sorted(documented - read)
+    assert read - documented == set(), sorted(read - documented)
