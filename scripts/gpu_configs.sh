@@ -1,7 +1,7 @@
 #!/bin/bash
 # the other BASELINE.json configurations on one GPU (parity cases, not the headline): configs[0], [3], [4]
 mkdir -p gpurun_out
-run() { name=$1; shift; timeout 600 python bench.py --steps 10 --warmup 3 --no-cpu-baseline "$@" > gpurun_out/cfg_$name.json 2> gpurun_out/cfg_$name.err; echo "$name exit $?"; python - gpurun_out/cfg_$name.json <<'PY'
+run() { name=$1; shift; timeout 600 python bench.py --steps 10 --warmup 3 --no-cpu-baseline --no-tconv-block "$@" > gpurun_out/cfg_$name.json 2> gpurun_out/cfg_$name.err; echo "$name exit $?"; python - gpurun_out/cfg_$name.json <<'PY'
 import json,sys
 try:
     d=json.load(open(sys.argv[1])); print("  img/s", round(d["value"]), "ms", round(d["ms_per_step"],3), "e2e", round(d["e2e"]["value"]), "loss", round(d["loss"],4), d["config"]["workload"][:60])
