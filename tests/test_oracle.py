@@ -69,6 +69,33 @@ def test_pool_and_upsample_conventions():
     assert np.array_equal(u.permute(0, 2, 3, 1).numpy(), O.np_upsample2x2(x))
 
 
+def test_conv_over_upsampled_input_is_four_parity_convs():
+    """The identity behind DESIGN.md section 7 item 3 (not built yet): a 3x3 'same' convolution over a 2x
+    nearest-upsampled tensor equals, per output parity (a, b), a 2x2 convolution over the low-resolution tensor whose
+    taps are sums of the original taps that fall on the same low-resolution pixel -- 4 taps instead of 9."""
+    rng = np.random.default_rng(5)
+    x = rng.standard_normal((2, 5, 6, 3))
+    w = rng.standard_normal((3, 3, 3, 4))                         # HWIO
+    xt = torch.tensor(x).permute(0, 3, 1, 2)
+    up = torch.nn.functional.interpolate(xt, scale_factor=2, mode="nearest")
+    ref = torch.nn.functional.conv2d(up, torch.tensor(w).permute(3, 2, 0, 1), padding=1).permute(0, 2, 3, 1).numpy()
+    N, H, W, _ = x.shape
+    xp = np.pad(x, ((0, 0), (1, 1), (1, 1), (0, 0)))               # low-res zero border = the conv's 'same' padding
+    out = np.zeros((N, 2 * H, 2 * W, 4))
+    for a in range(2):
+        for b in range(2):
+            # fine row 2i + a + (r - 1) lies in low-res row i + d with d = floor((a + r - 1) / 2) in {-1, 0} or {0, 1}
+            wsum = np.zeros((2, 2, 3, 4))
+            for r in range(3):
+                for c in range(3):
+                    wsum[(a + r - 1) // 2 - (a - 1), (b + c - 1) // 2 - (b - 1)] += w[r, c]
+            for dr in range(2):
+                for dc in range(2):
+                    win = xp[:, a + dr:a + dr + H, b + dc:b + dc + W, :]
+                    out[:, a::2, b::2, :] += win @ wsum[dr, dc]
+    assert rel_err(out, ref) < 1e-12
+
+
 def test_dice_closed_forms():
     rng = np.random.default_rng(2)
     y = (rng.uniform(size=(3, 8, 8, 1)) < 0.2).astype(np.float64)
